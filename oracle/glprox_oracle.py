@@ -1,0 +1,363 @@
+"""CPU oracle for the proximal-gradient group-LASSO hot path (TEST INFRASTRUCTURE ONLY).
+
+This file is a NumPy *restatement* of the algorithm implemented by the reference solvers
+  /root/reference/code/gl_ProxGD_primal.py   (ProxGD,  146 lines)
+  /root/reference/code/gl_FProxGD_primal.py  (FProxGD, 161 lines)
+for   min_x 0.5*||A x - b||_F^2 + mu * sum_i ||x(i,:)||_2 .
+
+It is the checker, not the product: only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs may import it.  The product path (the CUDA library behind
+convex-optimization_b200/) never imports anything from oracle/.
+
+Parity pin: PINNED.  tests/golden/make_golden.py imports the *unmodified* reference functions
+from /root/reference/code in the build container and stores their outputs (k, fval, f_hist, x,
+support) on seeded inputs in tests/golden/*.npz; tests/test_oracle.py asserts that this
+restatement reproduces every one of them (bit-for-bit in k / support, <=1e-13 relative in
+f_hist), plus the published report numbers (doc/report.md:446-447).
+
+Two restatements live here:
+  * `solve(...)`            -- same pass structure as the reference (5-7 products with A per
+                               iteration); this is what the CPU baseline times.
+  * `solve_two_stream(...)` -- the algebraically equivalent schedule the GPU executes (A streamed
+                               once forward and once transposed per iteration; A.x carried by
+                               linearity).  Used as the step-level oracle
+                               for the kernels and to prove the schedule equals the reference.
+"""
+import math
+import time
+
+import numpy as np
+
+# --- option tables (reference: gl_ProxGD_primal.py:10-19, gl_FProxGD_primal.py:10-19) -------------
+_COMMON = dict(thres=1e-3, step_type="line_search", ftol=1e-6, stable_len_threshold=70,
+               maxit_line_search_iter=5)
+DEFAULTS = {
+    "ProxGD": dict(_COMMON, maxit=2500, alpha0=2e-3, line_search_attenuation_coeffi=0.9),
+    "FProxGD": dict(_COMMON, maxit=1500, alpha0=1e-3, line_search_attenuation_coeffi=0.98),
+}
+CONTINUATION = (100.0, 10.0, 1.0)  # mu stages: gl_ProxGD_primal.py:53 / gl_FProxGD_primal.py:55
+
+
+def gen_data(seed=97006855, m=256, n=512, l=2, dtype=np.float64):
+    """Fixture generator, restated from code/main.py:37-51 (draw order A, perm, u, x0 matters)."""
+    rng = np.random.Generator(np.random.MT19937(seed=seed))
+    A = rng.standard_normal(size=(m, n))
+    nnz_rows = round(n * 0.1)
+    picked = rng.permutation(n)[:nnz_rows]
+    u = np.zeros((n, l))
+    u[picked, :] = rng.standard_normal(size=(nnz_rows, l))
+    b = A @ u
+    x0 = rng.standard_normal(size=(n, l))
+    mu = 1e-2
+    if dtype != np.float64:
+        A, b, x0, u = (z.astype(dtype) for z in (A, b, x0, u))
+    return A, b, x0, u, mu
+
+
+def row_norms(z):
+    """||z(i,:)||_2 per row, shape (n,1).  numpy LA.norm(z, axis=1) == sqrt(add.reduce(z*z, 1))."""
+    return np.sqrt(np.add.reduce(z * z, axis=1)).reshape(-1, 1)
+
+
+def group_prox(z, t, mu, thres):
+    """Prox of t*mu*sum_i||z_i|| with the reference's guarded denominator
+    (gl_ProxGD_primal.py:65-71 / gl_FProxGD_primal.py:71-77): multiply first, then divide; the
+    denominator gets +1.0 on rows whose norm is below `thres`."""
+    rn = row_norms(z)
+    shrink = np.clip(rn - t * mu, a_min=0, a_max=None)
+    return z * shrink / ((rn < thres) + rn)
+
+
+def objective(A, b, x, mu0):
+    """real_obj_func, gl_*_primal.py:24-27: always the *final* mu (mu_0)."""
+    res = A @ x - b
+    return 0.5 * np.sum(res ** 2) + mu0 * np.sum(row_norms(x))
+
+
+def sparsity(x):
+    """gl_*_primal.py:22."""
+    ax = np.abs(x)
+    return np.sum(ax > 1e-6 * np.max(ax)) / x.size
+
+
+def smooth_part(A, b, z):
+    """g(z) = 0.5*||A z - b||^2  (gl_ProxGD_primal.py:60-61 / gl_FProxGD_primal.py:62-63)."""
+    return 0.5 * np.sum((A @ z - b) ** 2)
+
+
+def _open_loop_step(step_type, alpha0, inner):
+    """Non-adaptive step rules, gl_ProxGD_primal.py:79-85 / gl_FProxGD_primal.py:82-88."""
+    it_hat = max(inner, 1000) - 999
+    if step_type == "fixed":
+        return alpha0
+    if step_type == "diminishing":
+        return alpha0 / np.sqrt(it_hat)
+    if step_type == "diminishing2":
+        return alpha0 / it_hat
+    raise ValueError("unsupported step_type %r" % (step_type,))
+
+
+class _History:
+    """f_hist / f_hist_best / sparsity_hist bookkeeping + the stop rule (:107-125 / :112-134)."""
+
+    def __init__(self, ftol, stable_cap):
+        self.f, self.fbest, self.s = [], [], []
+        self.best = np.inf
+        self.ftol, self.cap = ftol, stable_cap
+        self.k = 0
+
+    def record(self, f_now, s_now):
+        self.f.append(f_now)
+        self.best = min(self.best, f_now)
+        self.fbest.append(self.best)
+        self.s.append(s_now)
+        self.k += 1
+
+    def is_stable(self):
+        k = self.k
+        if k <= 1:
+            return False
+        with np.errstate(divide="ignore", invalid="ignore"):
+            df = abs(self.f[k - 1] - self.f[k - 2]) / abs(self.f[k - 2])
+            ds = abs(self.s[k - 1] - self.s[k - 2]) / abs(self.s[k - 2])
+        return bool(df < self.ftol and ds < self.ftol)
+
+
+def solve(algo, x0, A, b, mu0, opts=None, trace=None):
+    """Reference-structured solver.  algo in {"ProxGD", "FProxGD"}.
+
+    Returns (x, k, out) with out = {tt, fval, f_hist, f_hist_best} exactly like
+    gl_ProxGD_primal.py:138-146 / gl_FProxGD_primal.py:153-161.  `trace`, if a dict, receives
+    pass counters and the per-iteration accepted steps (test diagnostics only).
+    """
+    o = dict(DEFAULTS[algo])
+    o.update(opts or {})
+    maxit, ftol, alpha0, thres = o["maxit"], o["ftol"], o["alpha0"], o["thres"]
+    shrink_c, ls_cap, rule = (o["line_search_attenuation_coeffi"], o["maxit_line_search_iter"],
+                              o["step_type"])
+    accel = algo == "FProxGD"
+    hist = _History(ftol, o["stable_len_threshold"])
+    steps = []
+    xk = np.copy(x0)
+    x_last = None if accel else xk  # FProxGD returns the last prox output (unbound if none ran)
+    t_begin = time.time_ns()
+    for factor in CONTINUATION:
+        mu = factor * mu0
+        inner, stable = 0, 0
+        if accel:
+            vk, tk = np.copy(xk), alpha0          # gl_FProxGD_primal.py:68-69
+        while inner < maxit:
+            hist.record(objective(A, b, xk, mu0), sparsity(xk))
+            inner += 1
+            stable = stable + 1 if hist.is_stable() else 0
+            if stable > o["stable_len_threshold"]:
+                break
+            xk[np.abs(xk) < thres] = 0            # :127 / :136, element-wise, in place
+            if accel:
+                theta = 2 / (inner + 1)           # :138
+                base = (1 - theta) * xk + theta * vk
+            else:
+                base = xk
+            grad = A.T @ (A @ base - b)           # :129 / :140
+            if rule == "line_search":
+                g_base = smooth_part(A, b, base)
+                t = tk if accel else alpha0       # FProxGD carries t, ProxGD restarts (:91 / :94)
+                for _ in range(ls_cap):
+                    cand = group_prox(base - t * grad, t, mu, thres)
+                    if accel:                     # gl_FProxGD_primal.py:96-99
+                        d = cand - base
+                        ok = smooth_part(A, b, cand) <= g_base + np.sum(grad * d) + np.sum(d ** 2) / (2 * t)
+                    else:                         # gl_ProxGD_primal.py:73-74, 89-92
+                        gmap = (base - cand) / t
+                        ok = (smooth_part(A, b, base - t * gmap)
+                              <= g_base - t * np.sum(grad * gmap) + 0.5 * t * np.sum(gmap ** 2))
+                    if ok:
+                        break
+                    t *= shrink_c
+            else:
+                t = _open_loop_step(rule, alpha0, inner)
+            x_new = group_prox(base - t * grad, t, mu, thres)   # :132 / :144
+            steps.append(t)
+            if accel:
+                vk = xk + (x_new - xk) / theta    # :145 (xk is the thresholded iterate)
+                tk = t
+            xk = x_new
+            x_last = x_new
+    tt = _round_us(time.time_ns() - t_begin) / 1e6
+    if x_last is None:
+        raise UnboundLocalError("FProxGD ran no iteration (maxit=0), as in the reference")
+    out = {"tt": tt, "fval": objective(A, b, x_last, mu0), "f_hist": hist.f,
+           "f_hist_best": hist.fbest}
+    if trace is not None:
+        trace.update(steps=steps, sparsity_hist=hist.s)
+    return x_last, hist.k, out
+
+
+def _round_us(ns):
+    """Stopwatch kMicroSecond rounding, code/utils/stopwatch.py:54-56."""
+    return ns // 1000 + (1 if (ns // 100) % 10 >= 5 else 0)
+
+
+def gl_ProxGD_primal(x0, A, b, mu_0, opts):
+    return solve("ProxGD", x0, A, b, mu_0, opts)
+
+
+def gl_FProxGD_primal(x0, A, b, mu_0, opts):
+    return solve("FProxGD", x0, A, b, mu_0, opts)
+
+
+# =================================================================================================
+# Two-stream schedule (what the GPU executes).  One transposed and one forward stream of A per
+# iteration; every other product is obtained by linearity from carried m x l vectors.
+# =================================================================================================
+def hard_threshold(x, thres):
+    """Copy of x with |x| < thres set to zero (gl_ProxGD_primal.py:127 / gl_FProxGD_primal.py:136)."""
+    out = x.copy()
+    out[np.abs(out) < thres] = 0
+    return out
+
+
+def prox_epilogue(algo, grad, xt, v, theta, t, mu, thres):
+    """What the transposed pass's fused epilogue produces for one trial step t.
+
+    Returns (xn, xnt, vn, gd, dd, reg, mx):  candidate iterate, its thresholded copy, the FProxGD
+    momentum candidate, the two line-search inner products, sum_i||xn_i|| and max|xn|.
+    FProxGD: base y=(1-theta)*xt+theta*v, gd=<grad,xn-y>, dd=||xn-y||^2.
+    ProxGD:  base xt,                     gd=<grad,gt>,   dd=||gt||^2 with gt=(xt-xn)/t.
+    """
+    if algo == "FProxGD":
+        base = (1 - theta) * xt + theta * v
+    else:
+        base = xt
+    xn = group_prox(base - t * grad, t, mu, thres)
+    xnt = hard_threshold(xn, thres)
+    if algo == "FProxGD":
+        d = xn - base
+        vn = xt + (xn - xt) / theta
+    else:
+        d = (base - xn) / t
+        vn = None
+    gd, dd = np.sum(grad * d), np.sum(d ** 2)
+    reg = np.sum(row_norms(xn))
+    mx = np.max(np.abs(xn))
+    return xn, xnt, vn, gd, dd, reg, mx
+
+
+def solve_two_stream(algo, x0, A, b, mu0, opts=None, trace=None, matmul=None, rmatmul=None):
+    """Two-stream restatement; same return contract as `solve`.
+
+    matmul(X) -> A @ X and rmatmul(R) -> A.T @ R can be overridden (e.g. with fp32-rounded or
+    column-sharded products) to emulate the GPU arithmetic in tests.
+    """
+    o = dict(DEFAULTS[algo])
+    o.update(opts or {})
+    maxit, ftol, alpha0, thres = o["maxit"], o["ftol"], o["alpha0"], o["thres"]
+    shrink_c, ls_cap, rule = (o["line_search_attenuation_coeffi"], o["maxit_line_search_iter"],
+                              o["step_type"])
+    if rule not in ("line_search", "fixed", "diminishing", "diminishing2"):
+        raise ValueError("unsupported step_type %r" % (rule,))
+    accel = algo == "FProxGD"
+    fwd = matmul or (lambda X: A @ X)
+    bwd = rmatmul or (lambda R: A.T @ R)
+    n, l = x0.shape
+    hist = _History(ftol, o["stable_len_threshold"])
+    n_fwd = n_bwd = 0
+    t_begin = time.time_ns()
+
+    # ---- initial candidate: x0 itself, committed unconditionally
+    xn, xnt = np.array(x0, dtype=np.float64), hard_threshold(np.array(x0, dtype=np.float64), thres)
+    reg, mx = np.sum(row_norms(xn)), np.max(np.abs(xn)) if xn.size else 0.0
+    prod = fwd(np.concatenate([xn, xnt], axis=1)); n_fwd += 1
+    Axn, Axnt = prod[:, :l], prod[:, l:]
+    rr = np.sum((Axn - b) ** 2)
+    cnt = np.sum(np.abs(xn) > 1e-6 * mx)
+    vn = None
+    x = xt = v = Ax = Axt = Av = None
+    stage, inner, stable, t_k, theta, t, trial = 0, 0, 0, alpha0, 1.0, alpha0, 0
+    tested = False          # does the pending candidate carry a sufficient-decrease test?
+    first_commit = True
+    mu = CONTINUATION[0] * mu0
+    ran_any = False
+    while True:
+        # -------- decision on the pending candidate (K3, part 1)
+        if tested:
+            g_x = 0.5 * rr
+            if accel:
+                ok = g_x <= g_y + gd + dd / (2 * t)
+            else:
+                ok = g_x <= g_y - t * gd + 0.5 * t * dd
+            if not ok:
+                t *= shrink_c
+                trial += 1
+                tested = trial < ls_cap      # the (ls_cap+1)-th step is used untested
+                xn, xnt, vn, gd, dd, reg, mx = prox_epilogue(algo, grad, xt, v, theta, t, mu, thres)
+                prod = fwd(np.concatenate([xn, xnt], axis=1)); n_fwd += 1
+                Axn, Axnt = prod[:, :l], prod[:, l:]
+                rr = np.sum((Axn - b) ** 2)
+                cnt = np.sum(np.abs(xn) > 1e-6 * mx)
+                continue
+        # -------- commit (K3, part 2)
+        if accel and not first_commit:
+            v, Av = vn, Axt + (Axn - Axt) / theta
+            t_k = t
+        x, xt, Ax, Axt = xn, xnt, Axn, Axnt
+        first_commit = False
+        f_cur = 0.5 * rr + mu0 * reg
+        s_cur = cnt / (n * l)
+        # -------- loop tops / stage transitions (K3, part 3)
+        done = False
+        fresh_stage = stage == 0 and hist.k == 0 and inner == 0
+        while True:
+            if fresh_stage:
+                inner, stable = 0, 0
+                mu = CONTINUATION[stage] * mu0
+                if accel:
+                    v, Av, t_k = x, Ax, alpha0     # un-thresholded copy, gl_FProxGD_primal.py:68-69
+                fresh_stage = False
+            advance = False
+            if inner >= maxit:
+                advance = True
+            else:
+                hist.record(f_cur, s_cur)
+                inner += 1
+                stable = stable + 1 if hist.is_stable() else 0
+                if stable > o["stable_len_threshold"]:
+                    advance = True
+            if not advance:
+                break
+            stage += 1
+            if stage == len(CONTINUATION):
+                done = True
+                break
+            fresh_stage = True
+        if done:
+            break
+        # -------- set up the next iteration (K3, part 4): residual at the base point by linearity
+        ran_any = True
+        if accel:
+            theta = 2 / (inner + 1)
+            Abase = (1 - theta) * Axt + theta * Av
+        else:
+            theta = 1.0
+            Abase = Axt
+        r = Abase - b
+        g_y = 0.5 * np.sum(r ** 2)
+        if rule == "line_search":
+            t, tested = (t_k if accel else alpha0), ls_cap > 0
+        else:
+            t, tested = _open_loop_step(rule, alpha0, inner), False
+        trial = 0
+        # -------- transposed stream + fused epilogue, forward stream
+        grad = bwd(r); n_bwd += 1
+        xn, xnt, vn, gd, dd, reg, mx = prox_epilogue(algo, grad, xt, v, theta, t, mu, thres)
+        prod = fwd(np.concatenate([xn, xnt], axis=1)); n_fwd += 1
+        Axn, Axnt = prod[:, :l], prod[:, l:]
+        rr = np.sum((Axn - b) ** 2)
+        cnt = np.sum(np.abs(xn) > 1e-6 * mx)
+    tt = _round_us(time.time_ns() - t_begin) / 1e6
+    if accel and not ran_any:
+        raise UnboundLocalError("FProxGD ran no iteration (maxit=0), as in the reference")
+    out = {"tt": tt, "fval": f_cur, "f_hist": hist.f, "f_hist_best": hist.fbest}
+    if trace is not None:
+        trace.update(n_fwd=n_fwd, n_bwd=n_bwd, sparsity_hist=hist.s)
+    return x, hist.k, out

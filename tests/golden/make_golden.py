@@ -1,0 +1,88 @@
+#!/usr/bin/env python
+"""Generate golden vectors by running the UNMODIFIED reference solvers.
+
+Run in the build container only (needs /root/reference):
+    python tests/golden/make_golden.py
+Writes tests/golden/ref_*.npz.  The reference functions are imported from
+/root/reference/code (gl_ProxGD_primal.py, gl_FProxGD_primal.py); the inputs come from
+oracle.glprox_oracle.gen_data, which restates code/main.py:37-51 (main.py itself is not
+importable: it needs cvxpy/matplotlib/mosek/gurobi).
+"""
+import os
+import sys
+
+import numpy as np
+
+sys.dont_write_bytecode = True  # /root/reference is a read-only mount
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, "/root/reference/code")
+
+from gl_FProxGD_primal import gl_FProxGD_primal  # noqa: E402  (reference)
+from gl_ProxGD_primal import gl_ProxGD_primal  # noqa: E402  (reference)
+from oracle.glprox_oracle import gen_data, sparsity  # noqa: E402
+
+REF = {"ProxGD": gl_ProxGD_primal, "FProxGD": gl_FProxGD_primal}
+
+
+def mp_step(m, n):
+    """Marchenko-Pastur bound step used for every synthetic shape."""
+    return float(1.0 / (np.sqrt(m) + np.sqrt(n)) ** 2)
+
+
+# name -> (seed, m, n, l, dtype, opts)
+CASES = {
+    "fixture": (97006855, 256, 512, 2, "f8", {}),
+    "fixture_maxit3": (97006855, 256, 512, 2, "f8", {"maxit": 3}),
+    "fixture_maxit40": (97006855, 256, 512, 2, "f8", {"maxit": 40}),
+    "seed114514": (114514, 256, 512, 2, "f8", {}),
+    "seed1": (1, 256, 512, 2, "f8", {}),
+    "seed2": (2, 256, 512, 2, "f8", {}),
+    "fixed_step": (97006855, 256, 512, 2, "f8", {"step_type": "fixed", "alpha0": 5e-4}),
+    "diminishing": (97006855, 256, 512, 2, "f8", {"step_type": "diminishing", "alpha0": 5e-4,
+                                                  "maxit": 1200}),
+    "diminishing2": (97006855, 256, 512, 2, "f8", {"step_type": "diminishing2", "alpha0": 5e-4,
+                                                   "maxit": 1200}),
+    "thres1e-8": (97006855, 256, 512, 2, "f8", {"thres": 1e-8}),
+    "ragged": (5, 193, 391, 2, "f8", {"alpha0": mp_step(193, 391), "maxit": 60}),
+    "l1": (6, 128, 300, 1, "f8", {"alpha0": mp_step(128, 300), "maxit": 60}),
+    "l3": (8, 96, 260, 3, "f8", {"alpha0": mp_step(96, 260), "maxit": 60}),
+    "l5": (9, 64, 256, 5, "f8", {"alpha0": mp_step(64, 256), "maxit": 40}),
+    "mid": (11, 1024, 4096, 2, "f8", {"alpha0": mp_step(1024, 4096), "maxit": 50}),
+    "harsh_ls": (97006855, 256, 512, 2, "f8", {"alpha0": 1.2e-3, "maxit": 80}),
+    # fp32 configs: the oracle is the fp64 reference on the fp32-rounded inputs
+    "mid_f32in": (11, 1024, 4096, 2, "f4", {"alpha0": mp_step(1024, 4096), "maxit": 50}),
+    "fixture_f32in": (97006855, 256, 512, 2, "f4", {}),
+}
+
+
+def run_case(name):
+    seed, m, n, l, dt, opts = CASES[name]
+    A, b, x0, u, mu = gen_data(seed, m, n, l)
+    if dt == "f4":  # round the inputs to fp32, then run the reference in fp64 on them
+        A, b, x0 = (z.astype(np.float32).astype(np.float64) for z in (A, b, x0))
+    rec = {"seed": seed, "m": m, "n": n, "l": l, "in_dtype": dt, "mu": mu,
+           "opts_keys": np.array(sorted(opts.keys())),
+           "opts_vals": np.array([str(opts[k]) for k in sorted(opts.keys())])}
+    for algo, fn in REF.items():
+        A_keep, b_keep, x0_keep = A.copy(), b.copy(), x0.copy()
+        x, k, out = fn(x0, A, b, mu, dict(opts))
+        assert np.array_equal(A, A_keep) and np.array_equal(b, b_keep) and np.array_equal(x0, x0_keep)
+        ax = np.abs(x)
+        rec[algo + "_k"] = k
+        rec[algo + "_fval"] = float(out["fval"])
+        rec[algo + "_f_hist"] = np.asarray(out["f_hist"], dtype=np.float64)
+        rec[algo + "_f_hist_best"] = np.asarray(out["f_hist_best"], dtype=np.float64)
+        rec[algo + "_x"] = x
+        rec[algo + "_support_nz"] = np.flatnonzero(np.sqrt((x * x).sum(1)) > 0)
+        rec[algo + "_support_rule"] = np.flatnonzero((ax > 1e-6 * ax.max()).any(axis=1))
+        rec[algo + "_sparsity"] = float(sparsity(x))
+        print("%-16s %-8s k=%5d fval=%.16e sparsity=%.6f" % (name, algo, k, out["fval"], sparsity(x)))
+    return rec
+
+
+if __name__ == "__main__":
+    names = sys.argv[1:] or list(CASES)
+    for nm in names:
+        np.savez_compressed(os.path.join(HERE, "ref_%s.npz" % nm), **run_case(nm))
