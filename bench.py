@@ -1,0 +1,398 @@
+#!/usr/bin/env python
+"""bench.py -- FProxGD iterations/s on the BASELINE.json workload, with roofline and CPU baseline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one drop-in solve of the hot path (gl_FProxGD_primal semantics) with `maxit` iterations
+per continuation stage (3*maxit iterations, no early stop possible for maxit <= 70) on the synthetic
+workload  m=32768 n=131072 l=2 fp32 (BASELINE.json configs[3]; ~17 GB of A, column-group sharded
+over the ranks).  value = iterations/s of the whole job with A resident in HBM; e2e = the same
+metric through the host-buffer entry point (NumPy in, NumPy out: upload of A, b, x0 and download of
+x inside the timed region).  One JSON line is printed by rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "convex-optimization_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "FProxGD iterations/s"
+UNIT = "it/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--m", type=int, default=32768)
+    ap.add_argument("--n", type=int, default=131072)
+    ap.add_argument("--l", type=int, default=2)
+    ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
+    ap.add_argument("--algo", default="FProxGD", choices=["FProxGD", "ProxGD"])
+    ap.add_argument("--maxit", type=int, default=50, help="iterations per continuation stage in one step")
+    ap.add_argument("--seed", type=int, default=97006855)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def mp_step(m, n):
+    """Marchenko-Pastur bound on 1/lambda_max(A^T A); the reference defaults diverge off the fixture."""
+    return float(1.0 / (math.sqrt(m) + math.sqrt(n)) ** 2)
+
+
+def mem_available_gb():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._pump, daemon=True)
+            self.thr.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_setup(args):
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        torch.cuda.set_device(0)
+    return rank, local, world
+
+
+def make_problem(args, rank, world):
+    """Synthetic problem of code/main.py:37-51 at scale: A ~ N(0,1) from the counter-based device
+    generator (identical values for any sharding), 10% non-zero row groups in u, b = A u."""
+    import torch
+    from glprox import _lib
+    lib = _lib.load()
+    m, n, l = args.m, args.n, args.l
+    tdt = torch.float32 if args.dtype == "f32" else torch.float64
+    gdt = _lib.GLP_F32 if args.dtype == "f32" else _lib.GLP_F64
+    assert n % world == 0, "n must divide evenly over the ranks"
+    n_loc = n // world
+    col0 = rank * n_loc
+    A = torch.empty((m, n_loc), dtype=tdt, device="cuda")
+    _lib.check(lib.glp_randn(A.data_ptr(), gdt, m, n_loc, A.stride(0), args.seed, 0, col0,
+                             torch.cuda.current_stream().cuda_stream))
+    rng = np.random.Generator(np.random.MT19937(seed=args.seed))
+    k = round(n * 0.1)
+    picked = rng.permutation(n)[:k]
+    u = np.zeros((n, l))
+    u[picked, :] = rng.standard_normal(size=(k, l))
+    x0 = rng.standard_normal(size=(n, l))
+    u_loc = torch.from_numpy(u[col0:col0 + n_loc]).to("cuda", tdt)
+    x0_loc = torch.from_numpy(x0[col0:col0 + n_loc]).to("cuda", tdt)
+    # b = A u through K1 (partial product per rank, summed over ranks)
+    from glprox import GroupLassoProblem
+    tmp = GroupLassoProblem(A, torch.zeros((m, l), dtype=tdt, device="cuda"))
+    Au = torch.empty((m, l), dtype=torch.float64, device="cuda")
+    _lib.check(lib.glp_fwd(tmp.handle, u_loc.data_ptr(), l, Au.data_ptr(), None))
+    torch.cuda.synchronize()
+    tmp.close()
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(Au)
+    b = Au.to(tdt)
+    return A, b, x0_loc, 1e-2
+
+
+def solver_opts(args):
+    return {"maxit": args.maxit, "alpha0": mp_step(args.m, args.n)}
+
+
+def run_ours(args):
+    import torch
+    from glprox import GroupLassoProblem, _lib
+    rank, local, world = dist_setup(args)
+    lib = _lib.load()
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch with torch.distributed.run)" % (args.gpus, world))
+    if world > 1:
+        raise SystemExit("multi-GPU sharding is not wired into this build yet")
+    A, b, x0, mu = make_problem(args, rank, world)
+    opts = solver_opts(args)
+    prob = GroupLassoProblem(A, b)
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput
+    for _ in range(args.warmup):
+        x, k, out = prob.solve(args.algo, x0, mu, opts)
+    _lib.check(lib.glp_set_profiling(prob.handle, 1))
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    iters = launches = 0
+    for _ in range(args.steps):
+        x, k, out = prob.solve(args.algo, x0, mu, opts)
+        iters += k
+        launches += out["glprox"]["n_launches"]
+    ev1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = t.item()
+    prof = _lib.GlpProfile()
+    _lib.check(lib.glp_get_profile(prob.handle, C.byref(prof)))
+    _lib.check(lib.glp_set_profiling(prob.handle, 0))
+    value = iters / (ms / 1e3)
+    fval = float(out["fval"])
+
+    # ---- roofline of the dominant kernels (the two streams of A), CUDA events on the solve stream
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    n_str = prof.fwd_launches + prof.tpass_launches
+    avg_ms = (prof.fwd_ms_sum + prof.tpass_ms_sum) / max(n_str, 1)
+    achieved = prof.bytes_per_launch / (avg_ms * 1e-3) / 1e9 if n_str else 0.0
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write)" if peaks else "fallback 6650 GB/s",
+                "kernels": {"glp_fwd_kernel": {"launches": int(prof.fwd_launches),
+                                               "avg_ms": prof.fwd_ms_sum / max(prof.fwd_launches, 1),
+                                               "GBps": prof.bytes_per_launch * prof.fwd_launches / max(prof.fwd_ms_sum, 1e-9) / 1e6},
+                            "glp_tpass_kernel": {"launches": int(prof.tpass_launches),
+                                                 "avg_ms": prof.tpass_ms_sum / max(prof.tpass_launches, 1),
+                                                 "GBps": prof.bytes_per_launch * prof.tpass_launches / max(prof.tpass_ms_sum, 1e-9) / 1e6}},
+                "bytes_per_launch": prof.bytes_per_launch,
+                "whole_iteration_GBps": 2.0 * prof.bytes_per_launch * value / 1e9}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": "group-lasso %s m=%d n=%d l=%d %s, mu=1e-2, alpha0=1/(sqrt(m)+sqrt(n))^2, "
+                                   "maxit=%d per stage (%d iterations per step)" % (
+                                       args.algo, args.m, args.n, args.l, args.dtype, args.maxit, 3 * args.maxit),
+                       "sharding": "column groups of A / row groups of x over %d rank(s)" % world,
+                       "l2_policy": "A (%.1f GB per rank) is far larger than the 126 MB L2; no flush needed" % (
+                           A.numel() * A.element_size() / 1e9)},
+            "iterations_per_step": iters // max(args.steps, 1), "final_objective": fval,
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline}
+    return line, (prob, A, b, x0, mu, opts, rank, world)
+
+
+def run_e2e(args, ctx, steps):
+    """Same metric through the host-buffer entry point: NumPy arrays in pinned host memory go in,
+    a NumPy x comes out; the upload of A, b, x0 and the download of x are inside the timed region."""
+    import torch
+    from gl_FProxGD_primal import gl_FProxGD_primal
+    from gl_ProxGD_primal import gl_ProxGD_primal
+    prob, A, b, x0, mu, opts, rank, world = ctx
+    need_gb = A.numel() * A.element_size() / 1e9
+    if mem_available_gb() < 1.5 * need_gb + 4:
+        return None, "host RAM too small for a %.1f GB host copy of A" % need_gb
+    fn = gl_FProxGD_primal if args.algo == "FProxGD" else gl_ProxGD_primal
+    A_h = torch.empty(A.shape, dtype=A.dtype, pin_memory=True)
+    A_h.copy_(A)
+    b_h = b.cpu().pin_memory()
+    x0_h = x0.cpu().pin_memory()
+    torch.cuda.synchronize()
+    An, bn, x0n = A_h.numpy(), b_h.numpy(), x0_h.numpy()
+    fn(x0n, An, bn, mu, dict(opts))  # warm-up (page-in, bounce buffers)
+    iters = 0
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        x, k, out = fn(x0n, An, bn, mu, dict(opts))
+        iters += k
+    dt = time.perf_counter() - t0
+    h2d = An.nbytes + bn.nbytes + x0n.nbytes
+    d2h = x.nbytes + 8 * k
+    return {"value": iters / dt, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+            "ms_per_step": 1e3 * dt / steps, "final_objective": float(out["fval"]),
+            "api": "gl_%s_primal(x0, A, b, mu, opts) with NumPy arrays (pinned host memory)" % args.algo}, (An, bn, x0n)
+
+
+def cpu_reference_solve(args, An, bn, x0n, mu, opts, sample_maxit, row_frac=1.0):
+    """The oracle port of the reference (same pass structure: 5 products with A per FProxGD iteration,
+    NumPy/BLAS on all host cores), on a bounded sample of the workload."""
+    from oracle import glprox_oracle as orc
+    o = dict(opts)
+    o["maxit"] = sample_maxit
+    x, k, out = orc.solve(args.algo, x0n, An, bn, mu, o)
+    return k, out["tt"], float(out["fval"])
+
+
+def blas_threads():
+    try:
+        from threadpoolctl import threadpool_info
+        return max([p.get("num_threads", 1) for p in threadpool_info()] or [1])
+    except Exception:
+        return len(os.sched_getaffinity(0))
+
+
+def host_problem(args):
+    """Host copy of the synthetic problem for the CPU legs.  Uses the GPU generator when a device is
+    present (identical values to the GPU arm), NumPy otherwise."""
+    import torch
+    if torch.cuda.is_available():
+        torch.cuda.set_device(0)
+        A, b, x0, mu = make_problem(args, 0, 1)
+        An, bn, x0n = A.cpu().numpy(), b.cpu().numpy(), x0.cpu().numpy()
+        del A
+        torch.cuda.empty_cache()
+        return An, bn, x0n, mu
+    from oracle import glprox_oracle as orc
+    A, b, x0, u, mu = orc.gen_data(args.seed, args.m, args.n, args.l, np.float32 if args.dtype == "f32" else np.float64)
+    return A, b, x0, mu
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU algorithm (oracle port; the Python reference cannot
+    travel to the GPU box) on the box's host cores, same config / metric / unit."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    need_gb = args.m * args.n * (4 if args.dtype == "f32" else 8) / 1e9
+    rows = args.m
+    if mem_available_gb() < 1.6 * need_gb + 4:
+        rows = max(64, int(args.m * (mem_available_gb() - 4) / (1.6 * need_gb)) // 64 * 64)
+    sub = argparse.Namespace(**vars(args))
+    sub.m = rows
+    An, bn, x0n, mu = host_problem(sub)
+    opts = {"alpha0": mp_step(args.m, args.n)}
+    cores = blas_threads()
+    sample_maxit = 1  # 3 iterations per step (one per continuation stage), ~5 products with A each
+    scale = rows / args.m  # a row sample does proportionally less work per iteration
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference_solve(args, An, bn, x0n, mu, opts, sample_maxit)
+    iters, secs = 0, 0.0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        k, tt, fval = cpu_reference_solve(args, An, bn, x0n, mu, opts, sample_maxit)
+        iters += k
+        secs += tt
+    wall = time.perf_counter() - t0
+    value = iters / secs * scale
+    sample = "%d iterations per step (maxit=1 per stage) on rows 0..%d of %d, all %d columns%s" % (
+        3 * sample_maxit, rows, args.m, args.n, "" if rows == args.m else "; it/s scaled by rows/m")
+    return {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * wall / max(args.steps, 1),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype,
+            "data": "synthetic",
+            "config": {"workload": "group-lasso %s m=%d n=%d l=%d %s, mu=1e-2, alpha0=1/(sqrt(m)+sqrt(n))^2" % (
+                args.algo, args.m, args.n, args.l, args.dtype)},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        line = run_reference(args)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+    line, ctx = run_ours(args)
+    prob, A, b, x0, mu, opts, rank, world = ctx
+    host = None
+    if not args.no_e2e:
+        e2e, host = run_e2e(args, ctx, args.steps)
+        line["e2e"] = e2e if e2e is not None else {"value": None, "unit": UNIT, "h2d_bytes_per_step": 0,
+                                                   "d2h_bytes_per_step": 0, "skipped": host}
+        if e2e is None:
+            host = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        if host is None:
+            need_gb = A.numel() * A.element_size() / 1e9
+            if mem_available_gb() >= 1.6 * need_gb + 4:
+                host = (A.cpu().numpy(), b.cpu().numpy(), x0.cpu().numpy())
+        if host is not None:
+            An, bn, x0n = host
+            k, tt, fval = cpu_reference_solve(args, An, bn, x0n, mu, opts, 1)
+            line["cpu_baseline"] = {"value": k / tt, "unit": UNIT, "cores": blas_threads(), "kind": "port",
+                                    "sample": "%d iterations (maxit=1 per stage) of the full-size workload, "
+                                              "oracle port of the reference on NumPy/BLAS" % k,
+                                    "seconds": tt}
+        else:
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": blas_threads(), "kind": "port",
+                                    "sample": "skipped: host RAM too small"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

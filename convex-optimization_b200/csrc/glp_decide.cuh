@@ -1,0 +1,135 @@
+// glp_decide.cuh -- K3: the decide kernel.  Runs between the forward stream of one trial and the
+// transposed stream of the next iteration.  Every CTA (a) reduces the per-block partial scalars of
+// the two streams in a fixed order, (b) advances the control state machine (glp_decide.h) -- all
+// CTAs compute the identical decision, CTA 0 publishes it -- and (c) performs its slice of the
+// O((m+n) l) vector work that the decision implies:
+//   Av   <- Axt_old + (Axn - Axt_old)/theta          (carried product of v, FProxGD :145 by linearity)
+//   r    <- (1-theta')*Axnt + theta'*Av - b          (residual at the next base point, :139-140)
+//   gy   <- sum(r^2)                                 (g(y) of the next sufficient-decrease test, :92)
+//   v    <- x , Av <- Ax  at a continuation-stage start (:68)
+#pragma once
+#include "glp_decide.h"
+#include "glp_device.cuh"
+#include "glp_types.cuh"
+
+namespace glp {
+
+struct DecideArgs {
+  const Ctrl* cin;
+  Ctrl* cout;
+  SolveConst sc;
+  const double* rr_partial;   int32_t n_rr;
+  const double* scal_partial; int32_t n_scal;   // [n_scal][4]
+  const double* cnt_partial;  int32_t n_cnt;
+  double* gy_partial[2];      int32_t n_gy;     // [gridDim] each
+  double* AX[2];              // [2l][ldm] : {A x | A xt} of the two state buffers
+  double* Av;                 // [l][ldm]
+  const double* b;            // [l][ldm]
+  void* r;                    // [l][ldm] dtype T
+  double* state[2];           // [3][l][ldn]
+  double* f_hist;
+  double* f_hist_best;
+};
+
+constexpr int DECIDE_THREADS = 256;
+
+__device__ __forceinline__ double dec_nmax(double a, double b) {
+  return (a != a) ? a : ((b != b) ? b : fmax(a, b));
+}
+
+template <typename T>
+__global__ void __launch_bounds__(DECIDE_THREADS)
+glp_decide_kernel(const DecideArgs a, const Geom g) {
+  __shared__ double s_part[DECIDE_THREADS / 32][6];
+  __shared__ Ctrl s_out;
+  __shared__ DecideOut s_act;
+  __shared__ double s_gy[DECIDE_THREADS / 32];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const Ctrl cin = *a.cin;
+
+  if (cin.done) {  // keep both control blocks identical once finished
+    if (blockIdx.x == 0 && tid == 0) *a.cout = cin;
+    return;
+  }
+
+  // ---- (a) fixed-order reductions: strided per thread, shuffle tree per warp, warps in order
+  double v_rr = 0.0, v_gd = 0.0, v_dd = 0.0, v_reg = 0.0, v_cnt = 0.0, v_gy = 0.0;
+  for (int i = tid; i < a.n_rr; i += DECIDE_THREADS) v_rr += __ldcg(&a.rr_partial[i]);
+  for (int i = tid; i < a.n_scal; i += DECIDE_THREADS) {
+    v_gd += __ldcg(&a.scal_partial[4 * i + 0]);
+    v_dd += __ldcg(&a.scal_partial[4 * i + 1]);
+    v_reg += __ldcg(&a.scal_partial[4 * i + 2]);
+  }
+  for (int i = tid; i < a.n_cnt; i += DECIDE_THREADS) v_cnt += __ldcg(&a.cnt_partial[i]);
+  const double* gy_in = a.gy_partial[cin.gy_sel];
+  for (int i = tid; i < a.n_gy; i += DECIDE_THREADS) v_gy += __ldcg(&gy_in[i]);
+  v_rr = warp_sum(v_rr); v_gd = warp_sum(v_gd); v_dd = warp_sum(v_dd);
+  v_reg = warp_sum(v_reg); v_cnt = warp_sum(v_cnt); v_gy = warp_sum(v_gy);
+  if (lane == 0) {
+    s_part[warp][0] = v_rr; s_part[warp][1] = v_gd; s_part[warp][2] = v_dd;
+    s_part[warp][3] = v_reg; s_part[warp][4] = v_cnt; s_part[warp][5] = v_gy;
+  }
+  __syncthreads();
+
+  // ---- (b) state machine (thread 0 of every CTA; identical inputs => identical decision)
+  if (tid == 0) {
+    Reduced red = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int w = 0; w < DECIDE_THREADS / 32; ++w) {
+      red.rr += s_part[w][0]; red.gd += s_part[w][1]; red.dd += s_part[w][2];
+      red.reg += s_part[w][3]; red.cnt += s_part[w][4]; red.gbase += s_part[w][5];
+    }
+    const bool writer = blockIdx.x == 0;
+    decide_step(a.sc, cin, red, double(g.n_total) * double(g.l), s_out, s_act,
+                writer ? a.f_hist : nullptr, writer ? a.f_hist_best : nullptr);
+    if (s_act.action == GLP_ACT_ITERATE) s_out.gy_sel = 1 - cin.gy_sel;
+    if (writer) *a.cout = s_out;
+  }
+  __syncthreads();
+  if (s_act.action != GLP_ACT_ITERATE) return;
+
+  // ---- (c) vector work of the commit, sliced over the grid
+  const int nc = s_act.new_cur;
+  const bool accel = a.sc.algo == 1;
+  const double th_old = s_act.theta_old, th = s_out.theta, omt = xsub(1.0, th);
+  const int64_t lenm = int64_t(g.l) * g.ldm, lenn = int64_t(g.l) * g.ldn;
+  const double* Axn = a.AX[nc];
+  const double* Axnt = a.AX[nc] + lenm;
+  const double* Axt_old = a.AX[1 - nc] + lenm;
+  T* r = static_cast<T*>(a.r);
+  double gy = 0.0;
+  const int64_t stride = int64_t(gridDim.x) * DECIDE_THREADS;
+  for (int64_t i = int64_t(blockIdx.x) * DECIDE_THREADS + tid; i < lenm; i += stride) {
+    double base;
+    if (accel) {
+      double av;
+      if (s_act.reset_v) {
+        av = Axn[i];
+      } else {
+        const double o = Axt_old[i];
+        av = xadd(o, xdiv(xsub(Axn[i], o), th_old));
+      }
+      a.Av[i] = av;
+      base = xadd(xmul(omt, Axnt[i]), xmul(th, av));
+    } else {
+      base = Axnt[i];
+    }
+    const double res = xsub(base, a.b[i]);
+    r[i] = T(res);
+    gy += res * res;
+  }
+  if (accel && s_act.reset_v) {
+    const double* x = a.state[nc];
+    double* v = a.state[nc] + 2 * lenn;
+    for (int64_t i = int64_t(blockIdx.x) * DECIDE_THREADS + tid; i < lenn; i += stride) v[i] = x[i];
+  }
+  gy = warp_sum(gy);
+  if (lane == 0) s_gy[warp] = gy;
+  __syncthreads();
+  if (tid == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < DECIDE_THREADS / 32; ++w) tot += s_gy[w];
+    a.gy_partial[s_out.gy_sel][blockIdx.x] = tot;
+  }
+}
+
+}  // namespace glp

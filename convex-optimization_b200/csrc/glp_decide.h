@@ -1,0 +1,168 @@
+// glp_decide.h -- the scalar control flow of the solvers as one host/device function.
+//
+// Restates, as a state machine advanced once per forward stream, the control flow of
+//   gl_ProxGD_primal.py:53,76,103-132   and   gl_FProxGD_primal.py:55,68-69,79,108-147 :
+// sufficient-decrease test of the pending trial, step shrink / untested last step, commit,
+// objective + sparsity bookkeeping (f_hist, f_hist_best), the two-ratio stop rule with
+// stable_len, the `while inner_iter < maxit` bound, the mu-continuation stage switch (v and t reset
+// for FProxGD) and the step rule of the next iteration.
+// Compiled for the device (decide kernel, persistent kernel) and for the host (CPU unit test
+// against the golden vectors: tests/test_decide_host.py builds it with g++ -ffp-contract=off).
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#include "glp_types.cuh"
+
+#if defined(__CUDA_ARCH__)
+#define GLP_XMUL(a, b) __dmul_rn((a), (b))
+#define GLP_XADD(a, b) __dadd_rn((a), (b))
+#define GLP_XSUB(a, b) __dsub_rn((a), (b))
+#define GLP_XDIV(a, b) __ddiv_rn((a), (b))
+#define GLP_XSQRT(a) __dsqrt_rn((a))
+#else
+#define GLP_XMUL(a, b) ((a) * (b))
+#define GLP_XADD(a, b) ((a) + (b))
+#define GLP_XSUB(a, b) ((a) - (b))
+#define GLP_XDIV(a, b) ((a) / (b))
+#define GLP_XSQRT(a) sqrt((a))
+#endif
+#if defined(__CUDACC__)
+#define GLP_HDI __host__ __device__ inline
+#else
+#define GLP_HDI inline
+#endif
+
+namespace glp {
+
+// Globally reduced scalars of the pending candidate.
+struct Reduced {
+  double rr;    // sum((A xn - b)^2)
+  double gd;    // FProxGD <grad, xn - y>      | ProxGD <grad, gt>
+  double dd;    // FProxGD ||xn - y||^2        | ProxGD ||gt||^2
+  double reg;   // sum_i ||xn_i||_2
+  double cnt;   // #{ |xn| > 1e-6 * max|xn| }
+  double gbase; // sum(r^2) at the base point of the running iteration (from the previous decide)
+};
+
+enum DecideAction { GLP_ACT_NONE = 0, GLP_ACT_RETRY = 1, GLP_ACT_ITERATE = 2, GLP_ACT_FINISH = 3 };
+
+struct DecideOut {
+  int32_t action;
+  int32_t reset_v;      // stage start: v <- x (un-thresholded), Av <- Ax
+  int32_t first_commit; // the committed candidate was x0
+  int32_t new_cur;
+  double theta_old;     // theta the committed candidate was built with (Av update)
+};
+
+GLP_HDI void ctrl_init(Ctrl& c, const SolveConst& sc) {
+  c.done = 0; c.stage = 0; c.inner = 0; c.k = 0; c.stable = 0; c.trial = 0; c.cur = 0; c.retry = 0;
+  c.tested = 0; c.first_commit = 1; c.ran_any = 0; c.fault = 0;
+  c.stage_end[0] = c.stage_end[1] = c.stage_end[2] = 0; c.gy_sel = 0;
+  c.t = sc.alpha0; c.t_k = sc.alpha0; c.theta = 1.0; c.mu = 100.0 * sc.mu0;
+  c.f_cur = 0.0; c.s_cur = 0.0; c.f_prev = 0.0; c.s_prev = 0.0;
+  c.f_best = INFINITY; c.g_base = 0.0; c.n_fwd = 0; c.n_tpass = 0;
+}
+
+GLP_HDI double stage_mu(int stage, double mu0) {
+  return stage == 0 ? GLP_XMUL(100.0, mu0) : (stage == 1 ? GLP_XMUL(10.0, mu0) : mu0);
+}
+
+// f_hist may be null (then values are not stored).  size_total = n_total * l.
+GLP_HDI void decide_step(const SolveConst& sc, const Ctrl& in, const Reduced& red, double size_total,
+                         Ctrl& out, DecideOut& act, double* f_hist, double* f_hist_best) {
+  out = in;
+  act.action = GLP_ACT_NONE; act.reset_v = 0; act.first_commit = in.first_commit;
+  act.new_cur = in.cur; act.theta_old = in.theta;
+  if (in.done) return;
+  const bool accel = sc.algo == 1;
+
+  // ---- sufficient-decrease test of the pending trial
+  if (in.tested) {
+    const double g_x = GLP_XMUL(0.5, red.rr);
+    const double g_y = GLP_XMUL(0.5, red.gbase);
+    bool ok;
+    if (accel)  // g(x) <= g(y) + <grad, x-y> + ||x-y||^2/(2t)          gl_FProxGD_primal.py:99
+      ok = g_x <= GLP_XADD(GLP_XADD(g_y, red.gd), GLP_XDIV(red.dd, GLP_XMUL(2.0, in.t)));
+    else        // g(x - t*gt) <= g(x) - t*<grad,gt> + 0.5*t*||gt||^2    gl_ProxGD_primal.py:91-92
+      ok = g_x <= GLP_XADD(GLP_XSUB(g_y, GLP_XMUL(in.t, red.gd)), GLP_XMUL(GLP_XMUL(0.5, in.t), red.dd));
+    if (!ok) {
+      out.t = GLP_XMUL(in.t, sc.atten);
+      out.trial = in.trial + 1;
+      out.tested = out.trial < sc.ls_cap ? 1 : 0;  // the (ls_cap+1)-th step is used untested
+      out.retry = 1;
+      out.n_fwd = in.n_fwd + 1;
+      act.action = GLP_ACT_RETRY;
+      return;
+    }
+  }
+
+  // ---- commit the candidate
+  out.cur = 1 - in.cur;
+  act.new_cur = out.cur;
+  out.retry = 0;
+  out.first_commit = 0;
+  if (accel && !in.first_commit) out.t_k = in.t;
+  out.f_cur = GLP_XADD(GLP_XMUL(0.5, red.rr), GLP_XMUL(sc.mu0, red.reg));
+  out.s_cur = GLP_XDIV(red.cnt, size_total);
+
+  // ---- loop tops and stage switches
+  bool fresh = in.first_commit != 0;
+  for (;;) {
+    if (fresh) {
+      out.inner = 0; out.stable = 0;
+      out.mu = stage_mu(out.stage, sc.mu0);
+      if (accel) { out.t_k = sc.alpha0; act.reset_v = 1; }
+      fresh = false;
+    }
+    bool advance = false;
+    if (out.inner >= sc.maxit) {
+      advance = true;
+    } else {
+      if (f_hist != nullptr && out.k < sc.hist_cap) f_hist[out.k] = out.f_cur;
+      out.f_best = out.f_cur < out.f_best ? out.f_cur : out.f_best;  // min(f_best, f_now)
+      if (f_hist_best != nullptr && out.k < sc.hist_cap) f_hist_best[out.k] = out.f_best;
+      out.k += 1;
+      out.inner += 1;
+      bool stable_now = false;
+      if (out.k > 1) {
+        const double df = GLP_XDIV(fabs(GLP_XSUB(out.f_cur, out.f_prev)), fabs(out.f_prev));
+        const double ds = GLP_XDIV(fabs(GLP_XSUB(out.s_cur, out.s_prev)), fabs(out.s_prev));
+        stable_now = (df < sc.ftol) && (ds < sc.ftol);
+      }
+      out.f_prev = out.f_cur;
+      out.s_prev = out.s_cur;
+      out.stable = stable_now ? out.stable + 1 : 0;
+      if (out.stable > sc.stable_cap) advance = true;
+    }
+    if (!advance) break;
+    out.stage_end[out.stage] = out.k;
+    out.stage += 1;
+    if (out.stage == 3) {
+      out.done = 1;
+      act.action = GLP_ACT_FINISH;
+      return;
+    }
+    fresh = true;
+  }
+
+  // ---- step rule and extrapolation weight of the iteration that starts now
+  out.ran_any = 1;
+  out.theta = accel ? GLP_XDIV(2.0, double(out.inner + 1)) : 1.0;
+  out.trial = 0;
+  if (sc.step_type == 0) {  // line_search
+    out.t = accel ? out.t_k : sc.alpha0;
+    out.tested = sc.ls_cap > 0 ? 1 : 0;
+  } else {
+    const int it = (out.inner > 1000 ? out.inner : 1000) - 999;
+    if (sc.step_type == 1) out.t = sc.alpha0;
+    else if (sc.step_type == 2) out.t = GLP_XDIV(sc.alpha0, GLP_XSQRT(double(it)));
+    else out.t = GLP_XDIV(sc.alpha0, double(it));
+    out.tested = 0;
+  }
+  out.n_fwd = in.n_fwd + 1;
+  out.n_tpass = in.n_tpass + 1;
+  act.action = GLP_ACT_ITERATE;
+}
+
+}  // namespace glp

@@ -1,0 +1,159 @@
+// glp_prox.cuh -- the row-group epilogue of the transposed pass (K2's fused tail), also launched
+// stand-alone for line-search retries and for the initial iterate.
+//
+// For every row group j of x (a column j of A) it evaluates, in the reference's operation order,
+//   FProxGD  y   = (1-theta)*xt + theta*v                          gl_FProxGD_primal.py:139
+//            xn  = prox_th(y - t*grad, t)                           :71-77, :144
+//            vn  = xt + (xn - xt)/theta                             :145
+//            gd  = sum(grad*(xn-y)),  dd = sum((xn-y)**2)           :96-99
+//   ProxGD   xn  = prox_th(xt - t*grad, t)                          gl_ProxGD_primal.py:65-71, :132
+//            gt  = (xt - xn)/t ; gd = sum(grad*gt), dd = sum(gt**2) :73-74, :89-92
+//   both     xnt = xn with |.|<thres zeroed                         :127 / :136 (applied next iteration)
+//            reg = sum_i ||xn_i||_2 , mx = max|xn|                  :24-27, :22
+// prox_th keeps the reference's guard: z*max(rn-t*mu,0) / ((rn<thres)+rn), multiply before divide.
+#pragma once
+#include "glp_device.cuh"
+#include "glp_types.cuh"
+
+namespace glp {
+
+struct ProxScal {
+  double gd, dd, reg, mx;
+};
+
+__device__ __forceinline__ double nmax(double a, double b) {
+  return (a != a) ? a : ((b != b) ? b : fmax(a, b));
+}
+
+struct ProxResolved {
+  int algo, cur, init;
+  double theta, t, mu, thres;
+};
+
+__device__ __forceinline__ ProxResolved resolve(const ProxArgs& p) {
+  ProxResolved r;
+  r.algo = p.algo;
+  r.init = p.init;
+  r.thres = p.thres;
+  if (p.ctrl != nullptr) {
+    r.cur = p.ctrl->cur; r.theta = p.ctrl->theta; r.t = p.ctrl->t; r.mu = p.ctrl->mu;
+  } else {
+    r.cur = p.cur; r.theta = p.theta; r.t = p.t; r.mu = p.mu;
+  }
+  return r;
+}
+
+template <typename T>
+__device__ __forceinline__ void prox_group(const ProxArgs& p, const ProxResolved& r, const Geom& g,
+                                           int64_t j, ProxScal& sc) {
+  const int l = g.l;
+  const int64_t ldn = g.ldn;
+  const double* S = p.state[r.cur];
+  double* C = p.state[1 - r.cur];
+  const double* xt = S + int64_t(l) * ldn;
+  const double* v = S + 2 * int64_t(l) * ldn;
+  double* xn = C;
+  double* xnt = C + int64_t(l) * ldn;
+  double* vn = C + 2 * int64_t(l) * ldn;
+  T* xop = static_cast<T*>(p.xop);
+  const bool accel = r.algo == 1;
+
+  if (r.init) {
+    double nn = 0.0;
+    for (int c = 0; c < l; ++c) {
+      const double x = xn[c * ldn + j];
+      const double xz = fabs(x) < r.thres ? 0.0 : x;
+      xnt[c * ldn + j] = xz;
+      if (xop != nullptr) { xop[c * ldn + j] = T(x); xop[(l + c) * ldn + j] = T(xz); }
+      nn = xadd(nn, xmul(x, x));
+      sc.mx = nmax(sc.mx, fabs(x));
+    }
+    sc.reg = xadd(sc.reg, __dsqrt_rn(nn));
+    return;
+  }
+
+  const double omt = xsub(1.0, r.theta);
+  const double tmu = xmul(r.t, r.mu);
+  double nn = 0.0;
+  for (int c = 0; c < l; ++c) {
+    const double xtc = xt[c * ldn + j];
+    const double base = accel ? xadd(xmul(omt, xtc), xmul(r.theta, v[c * ldn + j])) : xtc;
+    const double z = xsub(base, xmul(r.t, __ldcg(&p.grad[c * ldn + j])));
+    nn = xadd(nn, xmul(z, z));
+  }
+  const double rn = __dsqrt_rn(nn);
+  double shrink = xsub(rn, tmu);
+  shrink = shrink < 0.0 ? 0.0 : shrink;  // np.clip(.., a_min=0): NaN stays NaN
+  const double den = xadd(rn < r.thres ? 1.0 : 0.0, rn);
+  double n2 = 0.0;
+  for (int c = 0; c < l; ++c) {
+    const double xtc = xt[c * ldn + j];
+    const double base = accel ? xadd(xmul(omt, xtc), xmul(r.theta, v[c * ldn + j])) : xtc;
+    const double gr = __ldcg(&p.grad[c * ldn + j]);
+    const double z = xsub(base, xmul(r.t, gr));
+    const double o = xdiv(xmul(z, shrink), den);
+    const double oz = fabs(o) < r.thres ? 0.0 : o;
+    xn[c * ldn + j] = o;
+    xnt[c * ldn + j] = oz;
+    if (xop != nullptr) { xop[c * ldn + j] = T(o); xop[(l + c) * ldn + j] = T(oz); }
+    double d;
+    if (accel) {
+      d = xsub(o, base);
+      vn[c * ldn + j] = xadd(xtc, xdiv(xsub(o, xtc), r.theta));
+    } else {
+      d = xdiv(xsub(base, o), r.t);
+    }
+    sc.gd = xadd(sc.gd, xmul(gr, d));
+    sc.dd = xadd(sc.dd, xmul(d, d));
+    n2 = xadd(n2, xmul(o, o));
+    sc.mx = nmax(sc.mx, fabs(o));
+  }
+  sc.reg = xadd(sc.reg, __dsqrt_rn(n2));
+}
+
+// Column block cb (TILE_COLS row groups) handled by the 256 threads tid = 0..255 of one CTA that
+// all call this function; the scalar partials land in scal_partial[cb][0..3] in a fixed order.
+template <typename T>
+__device__ __forceinline__ void prox_block(const ProxArgs& p, const ProxResolved& r, const Geom& g,
+                                           int64_t cb, int tid, double (*s_red)[4]) {
+  constexpr int TC = Elem<T>::TILE_COLS;
+  ProxScal sc = {0.0, 0.0, 0.0, 0.0};
+  for (int jj = tid; jj < TC; jj += CONSUMER_THREADS) {
+    const int64_t j = cb * TC + jj;
+    if (j < g.n) prox_group<T>(p, r, g, j, sc);
+  }
+  sc.gd = warp_sum(sc.gd);
+  sc.dd = warp_sum(sc.dd);
+  sc.reg = warp_sum(sc.reg);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sc.mx = nmax(sc.mx, __shfl_xor_sync(0xffffffffu, sc.mx, o));
+  const int warp = tid >> 5, lane = tid & 31;
+  if (lane == 0) { s_red[warp][0] = sc.gd; s_red[warp][1] = sc.dd; s_red[warp][2] = sc.reg; s_red[warp][3] = sc.mx; }
+  consumer_bar();
+  if (tid == 0) {
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+    for (int w = 0; w < NUM_CONSUMER_WARPS; ++w) {
+      a0 += s_red[w][0]; a1 += s_red[w][1]; a2 += s_red[w][2]; a3 = nmax(a3, s_red[w][3]);
+    }
+    double* out = p.scal_partial + 4 * cb;
+    out[0] = a0; out[1] = a1; out[2] = a2; out[3] = a3;
+  }
+  consumer_bar();
+}
+
+// Stand-alone launch: retries (ctrl->retry), the initial iterate (init) and the chunked generic-l path.
+// only_if_retry = 1: return unless ctrl->retry is set (the scheduler enqueues it unconditionally).
+template <typename T>
+__global__ void __launch_bounds__(CONSUMER_THREADS)
+glp_prox_kernel(const ProxArgs p, const Geom g, const int only_if_retry) {
+  __shared__ double s_red[NUM_CONSUMER_WARPS][4];
+  if (p.ctrl != nullptr) {
+    if (p.ctrl->done) return;
+    if (only_if_retry && !p.ctrl->retry) return;
+  }
+  const ProxResolved r = resolve(p);
+  for (int64_t cb = blockIdx.x; cb < g.ncb; cb += gridDim.x) prox_block<T>(p, r, g, cb, threadIdx.x, s_red);
+}
+
+}  // namespace glp

@@ -1,0 +1,102 @@
+// glp_types.cuh -- PODs shared by the host-side scheduler (solver.cu) and the kernels.
+#pragma once
+#include <stdint.h>
+
+namespace glp {
+
+// Device-resident control block of one solve.  It is double buffered: decide launch j reads
+// ctrl[j & 1] and writes ctrl[(j + 1) & 1]; the transposed / forward launches that follow read the
+// latter.  The host never has to know whether a line-search trial was accepted.
+struct Ctrl {
+  int32_t done;          // all three continuation stages finished: later launches are no-ops
+  int32_t stage;         // 0..2  (mu = {100, 10, 1} * mu0)
+  int32_t inner;         // inner_iter of the reference (post-increment value)
+  int32_t k;             // recorded objective values so far
+  int32_t stable;        // stable_len
+  int32_t trial;         // failed sufficient-decrease tests of the current iteration
+  int32_t cur;           // index (0/1) of the committed state buffers; candidates live in 1-cur
+  int32_t retry;         // 1: transposed launch re-runs only the prox epilogue with the new t
+  int32_t tested;        // pending candidate carries a sufficient-decrease test
+  int32_t first_commit;  // pending candidate is x0
+  int32_t ran_any;       // at least one iteration ran (FProxGD maxit==0 -> UnboundLocalError)
+  int32_t fault;
+  int32_t stage_end[3];
+  int32_t gy_sel;        // which of the two base-residual partial buffers is current
+  double t;              // trial step
+  double t_k;            // FProxGD: last accepted step (carried within a stage)
+  double theta;          // FProxGD: 2/(inner+1) of the running iteration
+  double mu;             // stage mu
+  double f_cur;          // objective (mu0) at the committed x
+  double s_cur;          // sparsity at the committed x
+  double f_prev, s_prev; // last recorded pair (stop rule)
+  double f_best;
+  double g_base;         // 0.5*||A base - b||^2 at the extrapolated / thresholded base point
+  int64_t n_fwd, n_tpass;
+};
+
+struct SolveConst {
+  int32_t algo;          // GLP_PROXGD / GLP_FPROXGD
+  int32_t step_type;
+  int32_t maxit;
+  int32_t stable_cap;
+  int32_t ls_cap;
+  int32_t hist_cap;
+  double thres, alpha0, ftol, atten, mu0;
+};
+
+// Geometry of one problem shard on one device.
+struct Geom {
+  int32_t m, n, l;       // n = local columns of A == local row groups of x
+  int32_t nrb, ncb;      // row blocks of TILE_ROWS, column blocks of TILE_COLS
+  int64_t ldm, ldn;      // padded vector lengths: nrb*TILE_ROWS, ncb*TILE_COLS
+  int32_t grid;          // CTAs of the streaming kernels (<= #SMs)
+  int32_t world;         // ranks sharing the rows of x (1 = single GPU)
+  int64_t n_total;       // sum of n over ranks (sparsity denominator)
+};
+
+// Forward stream  AX[:, q] = A * X[:, q]  for RC operand columns.
+struct FwdArgs {
+  const void* X[2];      // operand [RC][ldn] (dtype T), selected by sel
+  double* AX[2];         // output  [RC][ldm] fp64, selected by sel
+  const Ctrl* ctrl;      // nullable: when set, sel = 1 - ctrl->cur and done => no-op
+  int32_t sel;           // used when ctrl == nullptr
+  int32_t nb_cols;       // first nb_cols operand columns are compared against b[bcol0 + q]
+  int32_t bcol0;
+  int32_t count_mode;    // 1: aux warp evaluates the sparsity count of the candidate x
+  const double* b;       // [l][ldm]
+  double* partial;       // [(grid + nrb)][TILE_ROWS][RC]
+  unsigned* counter;     // [nrb], zero between launches
+  double* rr_partial;    // [nrb]  sum over rows of the block of (AX - b)^2
+  const double* scal_partial;  // [ncb][4] from the transposed epilogue (slot 3 = max|xn|)
+  const double* xcand[2];      // candidate x [l][ldn] fp64, selected like X
+  double* cnt_partial;   // [grid]
+  int32_t* fault;
+};
+
+// Transposed stream  G[:, c] = A^T * R[:, c]  for LC residual columns, optional fused epilogue.
+struct TpassArgs {
+  const void* R;         // [LC][ldm] (dtype T), zero padded
+  double* grad;          // [l][ldn] fp64, column gcol0 + c
+  int32_t gcol0;
+  int32_t fuse;          // 1: run the prox epilogue in the last-arriving CTA of each column block
+  const Ctrl* ctrl;      // nullable
+  double* partial;       // [(grid + ncb)][LC][TILE_COLS]
+  unsigned* counter;     // [ncb]
+  int32_t* fault;
+};
+
+// Prox epilogue operands (fused in the transposed stream or run stand-alone for retries / init).
+struct ProxArgs {
+  double* state[2];      // each: [3][l][ldn] = {x, xt, v}; committed = state[cur], candidates = state[1-cur]
+  void* xop;             // fp32 mode: operand copy [2l][ldn] float {xn | xnt}; fp64 mode: nullptr
+  const double* grad;    // [l][ldn]
+  double* scal_partial;  // [ncb][4] = {gd, dd, reg, max}
+  const Ctrl* ctrl;      // nullable: when null the explicit fields below are used
+  int32_t algo;
+  int32_t cur;
+  int32_t init;          // 1: candidate = x0 already stored in state[1-cur][0]; only threshold + scalars
+  int32_t pad;
+  double theta, t, mu, thres;
+};
+
+}  // namespace glp

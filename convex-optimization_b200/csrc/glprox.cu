@@ -1,0 +1,947 @@
+// glprox.cu -- libglprox.so: handle management, the streaming schedule and the C ABI (include/glprox.h).
+// Host side of the B200 proximal-gradient path; all numerics run in the sm_100a kernels of
+// glp_fwd.cuh / glp_tpass.cuh / glp_prox.cuh / glp_decide.cuh.  There is no CPU fallback: without an
+// sm_100 device every entry point that computes returns GLP_ERR_NO_DEVICE.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "../../include/glprox.h"
+#include "glp_decide.cuh"
+#include "glp_fwd.cuh"
+#include "glp_misc.cuh"
+#include "glp_tpass.cuh"
+#include "glp_types.cuh"
+
+using namespace glp;
+
+static_assert(sizeof(glp_opts) == 56 && sizeof(glp_result) == 80 && sizeof(glp_step_params) == 40,
+              "ABI structs changed: update glprox/_lib.py and tests/test_abi.py");
+
+// ------------------------------------------------------------------------------------------------
+// error plumbing
+// ------------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CU_TRY(expr)                                                                              \
+  do {                                                                                            \
+    cudaError_t e_ = (expr);                                                                      \
+    if (e_ != cudaSuccess)                                                                        \
+      return fail(GLP_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, \
+                  __LINE__);                                                                      \
+  } while (0)
+
+#define GLP_TRY(expr)        \
+  do {                       \
+    int rc_ = (expr);        \
+    if (rc_ != GLP_OK) return rc_; \
+  } while (0)
+
+extern "C" int glp_version(void) { return GLP_VERSION; }
+extern "C" const char* glp_last_error(void) { return g_err; }
+
+extern "C" int glp_device_count(void) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  int ok = 0;
+  for (int d = 0; d < n; ++d) {
+    int major = 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, d) == cudaSuccess && major == 10) ++ok;
+  }
+  return ok;
+}
+
+extern "C" int glp_default_opts(int algo, glp_opts* o) {
+  if (o == nullptr || (algo != GLP_PROXGD && algo != GLP_FPROXGD)) return fail(GLP_ERR_ARG, "bad algo/opts");
+  memset(o, 0, sizeof(*o));
+  // gl_ProxGD_primal.py:10-19 / gl_FProxGD_primal.py:10-19
+  o->maxit = algo == GLP_PROXGD ? 2500 : 1500;
+  o->thres = 1e-3;
+  o->step_type = GLP_STEP_LINE_SEARCH;
+  o->alpha0 = algo == GLP_PROXGD ? 2e-3 : 1e-3;
+  o->ftol = 1e-6;
+  o->stable_len_threshold = 70;
+  o->line_search_attenuation_coeffi = algo == GLP_PROXGD ? 0.9 : 0.98;
+  o->maxit_line_search_iter = 5;
+  o->backend = GLP_BACKEND_AUTO;
+  o->poll_interval = 0;
+  return GLP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// handle
+// ------------------------------------------------------------------------------------------------
+struct glp_handle {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  int dtype = GLP_F32;
+  Geom g{};
+  const void* A = nullptr;
+  int64_t lda = 0;
+  CUtensorMap tmap{};
+  int evict_first = 1;
+  int num_sms = 0;
+  void* nccl_comm = nullptr;
+
+  // device arena
+  void* arena = nullptr;
+  double *b = nullptr, *Av = nullptr, *grad = nullptr;
+  double* AX[2] = {nullptr, nullptr};
+  double* state[2] = {nullptr, nullptr};
+  double *scal_partial = nullptr, *cnt_partial = nullptr, *rr_partial = nullptr;
+  double* gy_partial[2] = {nullptr, nullptr};
+  void* r = nullptr;    // [l][ldm] dtype T
+  void* xop = nullptr;  // fp32: [2l][ldn] float
+  double *f_partial = nullptr, *t_partial = nullptr;
+  unsigned *f_counter = nullptr, *t_counter = nullptr;
+  Ctrl* ctrl = nullptr;  // [2]
+  int32_t* fault = nullptr;
+  double *f_hist = nullptr, *f_hist_best = nullptr;
+  int hist_cap = 0;
+  int decide_grid = 0;
+  int n_fchunks = 0;
+
+  // step-level scratch (lazily sized)
+  void* scratch = nullptr;
+  size_t scratch_bytes = 0;
+
+  // pinned host mirror + solve bookkeeping
+  Ctrl* h_ctrl = nullptr;  // [2] snapshots
+  cudaEvent_t ev_snap[2] = {nullptr, nullptr};
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  SolveConst sc{};
+  bool solving = false;
+  int64_t decide_launches = 0;
+  int64_t n_launches = 0;
+
+  // CUDA-event profile of the streaming launches
+  bool profiling = false;
+  std::vector<cudaEvent_t> ev_pool;
+  std::vector<int> ev_tag;  // per pair: 0 forward, 1 transposed
+  size_t ev_used = 0;       // pairs used in the current solve
+  glp_profile prof{};
+};
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int make_tensor_map(glp_handle* h) {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  CU_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  if (fn == nullptr || qres != cudaDriverEntryPointSuccess)
+    return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  const int esz = h->dtype == GLP_F32 ? 4 : 8;
+  const cuuint64_t dims[2] = {cuuint64_t(h->g.n), cuuint64_t(h->g.m)};
+  const cuuint64_t strides[1] = {cuuint64_t(h->lda) * esz};
+  const cuuint32_t box[2] = {cuuint32_t(TILE_ROW_BYTES / esz), cuuint32_t(TILE_ROWS)};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = reinterpret_cast<PFN_encodeTiled>(fn)(
+      &h->tmap, h->dtype == GLP_F32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2,
+      const_cast<void*>(h->A), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", int(r));
+  return GLP_OK;
+}
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ------------------------------------------------------------------------------------------------
+// CUDA-event profile of the streaming launches (roofline evidence measured on the launching stream)
+// ------------------------------------------------------------------------------------------------
+static void prof_mark(glp_handle* h, int tag, int end) {
+  if (!h->profiling) return;
+  const size_t idx = 2 * h->ev_used + size_t(end);
+  while (h->ev_pool.size() <= idx) {
+    cudaEvent_t e = nullptr;
+    if (cudaEventCreate(&e) != cudaSuccess) { h->profiling = false; return; }
+    h->ev_pool.push_back(e);
+  }
+  cudaEventRecord(h->ev_pool[idx], h->stream);
+  if (!end) {
+    if (h->ev_tag.size() <= h->ev_used) h->ev_tag.resize(h->ev_used + 1);
+    h->ev_tag[h->ev_used] = tag;
+  } else {
+    h->ev_used++;
+  }
+}
+
+static void prof_collect(glp_handle* h) {
+  if (!h->profiling || h->ev_used == 0) return;
+  std::vector<float> ms(h->ev_used, 0.f);
+  float mx[2] = {0.f, 0.f};
+  for (size_t i = 0; i < h->ev_used; ++i) {
+    if (cudaEventElapsedTime(&ms[i], h->ev_pool[2 * i], h->ev_pool[2 * i + 1]) != cudaSuccess) ms[i] = 0.f;
+    mx[h->ev_tag[i]] = std::max(mx[h->ev_tag[i]], ms[i]);
+  }
+  for (size_t i = 0; i < h->ev_used; ++i) {
+    const int tag = h->ev_tag[i];
+    if (ms[i] < 0.5f * mx[tag]) continue;  // no-op after `done`, or epilogue-only retry
+    if (tag == 0) {
+      h->prof.fwd_ms_min = h->prof.fwd_launches == 0 ? ms[i] : std::min<double>(h->prof.fwd_ms_min, ms[i]);
+      h->prof.fwd_launches++; h->prof.fwd_ms_sum += ms[i];
+    } else {
+      h->prof.tpass_ms_min = h->prof.tpass_launches == 0 ? ms[i] : std::min<double>(h->prof.tpass_ms_min, ms[i]);
+      h->prof.tpass_launches++; h->prof.tpass_ms_sum += ms[i];
+    }
+  }
+  h->ev_used = 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernel launch helpers (dtype / chunk-width dispatch)
+// ------------------------------------------------------------------------------------------------
+template <typename T, int RC>
+static cudaError_t launch_fwd_t(glp_handle* h, const FwdArgs& a) {
+  static bool attr_set[64] = {false};
+  auto kfn = glp_fwd_kernel<T, RC>;
+  if (!attr_set[h->device & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, fwd_smem_bytes<RC>());
+    if (e != cudaSuccess) return e;
+    attr_set[h->device & 63] = true;
+  }
+  prof_mark(h, 0, 0);
+  kfn<<<h->g.grid, FWD_THREADS, fwd_smem_bytes<RC>(), h->stream>>>(h->tmap, a, h->g, h->evict_first);
+  prof_mark(h, 0, 1);
+  h->n_launches++;
+  return cudaGetLastError();
+}
+
+static cudaError_t launch_fwd(glp_handle* h, int rc, const FwdArgs& a) {
+  if (h->dtype == GLP_F32) {
+    if (rc == 4) return launch_fwd_t<float, 4>(h, a);
+    if (rc == 2) return launch_fwd_t<float, 2>(h, a);
+    return launch_fwd_t<float, 1>(h, a);
+  }
+  if (rc == 4) return launch_fwd_t<double, 4>(h, a);
+  if (rc == 2) return launch_fwd_t<double, 2>(h, a);
+  return launch_fwd_t<double, 1>(h, a);
+}
+
+template <typename T, int LC>
+static cudaError_t launch_tpass_t(glp_handle* h, const TpassArgs& a, const ProxArgs& p) {
+  static bool attr_set[64] = {false};
+  auto kfn = glp_tpass_kernel<T, LC>;
+  if (!attr_set[h->device & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, tp_smem_bytes<T, LC>());
+    if (e != cudaSuccess) return e;
+    attr_set[h->device & 63] = true;
+  }
+  prof_mark(h, 1, 0);
+  kfn<<<h->g.grid, TP_THREADS, tp_smem_bytes<T, LC>(), h->stream>>>(h->tmap, a, p, h->g, h->evict_first);
+  prof_mark(h, 1, 1);
+  h->n_launches++;
+  return cudaGetLastError();
+}
+
+static cudaError_t launch_tpass(glp_handle* h, int lc, const TpassArgs& a, const ProxArgs& p) {
+  if (h->dtype == GLP_F32) return lc == 2 ? launch_tpass_t<float, 2>(h, a, p) : launch_tpass_t<float, 1>(h, a, p);
+  return lc == 2 ? launch_tpass_t<double, 2>(h, a, p) : launch_tpass_t<double, 1>(h, a, p);
+}
+
+static cudaError_t launch_prox(glp_handle* h, const ProxArgs& p, int only_if_retry) {
+  const int grid = std::min<int>(h->g.ncb, 4 * h->num_sms);
+  if (h->dtype == GLP_F32)
+    glp_prox_kernel<float><<<grid, CONSUMER_THREADS, 0, h->stream>>>(p, h->g, only_if_retry);
+  else
+    glp_prox_kernel<double><<<grid, CONSUMER_THREADS, 0, h->stream>>>(p, h->g, only_if_retry);
+  h->n_launches++;
+  return cudaGetLastError();
+}
+
+static cudaError_t launch_decide(glp_handle* h, const DecideArgs& a) {
+  if (h->dtype == GLP_F32)
+    glp_decide_kernel<float><<<h->decide_grid, DECIDE_THREADS, 0, h->stream>>>(a, h->g);
+  else
+    glp_decide_kernel<double><<<h->decide_grid, DECIDE_THREADS, 0, h->stream>>>(a, h->g);
+  h->n_launches++;
+  return cudaGetLastError();
+}
+
+// Operand columns of the forward stream are processed in chunks of 4, 2 or 1.
+static int next_chunk(int remaining) { return remaining >= 4 ? 4 : (remaining >= 2 ? 2 : 1); }
+static int count_fchunks(int ncols) {
+  int n = 0;
+  for (int q = 0; q < ncols; q += next_chunk(ncols - q)) ++n;
+  return n;
+}
+
+template <typename S, typename D>
+static cudaError_t to_planar(cudaStream_t st, const S* src, D* dst, int64_t rows, int cols, int64_t ld) {
+  const int64_t total = rows * cols;
+  if (total == 0) return cudaSuccess;
+  const int grid = int(std::min<int64_t>((total + 255) / 256, 2048));
+  to_planar_kernel<S, D><<<grid, 256, 0, st>>>(src, dst, rows, cols, ld);
+  return cudaGetLastError();
+}
+template <typename S, typename D>
+static cudaError_t from_planar(cudaStream_t st, const S* src, D* dst, int64_t rows, int cols, int64_t ld) {
+  const int64_t total = rows * cols;
+  if (total == 0) return cudaSuccess;
+  const int grid = int(std::min<int64_t>((total + 255) / 256, 2048));
+  from_planar_kernel<S, D><<<grid, 256, 0, st>>>(src, dst, rows, cols, ld);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// create / destroy
+// ------------------------------------------------------------------------------------------------
+static int check_device(int device, int* num_sms) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    return fail(GLP_ERR_NO_DEVICE, "no CUDA device visible (%s); libglprox has no CPU fallback",
+                e == cudaSuccess ? "count is 0" : cudaGetErrorString(e));
+  }
+  if (device < 0 || device >= n) return fail(GLP_ERR_ARG, "device %d out of range (have %d)", device, n);
+  int major = 0;
+  CU_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+  if (major != 10)
+    return fail(GLP_ERR_NO_DEVICE, "device %d has compute capability %d.x; this library is sm_100a only", device, major);
+  CU_TRY(cudaDeviceGetAttribute(num_sms, cudaDevAttrMultiProcessorCount, device));
+  return GLP_OK;
+}
+
+extern "C" int glp_destroy(glp_handle* h) {
+  if (h == nullptr) return GLP_OK;
+  cudaSetDevice(h->device);
+  if (h->stream != nullptr || true) cudaStreamSynchronize(h->stream);
+  if (h->arena) cudaFree(h->arena);
+  if (h->scratch) cudaFree(h->scratch);
+  if (h->f_hist) cudaFree(h->f_hist);
+  if (h->h_ctrl) cudaFreeHost(h->h_ctrl);
+  for (int i = 0; i < 2; ++i)
+    if (h->ev_snap[i]) cudaEventDestroy(h->ev_snap[i]);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
+  cudaGetLastError();
+  delete h;
+  return GLP_OK;
+}
+
+extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int l, int dtype, const void* A_dev,
+                          int64_t lda, const void* b_dev, void* nccl_comm, void* stream) {
+  if (out == nullptr) return fail(GLP_ERR_ARG, "out is null");
+  *out = nullptr;
+  if (dtype != GLP_F32 && dtype != GLP_F64) return fail(GLP_ERR_ARG, "dtype must be GLP_F32 or GLP_F64");
+  if (m <= 0 || n_local <= 0 || l <= 0) return fail(GLP_ERR_ARG, "m, n, l must be positive (got %d %d %d)", m, n_local, l);
+  if (A_dev == nullptr || b_dev == nullptr) return fail(GLP_ERR_ARG, "A_dev / b_dev is null");
+  const int esz = dtype == GLP_F32 ? 4 : 8;
+  if (lda < n_local) return fail(GLP_ERR_ARG, "lda (%lld) < n (%d)", (long long)lda, n_local);
+  if ((lda * esz) % 16 != 0 || (reinterpret_cast<uintptr_t>(A_dev) % 16) != 0)
+    return fail(GLP_ERR_ARG, "A_dev and lda*sizeof(T) must be 16-byte aligned for TMA (lda=%lld)", (long long)lda);
+  int num_sms = 0;
+  GLP_TRY(check_device(device, &num_sms));
+  CU_TRY(cudaSetDevice(device));
+
+  glp_handle* h = new glp_handle();
+  h->device = device;
+  h->stream = static_cast<cudaStream_t>(stream);
+  h->dtype = dtype;
+  h->A = A_dev;
+  h->lda = lda;
+  h->num_sms = num_sms;
+  h->nccl_comm = nccl_comm;
+  const int tc = TILE_ROW_BYTES / esz;
+  Geom& g = h->g;
+  g.m = m; g.n = n_local; g.l = l;
+  g.nrb = (m + TILE_ROWS - 1) / TILE_ROWS;
+  g.ncb = (n_local + tc - 1) / tc;
+  g.ldm = int64_t(g.nrb) * TILE_ROWS;
+  g.ldn = int64_t(g.ncb) * tc;
+  const int64_t ntiles = int64_t(g.nrb) * g.ncb;
+  g.grid = int(std::min<int64_t>(num_sms, ntiles));
+  g.world = 1;
+  g.n_total = n_local;
+  h->evict_first = (double(m) * double(lda) * esz > 64.0 * 1024 * 1024) ? 1 : 0;
+  h->n_fchunks = count_fchunks(2 * l);
+  const int64_t vec_len = int64_t(l) * std::max(g.ldm, g.ldn);
+  h->decide_grid = int(std::max<int64_t>(1, std::min<int64_t>(num_sms, (vec_len + 4 * DECIDE_THREADS - 1) / (4 * DECIDE_THREADS))));
+
+  int rc = make_tensor_map(h);
+  if (rc != GLP_OK) { glp_destroy(h); return rc; }
+
+  // ---- carve the arena
+  size_t off = 0;
+  auto carve = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+  const size_t lm = size_t(l) * g.ldm, ln = size_t(l) * g.ldn;
+  const size_t o_b = carve(lm * 8), o_ax0 = carve(2 * lm * 8), o_ax1 = carve(2 * lm * 8), o_av = carve(lm * 8);
+  const size_t o_r = carve(lm * esz);
+  const size_t o_s0 = carve(3 * ln * 8), o_s1 = carve(3 * ln * 8), o_grad = carve(ln * 8);
+  const size_t o_xop = carve(dtype == GLP_F32 ? 2 * ln * 4 : 0);
+  const size_t o_scal = carve(size_t(g.ncb) * 4 * 8), o_cnt = carve(size_t(g.grid) * 8);
+  const size_t o_rr = carve(size_t(h->n_fchunks) * g.nrb * 8);
+  const size_t o_gy0 = carve(size_t(h->decide_grid) * 8), o_gy1 = carve(size_t(h->decide_grid) * 8);
+  const size_t o_fp = carve(size_t(g.grid + g.nrb) * TILE_ROWS * 4 * 8);
+  const size_t o_tp = carve(size_t(g.grid + g.ncb) * 2 * tc * 8);
+  const size_t o_fc = carve(size_t(g.nrb) * 4), o_tc = carve(size_t(g.ncb) * 4);
+  const size_t o_ctrl = carve(2 * sizeof(Ctrl)), o_fault = carve(16);
+  cudaError_t e = cudaMalloc(&h->arena, off);
+  if (e != cudaSuccess) { glp_destroy(h); return fail(GLP_ERR_CUDA, "cudaMalloc(%zu) failed: %s", off, cudaGetErrorString(e)); }
+  e = cudaMemsetAsync(h->arena, 0, off, h->stream);
+  if (e != cudaSuccess) { glp_destroy(h); return fail(GLP_ERR_CUDA, "cudaMemsetAsync failed: %s", cudaGetErrorString(e)); }
+  char* base = static_cast<char*>(h->arena);
+  h->b = reinterpret_cast<double*>(base + o_b);
+  h->AX[0] = reinterpret_cast<double*>(base + o_ax0);
+  h->AX[1] = reinterpret_cast<double*>(base + o_ax1);
+  h->Av = reinterpret_cast<double*>(base + o_av);
+  h->r = base + o_r;
+  h->state[0] = reinterpret_cast<double*>(base + o_s0);
+  h->state[1] = reinterpret_cast<double*>(base + o_s1);
+  h->grad = reinterpret_cast<double*>(base + o_grad);
+  h->xop = dtype == GLP_F32 ? static_cast<void*>(base + o_xop) : nullptr;
+  h->scal_partial = reinterpret_cast<double*>(base + o_scal);
+  h->cnt_partial = reinterpret_cast<double*>(base + o_cnt);
+  h->rr_partial = reinterpret_cast<double*>(base + o_rr);
+  h->gy_partial[0] = reinterpret_cast<double*>(base + o_gy0);
+  h->gy_partial[1] = reinterpret_cast<double*>(base + o_gy1);
+  h->f_partial = reinterpret_cast<double*>(base + o_fp);
+  h->t_partial = reinterpret_cast<double*>(base + o_tp);
+  h->f_counter = reinterpret_cast<unsigned*>(base + o_fc);
+  h->t_counter = reinterpret_cast<unsigned*>(base + o_tc);
+  h->ctrl = reinterpret_cast<Ctrl*>(base + o_ctrl);
+  h->fault = reinterpret_cast<int32_t*>(base + o_fault);
+
+  // b: row-major [m][l] dtype T -> planar fp64 [l][ldm]
+  if (dtype == GLP_F32) e = to_planar(h->stream, static_cast<const float*>(b_dev), h->b, m, l, g.ldm);
+  else e = to_planar(h->stream, static_cast<const double*>(b_dev), h->b, m, l, g.ldm);
+  if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&h->h_ctrl), 2 * sizeof(Ctrl));
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&h->ev_snap[i], cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
+  if (e != cudaSuccess) { glp_destroy(h); return fail(GLP_ERR_CUDA, "handle setup failed: %s", cudaGetErrorString(e)); }
+  *out = h;
+  return GLP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// stream enqueue helpers
+// ------------------------------------------------------------------------------------------------
+static int esize(const glp_handle* h) { return h->dtype == GLP_F32 ? 4 : 8; }
+
+// Forward stream over `ncols` operand columns.  Xb[s] / AXb[s]: planar operand / output bases.
+static int enqueue_fwd(glp_handle* h, const Ctrl* ctrl, int sel, const void* const Xb[2], double* const AXb[2],
+                       const double* const xcand[2], int ncols, int count_mode) {
+  const Geom& g = h->g;
+  int chunk = 0;
+  for (int q = 0; q < ncols; ++chunk) {
+    const int rc = next_chunk(ncols - q);
+    FwdArgs a{};
+    for (int s = 0; s < 2; ++s) {
+      a.X[s] = static_cast<const char*>(Xb[s]) + size_t(q) * g.ldn * esize(h);
+      a.AX[s] = AXb[s] + size_t(q) * g.ldm;
+      a.xcand[s] = xcand ? xcand[s] : nullptr;
+    }
+    a.ctrl = ctrl;
+    a.sel = sel;
+    a.nb_cols = std::max(0, std::min(rc, g.l - q));
+    a.bcol0 = q;
+    a.count_mode = (chunk == 0 && count_mode) ? 1 : 0;
+    a.b = h->b;
+    a.partial = h->f_partial;
+    a.counter = h->f_counter;
+    a.rr_partial = h->rr_partial + size_t(chunk) * g.nrb;
+    a.scal_partial = h->scal_partial;
+    a.cnt_partial = h->cnt_partial;
+    a.fault = h->fault;
+    CU_TRY(launch_fwd(h, rc, a));
+    q += rc;
+  }
+  return GLP_OK;
+}
+
+// Transposed stream over the l residual columns + prox epilogue (fused when l <= 2).
+static int enqueue_tpass(glp_handle* h, const Ctrl* ctrl, const ProxArgs* p, double* grad) {
+  const Geom& g = h->g;
+  ProxArgs pa{};
+  if (p) pa = *p;
+  const bool fuse = p != nullptr && g.l <= 2;
+  for (int q = 0; q < g.l;) {
+    const int lc = (g.l - q) >= 2 ? 2 : 1;
+    TpassArgs a{};
+    a.R = static_cast<const char*>(h->r) + size_t(q) * g.ldm * esize(h);
+    a.grad = grad;
+    a.gcol0 = q;
+    a.fuse = fuse ? 1 : 0;
+    a.ctrl = ctrl;
+    a.partial = h->t_partial;
+    a.counter = h->t_counter;
+    a.fault = h->fault;
+    CU_TRY(launch_tpass(h, lc, a, pa));
+    q += lc;
+  }
+  if (p != nullptr && !fuse) CU_TRY(launch_prox(h, pa, 0));
+  return GLP_OK;
+}
+
+static ProxArgs solver_prox_args(glp_handle* h, const Ctrl* ctrl) {
+  ProxArgs p{};
+  p.state[0] = h->state[0];
+  p.state[1] = h->state[1];
+  p.xop = h->xop;
+  p.grad = h->grad;
+  p.scal_partial = h->scal_partial;
+  p.ctrl = ctrl;
+  p.algo = h->sc.algo;
+  p.thres = h->sc.thres;
+  return p;
+}
+
+static int enqueue_solver_fwd(glp_handle* h, const Ctrl* ctrl) {
+  const void* Xb[2];
+  const double* xc[2] = {h->state[0], h->state[1]};
+  for (int s = 0; s < 2; ++s) Xb[s] = h->dtype == GLP_F32 ? h->xop : static_cast<const void*>(h->state[s]);
+  return enqueue_fwd(h, ctrl, 0, Xb, h->AX, xc, 2 * h->g.l, 1);
+}
+
+// ------------------------------------------------------------------------------------------------
+// whole solve
+// ------------------------------------------------------------------------------------------------
+extern "C" int glp_solve_begin(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o) {
+  if (h == nullptr || x0_dev == nullptr || o == nullptr) return fail(GLP_ERR_ARG, "null argument");
+  if (algo != GLP_PROXGD && algo != GLP_FPROXGD) return fail(GLP_ERR_ARG, "unknown algo %d", algo);
+  if (o->step_type < GLP_STEP_LINE_SEARCH || o->step_type > GLP_STEP_DIMINISHING2)
+    return fail(GLP_ERR_ARG, "unsupported step_type %d", o->step_type);
+  if (o->maxit < 0 || o->maxit > (1 << 26)) return fail(GLP_ERR_ARG, "maxit out of range");
+  CU_TRY(cudaSetDevice(h->device));
+  const Geom& g = h->g;
+  SolveConst& sc = h->sc;
+  sc.algo = algo; sc.step_type = o->step_type; sc.maxit = o->maxit; sc.stable_cap = o->stable_len_threshold;
+  sc.ls_cap = o->maxit_line_search_iter; sc.thres = o->thres; sc.alpha0 = o->alpha0; sc.ftol = o->ftol;
+  sc.atten = o->line_search_attenuation_coeffi; sc.mu0 = mu0;
+  sc.hist_cap = 3 * o->maxit + 8;
+  if (h->hist_cap < sc.hist_cap) {
+    if (h->f_hist) CU_TRY(cudaFree(h->f_hist));
+    h->f_hist = nullptr;
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->f_hist), size_t(2) * sc.hist_cap * sizeof(double)));
+    h->hist_cap = sc.hist_cap;
+  }
+  h->f_hist_best = h->f_hist + h->hist_cap;
+  h->n_launches = 0;
+  CU_TRY(cudaEventRecord(h->ev0, h->stream));
+
+  Ctrl c0;
+  memset(&c0, 0, sizeof(c0));
+  ctrl_init(c0, sc);
+  c0.n_fwd = 1;
+  CU_TRY(cudaMemcpyAsync(&h->ctrl[0], &c0, sizeof(Ctrl), cudaMemcpyHostToDevice, h->stream));
+  CU_TRY(cudaMemcpyAsync(&h->ctrl[1], &c0, sizeof(Ctrl), cudaMemcpyHostToDevice, h->stream));
+  CU_TRY(cudaMemsetAsync(h->fault, 0, sizeof(int32_t), h->stream));
+  CU_TRY(cudaMemsetAsync(h->gy_partial[0], 0, size_t(h->decide_grid) * 8, h->stream));
+  CU_TRY(cudaMemsetAsync(h->gy_partial[1], 0, size_t(h->decide_grid) * 8, h->stream));
+
+  // x0 -> candidate slot of cur = 0, then threshold + scalars (init epilogue) and the first forward stream
+  if (h->dtype == GLP_F32) CU_TRY(to_planar(h->stream, static_cast<const float*>(x0_dev), h->state[1], g.n, g.l, g.ldn));
+  else CU_TRY(to_planar(h->stream, static_cast<const double*>(x0_dev), h->state[1], g.n, g.l, g.ldn));
+  ProxArgs p = solver_prox_args(h, nullptr);
+  p.cur = 0;
+  p.init = 1;
+  CU_TRY(launch_prox(h, p, 0));
+  GLP_TRY(enqueue_solver_fwd(h, &h->ctrl[0]));
+  h->decide_launches = 0;
+  h->solving = true;
+  return GLP_OK;
+}
+
+extern "C" int glp_solve_step(glp_handle* h, int slots) {
+  if (h == nullptr || !h->solving) return fail(GLP_ERR_STATE, "glp_solve_step before glp_solve_begin");
+  CU_TRY(cudaSetDevice(h->device));
+  for (int s = 0; s < slots; ++s) {
+    const int64_t j = h->decide_launches++;
+    const Ctrl* cin = &h->ctrl[j & 1];
+    Ctrl* cout = &h->ctrl[(j + 1) & 1];
+    DecideArgs d{};
+    d.cin = cin; d.cout = cout; d.sc = h->sc;
+    d.rr_partial = h->rr_partial; d.n_rr = h->n_fchunks * h->g.nrb;
+    d.scal_partial = h->scal_partial; d.n_scal = h->g.ncb;
+    d.cnt_partial = h->cnt_partial; d.n_cnt = h->g.grid;
+    d.gy_partial[0] = h->gy_partial[0]; d.gy_partial[1] = h->gy_partial[1]; d.n_gy = h->decide_grid;
+    d.AX[0] = h->AX[0]; d.AX[1] = h->AX[1]; d.Av = h->Av; d.b = h->b; d.r = h->r;
+    d.state[0] = h->state[0]; d.state[1] = h->state[1];
+    d.f_hist = h->f_hist; d.f_hist_best = h->f_hist_best;
+    CU_TRY(launch_decide(h, d));
+    ProxArgs p = solver_prox_args(h, cout);
+    GLP_TRY(enqueue_tpass(h, cout, &p, h->grad));
+    GLP_TRY(enqueue_solver_fwd(h, cout));
+  }
+  return GLP_OK;
+}
+
+static void fill_result(const glp_handle* h, const Ctrl& c, glp_result* res) {
+  if (res == nullptr) return;
+  res->iters = c.k;
+  res->done = c.done;
+  res->backend_used = GLP_BACKEND_STREAM;
+  res->fval = c.f_cur;
+  res->sparsity = c.s_cur;
+  res->n_fwd = c.n_fwd;
+  res->n_tpass = c.n_tpass;
+  res->n_launches = h->n_launches;
+  for (int i = 0; i < 3; ++i) res->stage_end[i] = c.stage_end[i];
+}
+
+static int check_fault(glp_handle* h, cudaError_t sync_err) {
+  if (sync_err != cudaSuccess) {
+    h->solving = false;
+    return fail(GLP_ERR_DEVICE_FAULT, "kernel fault during solve: %s", cudaGetErrorString(sync_err));
+  }
+  return GLP_OK;
+}
+
+extern "C" int glp_solve_poll(glp_handle* h, glp_result* res) {
+  if (h == nullptr || !h->solving) return fail(GLP_ERR_STATE, "glp_solve_poll before glp_solve_begin");
+  CU_TRY(cudaSetDevice(h->device));
+  CU_TRY(cudaMemcpyAsync(&h->h_ctrl[0], &h->ctrl[h->decide_launches & 1], sizeof(Ctrl), cudaMemcpyDeviceToHost, h->stream));
+  GLP_TRY(check_fault(h, cudaStreamSynchronize(h->stream)));
+  if (res) { memset(res, 0, sizeof(*res)); fill_result(h, h->h_ctrl[0], res); }
+  return GLP_OK;
+}
+
+extern "C" int glp_solve_end(glp_handle* h, void* x_out_dev, glp_result* res, double* f_hist_host, int hist_cap) {
+  if (h == nullptr || !h->solving) return fail(GLP_ERR_STATE, "glp_solve_end before glp_solve_begin");
+  CU_TRY(cudaSetDevice(h->device));
+  const Geom& g = h->g;
+  CU_TRY(cudaMemcpyAsync(&h->h_ctrl[0], &h->ctrl[h->decide_launches & 1], sizeof(Ctrl), cudaMemcpyDeviceToHost, h->stream));
+  int32_t fault = 0;
+  CU_TRY(cudaMemcpyAsync(&fault, h->fault, sizeof(fault), cudaMemcpyDeviceToHost, h->stream));
+  GLP_TRY(check_fault(h, cudaStreamSynchronize(h->stream)));
+  const Ctrl c = h->h_ctrl[0];
+  h->solving = false;
+  if (res) memset(res, 0, sizeof(*res));
+  if (fault != 0) {
+    if (res) res->status = GLP_ERR_DEVICE_FAULT;
+    return fail(GLP_ERR_DEVICE_FAULT, "pipeline watchdog fired inside a streaming kernel");
+  }
+  if (x_out_dev != nullptr) {
+    const double* x = h->state[c.cur];
+    if (h->dtype == GLP_F32) CU_TRY(from_planar(h->stream, x, static_cast<float*>(x_out_dev), g.n, g.l, g.ldn));
+    else CU_TRY(from_planar(h->stream, x, static_cast<double*>(x_out_dev), g.n, g.l, g.ldn));
+  }
+  if (f_hist_host != nullptr && hist_cap > 0 && c.k > 0)
+    CU_TRY(cudaMemcpyAsync(f_hist_host, h->f_hist, sizeof(double) * std::min(hist_cap, std::min(c.k, h->sc.hist_cap)),
+                           cudaMemcpyDeviceToHost, h->stream));
+  CU_TRY(cudaEventRecord(h->ev1, h->stream));
+  GLP_TRY(check_fault(h, cudaStreamSynchronize(h->stream)));
+  float ms = 0.f;
+  CU_TRY(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+  prof_collect(h);
+  fill_result(h, c, res);
+  if (res) res->device_ms = ms;
+  if (h->sc.algo == GLP_FPROXGD && !c.ran_any) {
+    if (res) res->status = GLP_ERR_UNBOUND;
+    return fail(GLP_ERR_UNBOUND, "FProxGD ran no iteration (maxit == 0): the reference raises UnboundLocalError");
+  }
+  if (res) res->status = c.done ? GLP_OK : GLP_ERR_STATE;
+  return GLP_OK;
+}
+
+extern "C" int glp_solve(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o, void* x_out_dev,
+                         glp_result* res, double* f_hist_host, int hist_cap) {
+  GLP_TRY(glp_solve_begin(h, algo, x0_dev, mu0, o));
+  // Host runs ahead of the device: batch i+1 is enqueued before the control snapshot taken after
+  // batch i is inspected, so the stream never drains while the solve is in progress.
+  const int64_t max_slots = int64_t(3) * o->maxit * (int64_t(o->maxit_line_search_iter) + 1) + 8;
+  int batch = o->poll_interval > 0 ? o->poll_interval : 32;
+  int64_t issued = 0;
+  int pending = -1;  // snapshot slot whose event has not been inspected yet
+  bool done = false;
+  int cur_slot = 0;
+  while (!done && issued < max_slots) {
+    GLP_TRY(glp_solve_step(h, batch));
+    issued += batch;
+    CU_TRY(cudaMemcpyAsync(&h->h_ctrl[cur_slot], &h->ctrl[h->decide_launches & 1], sizeof(Ctrl), cudaMemcpyDeviceToHost, h->stream));
+    CU_TRY(cudaEventRecord(h->ev_snap[cur_slot], h->stream));
+    if (pending >= 0) {
+      GLP_TRY(check_fault(h, cudaEventSynchronize(h->ev_snap[pending])));
+      if (h->h_ctrl[pending].done) done = true;
+    }
+    pending = cur_slot;
+    cur_slot ^= 1;
+  }
+  return glp_solve_end(h, x_out_dev, res, f_hist_host, hist_cap);
+}
+
+// ------------------------------------------------------------------------------------------------
+// step-level entry points (kernel parity tests drive these)
+// ------------------------------------------------------------------------------------------------
+static int ensure_scratch(glp_handle* h, size_t bytes) {
+  if (h->scratch_bytes >= bytes) return GLP_OK;
+  if (h->scratch) CU_TRY(cudaFree(h->scratch));
+  h->scratch = nullptr;
+  h->scratch_bytes = 0;
+  CU_TRY(cudaMalloc(&h->scratch, bytes));
+  h->scratch_bytes = bytes;
+  return GLP_OK;
+}
+
+__global__ void sum_partials_kernel(const double* __restrict__ part, int n, int stride, int offset, int is_max,
+                                    double* __restrict__ out) {
+  // single CTA, fixed order: thread-strided, warp tree, warps in order
+  __shared__ double s[8];
+  double v = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const double x = part[size_t(i) * stride + offset];
+    v = is_max ? ((v != v) ? v : ((x != x) ? x : fmax(v, x))) : v + x;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const double y = __shfl_xor_sync(0xffffffffu, v, o);
+    v = is_max ? ((v != v) ? v : ((y != y) ? y : fmax(v, y))) : v + y;
+  }
+  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = s[0];
+    for (int w = 1; w < int(blockDim.x >> 5); ++w) t = is_max ? ((t != t) ? t : ((s[w] != s[w]) ? s[w] : fmax(t, s[w]))) : t + s[w];
+    *out = t;
+  }
+}
+
+extern "C" int glp_fwd(glp_handle* h, const void* X_dev, int ncols, double* AX_dev, double* rr_dev) {
+  if (h == nullptr || X_dev == nullptr || AX_dev == nullptr || ncols <= 0) return fail(GLP_ERR_ARG, "bad argument");
+  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
+  CU_TRY(cudaSetDevice(h->device));
+  const Geom& g = h->g;
+  const int es = esize(h);
+  const size_t xb = align_up(size_t(ncols) * g.ldn * es, 256), ab = align_up(size_t(ncols) * g.ldm * 8, 256);
+  const int nch = count_fchunks(ncols);
+  const size_t rb = align_up(size_t(nch) * g.nrb * 8, 256);
+  GLP_TRY(ensure_scratch(h, xb + ab + rb));
+  char* base = static_cast<char*>(h->scratch);
+  void* Xp = base;
+  double* AXp = reinterpret_cast<double*>(base + xb);
+  double* rrp = reinterpret_cast<double*>(base + xb + ab);
+  CU_TRY(cudaMemsetAsync(base, 0, xb + ab + rb, h->stream));
+  if (h->dtype == GLP_F32) CU_TRY(to_planar(h->stream, static_cast<const float*>(X_dev), static_cast<float*>(Xp), g.n, ncols, g.ldn));
+  else CU_TRY(to_planar(h->stream, static_cast<const double*>(X_dev), static_cast<double*>(Xp), g.n, ncols, g.ldn));
+  const void* Xb[2] = {Xp, Xp};
+  double* AXb[2] = {AXp, AXp};
+  double* saved_rr = h->rr_partial;
+  h->rr_partial = rrp;  // chunk-indexed inside enqueue_fwd
+  int rc = enqueue_fwd(h, nullptr, 0, Xb, AXb, nullptr, ncols, 0);
+  h->rr_partial = saved_rr;
+  GLP_TRY(rc);
+  CU_TRY(from_planar(h->stream, AXp, AX_dev, g.m, ncols, g.ldm));
+  if (rr_dev != nullptr) {
+    sum_partials_kernel<<<1, 256, 0, h->stream>>>(rrp, nch * g.nrb, 1, 0, 0, rr_dev);
+    CU_TRY(cudaGetLastError());
+  }
+  return GLP_OK;
+}
+
+extern "C" int glp_tpass_prox(glp_handle* h, const glp_step_params* sp, const double* R_dev, double* G_dev,
+                              const double* xt_dev, const double* v_dev, double* xn_dev, double* xnt_dev,
+                              double* vn_dev, double* scalars_dev) {
+  if (h == nullptr || R_dev == nullptr) return fail(GLP_ERR_ARG, "bad argument");
+  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
+  if (sp != nullptr && (xt_dev == nullptr || xn_dev == nullptr || xnt_dev == nullptr || scalars_dev == nullptr))
+    return fail(GLP_ERR_ARG, "epilogue requested but xt/xn/xnt/scalars missing");
+  if (sp != nullptr && sp->algo == GLP_FPROXGD && (v_dev == nullptr || vn_dev == nullptr))
+    return fail(GLP_ERR_ARG, "FProxGD epilogue needs v and vn");
+  CU_TRY(cudaSetDevice(h->device));
+  const Geom& g = h->g;
+  const size_t ln = size_t(g.l) * g.ldn;
+  // residual -> planar dtype T
+  if (h->dtype == GLP_F32) CU_TRY(to_planar(h->stream, R_dev, static_cast<float*>(h->r), g.m, g.l, g.ldm));
+  else CU_TRY(to_planar(h->stream, R_dev, static_cast<double*>(h->r), g.m, g.l, g.ldm));
+  ProxArgs p{};
+  if (sp != nullptr) {
+    CU_TRY(to_planar(h->stream, xt_dev, h->state[0] + ln, g.n, g.l, g.ldn));
+    if (v_dev) CU_TRY(to_planar(h->stream, v_dev, h->state[0] + 2 * ln, g.n, g.l, g.ldn));
+    p = solver_prox_args(h, nullptr);
+    p.algo = sp->algo; p.cur = 0; p.init = 0;
+    p.theta = sp->theta; p.t = sp->t; p.mu = sp->mu; p.thres = sp->thres;
+  }
+  GLP_TRY(enqueue_tpass(h, nullptr, sp ? &p : nullptr, h->grad));
+  if (G_dev) CU_TRY(from_planar(h->stream, h->grad, G_dev, g.n, g.l, g.ldn));
+  if (sp != nullptr) {
+    CU_TRY(from_planar(h->stream, h->state[1], xn_dev, g.n, g.l, g.ldn));
+    CU_TRY(from_planar(h->stream, h->state[1] + ln, xnt_dev, g.n, g.l, g.ldn));
+    if (vn_dev && sp->algo == GLP_FPROXGD) CU_TRY(from_planar(h->stream, h->state[1] + 2 * ln, vn_dev, g.n, g.l, g.ldn));
+    for (int k = 0; k < 4; ++k) {
+      sum_partials_kernel<<<1, 256, 0, h->stream>>>(h->scal_partial, g.ncb, 4, k, k == 3 ? 1 : 0, scalars_dev + k);
+      CU_TRY(cudaGetLastError());
+    }
+  }
+  return GLP_OK;
+}
+
+extern "C" int glp_set_profiling(glp_handle* h, int on) {
+  if (h == nullptr) return fail(GLP_ERR_ARG, "null handle");
+  h->profiling = on != 0;
+  h->ev_used = 0;
+  memset(&h->prof, 0, sizeof(h->prof));
+  return GLP_OK;
+}
+
+extern "C" int glp_get_profile(glp_handle* h, glp_profile* out) {
+  if (h == nullptr || out == nullptr) return fail(GLP_ERR_ARG, "null argument");
+  *out = h->prof;
+  out->bytes_per_launch = double(h->g.m) * double(h->g.n) * esize(h);
+  return GLP_OK;
+}
+
+extern "C" int glp_debug_read(glp_handle* h, int which, double* out_host) {
+  if (h == nullptr || out_host == nullptr) return fail(GLP_ERR_ARG, "bad argument");
+  CU_TRY(cudaSetDevice(h->device));
+  const Geom& g = h->g;
+  Ctrl c;
+  CU_TRY(cudaMemcpyAsync(&c, &h->ctrl[h->decide_launches & 1], sizeof(Ctrl), cudaMemcpyDeviceToHost, h->stream));
+  CU_TRY(cudaStreamSynchronize(h->stream));
+  const size_t ln = size_t(g.l) * g.ldn, lm = size_t(g.l) * g.ldm;
+  const double* src = nullptr;
+  bool is_m = false;
+  switch (which) {
+    case 0: src = h->state[c.cur]; break;
+    case 1: src = h->state[c.cur] + ln; break;
+    case 2: src = h->state[c.cur] + 2 * ln; break;
+    case 3: src = h->AX[c.cur]; is_m = true; break;
+    case 4: src = h->AX[c.cur] + lm; is_m = true; break;
+    case 5: src = h->Av; is_m = true; break;
+    case 7: src = h->grad; break;
+    case 8: src = h->state[1 - c.cur]; break;
+    case 9: src = h->state[1 - c.cur] + ln; break;
+    case 10: src = h->state[1 - c.cur] + 2 * ln; break;
+    case 11: src = h->AX[1 - c.cur]; is_m = true; break;
+    case 12: src = h->AX[1 - c.cur] + lm; is_m = true; break;
+    default: return fail(GLP_ERR_ARG, "unknown vector id %d", which);
+  }
+  const int64_t rows = is_m ? g.m : g.n, ld = is_m ? g.ldm : g.ldn;
+  GLP_TRY(ensure_scratch(h, size_t(rows) * g.l * 8));
+  CU_TRY(from_planar(h->stream, src, static_cast<double*>(h->scratch), rows, g.l, ld));
+  CU_TRY(cudaMemcpyAsync(out_host, h->scratch, size_t(rows) * g.l * 8, cudaMemcpyDeviceToHost, h->stream));
+  CU_TRY(cudaStreamSynchronize(h->stream));
+  return GLP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// one-shot solve with host buffers
+// ------------------------------------------------------------------------------------------------
+// Pageable host memory reaches HBM through two pinned bounce buffers so that the host-side memcpy of
+// chunk i+1 overlaps the DMA of chunk i (a plain cudaMemcpy2D from pageable memory serialises them).
+static int upload_matrix(cudaStream_t st, void* dst, size_t dpitch, const void* src, size_t spitch, size_t width,
+                         size_t rows) {
+  const size_t kChunk = size_t(32) << 20;
+  char* pin[2] = {nullptr, nullptr};
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  size_t rows_per = std::max<size_t>(1, kChunk / std::max<size_t>(width, 1));
+  rows_per = std::min(rows_per, rows);
+  cudaError_t e = cudaSuccess;
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+    e = cudaMallocHost(reinterpret_cast<void**>(&pin[i]), rows_per * width);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming);
+  }
+  int slot = 0;
+  for (size_t r0 = 0; r0 < rows && e == cudaSuccess; r0 += rows_per, slot ^= 1) {
+    const size_t nr = std::min(rows_per, rows - r0);
+    e = cudaEventSynchronize(ev[slot]);  // previous DMA out of this bounce buffer finished
+    if (e != cudaSuccess) break;
+    const char* s = static_cast<const char*>(src) + r0 * spitch;
+    if (spitch == width) memcpy(pin[slot], s, nr * width);
+    else for (size_t r = 0; r < nr; ++r) memcpy(pin[slot] + r * width, s + r * spitch, width);
+    e = cudaMemcpy2DAsync(static_cast<char*>(dst) + r0 * dpitch, dpitch, pin[slot], width, width, nr,
+                          cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaEventRecord(ev[slot], st);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  for (int i = 0; i < 2; ++i) {
+    if (ev[i]) cudaEventDestroy(ev[i]);
+    if (pin[i]) cudaFreeHost(pin[i]);
+  }
+  if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "matrix upload failed: %s", cudaGetErrorString(e));
+  return GLP_OK;
+}
+
+extern "C" int glp_solve_host(int device, int algo, int dtype, int m, int n, int l, const void* A_host, int64_t lda,
+                              const void* b_host, const void* x0_host, double mu0, const glp_opts* opts,
+                              void* x_out_host, glp_result* res, double* f_hist_host, int hist_cap) {
+  if (A_host == nullptr || b_host == nullptr || x0_host == nullptr || x_out_host == nullptr || opts == nullptr)
+    return fail(GLP_ERR_ARG, "null argument");
+  if (dtype != GLP_F32 && dtype != GLP_F64) return fail(GLP_ERR_ARG, "dtype must be GLP_F32 or GLP_F64");
+  if (m <= 0 || n <= 0 || l <= 0 || lda < n) return fail(GLP_ERR_ARG, "bad shape");
+  int sms = 0;
+  GLP_TRY(check_device(device, &sms));
+  CU_TRY(cudaSetDevice(device));
+  const size_t es = dtype == GLP_F32 ? 4 : 8;
+  const size_t ldd = align_up(size_t(n), 16 / es);  // device pitch in elements, 16-byte aligned rows
+  void *dA = nullptr, *db = nullptr, *dx0 = nullptr, *dx = nullptr;
+  glp_handle* h = nullptr;
+  cudaStream_t st = nullptr;
+  int rc = GLP_OK;
+  auto cleanup = [&]() {
+    if (h) glp_destroy(h);
+    if (st) cudaStreamDestroy(st);
+    if (dA) cudaFree(dA);
+    if (db) cudaFree(db);
+    if (dx0) cudaFree(dx0);
+    if (dx) cudaFree(dx);
+  };
+#define HOST_TRY(expr)                                                                        \
+  do {                                                                                        \
+    cudaError_t e_ = (expr);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      cleanup();                                                                              \
+      return fail(GLP_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));            \
+    }                                                                                         \
+  } while (0)
+  HOST_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  HOST_TRY(cudaMalloc(&dA, size_t(m) * ldd * es));
+  HOST_TRY(cudaMalloc(&db, size_t(m) * l * es));
+  HOST_TRY(cudaMalloc(&dx0, size_t(n) * l * es));
+  HOST_TRY(cudaMalloc(&dx, size_t(n) * l * es));
+  if (ldd != size_t(n)) HOST_TRY(cudaMemsetAsync(dA, 0, size_t(m) * ldd * es, st));
+  rc = upload_matrix(st, dA, ldd * es, A_host, size_t(lda) * es, size_t(n) * es, size_t(m));
+  if (rc != GLP_OK) { cleanup(); return rc; }
+  HOST_TRY(cudaMemcpyAsync(db, b_host, size_t(m) * l * es, cudaMemcpyHostToDevice, st));
+  HOST_TRY(cudaMemcpyAsync(dx0, x0_host, size_t(n) * l * es, cudaMemcpyHostToDevice, st));
+  rc = glp_create(&h, device, m, n, l, dtype, dA, int64_t(ldd), db, nullptr, st);
+  if (rc == GLP_OK) rc = glp_solve(h, algo, dx0, mu0, opts, dx, res, f_hist_host, hist_cap);
+  if (rc == GLP_OK) {
+    HOST_TRY(cudaMemcpyAsync(x_out_host, dx, size_t(n) * l * es, cudaMemcpyDeviceToHost, st));
+    HOST_TRY(cudaStreamSynchronize(st));
+  }
+#undef HOST_TRY
+  cleanup();
+  return rc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// synthetic data
+// ------------------------------------------------------------------------------------------------
+extern "C" int glp_randn(void* dst_dev, int dtype, int64_t rows, int64_t cols, int64_t ld, uint64_t seed, int64_t row0,
+                         int64_t col0, void* stream) {
+  if (dst_dev == nullptr || rows < 0 || cols < 0 || ld < cols) return fail(GLP_ERR_ARG, "bad argument");
+  if (dtype != GLP_F32 && dtype != GLP_F64) return fail(GLP_ERR_ARG, "dtype must be GLP_F32 or GLP_F64");
+  if (rows * cols == 0) return GLP_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
+  if (dtype == GLP_F32) randn_kernel<float><<<grid, 256, 0, st>>>(static_cast<float*>(dst_dev), rows, cols, ld, seed, row0, col0);
+  else randn_kernel<double><<<grid, 256, 0, st>>>(static_cast<double*>(dst_dev), rows, cols, ld, seed, row0, col0);
+  CU_TRY(cudaGetLastError());
+  return GLP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// multi-GPU plumbing: NCCL is bound at run time (dlopen) so that the library loads on machines
+// without NCCL and has no link-time dependency on torch's bundled copy.
+// ------------------------------------------------------------------------------------------------
+#include "glp_nccl.inl"

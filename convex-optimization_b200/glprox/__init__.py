@@ -1,0 +1,10 @@
+"""glprox: B200-native proximal-gradient group-LASSO solvers (host side).
+
+Everything numerical lives in libglprox.so (csrc/, hand-written sm_100a CUDA, C ABI in
+include/glprox.h).  Importing this package does not load the library; the first solve does, and
+fails loudly if it is missing.
+"""
+from . import _lib  # noqa: F401
+from .solver import DEFAULT_OPTS, GroupLassoProblem, merge_opts, solve  # noqa: F401
+
+__all__ = ["solve", "GroupLassoProblem", "DEFAULT_OPTS", "merge_opts"]

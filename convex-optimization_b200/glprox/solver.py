@@ -1,0 +1,242 @@
+"""Host side of the drop-in solvers: option semantics, marshalling, handle lifetime.
+
+Mirrors the reference interface  (x, iter, out) = gl_X(x0, A, b, mu_0, opts)
+(code/gl_ProxGD_primal.py:9,146 ; code/gl_FProxGD_primal.py:9,161 ; caller code/main.py:113-116).
+All numerics happen in libglprox.so (hand-written sm_100a kernels); this module only merges
+options, moves buffers and formats the reference's `out` dictionary.
+"""
+import ctypes as C
+import logging
+import time
+
+import numpy as np
+
+from . import _lib
+
+logger = logging.getLogger("opt")  # same logger name as the reference (gl_ProxGD_primal.py:6)
+
+# gl_ProxGD_primal.py:10-19 / gl_FProxGD_primal.py:10-19
+DEFAULT_OPTS = {
+    "ProxGD": {"maxit": 2500, "thres": 1e-3, "step_type": "line_search", "alpha0": 2e-3, "ftol": 1e-6,
+               "stable_len_threshold": 70, "line_search_attenuation_coeffi": 0.9,
+               "maxit_line_search_iter": 5},
+    "FProxGD": {"maxit": 1500, "thres": 1e-3, "step_type": "line_search", "alpha0": 1e-3, "ftol": 1e-6,
+                "stable_len_threshold": 70, "line_search_attenuation_coeffi": 0.98,
+                "maxit_line_search_iter": 5},
+}
+ALGO_ID = {"ProxGD": _lib.GLP_PROXGD, "FProxGD": _lib.GLP_FPROXGD}
+# additive keys (not in the reference): dtype 'fp32'|'fp64', backend 'auto'|'stream'|'persistent',
+# device (int), poll_interval (int)
+
+
+def merge_opts(algo, opts):
+    """`{**default_opts, **opts}` (gl_*_primal.py:21): caller keys win, unknown keys are ignored."""
+    merged = dict(DEFAULT_OPTS[algo])
+    merged.update(opts or {})
+    return merged
+
+
+def pack_opts(algo, merged):
+    st = merged["step_type"]
+    if st not in _lib.STEP_TYPES:
+        # the reference logs "Unsupported type." and then dies with TypeError (gl_ProxGD_primal.py:100-101)
+        logger.error("Unsupported type.")
+        raise ValueError("unsupported step_type %r (expected one of %s)" % (st, sorted(_lib.STEP_TYPES)))
+    backend = merged.get("backend", "auto")
+    if backend not in _lib.BACKENDS:
+        raise ValueError("unknown backend %r" % (backend,))
+    o = _lib.GlpOpts()
+    o.maxit = int(merged["maxit"])
+    o.step_type = _lib.STEP_TYPES[st]
+    o.stable_len_threshold = int(merged["stable_len_threshold"])
+    o.maxit_line_search_iter = int(merged["maxit_line_search_iter"])
+    o.thres = float(merged["thres"])
+    o.alpha0 = float(merged["alpha0"])
+    o.ftol = float(merged["ftol"])
+    o.line_search_attenuation_coeffi = float(merged["line_search_attenuation_coeffi"])
+    o.backend = _lib.BACKENDS[backend]
+    o.poll_interval = int(merged.get("poll_interval", 0))
+    return o
+
+
+def _running_min(f):
+    """f_hist_best with Python's min(f_best, f_now) semantics (NaN never replaces the best)."""
+    f = np.asarray(f, dtype=np.float64)
+    if f.size == 0 or not np.isnan(f).any():
+        return list(np.minimum.accumulate(f)) if f.size else []
+    best, out = np.inf, []
+    for v in f:
+        best = v if v < best else best
+        out.append(np.float64(best))
+    return out
+
+
+def _format_out(res, f_hist, tt):
+    fh = [np.float64(v) for v in f_hist]
+    return {
+        "tt": float(tt),
+        "fval": np.float64(res.fval),
+        "f_hist": fh,
+        "f_hist_best": _running_min(f_hist),
+        "glprox": {"device_ms": res.device_ms, "n_fwd": int(res.n_fwd), "n_tpass": int(res.n_tpass),
+                   "n_launches": int(res.n_launches), "sparsity": res.sparsity,
+                   "stage_end": [int(v) for v in res.stage_end],
+                   "backend": {1: "stream", 2: "persistent"}.get(res.backend_used, "?")},
+    }
+
+
+def _raise_for(rc):
+    if rc == _lib.GLP_ERR_UNBOUND:
+        # gl_FProxGD_primal.py:156,161 with maxit == 0
+        raise UnboundLocalError("cannot access local variable 'x' where it is not associated with a value")
+    _lib.check(rc)
+
+
+def _mode_dtype(A_dtype, merged):
+    want = merged.get("dtype")
+    if want is None:
+        return np.float32 if A_dtype == np.float32 else np.float64
+    table = {"fp32": np.float32, "float32": np.float32, "f32": np.float32,
+             "fp64": np.float64, "float64": np.float64, "f64": np.float64}
+    if want not in table:
+        raise ValueError("opts['dtype'] must be 'fp32' or 'fp64', got %r" % (want,))
+    return table[want]
+
+
+def _log_history(f_hist, res):
+    """The reference emits these at DEBUG level while iterating (gl_*_primal.py:45,54,134-136);
+    here they are reproduced after the fact from the device-recorded history."""
+    if not logger.isEnabledFor(logging.DEBUG):
+        return
+    for k in range(100, len(f_hist) + 1, 100):
+        logger.debug("iter= {:5}, objective= {:10E}".format(k, float(f_hist[k - 1])))
+
+
+def solve(algo, x0, A, b, mu_0, opts):
+    """Drop-in body shared by gl_ProxGD_primal / gl_FProxGD_primal."""
+    merged = merge_opts(algo, opts)
+    o = pack_opts(algo, merged)
+    try:
+        import torch
+        is_torch = isinstance(A, torch.Tensor)
+    except ImportError:  # torch is only plumbing for the device-tensor path
+        is_torch = False
+    if is_torch:
+        return _solve_torch(algo, x0, A, b, mu_0, merged, o)
+    return _solve_numpy(algo, x0, A, b, mu_0, merged, o)
+
+
+def _solve_numpy(algo, x0, A, b, mu_0, merged, o):
+    lib = _lib.load()
+    A = np.asarray(A)
+    dt = _mode_dtype(A.dtype, merged)
+    if A.ndim != 2:
+        raise ValueError("A must be 2-D")
+    m, n = A.shape
+    x0 = np.asarray(x0)
+    b = np.asarray(b)
+    if x0.ndim != 2 or b.ndim != 2 or x0.shape[0] != n or b.shape[0] != m or x0.shape[1] != b.shape[1]:
+        raise ValueError("shape mismatch: A %s, x0 %s, b %s" % (A.shape, x0.shape, b.shape))
+    l = x0.shape[1]
+    t0 = time.perf_counter()
+    Ac = np.ascontiguousarray(A, dtype=dt)
+    bc = np.ascontiguousarray(b, dtype=dt)
+    x0c = np.ascontiguousarray(x0, dtype=dt)
+    x = np.empty((n, l), dtype=dt)
+    cap = 3 * int(o.maxit) + 8
+    f_hist = np.empty(cap, dtype=np.float64)
+    res = _lib.GlpResult()
+    rc = lib.glp_solve_host(int(merged.get("device", 0)), ALGO_ID[algo],
+                            _lib.GLP_F32 if dt == np.float32 else _lib.GLP_F64, m, n, l,
+                            Ac.ctypes.data, Ac.strides[0] // Ac.itemsize, bc.ctypes.data, x0c.ctypes.data,
+                            float(mu_0), C.byref(o), x.ctypes.data, C.byref(res), f_hist.ctypes.data, cap)
+    _raise_for(rc)
+    tt = time.perf_counter() - t0
+    fh = f_hist[:res.iters]
+    _log_history(fh, res)
+    return x, int(res.iters), _format_out(res, fh, tt)
+
+
+class GroupLassoProblem:
+    """A and b resident in HBM behind a libglprox handle (torch provides memory and the stream).
+
+    Lets a caller solve repeatedly without re-uploading A -- the reference re-reads A from host
+    memory for every product (gl_ProxGD_primal.py:24-27,60-61)."""
+
+    def __init__(self, A, b, comm=None, n_total=None):
+        import torch
+        lib = _lib.load()
+        if not (isinstance(A, torch.Tensor) and A.is_cuda and A.dim() == 2):
+            raise ValueError("A must be a 2-D CUDA tensor")
+        if A.dtype not in (torch.float32, torch.float64):
+            raise ValueError("A must be float32 or float64")
+        if A.stride(1) != 1:
+            A = A.contiguous()
+        es = A.element_size()
+        if (A.stride(0) * es) % 16 != 0 or A.data_ptr() % 16 != 0:
+            pad = (-A.shape[1]) % (16 // es)
+            Ap = torch.zeros((A.shape[0], A.shape[1] + pad), dtype=A.dtype, device=A.device)
+            Ap[:, :A.shape[1]] = A
+            A = Ap[:, :A.shape[1]]
+        self.A = A
+        self.b = b.to(device=A.device, dtype=A.dtype).contiguous()
+        self.m, self.n = A.shape
+        self.l = self.b.shape[1]
+        self.dtype = A.dtype
+        self.device = A.device
+        self.stream = torch.cuda.current_stream(A.device)
+        self._h = C.c_void_p()
+        with torch.cuda.device(A.device):
+            _lib.check(lib.glp_create(C.byref(self._h), A.device.index, self.m, self.n, self.l,
+                                      _lib.GLP_F32 if A.dtype == torch.float32 else _lib.GLP_F64,
+                                      A.data_ptr(), A.stride(0), self.b.data_ptr(),
+                                      comm, self.stream.cuda_stream))
+
+    @property
+    def handle(self):
+        return self._h
+
+    def close(self):
+        if self._h:
+            _lib.load().glp_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def solve(self, algo, x0, mu_0, opts=None):
+        import torch
+        lib = _lib.load()
+        merged = merge_opts(algo, opts)
+        o = pack_opts(algo, merged)
+        x0d = x0.to(device=self.device, dtype=self.dtype).contiguous()
+        x = torch.empty_like(x0d)
+        cap = 3 * int(o.maxit) + 8
+        f_hist = np.empty(cap, dtype=np.float64)
+        res = _lib.GlpResult()
+        t0 = time.perf_counter()
+        with torch.cuda.device(self.device):
+            rc = lib.glp_solve(self._h, ALGO_ID[algo], x0d.data_ptr(), float(mu_0), C.byref(o), x.data_ptr(),
+                               C.byref(res), f_hist.ctypes.data, cap)
+        _raise_for(rc)
+        tt = time.perf_counter() - t0
+        fh = f_hist[:res.iters]
+        _log_history(fh, res)
+        return x, int(res.iters), _format_out(res, fh, tt)
+
+
+def _solve_torch(algo, x0, A, b, mu_0, merged, o):
+    import torch
+    if not A.is_cuda:
+        raise ValueError("torch tensors must live on a CUDA device (NumPy arrays take the host path)")
+    want = _mode_dtype(np.float32 if A.dtype == torch.float32 else np.float64, merged)
+    tdt = torch.float32 if want == np.float32 else torch.float64
+    prob = GroupLassoProblem(A.to(tdt), b)
+    try:
+        x, k, out = prob.solve(algo, x0, mu_0, merged)
+    finally:
+        prob.close()
+    return x, k, out

@@ -1,0 +1,183 @@
+/* glprox.h -- C ABI of libglprox.so: B200 (sm_100a) proximal-gradient group-LASSO solvers.
+ *
+ *   min_x 0.5*||A x - b||_F^2 + mu * sum_i ||x(i,:)||_2 ,   A: m x n,  x: n x l,  b: m x l
+ *
+ * The reference (magic3007/convex-optimization) has NO FFI layer: its boundary for this path is the
+ * Python callable  [x, iter, out] = gl_ProxGD_primal(x0, A, b, mu, opts)
+ *   (code/gl_ProxGD_primal.py:9,146 ; code/gl_FProxGD_primal.py:9,161 ; invoked at code/main.py:114).
+ * The drop-in Python modules in convex-optimization_b200/ keep that signature and bind the entry
+ * points below with ctypes.  Everything here is plain C: pointers, sizes,
+ * PODs; no torch / C++ types cross the boundary, nothing throws across it.
+ *
+ * Conventions
+ *   - Every function returns 0 on success and a negative glp_status on failure;
+ *     glp_last_error() returns a thread-local human readable message.
+ *   - "matrix dtype" T is GLP_F32 or GLP_F64.  A, b, x0, x_out use T and the reference's
+ *     row-major layouts (A[m][lda], b[m][l], x[n][l]).  Vector state inside the library is fp64.
+ *   - *_dev pointers are device pointers on the handle's device, *_host are host pointers.
+ *   - A handle is single-threaded; all work is enqueued on the stream given at creation.
+ */
+#ifndef GLPROX_H_
+#define GLPROX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GLP_VERSION 100 /* 0.1.0 */
+
+typedef enum glp_status {
+  GLP_OK = 0,
+  GLP_ERR_ARG = -1,      /* bad argument (shape, dtype, alignment, unknown enum) */
+  GLP_ERR_CUDA = -2,     /* a CUDA runtime/driver call failed */
+  GLP_ERR_NO_DEVICE = -3,/* no sm_100 device: there is NO CPU fallback */
+  GLP_ERR_NCCL = -4,
+  GLP_ERR_STATE = -5,    /* call sequence error (e.g. step before begin) */
+  GLP_ERR_DEVICE_FAULT = -6, /* a kernel reported an internal fault (pipeline watchdog) */
+  GLP_ERR_UNBOUND = -7   /* FProxGD with maxit == 0: the reference raises UnboundLocalError
+                            (gl_FProxGD_primal.py:156,161) */
+} glp_status;
+
+enum { GLP_F32 = 0, GLP_F64 = 1 };
+enum { GLP_PROXGD = 0, GLP_FPROXGD = 1 };
+/* step_type strings of gl_ProxGD_primal.py:78-101 / gl_FProxGD_primal.py:81-106 */
+enum { GLP_STEP_LINE_SEARCH = 0, GLP_STEP_FIXED = 1, GLP_STEP_DIMINISHING = 2, GLP_STEP_DIMINISHING2 = 3 };
+enum { GLP_BACKEND_AUTO = 0, GLP_BACKEND_STREAM = 1, GLP_BACKEND_PERSISTENT = 2 };
+
+/* POD mirror of the reference's `opts` dict after the merge with default_opts
+ * (gl_ProxGD_primal.py:10-21,38-43 ; gl_FProxGD_primal.py:10-21,38-43).  glp_default_opts fills
+ * the per-solver defaults. */
+typedef struct glp_opts {
+  int32_t maxit;                          /* per mu-stage (3 stages) */
+  int32_t step_type;                      /* GLP_STEP_* */
+  int32_t stable_len_threshold;
+  int32_t maxit_line_search_iter;
+  double thres;
+  double alpha0;
+  double ftol;
+  double line_search_attenuation_coeffi;
+  int32_t backend;                        /* GLP_BACKEND_* (additive key, default AUTO) */
+  int32_t poll_interval;                  /* iterations enqueued between host polls (0 = auto) */
+} glp_opts;
+
+typedef struct glp_result {
+  int32_t status;        /* glp_status of the solve */
+  int32_t iters;         /* k: number of recorded objective values (== len(f_hist)) */
+  int32_t done;          /* 1 once all three continuation stages have finished */
+  int32_t backend_used;  /* GLP_BACKEND_STREAM / GLP_BACKEND_PERSISTENT */
+  double fval;           /* out["fval"]: objective (with mu_0) at the returned x */
+  double device_ms;      /* CUDA-event time of the solve on this device */
+  double sparsity;       /* reference sparsity rule evaluated at the returned x */
+  int64_t n_fwd;         /* forward streams of A executed */
+  int64_t n_tpass;       /* transposed streams of A executed */
+  int64_t n_launches;    /* kernels launched by the library for this solve */
+  int32_t stage_end[3];  /* k at the end of each continuation stage */
+  int32_t reserved;
+} glp_result;
+
+/* Parameters of one transposed-pass epilogue (K2), used by the step-level entry point. */
+typedef struct glp_step_params {
+  int32_t algo;     /* GLP_PROXGD / GLP_FPROXGD */
+  int32_t reserved;
+  double theta;     /* FProxGD extrapolation weight 2/(inner+1); ignored for ProxGD */
+  double t;         /* trial step */
+  double mu;        /* stage mu */
+  double thres;
+} glp_step_params;
+
+typedef struct glp_handle glp_handle;
+
+/* ---- library ---------------------------------------------------------------------------------*/
+int glp_version(void);
+const char* glp_last_error(void);
+/* Number of visible sm_100 devices (0 when there is none; negative on CUDA error). */
+int glp_device_count(void);
+int glp_default_opts(int algo, glp_opts* out);
+
+/* ---- handle: one per (device, problem).  A and b stay resident in HBM --------------------------
+ * Replaces: the closure over (A, b) inside the reference solvers (gl_ProxGD_primal.py:24-27,60-61).
+ * A_dev: m x n_local, row-major, leading dimension lda (elements); lda*sizeof(T) and A_dev must be
+ * 16-byte aligned (TMA).  b_dev: m x l row-major, dtype T.  In a multi-GPU job each rank holds a
+ * column block A[:, J_g] and passes the ncclComm_t it created with glp_nccl_* (or NULL).
+ * stream: cudaStream_t (NULL = legacy default stream). */
+int glp_create(glp_handle** out, int device, int m, int n_local, int l, int dtype,
+               const void* A_dev, int64_t lda, const void* b_dev, void* nccl_comm, void* stream);
+int glp_destroy(glp_handle* h);
+
+/* ---- K1: forward skinny product with fused residual epilogue ---------------------------------
+ * Replaces `A @ x` / `0.5*np.sum((A @ x - b)**2)` (gl_ProxGD_primal.py:25,61 ; gl_FProxGD_primal.py:25,63).
+ * X_dev: n_local x ncols row-major dtype T.  AX_dev: m x ncols row-major fp64 (this rank's partial
+ * product in a multi-GPU job).  rr_dev (nullable): one fp64 = sum((AX[:, :l] - b)^2) over the
+ * first min(ncols, l) columns. */
+int glp_fwd(glp_handle* h, const void* X_dev, int ncols, double* AX_dev, double* rr_dev);
+
+/* ---- K2: transposed product, optionally with the fused prox epilogue ---------------------------
+ * Replaces `A.T @ r` (gl_ProxGD_primal.py:129 ; gl_FProxGD_primal.py:66) and, fused, prox_th /
+ * extrapolation / line-search inner products (gl_ProxGD_primal.py:65-74 ; gl_FProxGD_primal.py:71-77,
+ * 96-99,139,144-145).  R_dev: m x l fp64 row-major.  G_dev: n_local x l fp64 (gradient, nullable).
+ * With p != NULL the epilogue runs on (xt, v) [n_local x l fp64 row-major; v nullable for ProxGD] and
+ * writes xn, xnt, vn (nullable) and scalars[4] = {gd, dd, sum_i||xn_i||, max|xn|}. */
+int glp_tpass_prox(glp_handle* h, const glp_step_params* p, const double* R_dev, double* G_dev,
+                   const double* xt_dev, const double* v_dev, double* xn_dev, double* xnt_dev,
+                   double* vn_dev, double* scalars_dev);
+
+/* ---- whole solve ------------------------------------------------------------------------------
+ * Replaces gl_ProxGD_primal / gl_FProxGD_primal bodies.  x0_dev, x_out_dev: n_local x l row-major
+ * dtype T.  f_hist_host (nullable): receives min(iters, hist_cap) objective values.
+ * glp_solve == begin + (step/poll)* + end. */
+int glp_solve(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* opts,
+              void* x_out_dev, glp_result* res, double* f_hist_host, int hist_cap);
+
+int glp_solve_begin(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* opts);
+/* Enqueue `slots` decide/transposed/forward rounds (one iteration each unless a line-search trial
+ * is rejected); no host synchronisation. */
+int glp_solve_step(glp_handle* h, int slots);
+/* Synchronise and report progress (res->done, res->iters, res->fval so far). */
+int glp_solve_poll(glp_handle* h, glp_result* res);
+int glp_solve_end(glp_handle* h, void* x_out_dev, glp_result* res, double* f_hist_host, int hist_cap);
+
+/* ---- measurement: CUDA-event timing of every streaming launch on the handle's stream ------------
+ * With profiling on, each forward / transposed launch of a solve is bracketed by a pair of events;
+ * glp_get_profile (after glp_solve/glp_solve_end) aggregates the launches that actually streamed A
+ * (duration >= half of the longest of their kind; no-op and epilogue-only launches are left out). */
+typedef struct glp_profile {
+  int64_t fwd_launches;   /* forward launches that streamed A */
+  int64_t tpass_launches; /* transposed launches that streamed A */
+  double fwd_ms_sum, fwd_ms_min;
+  double tpass_ms_sum, tpass_ms_min;
+  double bytes_per_launch; /* algorithmic bytes of one stream of A on this device: m*n_local*sizeof(T) */
+} glp_profile;
+int glp_set_profiling(glp_handle* h, int on);
+int glp_get_profile(glp_handle* h, glp_profile* out);
+
+/* Test/debug: copy an internal fp64 vector to the host in the reference's row-major layout.
+ * which: 0 x, 1 xt, 2 v (n_local x l);  3 Ax, 4 Axt, 5 Av (m x l);  7 grad (n_local x l);
+ *        8 xn, 9 xnt, 10 vn (candidates);  11 Axn, 12 Axnt. */
+int glp_debug_read(glp_handle* h, int which, double* out_host);
+
+/* ---- one-shot convenience with HOST buffers (what the NumPy drop-in path calls) ---------------
+ * Uploads A (m x n row-major, leading dimension lda), b, x0 from host memory, solves on `device`,
+ * downloads x.  host<->device copies are part of the call. */
+int glp_solve_host(int device, int algo, int dtype, int m, int n, int l, const void* A_host,
+                   int64_t lda, const void* b_host, const void* x0_host, double mu0,
+                   const glp_opts* opts, void* x_out_host, glp_result* res, double* f_hist_host,
+                   int hist_cap);
+
+/* ---- multi-GPU plumbing (one process per GPU; rendezvous of the id is the host's job) ----------*/
+int glp_nccl_unique_id(void* id128 /* 128 bytes out */);
+int glp_nccl_comm_create(void** comm_out, const void* id128, int rank, int world, int device);
+int glp_nccl_comm_destroy(void* comm);
+
+/* ---- synthetic data: counter-based N(0,1) generator (bench / large fixtures) --------------------
+ * Fills dst_dev[rows][ld] (dtype T) with value(seed, global_row, global_col) so that any
+ * row/column block of the same logical matrix can be generated independently on any rank. */
+int glp_randn(void* dst_dev, int dtype, int64_t rows, int64_t cols, int64_t ld, uint64_t seed,
+              int64_t row0, int64_t col0, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GLPROX_H_ */
