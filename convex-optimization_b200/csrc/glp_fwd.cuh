@@ -18,6 +18,7 @@
 // every SM moves the same number of bytes; row blocks that straddle CTAs are completed by the last
 // arriver, which sums the partials in CTA order (deterministic).
 #pragma once
+#include "glp_comm.cuh"
 #include "glp_device.cuh"
 #include "glp_partition.h"
 #include "glp_types.cuh"
@@ -32,6 +33,32 @@ constexpr int FWD_THREADS = CONSUMER_THREADS + 64;
 
 __device__ __forceinline__ double nan_max(double a, double b) {
   return (a != a) ? a : ((b != b) ? b : fmax(a, b));
+}
+
+// Multi-GPU: called once per CTA by consumer warp 0 and (count launches) once by the aux warp, all 32
+// lanes.  The last arrival of the launch publishes this rank's sparsity count and raises flag_ax on
+// every peer; every slab store of the launch happens-before it (system fence + counter chain).
+__device__ __forceinline__ void fwd_finish(const FwdArgs& a, int lane) {
+  unsigned prev = 0;
+  if (lane == 0) {
+    __threadfence_system();
+    prev = atomicAdd(a.fin, 1u);
+  }
+  prev = __shfl_sync(0xffffffffu, prev, 0);
+  const unsigned target = gridDim.x * (a.count_mode ? 2u : 1u);
+  if (prev + 1 != target) return;
+  __threadfence();
+  if (lane == 0) *a.fin = 0u;
+  double cnt = 0.0;
+  if (a.count_mode) {
+    for (int i = lane; i < int(gridDim.x); i += 32) cnt += __ldcg(&a.cnt_partial[i]);
+    cnt = warp_sum(cnt);
+  }
+  if (lane < a.comm.world) {
+    if (a.count_mode) mail_sc(a.comm, lane, a.par, a.comm.rank)[4] = cnt;
+    __threadfence_system();
+    st_release_sys(mail_flag(a.comm, lane, MAIL_FLAG_AX, a.comm.rank), a.seq_f);
+  }
 }
 
 template <typename T, int RC>
@@ -100,9 +127,16 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
     // ------------------------------------------------------------------ aux: sparsity count
     if (a.count_mode) {
       double mx = 0.0;
-      for (int i = lane; i < g.ncb; i += 32) mx = nan_max(mx, __ldcg(&a.scal_partial[4 * i + 3]));
+      if (a.comm.world > 1) {
+        // global max|xn|: every rank's prox launch pushed its local maximum into this mailbox
+        if (lane < a.comm.world) wait_flag(mail_flag(a.comm, a.comm.rank, MAIL_FLAG_SC, lane), a.seq_t, a.fault);
+        __syncwarp();
+        for (int r = 0; r < a.comm.world; ++r) mx = nan_max(mx, ld_mail(mail_sc(a.comm, a.comm.rank, a.par, r)));
+      } else {
+        for (int i = lane; i < g.ncb; i += 32) mx = nan_max(mx, __ldcg(&a.scal_partial[4 * i + 3]));
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) mx = nan_max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        for (int o = 16; o > 0; o >>= 1) mx = nan_max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      }
       const double cut = xmul(1e-6, mx);
       const double* xc = a.xcand[sel];
       const int64_t j0 = tile_lo(c, G, g.n), j1 = tile_lo(c + 1, G, g.n);
@@ -112,6 +146,7 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
       if (lane == 0) a.cnt_partial[c] = double(cnt);
+      if (a.comm.world > 1) fwd_finish(a, lane);
     }
     return;
   }
@@ -184,7 +219,14 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
         for (int64_t cc = first; cc <= last; ++cc)
           sum += __ldcg(&a.partial[((cc + rb) * TILE_ROWS + row) * RC + q]);
         const int64_t grow = rb * TILE_ROWS + row;
-        if (grow < g.m) {
+        if (a.comm.world > 1) {
+          // push this rank's finished row block into everybody's slab (NVLink stores, 512 B runs)
+          if (grow < g.m) {
+            const int64_t off = int64_t(a.col0 + q) * g.ldm + grow;
+            for (int r = 0; r < a.comm.world; ++r) mail_slab(a.comm, r, a.par, a.comm.rank)[off] = sum;
+          }
+          __threadfence_system();
+        } else if (grow < g.m) {
           a.AX[sel][int64_t(q) * g.ldm + grow] = sum;
           if (q < a.nb_cols) {
             const double d = sum - a.b[int64_t(a.bcol0 + q) * g.ldm + grow];
@@ -204,6 +246,7 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
       }
     }
   }
+  if (a.comm.world > 1 && warp == 0) fwd_finish(a, lane);
 }
 
 }  // namespace glp

@@ -12,6 +12,7 @@
 //            reg = sum_i ||xn_i||_2 , mx = max|xn|                  :24-27, :22
 // prox_th keeps the reference's guard: z*max(rn-t*mu,0) / ((rn<thres)+rn), multiply before divide.
 #pragma once
+#include "glp_comm.cuh"
 #include "glp_device.cuh"
 #include "glp_types.cuh"
 
@@ -154,6 +155,7 @@ glp_prox_kernel(const ProxArgs p, const Geom g, const int only_if_retry) {
   }
   const ProxResolved r = resolve(p);
   for (int64_t cb = blockIdx.x; cb < g.ncb; cb += gridDim.x) prox_block<T>(p, r, g, cb, threadIdx.x, s_red);
+  if (threadIdx.x < 32) prox_post_arrive(p.post, p.scal_partial, g.ncb, threadIdx.x);
 }
 
 }  // namespace glp

@@ -58,6 +58,7 @@ glp_tpass_kernel(const __grid_constant__ CUtensorMap tmapA, const TpassArgs a, c
     if (a.fuse && warp < NUM_CONSUMER_WARPS) {
       const ProxResolved r = resolve(p);
       for (int64_t cb = blockIdx.x; cb < g.ncb; cb += gridDim.x) prox_block<T>(p, r, g, cb, tid, s_red);
+      if (warp == 0) prox_post_arrive(p.post, p.scal_partial, g.ncb, lane);
     }
     return;
   }
@@ -186,6 +187,7 @@ glp_tpass_kernel(const __grid_constant__ CUtensorMap tmapA, const TpassArgs a, c
       }
     }
   }
+  if (a.fuse && warp == 0) prox_post_arrive(p.post, p.scal_partial, g.ncb, lane);
 }
 
 }  // namespace glp

@@ -54,6 +54,25 @@ struct Geom {
   int64_t n_total;       // sum of n over ranks (sparsity denominator)
 };
 
+// ---- multi-GPU: peer mailboxes ---------------------------------------------------------------------
+// Every rank owns one mailbox in its HBM; all ranks map all mailboxes (CUDA IPC between processes,
+// plain device pointers inside one process).  Producers STORE into the consumers' mailboxes over
+// NVLink (push model) and then raise a monotonically increasing 64-bit flag; consumers only ever
+// read their own HBM.  Layout of one mailbox in 8-byte words:
+//   [ 0,  8)  flag_ax[src]   sequence number of src's latest finished forward launch
+//   [ 8, 16)  flag_sc[src]   sequence number of src's latest prox-producing launch
+//   [16, 24)  flag_ep[src]   solve epoch (barrier at glp_solve_begin)
+//   [32, 32 + 2*8*8)         sc[par][src][8] = {max|xn|, gd, dd, reg, cnt, -, -, -}
+//   [256, 256 + 2*8*slab)    slab[par][src][ncols_total * ldm]   partial products A[:, J_src] * X[J_src]
+constexpr int MAX_WORLD = 8;
+constexpr int MAIL_FLAG_AX = 0, MAIL_FLAG_SC = 8, MAIL_FLAG_EP = 16, MAIL_SC = 32, MAIL_SLAB = 256;
+struct Comm {
+  int32_t world;               // 0 / 1: single GPU, no mailbox traffic
+  int32_t rank;
+  int64_t slab_words;          // 2*l*ldm
+  unsigned long long* mail[MAX_WORLD];
+};
+
 // Forward stream  AX[:, q] = A * X[:, q]  for RC operand columns.
 struct FwdArgs {
   const void* X[2];      // operand [RC][ldn] (dtype T), selected by sel
@@ -71,6 +90,14 @@ struct FwdArgs {
   const double* xcand[2];      // candidate x [l][ldn] fp64, selected like X
   double* cnt_partial;   // [grid]
   int32_t* fault;
+  // multi-GPU (comm.world > 1): the completed row blocks are pushed into every rank's slab instead
+  // of AX / rr_partial; the last CTA (and aux warp) to finish raises flag_ax = seq_f everywhere.
+  Comm comm;
+  unsigned long long seq_f;    // this launch
+  unsigned long long seq_t;    // prox-producing launch whose scalars (max|xn|) the count needs
+  int32_t par;                 // mailbox double-buffer index of this forward group
+  int32_t col0;                // first column of this chunk inside the 2l-column slab
+  unsigned* fin;               // local finish counter, zero between launches
 };
 
 // Transposed stream  G[:, c] = A^T * R[:, c]  for LC residual columns, optional fused epilogue.
@@ -85,6 +112,15 @@ struct TpassArgs {
   int32_t* fault;
 };
 
+// Where a prox-producing launch publishes its block-reduced scalars in a multi-GPU job.
+struct ProxPost {
+  Comm comm;                   // world <= 1: nothing is posted
+  unsigned long long seq_t;
+  int32_t par;
+  int32_t pad;
+  unsigned* fin;               // local finish counter, zero between launches
+};
+
 // Prox epilogue operands (fused in the transposed stream or run stand-alone for retries / init).
 struct ProxArgs {
   double* state[2];      // each: [3][l][ldn] = {x, xt, v}; committed = state[cur], candidates = state[1-cur]
@@ -97,6 +133,7 @@ struct ProxArgs {
   int32_t init;          // 1: candidate = x0 already stored in state[1-cur][0]; only threshold + scalars
   int32_t pad;
   double theta, t, mu, thres;
+  ProxPost post;
 };
 
 }  // namespace glp

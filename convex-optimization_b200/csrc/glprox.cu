@@ -9,9 +9,11 @@
 #include <string.h>
 
 #include <algorithm>
+#include <thread>
 #include <vector>
 
 #include "../../include/glprox.h"
+#include "glp_comm.cuh"
 #include "glp_decide.cuh"
 #include "glp_fwd.cuh"
 #include "glp_misc.cuh"
@@ -117,6 +119,20 @@ struct glp_handle {
   int hist_cap = 0;
   int decide_grid = 0;
   int n_fchunks = 0;
+
+  // multi-GPU: peer mailboxes (glp_comm.cuh)
+  Comm comm{};                     // world == 0: single GPU
+  void* mailbox = nullptr;         // this rank's mailbox (cudaMalloc, IPC-exportable)
+  size_t mailbox_bytes = 0;
+  void* ipc_mapped[MAX_WORLD] = {nullptr};
+  uint64_t epoch = 0;              // solves started on this handle (identical on all ranks: SPMD)
+  uint64_t idx_f = 0, idx_t = 0;   // forward / prox-producing launches of the current solve
+  uint64_t seq_t_cur = 0;          // flag value of the latest prox-producing launch
+  int group = 0;                   // forward group of the current solve (mailbox parity)
+  unsigned *fin_f = nullptr, *fin_t = nullptr;
+  double *rr_g = nullptr, *scal_red = nullptr, *cnt_red = nullptr;
+  int gather_grid = 0;
+  const Ctrl* cur_ctrl = nullptr;  // control block the launches of the current slot read
 
   // step-level scratch (lazily sized)
   void* scratch = nullptr;
@@ -325,6 +341,9 @@ extern "C" int glp_destroy(glp_handle* h) {
   if (h == nullptr) return GLP_OK;
   cudaSetDevice(h->device);
   if (h->stream != nullptr || true) cudaStreamSynchronize(h->stream);
+  for (int r = 0; r < MAX_WORLD; ++r)
+    if (h->ipc_mapped[r]) cudaIpcCloseMemHandle(h->ipc_mapped[r]);
+  if (h->mailbox) cudaFree(h->mailbox);
   if (h->arena) cudaFree(h->arena);
   if (h->scratch) cudaFree(h->scratch);
   if (h->f_hist) cudaFree(h->f_hist);
@@ -396,6 +415,8 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
   const size_t o_tp = carve(size_t(g.grid + g.ncb) * 2 * tc * 8);
   const size_t o_fc = carve(size_t(g.nrb) * 4), o_tc = carve(size_t(g.ncb) * 4);
   const size_t o_ctrl = carve(2 * sizeof(Ctrl)), o_fault = carve(16);
+  h->gather_grid = int(std::max<int64_t>(1, std::min<int64_t>(num_sms, (int64_t(2) * lm + GATHER_THREADS - 1) / GATHER_THREADS)));
+  const size_t o_fin = carve(16), o_rrg = carve(size_t(h->gather_grid) * 8), o_sred = carve(4 * 8), o_cred = carve(8);
   cudaError_t e = cudaMalloc(&h->arena, off);
   if (e != cudaSuccess) { glp_destroy(h); return fail(GLP_ERR_CUDA, "cudaMalloc(%zu) failed: %s", off, cudaGetErrorString(e)); }
   e = cudaMemsetAsync(h->arena, 0, off, h->stream);
@@ -421,6 +442,11 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
   h->t_counter = reinterpret_cast<unsigned*>(base + o_tc);
   h->ctrl = reinterpret_cast<Ctrl*>(base + o_ctrl);
   h->fault = reinterpret_cast<int32_t*>(base + o_fault);
+  h->fin_f = reinterpret_cast<unsigned*>(base + o_fin);
+  h->fin_t = h->fin_f + 1;
+  h->rr_g = reinterpret_cast<double*>(base + o_rrg);
+  h->scal_red = reinterpret_cast<double*>(base + o_sred);
+  h->cnt_red = reinterpret_cast<double*>(base + o_cred);
 
   // b: row-major [m][l] dtype T -> planar fp64 [l][ldm]
   if (dtype == GLP_F32) e = to_planar(h->stream, static_cast<const float*>(b_dev), h->b, m, l, g.ldm);
@@ -439,9 +465,13 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
 // ------------------------------------------------------------------------------------------------
 static int esize(const glp_handle* h) { return h->dtype == GLP_F32 ? 4 : 8; }
 
+static bool multi(const glp_handle* h) { return h->comm.world > 1; }
+static uint64_t seq_base(const glp_handle* h) { return h->epoch << 32; }
+
 // Forward stream over `ncols` operand columns.  Xb[s] / AXb[s]: planar operand / output bases.
+// exchange: multi-GPU solver launch (row blocks are pushed into the peers' slabs).
 static int enqueue_fwd(glp_handle* h, const Ctrl* ctrl, int sel, const void* const Xb[2], double* const AXb[2],
-                       const double* const xcand[2], int ncols, int count_mode) {
+                       const double* const xcand[2], int ncols, int count_mode, bool exchange) {
   const Geom& g = h->g;
   int chunk = 0;
   for (int q = 0; q < ncols; ++chunk) {
@@ -464,6 +494,14 @@ static int enqueue_fwd(glp_handle* h, const Ctrl* ctrl, int sel, const void* con
     a.scal_partial = h->scal_partial;
     a.cnt_partial = h->cnt_partial;
     a.fault = h->fault;
+    if (exchange && multi(h)) {
+      a.comm = h->comm;
+      a.seq_f = seq_base(h) | ++h->idx_f;
+      a.seq_t = h->seq_t_cur;
+      a.par = h->group & 1;
+      a.col0 = q;
+      a.fin = h->fin_f;
+    }
     CU_TRY(launch_fwd(h, rc, a));
     q += rc;
   }
@@ -471,11 +509,17 @@ static int enqueue_fwd(glp_handle* h, const Ctrl* ctrl, int sel, const void* con
 }
 
 // Transposed stream over the l residual columns + prox epilogue (fused when l <= 2).
-static int enqueue_tpass(glp_handle* h, const Ctrl* ctrl, const ProxArgs* p, double* grad) {
+static int enqueue_tpass(glp_handle* h, const Ctrl* ctrl, const ProxArgs* p, double* grad, bool exchange) {
   const Geom& g = h->g;
   ProxArgs pa{};
   if (p) pa = *p;
   const bool fuse = p != nullptr && g.l <= 2;
+  if (p != nullptr && exchange && multi(h)) {
+    pa.post.comm = h->comm;
+    pa.post.seq_t = h->seq_t_cur = seq_base(h) | ++h->idx_t;
+    pa.post.par = h->group & 1;
+    pa.post.fin = h->fin_t;
+  }
   for (int q = 0; q < g.l;) {
     const int lc = (g.l - q) >= 2 ? 2 : 1;
     TpassArgs a{};
@@ -511,13 +555,37 @@ static int enqueue_solver_fwd(glp_handle* h, const Ctrl* ctrl) {
   const void* Xb[2];
   const double* xc[2] = {h->state[0], h->state[1]};
   for (int s = 0; s < 2; ++s) Xb[s] = h->dtype == GLP_F32 ? h->xop : static_cast<const void*>(h->state[s]);
-  return enqueue_fwd(h, ctrl, 0, Xb, h->AX, xc, 2 * h->g.l, 1);
+  return enqueue_fwd(h, ctrl, 0, Xb, h->AX, xc, 2 * h->g.l, 1, true);
+}
+
+// Multi-GPU: sum the W slabs of the forward group that was just launched (rank order) into the
+// candidate product buffers, with the residual norm and the exchanged scalars.
+static int enqueue_gather(glp_handle* h, const Ctrl* ctrl) {
+  if (!multi(h)) return GLP_OK;
+  GatherArgs a{};
+  a.comm = h->comm;
+  a.ctrl = ctrl;
+  a.sel = 0;
+  a.par = h->group & 1;
+  a.seq_f = seq_base(h) | h->idx_f;
+  a.seq_t = h->seq_t_cur;
+  a.AX[0] = h->AX[0]; a.AX[1] = h->AX[1];
+  a.b = h->b;
+  a.rr_partial = h->rr_g;
+  a.scal_red = h->scal_red;
+  a.cnt_red = h->cnt_red;
+  a.fault = h->fault;
+  glp_gather_kernel<<<h->gather_grid, GATHER_THREADS, 0, h->stream>>>(a, h->g);
+  h->n_launches++;
+  CU_TRY(cudaGetLastError());
+  return GLP_OK;
 }
 
 // ------------------------------------------------------------------------------------------------
-// whole solve
+// whole solve, as phases: a multi-rank job on ONE device (tests) enqueues each phase for all of its
+// logical ranks before the next one, so that no launch ever waits for a later launch of the stream.
 // ------------------------------------------------------------------------------------------------
-extern "C" int glp_solve_begin(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o) {
+static int phase_prepare(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o) {
   if (h == nullptr || x0_dev == nullptr || o == nullptr) return fail(GLP_ERR_ARG, "null argument");
   if (algo != GLP_PROXGD && algo != GLP_FPROXGD) return fail(GLP_ERR_ARG, "unknown algo %d", algo);
   if (o->step_type < GLP_STEP_LINE_SEARCH || o->step_type > GLP_STEP_DIMINISHING2)
@@ -538,6 +606,9 @@ extern "C" int glp_solve_begin(glp_handle* h, int algo, const void* x0_dev, doub
   }
   h->f_hist_best = h->f_hist + h->hist_cap;
   h->n_launches = 0;
+  h->epoch++;
+  h->idx_f = h->idx_t = 0;
+  h->group = 0;
   CU_TRY(cudaEventRecord(h->ev0, h->stream));
 
   Ctrl c0;
@@ -549,17 +620,77 @@ extern "C" int glp_solve_begin(glp_handle* h, int algo, const void* x0_dev, doub
   CU_TRY(cudaMemsetAsync(h->fault, 0, sizeof(int32_t), h->stream));
   CU_TRY(cudaMemsetAsync(h->gy_partial[0], 0, size_t(h->decide_grid) * 8, h->stream));
   CU_TRY(cudaMemsetAsync(h->gy_partial[1], 0, size_t(h->decide_grid) * 8, h->stream));
-
-  // x0 -> candidate slot of cur = 0, then threshold + scalars (init epilogue) and the first forward stream
+  // x0 -> candidate slot of cur = 0
   if (h->dtype == GLP_F32) CU_TRY(to_planar(h->stream, static_cast<const float*>(x0_dev), h->state[1], g.n, g.l, g.ldn));
   else CU_TRY(to_planar(h->stream, static_cast<const double*>(x0_dev), h->state[1], g.n, g.l, g.ldn));
+  if (multi(h)) {
+    // every rank has drained its previous solve before it gets here: after the epoch barrier the
+    // mailboxes may be reused from parity 0
+    glp_epoch_post_kernel<<<1, 32, 0, h->stream>>>(h->comm, h->epoch);
+    CU_TRY(cudaGetLastError());
+  }
+  h->decide_launches = 0;
+  h->cur_ctrl = &h->ctrl[0];
+  h->solving = true;
+  return GLP_OK;
+}
+
+// threshold + scalars of x0 (init epilogue)
+static int phase_init_prox(glp_handle* h) {
+  if (multi(h)) {
+    glp_epoch_wait_kernel<<<1, 32, 0, h->stream>>>(h->comm, h->epoch, h->fault);
+    CU_TRY(cudaGetLastError());
+  }
   ProxArgs p = solver_prox_args(h, nullptr);
   p.cur = 0;
   p.init = 1;
+  if (multi(h)) {
+    p.post.comm = h->comm;
+    p.post.seq_t = h->seq_t_cur = seq_base(h) | ++h->idx_t;
+    p.post.par = h->group & 1;
+    p.post.fin = h->fin_t;
+  }
   CU_TRY(launch_prox(h, p, 0));
-  GLP_TRY(enqueue_solver_fwd(h, &h->ctrl[0]));
-  h->decide_launches = 0;
-  h->solving = true;
+  return GLP_OK;
+}
+
+static int phase_decide(glp_handle* h) {
+  const int64_t j = h->decide_launches++;
+  const Ctrl* cin = &h->ctrl[j & 1];
+  Ctrl* cout = &h->ctrl[(j + 1) & 1];
+  DecideArgs d{};
+  d.cin = cin; d.cout = cout; d.sc = h->sc;
+  if (multi(h)) {
+    d.rr_partial = h->rr_g; d.n_rr = h->gather_grid;
+    d.scal_partial = h->scal_red; d.n_scal = 1;
+    d.cnt_partial = h->cnt_red; d.n_cnt = 1;
+  } else {
+    d.rr_partial = h->rr_partial; d.n_rr = h->n_fchunks * h->g.nrb;
+    d.scal_partial = h->scal_partial; d.n_scal = h->g.ncb;
+    d.cnt_partial = h->cnt_partial; d.n_cnt = h->g.grid;
+  }
+  d.gy_partial[0] = h->gy_partial[0]; d.gy_partial[1] = h->gy_partial[1]; d.n_gy = h->decide_grid;
+  d.AX[0] = h->AX[0]; d.AX[1] = h->AX[1]; d.Av = h->Av; d.b = h->b; d.r = h->r;
+  d.state[0] = h->state[0]; d.state[1] = h->state[1];
+  d.f_hist = h->f_hist; d.f_hist_best = h->f_hist_best;
+  CU_TRY(launch_decide(h, d));
+  h->cur_ctrl = cout;
+  return GLP_OK;
+}
+
+static int phase_tpass(glp_handle* h) {
+  h->group++;
+  ProxArgs p = solver_prox_args(h, h->cur_ctrl);
+  return enqueue_tpass(h, h->cur_ctrl, &p, h->grad, true);
+}
+static int phase_fwd(glp_handle* h) { return enqueue_solver_fwd(h, h->cur_ctrl); }
+static int phase_gather(glp_handle* h) { return enqueue_gather(h, h->cur_ctrl); }
+
+extern "C" int glp_solve_begin(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o) {
+  GLP_TRY(phase_prepare(h, algo, x0_dev, mu0, o));
+  GLP_TRY(phase_init_prox(h));
+  GLP_TRY(phase_fwd(h));
+  GLP_TRY(phase_gather(h));
   return GLP_OK;
 }
 
@@ -567,22 +698,10 @@ extern "C" int glp_solve_step(glp_handle* h, int slots) {
   if (h == nullptr || !h->solving) return fail(GLP_ERR_STATE, "glp_solve_step before glp_solve_begin");
   CU_TRY(cudaSetDevice(h->device));
   for (int s = 0; s < slots; ++s) {
-    const int64_t j = h->decide_launches++;
-    const Ctrl* cin = &h->ctrl[j & 1];
-    Ctrl* cout = &h->ctrl[(j + 1) & 1];
-    DecideArgs d{};
-    d.cin = cin; d.cout = cout; d.sc = h->sc;
-    d.rr_partial = h->rr_partial; d.n_rr = h->n_fchunks * h->g.nrb;
-    d.scal_partial = h->scal_partial; d.n_scal = h->g.ncb;
-    d.cnt_partial = h->cnt_partial; d.n_cnt = h->g.grid;
-    d.gy_partial[0] = h->gy_partial[0]; d.gy_partial[1] = h->gy_partial[1]; d.n_gy = h->decide_grid;
-    d.AX[0] = h->AX[0]; d.AX[1] = h->AX[1]; d.Av = h->Av; d.b = h->b; d.r = h->r;
-    d.state[0] = h->state[0]; d.state[1] = h->state[1];
-    d.f_hist = h->f_hist; d.f_hist_best = h->f_hist_best;
-    CU_TRY(launch_decide(h, d));
-    ProxArgs p = solver_prox_args(h, cout);
-    GLP_TRY(enqueue_tpass(h, cout, &p, h->grad));
-    GLP_TRY(enqueue_solver_fwd(h, cout));
+    GLP_TRY(phase_decide(h));
+    GLP_TRY(phase_tpass(h));
+    GLP_TRY(phase_fwd(h));
+    GLP_TRY(phase_gather(h));
   }
   return GLP_OK;
 }
@@ -630,7 +749,8 @@ extern "C" int glp_solve_end(glp_handle* h, void* x_out_dev, glp_result* res, do
   if (res) memset(res, 0, sizeof(*res));
   if (fault != 0) {
     if (res) res->status = GLP_ERR_DEVICE_FAULT;
-    return fail(GLP_ERR_DEVICE_FAULT, "pipeline watchdog fired inside a streaming kernel");
+    return fail(GLP_ERR_DEVICE_FAULT, fault == 2 ? "a peer rank never raised its mailbox flag (20 s watchdog)"
+                                                 : "pipeline watchdog fired inside a streaming kernel");
   }
   if (x_out_dev != nullptr) {
     const double* x = h->state[c.cur];
@@ -655,30 +775,143 @@ extern "C" int glp_solve_end(glp_handle* h, void* x_out_dev, glp_result* res, do
   return GLP_OK;
 }
 
-extern "C" int glp_solve(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o, void* x_out_dev,
-                         glp_result* res, double* f_hist_host, int hist_cap) {
-  GLP_TRY(glp_solve_begin(h, algo, x0_dev, mu0, o));
+// ------------------------------------------------------------------------------------------------
+// multi-GPU: mailbox export / attach, and the one-process group driver
+// ------------------------------------------------------------------------------------------------
+extern "C" int glp_comm_export(glp_handle* h, int world, void* ipc_handle64_out, void** mailbox_dev_out) {
+  if (h == nullptr) return fail(GLP_ERR_ARG, "null handle");
+  if (world < 1 || world > MAX_WORLD) return fail(GLP_ERR_ARG, "world must be 1..%d (got %d)", MAX_WORLD, world);
+  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
+  CU_TRY(cudaSetDevice(h->device));
+  if (h->mailbox == nullptr) {
+    const size_t slab_words = size_t(2) * h->g.l * h->g.ldm;
+    h->mailbox_bytes = (size_t(MAIL_SLAB) + size_t(2) * MAX_WORLD * slab_words) * 8;
+    CU_TRY(cudaMalloc(&h->mailbox, h->mailbox_bytes));  // plain cudaMalloc: IPC-exportable
+    CU_TRY(cudaMemset(h->mailbox, 0, h->mailbox_bytes));
+    CU_TRY(cudaDeviceSynchronize());
+  }
+  if (ipc_handle64_out != nullptr) {
+    cudaIpcMemHandle_t ih;
+    static_assert(sizeof(ih) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    CU_TRY(cudaIpcGetMemHandle(&ih, h->mailbox));
+    memcpy(ipc_handle64_out, &ih, sizeof(ih));
+  }
+  if (mailbox_dev_out != nullptr) *mailbox_dev_out = h->mailbox;
+  return GLP_OK;
+}
+
+extern "C" int glp_comm_attach(glp_handle* h, int rank, int world, int64_t n_total, const void* peers, int kind) {
+  if (h == nullptr || peers == nullptr) return fail(GLP_ERR_ARG, "null argument");
+  if (world < 1 || world > MAX_WORLD || rank < 0 || rank >= world) return fail(GLP_ERR_ARG, "bad rank/world %d/%d", rank, world);
+  if (h->mailbox == nullptr) return fail(GLP_ERR_STATE, "glp_comm_attach before glp_comm_export");
+  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
+  if (kind != 0 && kind != 1) return fail(GLP_ERR_ARG, "kind must be 0 (IPC handles) or 1 (device pointers)");
+  if (n_total < h->g.n) return fail(GLP_ERR_ARG, "n_total (%lld) < local n (%d)", (long long)n_total, h->g.n);
+  CU_TRY(cudaSetDevice(h->device));
+  Comm c{};
+  c.world = world;
+  c.rank = rank;
+  c.slab_words = int64_t(2) * h->g.l * h->g.ldm;
+  for (int r = 0; r < world; ++r) {
+    void* ptr = nullptr;
+    if (r == rank) {
+      ptr = h->mailbox;
+    } else if (kind == 1) {
+      ptr = static_cast<void* const*>(peers)[r];
+      cudaPointerAttributes at{};
+      if (ptr != nullptr && cudaPointerGetAttributes(&at, ptr) == cudaSuccess && at.type == cudaMemoryTypeDevice &&
+          at.device != h->device) {
+        cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+          return fail(GLP_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d) failed: %s", at.device, cudaGetErrorString(e));
+        cudaGetLastError();
+      }
+    } else {
+      cudaIpcMemHandle_t ih;
+      memcpy(&ih, static_cast<const char*>(peers) + size_t(r) * sizeof(ih), sizeof(ih));
+      cudaError_t e = cudaIpcOpenMemHandle(&ptr, ih, cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess)
+        return fail(GLP_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d) failed: %s", r, cudaGetErrorString(e));
+      h->ipc_mapped[r] = ptr;
+    }
+    if (ptr == nullptr) return fail(GLP_ERR_ARG, "mailbox of rank %d is null", r);
+    c.mail[r] = static_cast<unsigned long long*>(ptr);
+  }
+  h->comm = c;
+  h->g.world = world;
+  h->g.n_total = n_total;
+  return GLP_OK;
+}
+
+static int drive_until_done(glp_handle** hs, int G, const glp_opts* o) {
   // Host runs ahead of the device: batch i+1 is enqueued before the control snapshot taken after
   // batch i is inspected, so the stream never drains while the solve is in progress.
+  glp_handle* h0 = hs[0];
   const int64_t max_slots = int64_t(3) * o->maxit * (int64_t(o->maxit_line_search_iter) + 1) + 8;
-  int batch = o->poll_interval > 0 ? o->poll_interval : 32;
+  const int batch = o->poll_interval > 0 ? o->poll_interval : 32;
   int64_t issued = 0;
   int pending = -1;  // snapshot slot whose event has not been inspected yet
   bool done = false;
   int cur_slot = 0;
   while (!done && issued < max_slots) {
-    GLP_TRY(glp_solve_step(h, batch));
+    for (int s = 0; s < batch; ++s) {
+      for (int i = 0; i < G; ++i) { CU_TRY(cudaSetDevice(hs[i]->device)); GLP_TRY(phase_decide(hs[i])); }
+      for (int i = 0; i < G; ++i) { CU_TRY(cudaSetDevice(hs[i]->device)); GLP_TRY(phase_tpass(hs[i])); }
+      for (int i = 0; i < G; ++i) { CU_TRY(cudaSetDevice(hs[i]->device)); GLP_TRY(phase_fwd(hs[i])); }
+      for (int i = 0; i < G; ++i) { CU_TRY(cudaSetDevice(hs[i]->device)); GLP_TRY(phase_gather(hs[i])); }
+    }
     issued += batch;
-    CU_TRY(cudaMemcpyAsync(&h->h_ctrl[cur_slot], &h->ctrl[h->decide_launches & 1], sizeof(Ctrl), cudaMemcpyDeviceToHost, h->stream));
-    CU_TRY(cudaEventRecord(h->ev_snap[cur_slot], h->stream));
+    CU_TRY(cudaSetDevice(h0->device));
+    CU_TRY(cudaMemcpyAsync(&h0->h_ctrl[cur_slot], &h0->ctrl[h0->decide_launches & 1], sizeof(Ctrl), cudaMemcpyDeviceToHost, h0->stream));
+    CU_TRY(cudaEventRecord(h0->ev_snap[cur_slot], h0->stream));
     if (pending >= 0) {
-      GLP_TRY(check_fault(h, cudaEventSynchronize(h->ev_snap[pending])));
-      if (h->h_ctrl[pending].done) done = true;
+      GLP_TRY(check_fault(h0, cudaEventSynchronize(h0->ev_snap[pending])));
+      if (h0->h_ctrl[pending].done) done = true;
     }
     pending = cur_slot;
     cur_slot ^= 1;
   }
+  return GLP_OK;
+}
+
+extern "C" int glp_solve(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o, void* x_out_dev,
+                         glp_result* res, double* f_hist_host, int hist_cap) {
+  GLP_TRY(glp_solve_begin(h, algo, x0_dev, mu0, o));
+  int rc = drive_until_done(&h, 1, o);
+  if (rc != GLP_OK) { h->solving = false; return rc; }
   return glp_solve_end(h, x_out_dev, res, f_hist_host, hist_cap);
+}
+
+// G logical ranks driven by one host thread.  Handles on one device must share a stream (then every
+// wait is already satisfied when its kernel starts); handles on different devices run concurrently.
+extern "C" int glp_group_solve(glp_handle** hs, int G, int algo, const void* const* x0_dev, double mu0,
+                               const glp_opts* o, void* const* x_out_dev, glp_result* res, double* f_hist_host,
+                               int hist_cap) {
+  if (hs == nullptr || x0_dev == nullptr || o == nullptr || G < 1 || G > MAX_WORLD) return fail(GLP_ERR_ARG, "bad argument");
+  for (int i = 0; i < G; ++i) {
+    if (hs[i] == nullptr) return fail(GLP_ERR_ARG, "null handle %d", i);
+    if (G > 1 && (hs[i]->comm.world != G || hs[i]->comm.rank != i))
+      return fail(GLP_ERR_STATE, "handle %d is not attached as rank %d of %d", i, i, G);
+    for (int j = 0; j < i; ++j)
+      if (hs[j]->device == hs[i]->device && hs[j]->stream != hs[i]->stream)
+        return fail(GLP_ERR_ARG, "logical ranks that share a device must share a stream");
+  }
+  int rc = GLP_OK;
+  for (int i = 0; i < G && rc == GLP_OK; ++i) rc = phase_prepare(hs[i], algo, x0_dev[i], mu0, o);
+  for (int i = 0; i < G && rc == GLP_OK; ++i) { cudaSetDevice(hs[i]->device); rc = phase_init_prox(hs[i]); }
+  for (int i = 0; i < G && rc == GLP_OK; ++i) { cudaSetDevice(hs[i]->device); rc = phase_fwd(hs[i]); }
+  for (int i = 0; i < G && rc == GLP_OK; ++i) { cudaSetDevice(hs[i]->device); rc = phase_gather(hs[i]); }
+  if (rc == GLP_OK) rc = drive_until_done(hs, G, o);
+  if (rc != GLP_OK) {
+    for (int i = 0; i < G; ++i) hs[i]->solving = false;
+    return rc;
+  }
+  for (int i = 0; i < G; ++i) {
+    int r2 = glp_solve_end(hs[i], x_out_dev ? x_out_dev[i] : nullptr, res ? &res[i] : nullptr,
+                           i == 0 ? f_hist_host : nullptr, i == 0 ? hist_cap : 0);
+    if (r2 != GLP_OK && rc == GLP_OK) rc = r2;
+  }
+  return rc;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -737,7 +970,7 @@ extern "C" int glp_fwd(glp_handle* h, const void* X_dev, int ncols, double* AX_d
   double* AXb[2] = {AXp, AXp};
   double* saved_rr = h->rr_partial;
   h->rr_partial = rrp;  // chunk-indexed inside enqueue_fwd
-  int rc = enqueue_fwd(h, nullptr, 0, Xb, AXb, nullptr, ncols, 0);
+  int rc = enqueue_fwd(h, nullptr, 0, Xb, AXb, nullptr, ncols, 0, false);
   h->rr_partial = saved_rr;
   GLP_TRY(rc);
   CU_TRY(from_planar(h->stream, AXp, AX_dev, g.m, ncols, g.ldm));
@@ -771,7 +1004,7 @@ extern "C" int glp_tpass_prox(glp_handle* h, const glp_step_params* sp, const do
     p.algo = sp->algo; p.cur = 0; p.init = 0;
     p.theta = sp->theta; p.t = sp->t; p.mu = sp->mu; p.thres = sp->thres;
   }
-  GLP_TRY(enqueue_tpass(h, nullptr, sp ? &p : nullptr, h->grad));
+  GLP_TRY(enqueue_tpass(h, nullptr, sp ? &p : nullptr, h->grad, false));
   if (G_dev) CU_TRY(from_planar(h->stream, h->grad, G_dev, g.n, g.l, g.ldn));
   if (sp != nullptr) {
     CU_TRY(from_planar(h->stream, h->state[1], xn_dev, g.n, g.l, g.ldn));
@@ -836,38 +1069,71 @@ extern "C" int glp_debug_read(glp_handle* h, int which, double* out_host) {
 // ------------------------------------------------------------------------------------------------
 // one-shot solve with host buffers
 // ------------------------------------------------------------------------------------------------
-// Pageable host memory reaches HBM through two pinned bounce buffers so that the host-side memcpy of
-// chunk i+1 overlaps the DMA of chunk i (a plain cudaMemcpy2D from pageable memory serialises them).
-static int upload_matrix(cudaStream_t st, void* dst, size_t dpitch, const void* src, size_t spitch, size_t width,
-                         size_t rows) {
-  const size_t kChunk = size_t(32) << 20;
+// Host matrix -> HBM.  Page-locked sources (cudaHostAlloc / cudaHostRegister, e.g. torch pinned
+// tensors) are DMA'd in place.  Pageable sources go through pinned bounce buffers filled by a few
+// host threads, each with its own stream, so that the host-side memcpy (one core moves ~10 GB/s)
+// does not cap the PCIe link.
+static int upload_rows_bounced(int device, void* dst, size_t dpitch, const char* src, size_t spitch, size_t width,
+                               size_t row_begin, size_t row_end, cudaError_t* err_out) {
+  const size_t kChunk = size_t(16) << 20;
+  cudaError_t e = cudaSetDevice(device);
+  cudaStream_t st = nullptr;
   char* pin[2] = {nullptr, nullptr};
   cudaEvent_t ev[2] = {nullptr, nullptr};
   size_t rows_per = std::max<size_t>(1, kChunk / std::max<size_t>(width, 1));
-  rows_per = std::min(rows_per, rows);
-  cudaError_t e = cudaSuccess;
+  rows_per = std::min(rows_per, std::max<size_t>(row_end - row_begin, 1));
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
   for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
     e = cudaMallocHost(reinterpret_cast<void**>(&pin[i]), rows_per * width);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming);
   }
   int slot = 0;
-  for (size_t r0 = 0; r0 < rows && e == cudaSuccess; r0 += rows_per, slot ^= 1) {
-    const size_t nr = std::min(rows_per, rows - r0);
+  for (size_t r0 = row_begin; r0 < row_end && e == cudaSuccess; r0 += rows_per, slot ^= 1) {
+    const size_t nr = std::min(rows_per, row_end - r0);
     e = cudaEventSynchronize(ev[slot]);  // previous DMA out of this bounce buffer finished
     if (e != cudaSuccess) break;
-    const char* s = static_cast<const char*>(src) + r0 * spitch;
+    const char* s = src + r0 * spitch;
     if (spitch == width) memcpy(pin[slot], s, nr * width);
     else for (size_t r = 0; r < nr; ++r) memcpy(pin[slot] + r * width, s + r * spitch, width);
     e = cudaMemcpy2DAsync(static_cast<char*>(dst) + r0 * dpitch, dpitch, pin[slot], width, width, nr,
                           cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaEventRecord(ev[slot], st);
   }
-  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e == cudaSuccess && st) e = cudaStreamSynchronize(st);
   for (int i = 0; i < 2; ++i) {
     if (ev[i]) cudaEventDestroy(ev[i]);
     if (pin[i]) cudaFreeHost(pin[i]);
   }
-  if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "matrix upload failed: %s", cudaGetErrorString(e));
+  if (st) cudaStreamDestroy(st);
+  *err_out = e;
+  return e == cudaSuccess ? 0 : 1;
+}
+
+static int upload_matrix(int device, cudaStream_t st, void* dst, size_t dpitch, const void* src, size_t spitch,
+                         size_t width, size_t rows) {
+  cudaPointerAttributes at{};
+  const bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
+  cudaGetLastError();
+  if (pinned) {
+    CU_TRY(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, rows, cudaMemcpyHostToDevice, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    return GLP_OK;
+  }
+  CU_TRY(cudaStreamSynchronize(st));  // dst may still be being cleared on st
+  const size_t bytes = width * rows;
+  int nthr = int(std::min<size_t>(6, std::max<size_t>(1, bytes >> 26)));  // one thread per 64 MiB, up to 6
+  nthr = int(std::min<size_t>(size_t(nthr), rows));
+  std::vector<std::thread> pool;
+  std::vector<cudaError_t> errs(size_t(nthr), cudaSuccess);
+  for (int t = 0; t < nthr; ++t) {
+    const size_t r0 = rows * size_t(t) / nthr, r1 = rows * size_t(t + 1) / nthr;
+    pool.emplace_back([=, &errs]() {
+      upload_rows_bounced(device, dst, dpitch, static_cast<const char*>(src), spitch, width, r0, r1, &errs[size_t(t)]);
+    });
+  }
+  for (auto& th : pool) th.join();
+  for (cudaError_t e : errs)
+    if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "matrix upload failed: %s", cudaGetErrorString(e));
   return GLP_OK;
 }
 
@@ -909,7 +1175,7 @@ extern "C" int glp_solve_host(int device, int algo, int dtype, int m, int n, int
   HOST_TRY(cudaMalloc(&dx0, size_t(n) * l * es));
   HOST_TRY(cudaMalloc(&dx, size_t(n) * l * es));
   if (ldd != size_t(n)) HOST_TRY(cudaMemsetAsync(dA, 0, size_t(m) * ldd * es, st));
-  rc = upload_matrix(st, dA, ldd * es, A_host, size_t(lda) * es, size_t(n) * es, size_t(m));
+  rc = upload_matrix(device, st, dA, ldd * es, A_host, size_t(lda) * es, size_t(n) * es, size_t(m));
   if (rc != GLP_OK) { cleanup(); return rc; }
   HOST_TRY(cudaMemcpyAsync(db, b_host, size_t(m) * l * es, cudaMemcpyHostToDevice, st));
   HOST_TRY(cudaMemcpyAsync(dx0, x0_host, size_t(n) * l * es, cudaMemcpyHostToDevice, st));

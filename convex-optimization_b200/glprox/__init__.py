@@ -5,6 +5,8 @@ include/glprox.h).  Importing this package does not load the library; the first 
 fails loudly if it is missing.
 """
 from . import _lib  # noqa: F401
-from .solver import DEFAULT_OPTS, GroupLassoProblem, merge_opts, solve  # noqa: F401
+from .solver import (DEFAULT_OPTS, GroupLassoProblem, attach_distributed, exchange_handles,  # noqa: F401
+                     merge_opts, shard_bounds, solve, solve_group)
 
-__all__ = ["solve", "GroupLassoProblem", "DEFAULT_OPTS", "merge_opts"]
+__all__ = ["solve", "GroupLassoProblem", "DEFAULT_OPTS", "merge_opts", "shard_bounds", "exchange_handles",
+           "attach_distributed", "solve_group"]

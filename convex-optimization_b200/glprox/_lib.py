@@ -71,6 +71,10 @@ SIGNATURES = {
     "glp_get_profile": (_I, [_VP, C.POINTER(GlpProfile)]),
     "glp_solve_host": (_I, [_I, _I, _I, _I, _I, _I, _VP, _I64, _VP, _VP, _D, C.POINTER(GlpOpts), _VP,
                             C.POINTER(GlpResult), _VP, _I]),
+    "glp_comm_export": (_I, [_VP, _I, _VP, C.POINTER(_VP)]),
+    "glp_comm_attach": (_I, [_VP, _I, _I, _I64, _VP, _I]),
+    "glp_group_solve": (_I, [C.POINTER(_VP), _I, _I, C.POINTER(_VP), _D, C.POINTER(GlpOpts), C.POINTER(_VP),
+                             C.POINTER(GlpResult), _VP, _I]),
     "glp_nccl_unique_id": (_I, [_VP]),
     "glp_nccl_comm_create": (_I, [C.POINTER(_VP), _VP, _I, _I, _I]),
     "glp_nccl_comm_destroy": (_I, [_VP]),

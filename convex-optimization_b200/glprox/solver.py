@@ -123,6 +123,8 @@ def solve(algo, x0, A, b, mu_0, opts):
         is_torch = False
     if is_torch:
         return _solve_torch(algo, x0, A, b, mu_0, merged, o)
+    if merged.get("dist"):
+        return _solve_numpy_sharded(algo, x0, A, b, mu_0, merged, o)
     return _solve_numpy(algo, x0, A, b, mu_0, merged, o)
 
 
@@ -155,6 +157,34 @@ def _solve_numpy(algo, x0, A, b, mu_0, merged, o):
     fh = f_hist[:res.iters]
     _log_history(fh, res)
     return x, int(res.iters), _format_out(res, fh, tt)
+
+
+def _solve_numpy_sharded(algo, x0, A, b, mu_0, merged, o):
+    """opts['dist'] = True (additive key): one process per GPU under torch.distributed; A is THIS
+    rank's column block A[:, J_rank] and x0 its row groups x0[J_rank, :] (host arrays, ideally
+    pinned); b is the full right-hand side on every rank.  Returns this rank's rows of x."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        raise RuntimeError("opts['dist'] needs an initialised torch.distributed process group")
+    dt = _mode_dtype(np.asarray(A).dtype, merged)
+    tdt = torch.float32 if dt == np.float32 else torch.float64
+    dev = torch.device("cuda", torch.cuda.current_device())
+    t0 = time.perf_counter()
+    Ad = torch.from_numpy(np.ascontiguousarray(A, dtype=dt)).to(dev, non_blocking=True)
+    bd = torch.from_numpy(np.ascontiguousarray(b, dtype=dt)).to(dev, non_blocking=True)
+    x0d = torch.from_numpy(np.ascontiguousarray(x0, dtype=dt)).to(dev, non_blocking=True)
+    n_tot = torch.tensor([Ad.shape[1]], device=dev, dtype=torch.int64)
+    dist.all_reduce(n_tot)
+    prob = GroupLassoProblem(Ad, bd)
+    try:
+        attach_distributed(prob, int(n_tot.item()))
+        x, k, out = prob.solve(algo, x0d, mu_0, merged)
+        xh = x.cpu().numpy()
+    finally:
+        prob.close()
+    out["tt"] = time.perf_counter() - t0
+    return xh, k, out
 
 
 class GroupLassoProblem:
@@ -196,6 +226,33 @@ class GroupLassoProblem:
     def handle(self):
         return self._h
 
+    # ---- multi-GPU: this problem is the column shard A[:, J_rank] of a larger one ------------------
+    def export_mailbox(self, world):
+        """(64-byte CUDA IPC handle, raw device pointer) of this rank's peer mailbox."""
+        lib = _lib.load()
+        blob = (C.c_char * 64)()
+        ptr = C.c_void_p()
+        with self._device_ctx():
+            _lib.check(lib.glp_comm_export(self._h, int(world), blob, C.byref(ptr)))
+        return bytes(blob.raw), ptr.value
+
+    def attach_peers(self, rank, world, n_total, peers, kind=0):
+        """peers: kind 0 -> world*64 bytes of IPC handles in rank order; kind 1 -> list of device pointers."""
+        lib = _lib.load()
+        if kind == 0:
+            if len(peers) != 64 * world:
+                raise ValueError("expected %d bytes of IPC handles, got %d" % (64 * world, len(peers)))
+            buf = C.create_string_buffer(bytes(peers), 64 * world)
+        else:
+            buf = (C.c_void_p * world)(*[int(p) for p in peers])
+        with self._device_ctx():
+            _lib.check(lib.glp_comm_attach(self._h, int(rank), int(world), int(n_total), buf, int(kind)))
+        self.rank, self.world, self.n_total = int(rank), int(world), int(n_total)
+
+    def _device_ctx(self):
+        import torch
+        return torch.cuda.device(self.device)
+
     def close(self):
         if self._h:
             _lib.load().glp_destroy(self._h)
@@ -226,6 +283,68 @@ class GroupLassoProblem:
         fh = f_hist[:res.iters]
         _log_history(fh, res)
         return x, int(res.iters), _format_out(res, fh, tt)
+
+
+def shard_bounds(n, world, align=128):
+    """Contiguous column blocks J_0..J_{world-1} of [0, n): sizes differ by at most `align` and all
+    but the last are multiples of `align` (TMA tile width in elements), so that every x row group
+    lives on exactly one rank and the prox stays rank-local."""
+    if world < 1:
+        raise ValueError("world must be >= 1")
+    blocks = -(-n // align)
+    cuts = [min(n, ((r * blocks) // world) * align) for r in range(world)] + [n]
+    if any(cuts[r + 1] <= cuts[r] for r in range(world)):
+        raise ValueError("n=%d is too small to shard over %d ranks in blocks of %d columns" % (n, world, align))
+    return [(cuts[r], cuts[r + 1]) for r in range(world)]
+
+
+def exchange_handles(mine, group=None):
+    """All-gather one fixed-size byte string per rank over torch.distributed (any backend); returns
+    the concatenation in rank order.  This is the only host-side communication of a sharded solve."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+    t = torch.tensor(list(mine), dtype=torch.uint8, device=dev)
+    out = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(out, t, group=group)
+    return b"".join(bytes(o.cpu().numpy().tobytes()) for o in out)
+
+
+def attach_distributed(prob, n_total, group=None):
+    """One process per GPU: export this rank's mailbox, all-gather the IPC handles, map the peers."""
+    import torch.distributed as dist
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    blob, _ = prob.export_mailbox(world)
+    prob.attach_peers(rank, world, n_total, exchange_handles(blob, group), kind=0)
+    dist.barrier(group)  # every mailbox is mapped everywhere before the first push
+    return prob
+
+
+def solve_group(probs, algo, x0_shards, mu_0, opts=None):
+    """One process driving G shards (G devices, or G logical ranks on one device + stream).
+    Returns (list of x shards, k, out)."""
+    import torch
+    lib = _lib.load()
+    G = len(probs)
+    merged = merge_opts(algo, opts)
+    o = pack_opts(algo, merged)
+    x0d = [x0.to(device=p.device, dtype=p.dtype).contiguous() for p, x0 in zip(probs, x0_shards)]
+    xs = [torch.empty_like(x) for x in x0d]
+    cap = 3 * int(o.maxit) + 8
+    f_hist = np.empty(cap, dtype=np.float64)
+    res = (_lib.GlpResult * G)()
+    hs = (C.c_void_p * G)(*[p.handle.value for p in probs])
+    x0p = (C.c_void_p * G)(*[x.data_ptr() for x in x0d])
+    xp = (C.c_void_p * G)(*[x.data_ptr() for x in xs])
+    t0 = time.perf_counter()
+    rc = lib.glp_group_solve(hs, G, ALGO_ID[algo], x0p, float(mu_0), C.byref(o), xp, res, f_hist.ctypes.data, cap)
+    _raise_for(rc)
+    tt = time.perf_counter() - t0
+    fh = f_hist[:res[0].iters]
+    out = _format_out(res[0], fh, tt)
+    out["glprox"]["per_rank"] = [{"iters": int(r.iters), "fval": r.fval, "n_fwd": int(r.n_fwd)} for r in res]
+    return xs, int(res[0].iters), out
 
 
 def _solve_torch(algo, x0, A, b, mu_0, merged, o):

@@ -166,7 +166,29 @@ int glp_solve_host(int device, int algo, int dtype, int m, int n, int l, const v
                    const glp_opts* opts, void* x_out_host, glp_result* res, double* f_hist_host,
                    int hist_cap);
 
-/* ---- multi-GPU plumbing (one process per GPU; rendezvous of the id is the host's job) ----------*/
+/* ---- multi-GPU: column-block shards of A, exchange through peer mailboxes over NVLink -------------
+ * The reference is single-process; this is what sharding its products needs:
+ * rank g holds A[:, J_g] (glp_create with n_local = |J_g|) and the row groups x[J_g, :]; the prox is
+ * rank-local; per forward stream every rank pushes its m x 2l partial product and five scalars into
+ * every peer's mailbox from inside the streaming kernel, and each rank sums the W contributions in
+ * rank order (bit-identical on all ranks).
+ *   1. glp_comm_export on every rank: allocates this rank's mailbox, returns its 64-byte CUDA IPC
+ *      handle (and/or the raw device pointer, for ranks that live in one process);
+ *   2. the host exchanges the handles (torch.distributed.all_gather in the Python host);
+ *   3. glp_comm_attach(rank, world, n_total, peers, kind): kind 0 = world x 64-byte IPC handles,
+ *      kind 1 = world device pointers.  n_total = sum of n_local (sparsity denominator).
+ * After that glp_solve* on every rank (same algo/opts/mu0, SPMD) runs the sharded solve; x0 / x_out
+ * are the local row groups.  glp_fwd / glp_tpass_prox stay rank-local (partial products). */
+int glp_comm_export(glp_handle* h, int world, void* ipc_handle64_out, void** mailbox_dev_out);
+int glp_comm_attach(glp_handle* h, int rank, int world, int64_t n_total, const void* peers, int kind);
+/* G logical ranks driven by one host thread (one process, G devices -- or G shards on ONE device and
+ * one stream, which is how the exchange is tested on a single GPU).  Arrays have G entries; f_hist
+ * is rank 0's (identical on all ranks). */
+int glp_group_solve(glp_handle** hs, int G, int algo, const void* const* x0_dev, double mu0,
+                    const glp_opts* opts, void* const* x_out_dev, glp_result* res, double* f_hist_host,
+                    int hist_cap);
+
+/* ---- NCCL plumbing (baseline exchange for A/B measurements; rendezvous of the id is the host's job) */
 int glp_nccl_unique_id(void* id128 /* 128 bytes out */);
 int glp_nccl_comm_create(void** comm_out, const void* id128, int rank, int world, int device);
 int glp_nccl_comm_destroy(void* comm);

@@ -1,0 +1,52 @@
+"""Worker of tests/test_gpu_multigpu.py (launched with torch.distributed.run, one process per GPU):
+sharded drop-in solves through opts['dist'], checked against the golden vectors of the reference.
+Prints one line 'DIST_PARITY_OK <world>' from rank 0 on success."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "convex-optimization_b200"), os.path.join(ROOT, "tests")):
+    sys.path.insert(0, p)
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from conftest import golden_inputs, load_golden
+    from gl_FProxGD_primal import gl_FProxGD_primal
+    from gl_ProxGD_primal import gl_ProxGD_primal
+    from glprox import shard_bounds
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    for name in ("fixture_maxit40", "harsh_ls", "fixture"):
+        rec = load_golden(name)
+        A, b, x0, u, mu = golden_inputs(rec)
+        c0, c1 = shard_bounds(A.shape[1], world, 64)[rank]
+        for algo, fn in (("FProxGD", gl_FProxGD_primal), ("ProxGD", gl_ProxGD_primal)):
+            if name == "fixture" and algo == "ProxGD":
+                continue
+            opts = dict(rec["opts"])
+            opts["dist"] = True
+            x, k, out = fn(x0[c0:c1].copy(), np.ascontiguousarray(A[:, c0:c1]), b, mu, opts)
+            assert k == int(rec[algo + "_k"]), (name, algo, k)
+            fh, ref = np.asarray(out["f_hist"]), rec[algo + "_f_hist"]
+            assert np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-10, (name, algo)
+            assert abs(out["fval"] - rec[algo + "_fval"]) <= 1e-10 * abs(rec[algo + "_fval"])
+            assert np.max(np.abs(x - rec[algo + "_x"][c0:c1])) <= 1e-8
+            # all ranks took bit-identical decisions
+            t = torch.tensor([out["fval"], float(k)], device="cuda", dtype=torch.float64)
+            lst = [torch.empty_like(t) for _ in range(world)]
+            dist.all_gather(lst, t)
+            assert all(torch.equal(lst[0], z) for z in lst)
+    dist.barrier()
+    if rank == 0:
+        print("DIST_PARITY_OK %d" % world, flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
