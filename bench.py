@@ -407,8 +407,14 @@ def main():
         else:
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": blas_threads(), "kind": "port",
                                     "sample": "skipped: host RAM too small"}
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
     if rank == 0:
+        sys.stderr.flush()
         print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
