@@ -44,7 +44,9 @@ __device__ __forceinline__ ProxResolved resolve(const ProxArgs& p) {
   return r;
 }
 
-template <typename T>
+// SMEM = true: every operand (state, grad) lives in shared memory (persistent kernel); the gradient is
+// then read with a plain load (ld.global.cg on a shared address would fault).
+template <typename T, bool SMEM = false>
 __device__ __forceinline__ void prox_group(const ProxArgs& p, const ProxResolved& r, const Geom& g,
                                            int64_t j, ProxScal& sc) {
   const int l = g.l;
@@ -79,7 +81,7 @@ __device__ __forceinline__ void prox_group(const ProxArgs& p, const ProxResolved
   for (int c = 0; c < l; ++c) {
     const double xtc = xt[c * ldn + j];
     const double base = accel ? xadd(xmul(omt, xtc), xmul(r.theta, v[c * ldn + j])) : xtc;
-    const double z = xsub(base, xmul(r.t, __ldcg(&p.grad[c * ldn + j])));
+    const double z = xsub(base, xmul(r.t, SMEM ? p.grad[c * ldn + j] : __ldcg(&p.grad[c * ldn + j])));
     nn = xadd(nn, xmul(z, z));
   }
   const double rn = __dsqrt_rn(nn);
@@ -90,7 +92,7 @@ __device__ __forceinline__ void prox_group(const ProxArgs& p, const ProxResolved
   for (int c = 0; c < l; ++c) {
     const double xtc = xt[c * ldn + j];
     const double base = accel ? xadd(xmul(omt, xtc), xmul(r.theta, v[c * ldn + j])) : xtc;
-    const double gr = __ldcg(&p.grad[c * ldn + j]);
+    const double gr = SMEM ? p.grad[c * ldn + j] : __ldcg(&p.grad[c * ldn + j]);
     const double z = xsub(base, xmul(r.t, gr));
     const double o = xdiv(xmul(z, shrink), den);
     const double oz = fabs(o) < r.thres ? 0.0 : o;

@@ -17,6 +17,7 @@
 #include "glp_decide.cuh"
 #include "glp_fwd.cuh"
 #include "glp_misc.cuh"
+#include "glp_persist.cuh"
 #include "glp_tpass.cuh"
 #include "glp_types.cuh"
 
@@ -133,6 +134,7 @@ struct glp_handle {
   double *rr_g = nullptr, *scal_red = nullptr, *cnt_red = nullptr;
   int gather_grid = 0;
   const Ctrl* cur_ctrl = nullptr;  // control block the launches of the current slot read
+  int backend_used = GLP_BACKEND_STREAM;
 
   // step-level scratch (lazily sized)
   void* scratch = nullptr;
@@ -688,6 +690,7 @@ static int phase_gather(glp_handle* h) { return enqueue_gather(h, h->cur_ctrl); 
 
 extern "C" int glp_solve_begin(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o) {
   GLP_TRY(phase_prepare(h, algo, x0_dev, mu0, o));
+  h->backend_used = GLP_BACKEND_STREAM;
   GLP_TRY(phase_init_prox(h));
   GLP_TRY(phase_fwd(h));
   GLP_TRY(phase_gather(h));
@@ -710,7 +713,7 @@ static void fill_result(const glp_handle* h, const Ctrl& c, glp_result* res) {
   if (res == nullptr) return;
   res->iters = c.k;
   res->done = c.done;
-  res->backend_used = GLP_BACKEND_STREAM;
+  res->backend_used = h->backend_used;
   res->fval = c.f_cur;
   res->sparsity = c.s_cur;
   res->n_fwd = c.n_fwd;
@@ -874,10 +877,100 @@ static int drive_until_done(glp_handle** hs, int G, const glp_opts* o) {
   return GLP_OK;
 }
 
+// ---- persistent backend: the whole solve in one cluster launch (glp_persist.cuh) -----------------
+struct PersistPlan { int C; int nc; size_t smem; };
+
+static bool persist_plan(const glp_handle* h, PersistPlan* out) {
+  if (multi(h) || h->g.l > PERSIST_MAX_L) return false;
+  int want = 0;
+  if (const char* e = getenv("GLPROX_CLUSTER")) want = atoi(e);
+  const int cands[2] = {8, 16};
+  for (int C : cands) {
+    if (want != 0 && want != C) continue;
+    int nc = (h->g.n + C - 1) / C;
+    nc += nc & 1;
+    if (nc < 2) nc = 2;
+    if (nc > PERSIST_MAX_NC) continue;
+    const PersistLayout lay = persist_layout(h->g.m, nc, h->g.l, h->dtype == GLP_F32 ? 4 : 8);
+    if (lay.total > size_t(227) * 1024) continue;
+    out->C = C; out->nc = nc; out->smem = lay.total;
+    return true;
+  }
+  return false;
+}
+
+template <typename T, int L>
+static cudaError_t launch_persist_t(glp_handle* h, const PersistPlan& pl, const PersistArgs& a) {
+  auto kfn = glp_persist_kernel<T, L>;
+  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem));
+  if (e != cudaSuccess) return e;
+  if (pl.C > 8) {
+    e = cudaFuncSetAttribute(kfn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) return e;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned(pl.C), 1, 1);
+  cfg.blockDim = dim3(PERSIST_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = pl.smem;
+  cfg.stream = h->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = unsigned(pl.C);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  e = cudaLaunchKernelEx(&cfg, kfn, a);
+  h->n_launches++;
+  return e;
+}
+
+static int enqueue_persist(glp_handle* h, const PersistPlan& pl) {
+  PersistArgs a{};
+  a.A = h->A; a.lda = h->lda; a.b = h->b;
+  a.x0 = h->state[1]; a.x_out = h->state[0];
+  a.ctrl_out = &h->ctrl[0];
+  a.f_hist = h->f_hist; a.f_hist_best = h->f_hist_best;
+  a.sc = h->sc;
+  a.m = h->g.m; a.n = h->g.n; a.l = h->g.l; a.nc = pl.nc;
+  a.ldm = h->g.ldm; a.ldn = h->g.ldn;
+  cudaError_t e = cudaErrorInvalidValue;
+  const bool f32 = h->dtype == GLP_F32;
+  switch (h->g.l) {
+    case 1: e = f32 ? launch_persist_t<float, 1>(h, pl, a) : launch_persist_t<double, 1>(h, pl, a); break;
+    case 2: e = f32 ? launch_persist_t<float, 2>(h, pl, a) : launch_persist_t<double, 2>(h, pl, a); break;
+    case 3: e = f32 ? launch_persist_t<float, 3>(h, pl, a) : launch_persist_t<double, 3>(h, pl, a); break;
+    case 4: e = f32 ? launch_persist_t<float, 4>(h, pl, a) : launch_persist_t<double, 4>(h, pl, a); break;
+    default: break;
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(GLP_ERR_CUDA, "persistent cluster launch (C=%d, %zu B smem) failed: %s", pl.C, pl.smem, cudaGetErrorString(e));
+  }
+  return GLP_OK;
+}
+
 extern "C" int glp_solve(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o, void* x_out_dev,
                          glp_result* res, double* f_hist_host, int hist_cap) {
-  GLP_TRY(glp_solve_begin(h, algo, x0_dev, mu0, o));
-  int rc = drive_until_done(&h, 1, o);
+  if (h == nullptr || o == nullptr) return fail(GLP_ERR_ARG, "null argument");
+  if (o->backend < GLP_BACKEND_AUTO || o->backend > GLP_BACKEND_PERSISTENT) return fail(GLP_ERR_ARG, "unknown backend %d", o->backend);
+  PersistPlan pl{};
+  const bool fits = persist_plan(h, &pl);
+  if (o->backend == GLP_BACKEND_PERSISTENT && !fits)
+    return fail(GLP_ERR_ARG, "backend 'persistent' needs a single-GPU problem with l <= %d whose A fits in one cluster's "
+                "shared memory (m=%d n=%d l=%d does not)", PERSIST_MAX_L, h->g.m, h->g.n, h->g.l);
+  GLP_TRY(phase_prepare(h, algo, x0_dev, mu0, o));
+  int rc;
+  if (fits && o->backend != GLP_BACKEND_STREAM) {
+    h->backend_used = GLP_BACKEND_PERSISTENT;
+    rc = enqueue_persist(h, pl);
+  } else {
+    h->backend_used = GLP_BACKEND_STREAM;
+    rc = phase_init_prox(h);
+    if (rc == GLP_OK) rc = phase_fwd(h);
+    if (rc == GLP_OK) rc = phase_gather(h);
+    if (rc == GLP_OK) rc = drive_until_done(&h, 1, o);
+  }
   if (rc != GLP_OK) { h->solving = false; return rc; }
   return glp_solve_end(h, x_out_dev, res, f_hist_host, hist_cap);
 }
@@ -897,7 +990,7 @@ extern "C" int glp_group_solve(glp_handle** hs, int G, int algo, const void* con
         return fail(GLP_ERR_ARG, "logical ranks that share a device must share a stream");
   }
   int rc = GLP_OK;
-  for (int i = 0; i < G && rc == GLP_OK; ++i) rc = phase_prepare(hs[i], algo, x0_dev[i], mu0, o);
+  for (int i = 0; i < G && rc == GLP_OK; ++i) { rc = phase_prepare(hs[i], algo, x0_dev[i], mu0, o); hs[i]->backend_used = GLP_BACKEND_STREAM; }
   for (int i = 0; i < G && rc == GLP_OK; ++i) { cudaSetDevice(hs[i]->device); rc = phase_init_prox(hs[i]); }
   for (int i = 0; i < G && rc == GLP_OK; ++i) { cudaSetDevice(hs[i]->device); rc = phase_fwd(hs[i]); }
   for (int i = 0; i < G && rc == GLP_OK; ++i) { cudaSetDevice(hs[i]->device); rc = phase_gather(hs[i]); }

@@ -37,15 +37,24 @@ def _support(x):
     return np.flatnonzero((ax > 1e-6 * ax.max()).any(axis=1)), np.flatnonzero(np.sqrt((x * x).sum(1)) > 0)
 
 
+# cases whose A fits in one cluster's shared memory also run on the persistent kernel (K4)
+PERSISTENT_FITS = {"fixture", "seed114514", "seed1", "seed2", "fixture_maxit3", "fixture_maxit40", "ragged", "l1",
+                   "l3", "harsh_ls", "diminishing", "diminishing2", "thres1e-8", "fixed_step"}
+
+
+@pytest.mark.parametrize("backend", ["stream", "persistent"])
 @pytest.mark.parametrize("algo", ["ProxGD", "FProxGD"])
 @pytest.mark.parametrize("name", FP64_CASES)
-def test_fp64_solver_matches_reference(name, algo):
-    if name == "fixed_step" and algo == "ProxGD":
-        pytest.skip("7500 slow-path iterations; covered by diminishing*")
+def test_fp64_solver_matches_reference(name, algo, backend):
+    if name == "fixed_step" and algo == "ProxGD" and backend == "stream":
+        pytest.skip("7500 launch-bound iterations; the persistent backend covers it")
+    if backend == "persistent" and name not in PERSISTENT_FITS:
+        pytest.skip("A does not fit in one cluster (or l > 4)")
     rec = load_golden(name)
     A, b, x0, u, mu = golden_inputs(rec)
     keep = (A.copy(), b.copy(), x0.copy())
-    x, k, out = _fn(algo)(x0, A, b, mu, dict(rec["opts"]))
+    x, k, out = _fn(algo)(x0, A, b, mu, dict(rec["opts"], backend=backend))
+    assert out["glprox"]["backend"] == backend
     assert np.array_equal(A, keep[0]) and np.array_equal(b, keep[1]) and np.array_equal(x0, keep[2])
     assert isinstance(k, int) and isinstance(out["tt"], float) and isinstance(x, np.ndarray)
     assert {"tt", "fval", "f_hist", "f_hist_best"} <= set(out)
@@ -65,14 +74,36 @@ def test_fp64_solver_matches_reference(name, algo):
     assert np.max(np.abs(x - rec[algo + "_x"])) <= 1e-8
     # A was streamed ~twice per iteration (once transposed per iteration, once forward per trial)
     assert out["glprox"]["n_tpass"] <= k
+    if backend == "persistent":
+        assert out["glprox"]["n_launches"] == 1
 
 
+def test_backend_selection():
+    from glprox import _lib
+    A, b, x0, u, mu = orc.gen_data(3, 64, 128, 2)
+    o = {"maxit": 5, "alpha0": 1e-3}
+    assert _fn("FProxGD")(x0, A, b, mu, o)[2]["glprox"]["backend"] == "persistent"   # auto: fits
+    assert _fn("FProxGD")(x0, A, b, mu, dict(o, backend="stream"))[2]["glprox"]["backend"] == "stream"
+    A, b, x0, u, mu = orc.gen_data(3, 512, 4096, 2)
+    o = {"maxit": 2, "alpha0": 1e-4}
+    assert _fn("FProxGD")(x0, A, b, mu, o)[2]["glprox"]["backend"] == "stream"       # auto: too large
+    with pytest.raises(_lib.GlproxError):
+        _fn("FProxGD")(x0, A, b, mu, dict(o, backend="persistent"))
+    with pytest.raises(ValueError):
+        _fn("FProxGD")(x0, A, b, mu, dict(o, backend="cpu"))
+
+
+@pytest.mark.parametrize("backend", ["stream", "persistent"])
 @pytest.mark.parametrize("algo", ["ProxGD", "FProxGD"])
 @pytest.mark.parametrize("name", ["mid_f32in", "fixture_f32in"])
-def test_fp32_solver_matches_fp64_reference_on_rounded_inputs(name, algo):
+def test_fp32_solver_matches_fp64_reference_on_rounded_inputs(name, algo, backend):
+    if backend == "persistent" and name == "mid_f32in":
+        pytest.skip("A does not fit in one cluster")
     rec = load_golden(name)
     A, b, x0, u, mu = golden_inputs(rec)  # fp32-representable values held in fp64
-    x, k, out = _fn(algo)(x0.astype(np.float32), A.astype(np.float32), b.astype(np.float32), mu, dict(rec["opts"]))
+    x, k, out = _fn(algo)(x0.astype(np.float32), A.astype(np.float32), b.astype(np.float32), mu,
+                          dict(rec["opts"], backend=backend))
+    assert out["glprox"]["backend"] == backend
     assert x.dtype == np.float32
     ref_f = rec[algo + "_fval"]
     # (a) the objective the solver reports, (b) the objective of its x re-evaluated in fp64
