@@ -88,9 +88,11 @@ class ClockSampler:
 
     def _pump(self):
         for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+            self.lines.append((time.time(), ln.strip()))
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
+        """Summary of the samples taken in [t0, t1] (the timed region); if the region was shorter than
+        the sampling period, of all samples since start() (warm-up runs the same kernels)."""
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -100,7 +102,9 @@ class ClockSampler:
             self.proc.kill()
         sm, smax, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        inside = [ln for (ts, ln) in self.lines if t0 is not None and t0 <= ts <= (t1 or ts) + 0.25]
+        window = "timed region" if inside else "warm-up + timed region"
+        for ln in (inside or [ln for (_, ln) in self.lines]):
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -112,7 +116,7 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(nm)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
 def dist_setup(args):
@@ -191,12 +195,13 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     # ---- device-resident throughput
+    sampler = ClockSampler(local)
+    sampler.start()
     for _ in range(args.warmup):
         x, k, out = prob.solve(args.algo, x0, mu, opts)
     _lib.check(lib.glp_set_profiling(prob.handle, 1))
-    sampler = ClockSampler(local)
-    sampler.start()
     barrier()
+    t_wall0 = time.time()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     iters = launches = 0
@@ -206,7 +211,10 @@ def run_ours(args):
         launches += out["glprox"]["n_launches"]
     ev1.record()
     barrier()
-    clocks = sampler.stop()
+    t_wall1 = time.time()
+    if t_wall1 - t_wall0 < 0.5:
+        time.sleep(0.3)  # let one more nvidia-smi sample land
+    clocks = sampler.stop(t_wall0, t_wall1)
     ms = ev0.elapsed_time(ev1)
     if world > 1:
         import torch.distributed as dist
@@ -229,8 +237,15 @@ def run_ours(args):
     n_str = prof.fwd_launches + prof.tpass_launches
     avg_ms = (prof.fwd_ms_sum + prof.tpass_ms_sum) / max(n_str, 1)
     achieved = prof.bytes_per_launch / (avg_ms * 1e-3) / 1e9 if n_str else 0.0
+    traffic = None
+    try:  # dram__bytes_read+write per launch from the committed `ncu --set full` capture of this workload
+        cap = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        key = "%s_m%d_n%d_l%d_g%d" % (args.dtype, args.m, args.n, args.l, world)
+        traffic = cap.get(key, {}).get("bytes_per_launch")
+    except (OSError, ValueError):
+        pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None,
+                "frac": achieved / peak, "traffic": traffic,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write)" if peaks else "fallback 6650 GB/s",
                 "kernels": {"glp_fwd_kernel": {"launches": int(prof.fwd_launches),
                                                "avg_ms": prof.fwd_ms_sum / max(prof.fwd_launches, 1),
@@ -241,6 +256,21 @@ def run_ours(args):
                 "bytes_per_launch": prof.bytes_per_launch,
                 "whole_iteration_GBps": 2.0 * prof.bytes_per_launch * value / 1e9}
 
+    if args.l >= 16 and args.dtype == "f32" and world == 1:
+        # wide multi-RHS mode: both products run on tcgen05 (3xTF32); the bounding roofline is the tensor pipe
+        passes = 3
+        n_it = max(int(prof.tpass_launches), 1)
+        flops = passes * 2.0 * args.m * args.n * 3 * args.l * n_it
+        t_s = (prof.fwd_ms_sum + prof.tpass_ms_sum) * 1e-3
+        tf = flops / max(t_s, 1e-12) / 1e12
+        tpeak = float(peaks.get("bf16_tflops", 1590.0)) / 2.0
+        hbm_stream = 2.0 * prof.bytes_per_launch * (prof.fwd_launches + prof.tpass_launches) / max(t_s, 1e-12) / 1e9
+        roofline = {"bound": "tensor", "achieved": tf, "peak": tpeak, "unit": "TFLOP/s", "frac": tf / tpeak, "traffic": None,
+                    "peak_source": "MEASURED_PEAKS.json bf16_tflops / 2 (kind::tf32 runs at half the bf16 rate)",
+                    "work": "3 compensated TF32 products per stream: Ah.Xh + Ah.Xl + Al.Xh, issued flops counted",
+                    "hbm_GBps_of_hi_lo_streams": hbm_stream, "hbm_peak": peak,
+                    "kernels": {"glp_gemm_tf32_kernel<fwd>": {"launches": int(prof.fwd_launches), "avg_ms": prof.fwd_ms_sum / max(prof.fwd_launches, 1)},
+                                "glp_gemm_tf32_kernel<tpass>": {"launches": int(prof.tpass_launches), "avg_ms": prof.tpass_ms_sum / max(prof.tpass_launches, 1)}}}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
@@ -300,6 +330,58 @@ def run_e2e(args, ctx, steps):
     return {"value": iters / dt, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
             "ms_per_step": 1e3 * dt / steps, "final_objective": float(out["fval"]),
             "api": "gl_%s_primal(x0, A, b, mu, opts) with NumPy arrays (pinned host memory)" % args.algo}, (An, bn, x0n)
+
+
+def time_to_tol(f_hist, f_ref, seconds, tol=1e-8):
+    """First k with |f_hist[k] - f_ref| / |f_ref| <= tol, and the wall-clock share of the solve up to
+    it (iterations cost the same; SURVEY.md 8(d) 'time-to-1e-8')."""
+    fh = np.asarray(f_hist, dtype=np.float64)
+    hit = np.flatnonzero(np.abs(fh - f_ref) <= tol * abs(f_ref))
+    if hit.size == 0 or fh.size == 0:
+        return None, None
+    k = int(hit[0]) + 1
+    return k, seconds * k / fh.size
+
+
+def run_homework(args):
+    """BASELINE.json configs[0]/[1]: the reference's own fixture (m=256 n=512 l=2 mu=1e-2, fp64, default
+    opts, seed 97006855) on the persistent cluster kernel, next to the CPU oracle port timed in the same
+    process.  Reported beside the headline line: it/s, seconds to reach 1e-8 of (i) the solver's own
+    final objective (drop-in defaults) and (ii) the true optimum f* with opts={'thres': 1e-8}."""
+    import torch
+    from glprox import GroupLassoProblem
+    from oracle import glprox_oracle as orc
+    F_STAR = 6.1037724766016532e-01   # high-accuracy optimum (SURVEY.md 8(c)); Mosek/Gurobi publish 6.10377E-01
+    A, b, x0, u, mu = orc.gen_data(97006855, 256, 512, 2)
+    prob = GroupLassoProblem(torch.from_numpy(A).cuda(), torch.from_numpy(b).cuda())
+    x0d = torch.from_numpy(x0).cuda()
+    res = {"workload": "Test_group_lasso fixture m=256 n=512 l=2 mu=1e-2 fp64, default opts",
+           "published_optimum_mosek_gurobi": 6.10377e-01, "f_star": F_STAR}
+    for algo in ("FProxGD", "ProxGD"):
+        row = {}
+        for be in ("persistent", "stream"):
+            best = None
+            for _ in range(3):
+                x, k, out = prob.solve(algo, x0d, mu, {"backend": be})
+                ms = out["glprox"]["device_ms"]
+                best = ms if best is None else min(best, ms)
+            kk, tsec = time_to_tol(out["f_hist"], float(out["fval"]), best / 1e3)
+            row[be] = {"iters": k, "fval": float(out["fval"]), "ms": best, "it_per_s": k / (best / 1e3),
+                       "k_to_1e-8_of_final": kk, "s_to_1e-8_of_final": tsec,
+                       "launches": out["glprox"]["n_launches"]}
+        x, k, out = prob.solve(algo, x0d, mu, {"backend": "persistent", "thres": 1e-8})
+        kk, tsec = time_to_tol(out["f_hist"], F_STAR, out["glprox"]["device_ms"] / 1e3)
+        row["persistent_thres1e-8"] = {"iters": k, "fval": float(out["fval"]), "ms": out["glprox"]["device_ms"],
+                                       "k_to_1e-8_of_fstar": kk, "s_to_1e-8_of_fstar": tsec}
+        xr, kr, outr = orc.solve(algo, x0, A, b, mu, {})
+        kk, tsec = time_to_tol(outr["f_hist"], float(outr["fval"]), outr["tt"])
+        row["cpu_port"] = {"iters": kr, "fval": float(outr["fval"]), "ms": 1e3 * outr["tt"], "it_per_s": kr / outr["tt"],
+                           "k_to_1e-8_of_final": kk, "s_to_1e-8_of_final": tsec, "cores": blas_threads()}
+        row["rel_obj_diff_gpu_vs_cpu"] = abs(row["persistent"]["fval"] - row["cpu_port"]["fval"]) / abs(row["cpu_port"]["fval"])
+        row["published_cpu_seconds"] = {"FProxGD": 1.09, "ProxGD": 1.53}[algo]   # doc/report.md:446-447
+        res[algo] = row
+    prob.close()
+    return res
 
 
 def cpu_reference_solve(args, An, bn, x0n, mu, opts, sample_maxit, row_frac=1.0):
@@ -393,6 +475,10 @@ def main():
         if e2e is None:
             host = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            line["homework_fixture"] = run_homework(args)
+        except Exception as e:  # noqa: BLE001  (secondary report; never lose the headline line)
+            line["homework_fixture"] = {"error": repr(e)}
         if host is None:
             need_gb = A.numel() * A.element_size() / 1e9
             if mem_available_gb() >= 1.6 * need_gb + 4:

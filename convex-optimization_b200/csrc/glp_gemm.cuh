@@ -1,0 +1,382 @@
+// glp_gemm.cuh -- K5: tensor-core products for the wide multi-RHS mode (l >= 16, fp32 data).
+//
+// With l = 128 right-hand sides the two products of an iteration are real GEMMs
+//   forward     A  [m x n] . [xn | xnt] [n x 2l]      (gl_*_primal.py:25,61/63, batched over 2l columns)
+//   transposed  A^T[n x m] . r          [m x l]       (gl_ProxGD_primal.py:129 / gl_FProxGD_primal.py:66)
+// and belong on the 5th-generation tensor cores.  Both are computed by ONE kernel
+//   D[M x N] = P[M x K] . Q[N x K]^T ,  P row-major (K contiguous), Q planar (K contiguous), D planar fp64
+// with P = A (forward) or the resident transposed copy A^T (transposed pass), so both operands are
+// K-major and need no MN-major descriptors.
+//
+// Structure (one persistent CTA per SM, 6 warps):
+//   warp 0   TMA producer: 128 x 32 (P) and NT x 32 (Q) fp32 boxes, 128-byte swizzle, into a 3-6 stage ring
+//   warp 1   allocates TMEM, one elected lane issues tcgen05.mma.cta_group::1.kind::tf32 (M=128, N=NT<=128, K=8),
+//            tcgen05.commit releases the smem stage / publishes a chunk accumulator
+//   warps2-9 epilogue: tcgen05.ld 32 lanes x 16 columns at a time into fp64 REGISTER accumulators (64 per
+//            thread) that live across the K chunks of a tile; the chunk accumulator is double buffered in
+//            TMEM so the drain of chunk i overlaps the MMAs of chunk i+1; coalesced planar fp64 stores
+// Precision: kind::tf32 keeps 10 mantissa bits of each operand and the tensor core accumulates in fp32
+// with truncation (measured: a relative bias of ~(K/8)*2^-24 on the result).  PASSES = 3 runs the
+// error-compensated product  P.Q ~= Ph.Qh + (Ph.Ql + Pl.Qh)  on hi/lo fp32 splits resident in HBM; the
+// main term is accumulated in TMEM over short K chunks only (k_chunk_blocks*32 elements) and summed in
+// fp64 by the epilogue, the two small correction terms in a third TMEM accumulator over the whole tile.
+#pragma once
+#include "glp_device.cuh"
+#include "glp_types.cuh"
+
+namespace glp {
+
+constexpr int GEMM_BM = 128;
+constexpr int GEMM_BK = 32;                 // fp32 elements = 128 bytes = one swizzle row
+constexpr int GEMM_EPI_WARPS = 8;
+constexpr int GEMM_THREADS = (2 + GEMM_EPI_WARPS) * 32;
+constexpr int GEMM_UMMA_K = 8;              // tf32
+
+struct GemmArgs {
+  int64_t M, K;
+  int32_t N;
+  int32_t k_chunk_blocks;                   // K blocks accumulated in fp32 before an fp64 flush (0 = all)
+  double* D;                                // planar fp64 [N][ldd]
+  int64_t ldd;
+  int32_t* fault;
+  // solver launches: destination / skip decided on the device from the control block
+  const Ctrl* ctrl;                         // nullable
+  double* D_alt;                            // role 1: D = ctrl->cur ? D : D_alt  (candidate product buffer 1 - cur)
+  int32_t role;                             // 0 plain, 1 forward (skip when done), 2 transposed (skip when done or retry)
+  int32_t pad;
+};
+
+template <int NT, int PASSES> constexpr int gemm_stage_bytes() {
+  return (PASSES == 3 ? 2 : 1) * (GEMM_BM * 128 + NT * 128);
+}
+template <int NT, int PASSES> constexpr int gemm_stages() {
+  return (200 * 1024) / gemm_stage_bytes<NT, PASSES>() > 8 ? 8 : (200 * 1024) / gemm_stage_bytes<NT, PASSES>();
+}
+template <int NT, int PASSES> constexpr int gemm_smem_bytes() {
+  return gemm_stages<NT, PASSES>() * gemm_stage_bytes<NT, PASSES>() + 1024 /*align*/ + 256 /*barriers*/;
+}
+
+// ---- tcgen05 wrappers (hand-written PTX) -----------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D[tmem] (+)= A[smem desc] . B[smem desc]^T, issued by ONE thread for the whole CTA
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// mbarrier arrive when all previously issued MMAs of this thread have completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major operand tile [rows][32 fp32] written by TMA with CU_TENSOR_MAP_SWIZZLE_128B: 8-row groups are
+// 1024 bytes apart (SBO), LBO unused, descriptor version 1 (Blackwell), layout type 2 (SWIZZLE_128B).
+__device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= uint64_t((smem_addr >> 4) & 0x3fffu);
+  d |= uint64_t(1024u >> 4) << 32;
+  d |= uint64_t(1) << 46;
+  d |= uint64_t(2) << 61;
+  return d;
+}
+// kind::tf32, fp32 accumulate, both operands K-major, M = 128
+template <int NT> __device__ __forceinline__ constexpr uint32_t umma_idesc_tf32() {
+  return (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(NT >> 3) << 17) | (uint32_t(GEMM_BM >> 4) << 24);
+}
+
+// hi = a with the 13 low mantissa bits cleared after rounding to nearest (what kind::tf32 keeps), lo = a - hi
+__global__ void glp_split_tf32_kernel(const float* src, float* hi, float* lo,  // hi may alias src (in place)
+                                      int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst) {
+  const int64_t total = rows * cols;
+  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t i = e / cols, j = e - i * cols;
+    const float a = src[i * ld_src + j];
+    uint32_t u = __float_as_uint(a);
+    u = (u + 0x00000fffu + ((u >> 13) & 1u)) & 0xffffe000u;  // round to nearest even on bit 13
+    float h = __uint_as_float(u);
+    if (!(fabsf(h) <= 3.0e38f)) h = a;                        // inf / nan / overflow of the rounding: keep a
+    hi[i * ld_dst + j] = h;
+    lo[i * ld_dst + j] = a - h;
+  }
+}
+
+// dst[j][i] = src[i][j]  (32 x 32 tiles through shared memory), optionally split into hi / lo
+__global__ void glp_transpose_split_kernel(const float* __restrict__ src, float* __restrict__ hi, float* __restrict__ lo,
+                                           int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst) {
+  __shared__ float t[32][33];
+  const int64_t bi = int64_t(blockIdx.y) * 32, bj = int64_t(blockIdx.x) * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int64_t i = bi + r, j = bj + threadIdx.x;
+    t[r][threadIdx.x] = (i < rows && j < cols) ? src[i * ld_src + j] : 0.f;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int64_t j = bj + r, i = bi + threadIdx.x;
+    if (j < cols && i < rows) {
+      const float a = t[threadIdx.x][r];
+      uint32_t u = __float_as_uint(a);
+      u = (u + 0x00000fffu + ((u >> 13) & 1u)) & 0xffffe000u;
+      float h = __uint_as_float(u);
+      if (!(fabsf(h) <= 3.0e38f)) h = a;
+      hi[j * ld_dst + i] = h;
+      lo[j * ld_dst + i] = a - h;
+    }
+  }
+}
+
+template <int NT, int PASSES>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_constant__ CUtensorMap tmPl,
+                     const __grid_constant__ CUtensorMap tmQh, const __grid_constant__ CUtensorMap tmQl,
+                     const GemmArgs a) {
+  constexpr int STAGES = gemm_stages<NT, PASSES>();
+  constexpr int STAGE_BYTES = gemm_stage_bytes<NT, PASSES>();
+  constexpr int P_BYTES = GEMM_BM * 128, Q_BYTES = NT * 128;
+  // TMEM: two chunk accumulators (main term, double buffered) + one whole-tile accumulator of the two
+  // correction terms (their magnitude is 2^-11 of the main term, so their rounding is harmless)
+  constexpr uint32_t TMEM_NEED = (PASSES == 3 ? 3 : 2) * NT;
+  constexpr uint32_t TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
+  constexpr int HC = NT / 2;  // columns per epilogue thread
+  static_assert(NT == 32 || NT == 64 || NT == 128, "NT");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tfull = empty + STAGES;   // [2] chunk accumulator ready
+  uint64_t* tempty = tfull + 2;       // [2] chunk accumulator drained
+  uint64_t* cempty = tempty + 2;      // [1] correction accumulator drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(cempty + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  double* Dout = a.D;
+  if (a.ctrl != nullptr) {  // grid-uniform
+    if (a.ctrl->done || (a.role == 2 && a.ctrl->retry)) return;
+    if (a.role == 1 && a.ctrl->cur == 0) Dout = a.D_alt;
+  }
+  const int64_t tiles = (a.M + GEMM_BM - 1) / GEMM_BM;
+  const int64_t nkb = (a.K + GEMM_BK - 1) / GEMM_BK;
+  const int64_t kc = a.k_chunk_blocks > 0 ? a.k_chunk_blocks : nkb;
+  const int64_t nchunks = (nkb + kc - 1) / kc;
+
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], GEMM_EPI_WARPS); }
+    mbar_init(cempty, GEMM_EPI_WARPS);
+    fence_mbar_init();
+    fence_proxy_async();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      prefetch_tensormap(&tmPh); prefetch_tensormap(&tmQh);
+      const uint64_t pol_stream = policy_evict_first(), pol_keep = policy_evict_normal();
+      int stage = 0; uint32_t phase = 0;
+      for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        for (int64_t kb = 0; kb < nkb; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1u, a.fault);
+          mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
+          uint8_t* s = smem + stage * STAGE_BYTES;
+          const int32_t k0 = int32_t(kb * GEMM_BK), r0 = int32_t(tile * GEMM_BM);
+          tma_load_2d(s, &tmPh, &full[stage], k0, r0, pol_stream);
+          tma_load_2d(s + P_BYTES, &tmQh, &full[stage], k0, 0, pol_keep);
+          if (PASSES == 3) {
+            tma_load_2d(s + P_BYTES + Q_BYTES, &tmPl, &full[stage], k0, r0, pol_stream);
+            tma_load_2d(s + 2 * P_BYTES + Q_BYTES, &tmQl, &full[stage], k0, 0, pol_keep);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_tf32<NT>();
+      int stage = 0; uint32_t phase = 0;
+      int acc = 0; uint32_t acc_phase = 0, c_phase = 0;
+      const uint32_t c_tmem = tmem_base + uint32_t(2 * NT);
+      for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        if (PASSES == 3) {
+          mbar_wait(cempty, c_phase ^ 1u, a.fault);  // epilogue has read the previous tile's corrections
+          c_phase ^= 1u;
+        }
+        uint32_t c_accumulate = 0;
+        for (int64_t ch = 0; ch < nchunks; ++ch) {
+          mbar_wait(&tempty[acc], acc_phase ^ 1u, a.fault);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + uint32_t(acc * NT);
+          const int64_t kb1 = (ch + 1) * kc < nkb ? (ch + 1) * kc : nkb;
+          uint32_t accumulate = 0;
+          for (int64_t kb = ch * kc; kb < kb1; ++kb) {
+            mbar_wait(&full[stage], phase, a.fault);
+            tc_fence_after();
+            const uint32_t sbase = smem_u32(smem + stage * STAGE_BYTES);
+            const uint64_t dPh = umma_desc_k_sw128(sbase), dQh = umma_desc_k_sw128(sbase + P_BYTES);
+#pragma unroll
+            for (int k4 = 0; k4 < GEMM_BK / GEMM_UMMA_K; ++k4) {
+              umma_tf32(d_tmem, dPh + uint64_t(2 * k4), dQh + uint64_t(2 * k4), idesc, accumulate);
+              accumulate = 1;
+            }
+            if (PASSES == 3) {
+              const uint64_t dPl = umma_desc_k_sw128(sbase + P_BYTES + Q_BYTES);
+              const uint64_t dQl = umma_desc_k_sw128(sbase + 2 * P_BYTES + Q_BYTES);
+#pragma unroll
+              for (int k4 = 0; k4 < GEMM_BK / GEMM_UMMA_K; ++k4) {
+                umma_tf32(c_tmem, dPh + uint64_t(2 * k4), dQl + uint64_t(2 * k4), idesc, c_accumulate);
+                c_accumulate = 1;
+                umma_tf32(c_tmem, dPl + uint64_t(2 * k4), dQh + uint64_t(2 * k4), idesc, 1u);
+              }
+            }
+            umma_commit(&empty[stage]);  // frees the smem stage when these MMAs have read it
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          }
+          umma_commit(&tfull[acc]);      // chunk accumulator (and, after the last chunk, the corrections) complete
+          if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (8 warps)
+    // warp -> (TMEM lane quarter it may read, half of the NT columns); fp64 accumulators live in registers
+    // across the K chunks of a tile, so the tensor core's fp32 accumulation never spans more than one chunk
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+      const int64_t row = tile * GEMM_BM + quarter * 32 + lane;
+      double sum[HC];
+#pragma unroll
+      for (int j = 0; j < HC; ++j) sum[j] = 0.0;
+      const uint32_t lane_off = uint32_t(quarter * 32) << 16;
+      for (int64_t ch = 0; ch < nchunks; ++ch) {
+        mbar_wait(&tfull[acc], acc_phase, a.fault);
+        tc_fence_after();
+        const uint32_t t0 = tmem_base + uint32_t(acc * NT + half * HC) + lane_off;
+#pragma unroll
+        for (int c0 = 0; c0 < HC; c0 += 16) {
+          uint32_t v[16];
+          tmem_ld_32x32b_x16(t0 + uint32_t(c0), v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) sum[c0 + j] += double(__uint_as_float(v[j]));
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+      if (PASSES == 3) {
+        const uint32_t t0 = tmem_base + uint32_t(2 * NT + half * HC) + lane_off;
+#pragma unroll
+        for (int c0 = 0; c0 < HC; c0 += 16) {
+          uint32_t v[16];
+          tmem_ld_32x32b_x16(t0 + uint32_t(c0), v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) sum[c0 + j] += double(__uint_as_float(v[j]));
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(cempty);
+      }
+      if (row < a.M) {
+#pragma unroll
+        for (int j = 0; j < HC; ++j) {
+          const int col = half * HC + j;
+          if (col < a.N) Dout[int64_t(col) * a.ldd + row] = sum[j];
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// After a tensor-core forward product: residual norm partials and the sparsity count of the candidate
+// (what K1 fuses into its epilogue / aux warp on the CUDA-core path).  gl_*_primal.py:22,24-27.
+struct PostFwdArgs {
+  const Ctrl* ctrl;
+  const double* AX[2];          // [2l][ldm]
+  const double* b;              // [l][ldm]
+  const double* scal_partial;   // [ncb][4], slot 3 = max|xn| per column block
+  const double* xcand[2];       // candidate x [l][ldn]
+  double* rr_out;               // [gridDim]
+  double* cnt_out;              // [gridDim]
+};
+__global__ void __launch_bounds__(256)
+glp_post_fwd_kernel(const PostFwdArgs a, const Geom g) {
+  __shared__ double s_red[8];
+  __shared__ double s_mx;
+  if (a.ctrl != nullptr && a.ctrl->done) return;
+  const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : 0;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  auto nmx = [](double x, double y) { return (x != x) ? x : ((y != y) ? y : fmax(x, y)); };
+  double mx = 0.0;
+  for (int i = tid; i < g.ncb; i += 256) mx = nmx(mx, __ldcg(&a.scal_partial[4 * i + 3]));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = nmx(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0) s_red[warp] = mx;
+  __syncthreads();
+  if (tid == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t = nmx(t, s_red[w]);
+    s_mx = t;
+  }
+  __syncthreads();
+  const double cut = xmul(1e-6, s_mx);
+  const int64_t stride = int64_t(gridDim.x) * 256, first = int64_t(blockIdx.x) * 256 + tid;
+  double cnt = 0.0, rr = 0.0;
+  const double* xc = a.xcand[sel];
+  for (int c = 0; c < g.l; ++c)
+    for (int64_t j = first; j < g.n; j += stride) cnt += fabs(xc[c * g.ldn + j]) > cut ? 1.0 : 0.0;
+  const double* ax = a.AX[sel];
+  for (int c = 0; c < g.l; ++c)
+    for (int64_t i = first; i < g.m; i += stride) {
+      const double d = ax[c * g.ldm + i] - a.b[c * g.ldm + i];
+      rr += d * d;
+    }
+  cnt = warp_sum(cnt); rr = warp_sum(rr);
+  __syncthreads();
+  if (lane == 0) s_red[warp] = rr;
+  __syncthreads();
+  double rr_tot = 0.0;
+  if (tid == 0) for (int w = 0; w < 8; ++w) rr_tot += s_red[w];
+  __syncthreads();
+  if (lane == 0) s_red[warp] = cnt;
+  __syncthreads();
+  if (tid == 0) {
+    double c_tot = 0.0;
+    for (int w = 0; w < 8; ++w) c_tot += s_red[w];
+    a.rr_out[blockIdx.x] = rr_tot;
+    a.cnt_out[blockIdx.x] = c_tot;
+  }
+}
+
+}  // namespace glp

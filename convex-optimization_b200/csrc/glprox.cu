@@ -16,6 +16,7 @@
 #include "glp_comm.cuh"
 #include "glp_decide.cuh"
 #include "glp_fwd.cuh"
+#include "glp_gemm.cuh"
 #include "glp_misc.cuh"
 #include "glp_persist.cuh"
 #include "glp_tpass.cuh"
@@ -135,6 +136,12 @@ struct glp_handle {
   int gather_grid = 0;
   const Ctrl* cur_ctrl = nullptr;  // control block the launches of the current slot read
   int backend_used = GLP_BACKEND_STREAM;
+  // wide multi-RHS mode (K5, glp_gemm.cuh): resident TF32 hi/lo splits of A and A^T
+  int tensor_mode = 0;             // 0 auto (3xTF32 when eligible), 1 off, 2 plain TF32
+  float *A_hi = nullptr, *A_lo = nullptr, *At_hi = nullptr, *At_lo = nullptr;
+  float *xop_lo = nullptr, *r_lo = nullptr;
+  double* cnt_g = nullptr;
+  int64_t n_gemm = 0;              // tensor-core launches of the current solve
 
   // step-level scratch (lazily sized)
   void* scratch = nullptr;
@@ -346,6 +353,13 @@ extern "C" int glp_destroy(glp_handle* h) {
   for (int r = 0; r < MAX_WORLD; ++r)
     if (h->ipc_mapped[r]) cudaIpcCloseMemHandle(h->ipc_mapped[r]);
   if (h->mailbox) cudaFree(h->mailbox);
+  if (h->A_hi) cudaFree(h->A_hi);
+  if (h->A_lo) cudaFree(h->A_lo);
+  if (h->At_hi) cudaFree(h->At_hi);
+  if (h->At_lo) cudaFree(h->At_lo);
+  if (h->xop_lo) cudaFree(h->xop_lo);
+  if (h->r_lo) cudaFree(h->r_lo);
+  if (h->cnt_g) cudaFree(h->cnt_g);
   if (h->arena) cudaFree(h->arena);
   if (h->scratch) cudaFree(h->scratch);
   if (h->f_hist) cudaFree(h->f_hist);
@@ -468,6 +482,101 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
 static int esize(const glp_handle* h) { return h->dtype == GLP_F32 ? 4 : 8; }
 
 static bool multi(const glp_handle* h) { return h->comm.world > 1; }
+
+// ---- wide multi-RHS mode: both products of an iteration run on the tensor cores (K5) ---------------
+static bool wide_active(const glp_handle* h) {
+  return h->dtype == GLP_F32 && h->g.l >= 16 && 2 * h->g.l <= 256 && !multi(h) && h->tensor_mode != 1;
+}
+static int wide_passes(const glp_handle* h) { return h->tensor_mode == 2 ? 1 : 3; }
+constexpr int WIDE_K_CHUNK = 8;  // the tensor core's fp32 accumulator spans 8 x 32 = 256 elements of K, then fp64
+
+static int split_f32(cudaStream_t st, const float* src, int64_t rows, int64_t cols, int64_t ld_src, float* hi, float* lo,
+                     int64_t ld_dst, bool transpose) {
+  if (transpose) {
+    dim3 grid(unsigned((cols + 31) / 32), unsigned((rows + 31) / 32));
+    if (grid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
+    glp_transpose_split_kernel<<<grid, dim3(32, 8), 0, st>>>(src, hi, lo, rows, cols, ld_src, ld_dst);
+  } else {
+    const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
+    glp_split_tf32_kernel<<<grid, 256, 0, st>>>(src, hi, lo, rows, cols, ld_src, ld_dst);
+  }
+  CU_TRY(cudaGetLastError());
+  return GLP_OK;
+}
+
+// One-time set-up: A = A_hi + A_lo and A^T = At_hi + At_lo resident in HBM (4 x |A|; "memory laid out for
+// 180 GB"), plus the lo halves of the two small operands.
+static int ensure_wide(glp_handle* h) {
+  if (h->A_hi != nullptr) return GLP_OK;
+  const Geom& g = h->g;
+  const size_t a_bytes = size_t(g.m) * g.ldn * 4, at_bytes = size_t(g.n) * g.ldm * 4;
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->A_hi), a_bytes));
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->A_lo), a_bytes));
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->At_hi), at_bytes));
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->At_lo), at_bytes));
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->xop_lo), size_t(2) * g.l * g.ldn * 4));
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->r_lo), size_t(g.l) * g.ldm * 4));
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->cnt_g), size_t(h->gather_grid) * 8));
+  CU_TRY(cudaMemsetAsync(h->A_hi, 0, a_bytes, h->stream));
+  CU_TRY(cudaMemsetAsync(h->A_lo, 0, a_bytes, h->stream));
+  CU_TRY(cudaMemsetAsync(h->At_hi, 0, at_bytes, h->stream));
+  CU_TRY(cudaMemsetAsync(h->At_lo, 0, at_bytes, h->stream));
+  CU_TRY(cudaMemsetAsync(h->xop_lo, 0, size_t(2) * g.l * g.ldn * 4, h->stream));
+  CU_TRY(cudaMemsetAsync(h->r_lo, 0, size_t(g.l) * g.ldm * 4, h->stream));
+  const float* A = static_cast<const float*>(h->A);
+  GLP_TRY(split_f32(h->stream, A, g.m, g.n, h->lda, h->A_hi, h->A_lo, g.ldn, false));
+  GLP_TRY(split_f32(h->stream, A, g.m, g.n, h->lda, h->At_hi, h->At_lo, g.ldm, true));
+  return GLP_OK;
+}
+
+static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
+                        const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
+                        int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl = nullptr, double* D_alt = nullptr,
+                        int role = 0);
+
+// forward product of the solver on the tensor cores: AX[1-cur] = A . [xn | xnt], then ||r||^2 and the count
+static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
+  const Geom& g = h->g;
+  float* xop = static_cast<float*>(h->xop);
+  GLP_TRY(split_f32(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_lo, g.ldn, false));  // hi in place
+  for (int c0 = 0; c0 < 2 * g.l; c0 += 128) {  // up to 128 operand columns per launch
+    const int nc = std::min(128, 2 * g.l - c0);
+    prof_mark(h, 0, 0);
+    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, nc, h->A_hi, h->A_lo, g.ldn,
+                         xop + int64_t(c0) * g.ldn, h->xop_lo + int64_t(c0) * g.ldn, g.ldn,
+                         h->AX[0] + int64_t(c0) * g.ldm, g.ldm, WIDE_K_CHUNK, h->fault, ctrl,
+                         h->AX[1] + int64_t(c0) * g.ldm, 1));
+    prof_mark(h, 0, 1);
+    h->n_launches++;
+  }
+  PostFwdArgs pa{};
+  pa.ctrl = ctrl;
+  pa.AX[0] = h->AX[0]; pa.AX[1] = h->AX[1];
+  pa.b = h->b;
+  pa.scal_partial = h->scal_partial;
+  pa.xcand[0] = h->state[0]; pa.xcand[1] = h->state[1];
+  pa.rr_out = h->rr_g;
+  pa.cnt_out = h->cnt_g;
+  glp_post_fwd_kernel<<<h->gather_grid, 256, 0, h->stream>>>(pa, g);
+  CU_TRY(cudaGetLastError());
+  h->n_launches += 2;
+  h->n_gemm++;
+  return GLP_OK;
+}
+
+// transposed product of the solver on the tensor cores: grad = A^T . r  (skipped by the kernel on a retry)
+static int enqueue_wide_tpass(glp_handle* h, const Ctrl* ctrl) {
+  const Geom& g = h->g;
+  float* r = static_cast<float*>(h->r);
+  GLP_TRY(split_f32(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_lo, g.ldm, false));
+  prof_mark(h, 1, 0);
+  GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.n, g.m, g.l, h->At_hi, h->At_lo, g.ldm, r, h->r_lo,
+                       g.ldm, h->grad, g.ldn, WIDE_K_CHUNK, h->fault, ctrl, nullptr, 2));
+  prof_mark(h, 1, 1);
+  h->n_launches += 2;
+  h->n_gemm++;
+  return GLP_OK;
+}
 static uint64_t seq_base(const glp_handle* h) { return h->epoch << 32; }
 
 // Forward stream over `ncols` operand columns.  Xb[s] / AXb[s]: planar operand / output bases.
@@ -554,6 +663,7 @@ static ProxArgs solver_prox_args(glp_handle* h, const Ctrl* ctrl) {
 }
 
 static int enqueue_solver_fwd(glp_handle* h, const Ctrl* ctrl) {
+  if (wide_active(h)) return enqueue_wide_fwd(h, ctrl);
   const void* Xb[2];
   const double* xc[2] = {h->state[0], h->state[1]};
   for (int s = 0; s < 2; ++s) Xb[s] = h->dtype == GLP_F32 ? h->xop : static_cast<const void*>(h->state[s]);
@@ -608,6 +718,8 @@ static int phase_prepare(glp_handle* h, int algo, const void* x0_dev, double mu0
   }
   h->f_hist_best = h->f_hist + h->hist_cap;
   h->n_launches = 0;
+  h->n_gemm = 0;
+  if (wide_active(h)) GLP_TRY(ensure_wide(h));
   h->epoch++;
   h->idx_f = h->idx_t = 0;
   h->group = 0;
@@ -666,6 +778,10 @@ static int phase_decide(glp_handle* h) {
     d.rr_partial = h->rr_g; d.n_rr = h->gather_grid;
     d.scal_partial = h->scal_red; d.n_scal = 1;
     d.cnt_partial = h->cnt_red; d.n_cnt = 1;
+  } else if (wide_active(h)) {
+    d.rr_partial = h->rr_g; d.n_rr = h->gather_grid;
+    d.scal_partial = h->scal_partial; d.n_scal = h->g.ncb;
+    d.cnt_partial = h->cnt_g; d.n_cnt = h->gather_grid;
   } else {
     d.rr_partial = h->rr_partial; d.n_rr = h->n_fchunks * h->g.nrb;
     d.scal_partial = h->scal_partial; d.n_scal = h->g.ncb;
@@ -683,6 +799,11 @@ static int phase_decide(glp_handle* h) {
 static int phase_tpass(glp_handle* h) {
   h->group++;
   ProxArgs p = solver_prox_args(h, h->cur_ctrl);
+  if (wide_active(h)) {
+    GLP_TRY(enqueue_wide_tpass(h, h->cur_ctrl));
+    CU_TRY(launch_prox(h, p, 0));
+    return GLP_OK;
+  }
   return enqueue_tpass(h, h->cur_ctrl, &p, h->grad, true);
 }
 static int phase_fwd(glp_handle* h) { return enqueue_solver_fwd(h, h->cur_ctrl); }
@@ -1111,6 +1232,14 @@ extern "C" int glp_tpass_prox(glp_handle* h, const glp_step_params* sp, const do
   return GLP_OK;
 }
 
+extern "C" int glp_set_tensor_mode(glp_handle* h, int mode) {
+  if (h == nullptr) return fail(GLP_ERR_ARG, "null handle");
+  if (mode < 0 || mode > 2) return fail(GLP_ERR_ARG, "tensor mode must be 0 (auto: 3xTF32), 1 (off) or 2 (plain TF32)");
+  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
+  h->tensor_mode = mode;
+  return GLP_OK;
+}
+
 extern "C" int glp_set_profiling(glp_handle* h, int on) {
   if (h == nullptr) return fail(GLP_ERR_ARG, "null handle");
   h->profiling = on != 0;
@@ -1281,6 +1410,110 @@ extern "C" int glp_solve_host(int device, int algo, int dtype, int m, int n, int
 #undef HOST_TRY
   cleanup();
   return rc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5: tensor-core products (glp_gemm.cuh)
+// ------------------------------------------------------------------------------------------------
+static int make_map_f32_k128(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t stride_bytes,
+                             uint32_t box_outer) {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  CU_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  if (fn == nullptr || qres != cudaDriverEntryPointSuccess)
+    return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  const cuuint64_t dims[2] = {inner, outer};
+  const cuuint64_t strides[1] = {stride_bytes};
+  const cuuint32_t box[2] = {cuuint32_t(GEMM_BK), box_outer};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = reinterpret_cast<PFN_encodeTiled>(fn)(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims,
+                                                     strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled (gemm operand) failed with CUresult %d", int(r));
+  return GLP_OK;
+}
+
+template <int NT, int PASSES>
+static cudaError_t launch_gemm_t(cudaStream_t st, int grid, const CUtensorMap& ph, const CUtensorMap& pl,
+                                 const CUtensorMap& qh, const CUtensorMap& ql, const GemmArgs& a) {
+  auto kfn = glp_gemm_tf32_kernel<NT, PASSES>;
+  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes<NT, PASSES>());
+  if (e != cudaSuccess) return e;
+  kfn<<<grid, GEMM_THREADS, gemm_smem_bytes<NT, PASSES>(), st>>>(ph, pl, qh, ql, a);
+  return cudaGetLastError();
+}
+
+// D[N][ldd] = P[M x K] . Q[N x K]^T ; passes 1 (TF32) or 3 (hi/lo compensated)
+static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
+                        const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
+                        int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl, double* D_alt, int role) {
+  if (N < 1 || N > 128) return fail(GLP_ERR_ARG, "gemm: N must be 1..128 per launch (got %d)", N);
+  if (passes != 1 && passes != 3) return fail(GLP_ERR_ARG, "gemm: passes must be 1 or 3");
+  if ((ldp * 4) % 16 || (ldq * 4) % 16 || (reinterpret_cast<uintptr_t>(Ph) % 16) || (reinterpret_cast<uintptr_t>(Qh) % 16))
+    return fail(GLP_ERR_ARG, "gemm: operands must be 16-byte aligned with 16-byte aligned pitches");
+  const int NT = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
+  CUtensorMap mph, mpl, mqh, mql;
+  GLP_TRY(make_map_f32_k128(&mph, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, GEMM_BM));
+  GLP_TRY(make_map_f32_k128(&mqh, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, uint32_t(NT)));
+  if (passes == 3) {
+    if (Pl == nullptr || Ql == nullptr) return fail(GLP_ERR_ARG, "gemm: passes = 3 needs the lo operands");
+    GLP_TRY(make_map_f32_k128(&mpl, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, GEMM_BM));
+    GLP_TRY(make_map_f32_k128(&mql, Ql, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, uint32_t(NT)));
+  } else {
+    mpl = mph; mql = mqh;
+  }
+  GemmArgs a{};
+  a.M = M; a.K = K; a.N = N; a.k_chunk_blocks = k_chunk; a.D = D; a.ldd = ldd; a.fault = fault;
+  a.ctrl = ctrl; a.D_alt = D_alt; a.role = role;
+  const int64_t tiles = (M + GEMM_BM - 1) / GEMM_BM;
+  const int grid = int(std::min<int64_t>(num_sms, tiles));
+  cudaError_t e;
+  if (passes == 1) e = NT == 32 ? launch_gemm_t<32, 1>(st, grid, mph, mpl, mqh, mql, a)
+                   : NT == 64 ? launch_gemm_t<64, 1>(st, grid, mph, mpl, mqh, mql, a)
+                              : launch_gemm_t<128, 1>(st, grid, mph, mpl, mqh, mql, a);
+  else e = NT == 32 ? launch_gemm_t<32, 3>(st, grid, mph, mpl, mqh, mql, a)
+         : NT == 64 ? launch_gemm_t<64, 3>(st, grid, mph, mpl, mqh, mql, a)
+                    : launch_gemm_t<128, 3>(st, grid, mph, mpl, mqh, mql, a);
+  if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "gemm launch failed: %s", cudaGetErrorString(e));
+  return GLP_OK;
+}
+
+extern "C" int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, int64_t K, int N, const void* P_hi,
+                             const void* P_lo, int64_t ldp, const void* Q_hi, const void* Q_lo, int64_t ldq,
+                             double* D_dev, int64_t ldd, int k_chunk_blocks) {
+  if (P_hi == nullptr || Q_hi == nullptr || D_dev == nullptr || M < 1 || K < 1) return fail(GLP_ERR_ARG, "bad argument");
+  int sms = 0;
+  GLP_TRY(check_device(device, &sms));
+  CU_TRY(cudaSetDevice(device));
+  if (N < 1 || N > 256) return fail(GLP_ERR_ARG, "gemm: N must be 1..256 (got %d)", N);
+  for (int c0 = 0; c0 < N; c0 += 128) {  // the kernel takes up to 128 columns per launch
+    const int nc = std::min(128, N - c0);
+    const float* qh = static_cast<const float*>(Q_hi) + int64_t(c0) * ldq;
+    const float* ql = Q_lo ? static_cast<const float*>(Q_lo) + int64_t(c0) * ldq : nullptr;
+    GLP_TRY(gemm_enqueue(static_cast<cudaStream_t>(stream), sms, passes, M, K, nc, static_cast<const float*>(P_hi),
+                         static_cast<const float*>(P_lo), ldp, qh, ql, ldq, D_dev + int64_t(c0) * ldd, ldd,
+                         k_chunk_blocks, nullptr, nullptr, nullptr, 0));
+  }
+  return GLP_OK;
+}
+
+extern "C" int glp_tf32_split(void* stream, const void* src, int64_t rows, int64_t cols, int64_t ld_src, void* hi,
+                              void* lo, int64_t ld_dst, int transpose) {
+  if (src == nullptr || hi == nullptr || lo == nullptr || rows < 1 || cols < 1) return fail(GLP_ERR_ARG, "bad argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (transpose) {
+    dim3 grid(unsigned((cols + 31) / 32), unsigned((rows + 31) / 32));
+    if (grid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
+    glp_transpose_split_kernel<<<grid, dim3(32, 8), 0, st>>>(static_cast<const float*>(src), static_cast<float*>(hi),
+                                                             static_cast<float*>(lo), rows, cols, ld_src, ld_dst);
+  } else {
+    const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
+    glp_split_tf32_kernel<<<grid, 256, 0, st>>>(static_cast<const float*>(src), static_cast<float*>(hi),
+                                                static_cast<float*>(lo), rows, cols, ld_src, ld_dst);
+  }
+  CU_TRY(cudaGetLastError());
+  return GLP_OK;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -75,6 +75,9 @@ SIGNATURES = {
     "glp_comm_attach": (_I, [_VP, _I, _I, _I64, _VP, _I]),
     "glp_group_solve": (_I, [C.POINTER(_VP), _I, _I, C.POINTER(_VP), _D, C.POINTER(GlpOpts), C.POINTER(_VP),
                              C.POINTER(GlpResult), _VP, _I]),
+    "glp_gemm_tf32": (_I, [_I, _VP, _I, _I64, _I64, _I, _VP, _VP, _I64, _VP, _VP, _I64, _VP, _I64, _I]),
+    "glp_set_tensor_mode": (_I, [_VP, _I]),
+    "glp_tf32_split": (_I, [_VP, _VP, _I64, _I64, _I64, _VP, _VP, _I64, _I]),
     "glp_nccl_unique_id": (_I, [_VP]),
     "glp_nccl_comm_create": (_I, [C.POINTER(_VP), _VP, _I, _I, _I]),
     "glp_nccl_comm_destroy": (_I, [_VP]),

@@ -26,7 +26,8 @@ DEFAULT_OPTS = {
 }
 ALGO_ID = {"ProxGD": _lib.GLP_PROXGD, "FProxGD": _lib.GLP_FPROXGD}
 # additive keys (not in the reference): dtype 'fp32'|'fp64', backend 'auto'|'stream'|'persistent',
-# device (int), poll_interval (int)
+# device (int), poll_interval (int), dist (bool), tensor_cores 'auto'|'off'|'tf32'|'3xtf32' (wide l >= 16 mode)
+TENSOR_MODES = {"auto": 0, "3xtf32": 0, "off": 1, "tf32": 2}
 
 
 def merge_opts(algo, opts):
@@ -123,8 +124,18 @@ def solve(algo, x0, A, b, mu_0, opts):
         is_torch = False
     if is_torch:
         return _solve_torch(algo, x0, A, b, mu_0, merged, o)
+    if merged.get("tensor_cores", "auto") not in TENSOR_MODES:
+        raise ValueError("opts['tensor_cores'] must be one of %s" % sorted(TENSOR_MODES))
     if merged.get("dist"):
         return _solve_numpy_sharded(algo, x0, A, b, mu_0, merged, o)
+    if TENSOR_MODES[merged.get("tensor_cores", "auto")] != 0:
+        # the one-shot host entry point always uses the default tensor mode; explicit modes go through a handle
+        import torch
+        dt = _mode_dtype(np.asarray(A).dtype, merged)
+        dev = torch.device("cuda", int(merged.get("device", 0)))
+        to = lambda z: torch.from_numpy(np.ascontiguousarray(z, dtype=dt)).to(dev)
+        x, k, out = _solve_torch(algo, to(x0), to(A), to(b), mu_0, merged, o)
+        return x.cpu().numpy(), k, out
     return _solve_numpy(algo, x0, A, b, mu_0, merged, o)
 
 
@@ -276,6 +287,7 @@ class GroupLassoProblem:
         res = _lib.GlpResult()
         t0 = time.perf_counter()
         with torch.cuda.device(self.device):
+            _lib.check(lib.glp_set_tensor_mode(self._h, TENSOR_MODES[merged.get("tensor_cores", "auto")]))
             rc = lib.glp_solve(self._h, ALGO_ID[algo], x0d.data_ptr(), float(mu_0), C.byref(o), x.data_ptr(),
                                C.byref(res), f_hist.ctypes.data, cap)
         _raise_for(rc)

@@ -193,6 +193,24 @@ int glp_nccl_unique_id(void* id128 /* 128 bytes out */);
 int glp_nccl_comm_create(void** comm_out, const void* id128, int rank, int world, int device);
 int glp_nccl_comm_destroy(void* comm);
 
+/* ---- K5: tensor-core products of the wide multi-RHS mode (tcgen05 / TMEM, kind::tf32) -------------
+ * D[N][ldd] (fp64, planar) = P[M x K] . Q[N x K]^T with P row-major (pitch ldp) and Q planar (pitch ldq),
+ * both fp32 device arrays, N <= 256.  Batched form of `A @ x` / `A.T @ r` (gl_*_primal.py:25,61,129 / :63,66)
+ * for l >= 16 right-hand sides.  passes = 1: plain TF32 operands; passes = 3: error-compensated
+ * Ph.Qh + Ph.Ql + Pl.Qh with the hi/lo splits of glp_tf32_split (fp32-class accuracy).
+ * k_chunk_blocks > 0: flush the fp32 accumulator to fp64 every k_chunk_blocks*32 elements of K. */
+int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, int64_t K, int N, const void* P_hi,
+                  const void* P_lo, int64_t ldp, const void* Q_hi, const void* Q_lo, int64_t ldq,
+                  double* D_dev, int64_t ldd, int k_chunk_blocks);
+/* Wide multi-RHS mode of the solvers (fp32 data, 16 <= l <= 128, single GPU): both products of an
+ * iteration run on glp_gemm_tf32 with A and A^T resident as TF32 hi/lo splits (4 x |A| of HBM).
+ * mode 0 (default): on, error-compensated 3xTF32;  1: off (CUDA-core streams);  2: on, plain TF32. */
+int glp_set_tensor_mode(glp_handle* h, int mode);
+/* hi = src rounded to TF32 (10 mantissa bits), lo = src - hi; transpose != 0 writes the transposes
+ * (hi[j][i], lo[j][i]) -- the resident A^T of the transposed pass. */
+int glp_tf32_split(void* stream, const void* src, int64_t rows, int64_t cols, int64_t ld_src, void* hi,
+                   void* lo, int64_t ld_dst, int transpose);
+
 /* ---- synthetic data: counter-based N(0,1) generator (bench / large fixtures) --------------------
  * Fills dst_dev[rows][ld] (dtype T) with value(seed, global_row, global_col) so that any
  * row/column block of the same logical matrix can be generated independently on any rank. */

@@ -1,0 +1,28 @@
+"""Timing probe of K5 at the BASELINE config-5 shapes (not a pytest file)."""
+import sys, os
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "convex-optimization_b200"))
+import torch
+from glprox import _lib
+lib = _lib.load()
+st = torch.cuda.current_stream().cuda_stream
+def run(M, K, N, passes, chunk, reps=5):
+    P = torch.randn((M, K), device="cuda"); Q = torch.randn((N, K), device="cuda")
+    Pl = torch.randn((M, K), device="cuda") * 1e-4 if passes == 3 else P
+    Ql = torch.randn((N, K), device="cuda") * 1e-4 if passes == 3 else Q
+    D = torch.empty((N, M), device="cuda", dtype=torch.float64)
+    def go():
+        _lib.check(lib.glp_gemm_tf32(0, st, passes, M, K, N, P.data_ptr(), Pl.data_ptr(), K, Q.data_ptr(), Ql.data_ptr(), K, D.data_ptr(), M, chunk))
+    go(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps): go()
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    flops = 2.0 * M * K * N * passes
+    byts = M * K * 4.0 * (2 if passes == 3 else 1)
+    print("M=%d K=%d N=%d passes=%d chunk=%d: %.3f ms  %.1f TFLOP/s (tensor work)  %.0f GB/s (P stream)" % (M, K, N, passes, chunk, ms, flops / ms / 1e9, byts / ms / 1e6), flush=True)
+for (M, K, N) in [(16384, 65536, 256), (65536, 16384, 128)]:
+    for passes in (1, 3):
+        for chunk in (0, 8, 32):
+            run(M, K, N, passes, chunk)

@@ -1,0 +1,79 @@
+"""GPU parity tests of K5, the tcgen05/TMEM product kernel of the wide multi-RHS mode, through the C ABI
+(glp_gemm_tf32 / glp_tf32_split).  Reference: fp64 torch matmul (the torch fp32 reference named in the
+task is replaced by fp64 here because the compensated mode is *more* accurate than an fp32 GEMM)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _tf32_trunc(t):
+    import torch
+    return (t.view(torch.int32) & -8192).view(torch.float32)
+
+
+def _run(M, K, N, passes, k_chunk=0, seed=0):
+    import torch
+    from glprox import _lib
+    lib = _lib.load()
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    ldp = (K + 3) // 4 * 4
+    P = torch.randn((M, ldp), generator=g, device="cuda", dtype=torch.float32)[:, :K]
+    Q = torch.randn((N, ldp), generator=g, device="cuda", dtype=torch.float32)[:, :K]
+    Ph, Pl = torch.zeros((M, ldp), device="cuda"), torch.zeros((M, ldp), device="cuda")
+    Qh, Ql = torch.zeros((N, ldp), device="cuda"), torch.zeros((N, ldp), device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.check(lib.glp_tf32_split(st, P.data_ptr(), M, K, ldp, Ph.data_ptr(), Pl.data_ptr(), ldp, 0))
+    _lib.check(lib.glp_tf32_split(st, Q.data_ptr(), N, K, ldp, Qh.data_ptr(), Ql.data_ptr(), ldp, 0))
+    ldd = (M + 7) // 8 * 8
+    D = torch.full((N, ldd), float("nan"), device="cuda", dtype=torch.float64)
+    _lib.check(lib.glp_gemm_tf32(0, st, passes, M, K, N, Ph.data_ptr(), Pl.data_ptr(), ldp, Qh.data_ptr(), Ql.data_ptr(),
+                                 ldp, D.data_ptr(), ldd, k_chunk))
+    torch.cuda.synchronize()
+    return P, Q, Ph, Pl, Qh, Ql, D[:, :M].t()
+
+
+def test_split_is_exact_and_hi_is_tf32():
+    import torch
+    P, Q, Ph, Pl, Qh, Ql, D = _run(128, 64, 16, 1)
+    assert torch.equal(Ph[:, :64] + Pl[:, :64], P)                      # a = hi + lo exactly
+    assert torch.equal(_tf32_trunc(Ph), Ph)                             # hi has 10 mantissa bits
+    assert (Pl[:, :64].abs() <= P.abs() * 2.0 ** -11 + 1e-45).all()    # round to nearest
+
+
+@pytest.mark.parametrize("shape", [(128, 32, 16), (128, 256, 64), (256, 1000, 128), (300, 4096, 256), (1000, 333, 200),
+                                   (4096, 2048, 256), (70, 40, 4)])
+def test_plain_tf32_matches_product_of_rounded_operands(shape):
+    M, K, N = shape
+    P, Q, Ph, Pl, Qh, Ql, D = _run(M, K, N, 1)
+    ref = Ph[:, :K].double() @ Qh[:, :K].double().t()                   # what the tensor core is asked to compute
+    scale = Ph[:, :K].double().abs() @ Qh[:, :K].double().abs().t() + 1e-300
+    assert ((D - ref).abs() / scale).max().item() <= 2e-6               # fp32 accumulation error only
+    full = P.double() @ Q.double().t()
+    assert ((D - full).abs() / scale).max().item() <= 2e-3              # TF32 operand rounding
+
+
+@pytest.mark.parametrize("k_chunk", [0, 8])
+@pytest.mark.parametrize("shape", [(128, 256, 64), (300, 4096, 256), (1000, 333, 200), (2048, 8192, 128)])
+def test_compensated_3xtf32_reaches_fp32_class_accuracy(shape, k_chunk):
+    M, K, N = shape
+    P, Q, Ph, Pl, Qh, Ql, D = _run(M, K, N, 3, k_chunk)
+    full = P.double() @ Q.double().t()
+    scale = P.double().abs() @ Q.double().abs().t() + 1e-300
+    err = ((D - full).abs() / scale).max().item()
+    assert err <= (5e-7 if k_chunk else 2e-5), err   # unchunked: the tensor core's fp32 accumulation spans all of K
+
+
+def test_transposing_split():
+    import torch
+    from glprox import _lib
+    lib = _lib.load()
+    A = torch.randn((193, 391), device="cuda")
+    hi, lo = torch.zeros((391, 200), device="cuda"), torch.zeros((391, 200), device="cuda")
+    _lib.check(lib.glp_tf32_split(torch.cuda.current_stream().cuda_stream, A.data_ptr(), 193, 391, 391, hi.data_ptr(),
+                                  lo.data_ptr(), 200, 1))
+    torch.cuda.synchronize()
+    assert torch.equal(hi[:, :193] + lo[:, :193], A.t())
+    assert torch.equal(_tf32_trunc(hi), hi)
