@@ -71,25 +71,27 @@ __global__ void glp_epoch_wait_kernel(const Comm c, const unsigned long long epo
 }
 
 // ---- scalar post: called by one full warp of the last CTA of a prox-producing launch ------------
-// scal_partial[ncb][4] = {gd, dd, reg, max}: lane-strided fixed-order sums, then one 32-byte record
+// scal_partial[ncb][SCAL_STRIDE] = {gd, dd, reg, max, sx, sy}: lane-strided fixed-order sums, then one record
 // per peer and the flag.
 __device__ __forceinline__ double comm_nmax(double a, double b) {
   return (a != a) ? a : ((b != b) ? b : fmax(a, b));
 }
 __device__ __forceinline__ void post_prox_scalars(const ProxPost& P, const double* scal_partial, int ncb, int lane) {
-  double gd = 0.0, dd = 0.0, reg = 0.0, mx = 0.0;
+  double gd = 0.0, dd = 0.0, reg = 0.0, mx = 0.0, sx = 0.0, sy = 0.0;
   for (int i = lane; i < ncb; i += 32) {
-    gd += __ldcg(&scal_partial[4 * i + 0]);
-    dd += __ldcg(&scal_partial[4 * i + 1]);
-    reg += __ldcg(&scal_partial[4 * i + 2]);
-    mx = comm_nmax(mx, __ldcg(&scal_partial[4 * i + 3]));
+    gd += __ldcg(&scal_partial[SCAL_STRIDE * i + 0]);
+    dd += __ldcg(&scal_partial[SCAL_STRIDE * i + 1]);
+    reg += __ldcg(&scal_partial[SCAL_STRIDE * i + 2]);
+    mx = comm_nmax(mx, __ldcg(&scal_partial[SCAL_STRIDE * i + 3]));
+    sx += __ldcg(&scal_partial[SCAL_STRIDE * i + 4]);
+    sy += __ldcg(&scal_partial[SCAL_STRIDE * i + 5]);
   }
-  gd = warp_sum(gd); dd = warp_sum(dd); reg = warp_sum(reg);
+  gd = warp_sum(gd); dd = warp_sum(dd); reg = warp_sum(reg); sx = warp_sum(sx); sy = warp_sum(sy);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = comm_nmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   if (lane < P.comm.world) {
     double* dst = mail_sc(P.comm, lane, P.par, P.comm.rank);
-    dst[0] = mx; dst[1] = gd; dst[2] = dd; dst[3] = reg;
+    dst[0] = mx; dst[1] = gd; dst[2] = dd; dst[3] = reg; dst[5] = sx; dst[6] = sy;
     __threadfence_system();
     st_release_sys(mail_flag(P.comm, lane, MAIL_FLAG_SC, P.comm.rank), P.seq_t);
   }
@@ -122,7 +124,7 @@ struct GatherArgs {
   double* AX[2];               // [2l][ldm]
   const double* b;             // [l][ldm]
   double* rr_partial;          // [gridDim]
-  double* scal_red;            // [4] = {gd, dd, reg, max}
+  double* scal_red;            // [SCAL_STRIDE] = {gd, dd, reg, max, sx, sy}
   double* cnt_red;             // [1]
   int32_t* fault;
 };
@@ -160,13 +162,15 @@ glp_gather_kernel(const GatherArgs a, const Geom g) {
     for (int w = 0; w < GATHER_THREADS / 32; ++w) tot += s_red[w];
     a.rr_partial[blockIdx.x] = tot;
     if (blockIdx.x == 0) {
-      double mx = 0.0, gd = 0.0, dd = 0.0, reg = 0.0, cnt = 0.0;
+      double mx = 0.0, gd = 0.0, dd = 0.0, reg = 0.0, cnt = 0.0, sx = 0.0, sy = 0.0;
       for (int r = 0; r < W; ++r) {
         const double* sc = mail_sc(a.comm, me, a.par, r);
         mx = comm_nmax(mx, ld_mail(sc + 0));
         gd += ld_mail(sc + 1); dd += ld_mail(sc + 2); reg += ld_mail(sc + 3); cnt += ld_mail(sc + 4);
+        sx += ld_mail(sc + 5); sy += ld_mail(sc + 6);
       }
       a.scal_red[0] = gd; a.scal_red[1] = dd; a.scal_red[2] = reg; a.scal_red[3] = mx;
+      a.scal_red[4] = sx; a.scal_red[5] = sy;
       a.cnt_red[0] = cnt;
     }
   }

@@ -19,7 +19,7 @@ struct DecideArgs {
   Ctrl* cout;
   SolveConst sc;
   const double* rr_partial;   int32_t n_rr;
-  const double* scal_partial; int32_t n_scal;   // [n_scal][4]
+  const double* scal_partial; int32_t n_scal;   // [n_scal][SCAL_STRIDE]
   const double* cnt_partial;  int32_t n_cnt;
   double* gy_partial[2];      int32_t n_gy;     // [gridDim] each
   double* AX[2];              // [2l][ldm] : {A x | A xt} of the two state buffers
@@ -40,7 +40,7 @@ __device__ __forceinline__ double dec_nmax(double a, double b) {
 template <typename T>
 __global__ void __launch_bounds__(DECIDE_THREADS)
 glp_decide_kernel(const DecideArgs a, const Geom g) {
-  __shared__ double s_part[DECIDE_THREADS / 32][6];
+  __shared__ double s_part[DECIDE_THREADS / 32][8];
   __shared__ Ctrl s_out;
   __shared__ DecideOut s_act;
   __shared__ double s_gy[DECIDE_THREADS / 32];
@@ -53,30 +53,35 @@ glp_decide_kernel(const DecideArgs a, const Geom g) {
   }
 
   // ---- (a) fixed-order reductions: strided per thread, shuffle tree per warp, warps in order
-  double v_rr = 0.0, v_gd = 0.0, v_dd = 0.0, v_reg = 0.0, v_cnt = 0.0, v_gy = 0.0;
+  double v_rr = 0.0, v_gd = 0.0, v_dd = 0.0, v_reg = 0.0, v_cnt = 0.0, v_gy = 0.0, v_sx = 0.0, v_sy = 0.0;
   for (int i = tid; i < a.n_rr; i += DECIDE_THREADS) v_rr += __ldcg(&a.rr_partial[i]);
   for (int i = tid; i < a.n_scal; i += DECIDE_THREADS) {
-    v_gd += __ldcg(&a.scal_partial[4 * i + 0]);
-    v_dd += __ldcg(&a.scal_partial[4 * i + 1]);
-    v_reg += __ldcg(&a.scal_partial[4 * i + 2]);
+    v_gd += __ldcg(&a.scal_partial[SCAL_STRIDE * i + 0]);
+    v_dd += __ldcg(&a.scal_partial[SCAL_STRIDE * i + 1]);
+    v_reg += __ldcg(&a.scal_partial[SCAL_STRIDE * i + 2]);
+    v_sx += __ldcg(&a.scal_partial[SCAL_STRIDE * i + 4]);
+    v_sy += __ldcg(&a.scal_partial[SCAL_STRIDE * i + 5]);
   }
   for (int i = tid; i < a.n_cnt; i += DECIDE_THREADS) v_cnt += __ldcg(&a.cnt_partial[i]);
   const double* gy_in = a.gy_partial[cin.gy_sel];
   for (int i = tid; i < a.n_gy; i += DECIDE_THREADS) v_gy += __ldcg(&gy_in[i]);
   v_rr = warp_sum(v_rr); v_gd = warp_sum(v_gd); v_dd = warp_sum(v_dd);
   v_reg = warp_sum(v_reg); v_cnt = warp_sum(v_cnt); v_gy = warp_sum(v_gy);
+  v_sx = warp_sum(v_sx); v_sy = warp_sum(v_sy);
   if (lane == 0) {
     s_part[warp][0] = v_rr; s_part[warp][1] = v_gd; s_part[warp][2] = v_dd;
     s_part[warp][3] = v_reg; s_part[warp][4] = v_cnt; s_part[warp][5] = v_gy;
+    s_part[warp][6] = v_sx; s_part[warp][7] = v_sy;
   }
   __syncthreads();
 
   // ---- (b) state machine (thread 0 of every CTA; identical inputs => identical decision)
   if (tid == 0) {
-    Reduced red = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    Reduced red = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     for (int w = 0; w < DECIDE_THREADS / 32; ++w) {
       red.rr += s_part[w][0]; red.gd += s_part[w][1]; red.dd += s_part[w][2];
       red.reg += s_part[w][3]; red.cnt += s_part[w][4]; red.gbase += s_part[w][5];
+      red.sx += s_part[w][6]; red.sy += s_part[w][7];
     }
     const bool writer = blockIdx.x == 0;
     decide_step(a.sc, cin, red, double(g.n_total) * double(g.l), s_out, s_act,
@@ -89,7 +94,7 @@ glp_decide_kernel(const DecideArgs a, const Geom g) {
 
   // ---- (c) vector work of the commit, sliced over the grid
   const int nc = s_act.new_cur;
-  const bool accel = a.sc.algo == 1;
+  const bool accel = a.sc.algo == ALGO_FPROXGD || a.sc.algo == ALGO_FGD;
   const double th_old = s_act.theta_old, th = s_out.theta, omt = xsub(1.0, th);
   const int64_t lenm = int64_t(g.l) * g.ldm, lenn = int64_t(g.l) * g.ldn;
   const double* Axn = a.AX[nc];

@@ -43,6 +43,8 @@ struct Reduced {
   double reg;   // sum_i ||xn_i||_2
   double cnt;   // #{ |xn| > 1e-6 * max|xn| }
   double gbase; // sum(r^2) at the base point of the running iteration (from the previous decide)
+  double sx;    // FGD: sum_i sqrt(||xn_i||^2 + delta^2) - delta   (gl_FGD_primal.py:64-67)
+  double sy;    // FGD: the same at the base point y
 };
 
 enum DecideAction { GLP_ACT_NONE = 0, GLP_ACT_RETRY = 1, GLP_ACT_ITERATE = 2, GLP_ACT_FINISH = 3 };
@@ -75,14 +77,18 @@ GLP_HDI void decide_step(const SolveConst& sc, const Ctrl& in, const Reduced& re
   act.action = GLP_ACT_NONE; act.reset_v = 0; act.first_commit = in.first_commit;
   act.new_cur = in.cur; act.theta_old = in.theta;
   if (in.done) return;
-  const bool accel = sc.algo == 1;
+  const bool accel = sc.algo == ALGO_FPROXGD || sc.algo == ALGO_FGD;
+  const bool plain = sc.algo == ALGO_GD || sc.algo == ALGO_SGD;   // no line search, no early stage break
 
   // ---- sufficient-decrease test of the pending trial
   if (in.tested) {
     const double g_x = GLP_XMUL(0.5, red.rr);
     const double g_y = GLP_XMUL(0.5, red.gbase);
     bool ok;
-    if (accel)  // g(x) <= g(y) + <grad, x-y> + ||x-y||^2/(2t)          gl_FProxGD_primal.py:99
+    if (sc.algo == ALGO_FGD) {  // g = 0.5||A.-b||^2 + mu*smoothed regulariser      gl_FGD_primal.py:64-67,98-101
+      const double gx = GLP_XADD(g_x, GLP_XMUL(in.mu, red.sx)), gy = GLP_XADD(g_y, GLP_XMUL(in.mu, red.sy));
+      ok = gx <= GLP_XADD(GLP_XADD(gy, red.gd), GLP_XDIV(red.dd, GLP_XMUL(2.0, in.t)));
+    } else if (accel)  // g(x) <= g(y) + <grad, x-y> + ||x-y||^2/(2t)          gl_FProxGD_primal.py:99
       ok = g_x <= GLP_XADD(GLP_XADD(g_y, red.gd), GLP_XDIV(red.dd, GLP_XMUL(2.0, in.t)));
     else        // g(x - t*gt) <= g(x) - t*<grad,gt> + 0.5*t*||gt||^2    gl_ProxGD_primal.py:91-92
       ok = g_x <= GLP_XADD(GLP_XSUB(g_y, GLP_XMUL(in.t, red.gd)), GLP_XMUL(GLP_XMUL(0.5, in.t), red.dd));
@@ -119,6 +125,8 @@ GLP_HDI void decide_step(const SolveConst& sc, const Ctrl& in, const Reduced& re
     if (out.inner >= sc.maxit) {
       advance = true;
     } else {
+      // SGD records the objective with the STAGE mu (gl_SGD_primal.py:50-53,78), everything else with mu_0
+      if (sc.algo == ALGO_SGD) out.f_cur = GLP_XADD(GLP_XMUL(0.5, red.rr), GLP_XMUL(out.mu, red.reg));
       if (f_hist != nullptr && out.k < sc.hist_cap) f_hist[out.k] = out.f_cur;
       out.f_best = out.f_cur < out.f_best ? out.f_cur : out.f_best;  // min(f_best, f_now)
       if (f_hist_best != nullptr && out.k < sc.hist_cap) f_hist_best[out.k] = out.f_best;
@@ -133,7 +141,7 @@ GLP_HDI void decide_step(const SolveConst& sc, const Ctrl& in, const Reduced& re
       out.f_prev = out.f_cur;
       out.s_prev = out.s_cur;
       out.stable = stable_now ? out.stable + 1 : 0;
-      if (out.stable > sc.stable_cap) advance = true;
+      if (out.stable > sc.stable_cap && !plain) advance = true;   // GD / SGD: the break is commented out (:90-91)
     }
     if (!advance) break;
     out.stage_end[out.stage] = out.k;
@@ -150,7 +158,10 @@ GLP_HDI void decide_step(const SolveConst& sc, const Ctrl& in, const Reduced& re
   out.ran_any = 1;
   out.theta = accel ? GLP_XDIV(2.0, double(out.inner + 1)) : 1.0;
   out.trial = 0;
-  if (sc.step_type == 0) {  // line_search
+  if (plain && (sc.step_type == 1 || out.mu > sc.mu0)) {   // gl_GD_primal.py:67-70 / gl_SGD_primal.py:65-68
+    out.t = sc.alpha0;
+    out.tested = 0;
+  } else if (sc.step_type == 0) {  // line_search
     out.t = accel ? out.t_k : sc.alpha0;
     out.tested = sc.ls_cap > 0 ? 1 : 0;
   } else {

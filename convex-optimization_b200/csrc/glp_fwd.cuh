@@ -133,7 +133,7 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
         __syncwarp();
         for (int r = 0; r < a.comm.world; ++r) mx = nan_max(mx, ld_mail(mail_sc(a.comm, a.comm.rank, a.par, r)));
       } else {
-        for (int i = lane; i < g.ncb; i += 32) mx = nan_max(mx, __ldcg(&a.scal_partial[4 * i + 3]));
+        for (int i = lane; i < g.ncb; i += 32) mx = nan_max(mx, __ldcg(&a.scal_partial[SCAL_STRIDE * i + 3]));
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) mx = nan_max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
       }

@@ -325,7 +325,7 @@ struct PostFwdArgs {
   const Ctrl* ctrl;
   const double* AX[2];          // [2l][ldm]
   const double* b;              // [l][ldm]
-  const double* scal_partial;   // [ncb][4], slot 3 = max|xn| per column block
+  const double* scal_partial;   // [ncb][SCAL_STRIDE], slot 3 = max|xn| per column block
   const double* xcand[2];       // candidate x [l][ldn]
   double* rr_out;               // [gridDim]
   double* cnt_out;              // [gridDim]
@@ -339,7 +339,7 @@ glp_post_fwd_kernel(const PostFwdArgs a, const Geom g) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   auto nmx = [](double x, double y) { return (x != x) ? x : ((y != y) ? y : fmax(x, y)); };
   double mx = 0.0;
-  for (int i = tid; i < g.ncb; i += 256) mx = nmx(mx, __ldcg(&a.scal_partial[4 * i + 3]));
+  for (int i = tid; i < g.ncb; i += 256) mx = nmx(mx, __ldcg(&a.scal_partial[SCAL_STRIDE * i + 3]));
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = nmx(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   if (lane == 0) s_red[warp] = mx;

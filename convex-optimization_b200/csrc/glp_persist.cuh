@@ -113,7 +113,7 @@ glp_persist_kernel(const PersistArgs a) {
   const int m = a.m, nc = a.nc;
   const int j0 = rank * nc;
   const int nloc = max(0, min(a.n - j0, nc));
-  const bool accel = a.sc.algo == 1;
+  const bool accel = a.sc.algo == ALGO_FPROXGD || a.sc.algo == ALGO_FGD;
 
   extern __shared__ __align__(16) uint8_t smem[];
   const PersistLayout lay = persist_layout(m, nc, L, int(sizeof(T)));
@@ -129,13 +129,13 @@ glp_persist_kernel(const PersistArgs a) {
   double* xop = reinterpret_cast<double*>(smem + lay.o_xop);  // [jl*2L + q]
   double* scr = reinterpret_cast<double*>(smem + lay.o_scr);
   double* slots = reinterpret_cast<double*>(smem + lay.o_slots);  // [par*8 + {mx,gd,dd,reg,cnt}]
-  double* s_w = reinterpret_cast<double*>(smem + lay.o_misc);     // [WARPS][4] warp partials
-  int* s_cnt = reinterpret_cast<int*>(smem + lay.o_misc + 512);   // [WARPS]
-  double* s_one = reinterpret_cast<double*>(smem + lay.o_misc + 640);  // [WARPS] single-value partials
+  double* s_w = reinterpret_cast<double*>(smem + lay.o_misc);     // [WARPS][6] warp partials
+  int* s_cnt = reinterpret_cast<int*>(smem + lay.o_misc + 768);   // [WARPS]
+  double* s_one = reinterpret_cast<double*>(smem + lay.o_misc + 896);  // [WARPS] single-value partials
   Ctrl* s_ctrl = reinterpret_cast<Ctrl*>(smem + lay.o_misc + 1024);
   Ctrl* s_new = s_ctrl + 1;
   DecideOut* s_act = reinterpret_cast<DecideOut*>(s_new + 1);
-  static_assert(PERSIST_WARPS * 32 <= 512 && 1024 + 2 * sizeof(Ctrl) + sizeof(DecideOut) <= 2048, "misc region");
+  static_assert(PERSIST_WARPS * 48 <= 768 && PERSIST_WARPS * 8 <= 128 && 1024 + 2 * sizeof(Ctrl) + sizeof(DecideOut) <= 2048, "misc region");
 
   // ---- load the resident data: A[:, J_rank] (zero padded), b, x0[J_rank]
   const T* Ag = static_cast<const T*>(a.A);
@@ -192,8 +192,8 @@ glp_persist_kernel(const PersistArgs a) {
     {
       ProxResolved pr;
       pr.algo = a.sc.algo; pr.cur = cur; pr.init = init;
-      pr.theta = s_ctrl->theta; pr.t = s_ctrl->t; pr.mu = s_ctrl->mu; pr.thres = a.sc.thres;
-      ProxScal ps = {0.0, 0.0, 0.0, 0.0};
+      pr.theta = s_ctrl->theta; pr.t = s_ctrl->t; pr.mu = s_ctrl->mu; pr.thres = a.sc.thres; pr.delta = a.sc.delta;
+      ProxScal ps = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
       for (int jl = tid; jl < nloc; jl += PERSIST_THREADS) prox_group<double, true>(p, pr, g, jl, ps);
       // four interleaved warp reductions (independent chains hide the fp64 latency)
 #pragma unroll
@@ -202,22 +202,35 @@ glp_persist_kernel(const PersistArgs a) {
         ps.dd += __shfl_xor_sync(0xffffffffu, ps.dd, o);
         ps.reg += __shfl_xor_sync(0xffffffffu, ps.reg, o);
         ps.mx = pmax_bits(ps.mx, __shfl_xor_sync(0xffffffffu, ps.mx, o));
+        ps.sx += __shfl_xor_sync(0xffffffffu, ps.sx, o);
+        ps.sy += __shfl_xor_sync(0xffffffffu, ps.sy, o);
       }
-      if (lane == 0) { s_w[warp * 4 + 0] = ps.gd; s_w[warp * 4 + 1] = ps.dd; s_w[warp * 4 + 2] = ps.reg; s_w[warp * 4 + 3] = ps.mx; }
+      if (lane == 0) {
+        s_w[warp * 6 + 0] = ps.gd; s_w[warp * 6 + 1] = ps.dd; s_w[warp * 6 + 2] = ps.reg; s_w[warp * 6 + 3] = ps.mx;
+        s_w[warp * 6 + 4] = ps.sx; s_w[warp * 6 + 5] = ps.sy;
+      }
     }
     const double* cand = xs + (1 - cur) * 3 * L * nc;  // {xn | xnt | vn}
     __syncthreads();  // #1 candidates + warp partials visible
     if (warp == 0) {
-      double v0 = 0.0, v1 = 0.0, v2 = 0.0, v3 = 0.0;
-      if (lane < PERSIST_WARPS) { v0 = s_w[lane * 4 + 0]; v1 = s_w[lane * 4 + 1]; v2 = s_w[lane * 4 + 2]; v3 = s_w[lane * 4 + 3]; }
+      double v0 = 0.0, v1 = 0.0, v2 = 0.0, v3 = 0.0, v4 = 0.0, v5 = 0.0;
+      if (lane < PERSIST_WARPS) {
+        v0 = s_w[lane * 6 + 0]; v1 = s_w[lane * 6 + 1]; v2 = s_w[lane * 6 + 2]; v3 = s_w[lane * 6 + 3];
+        v4 = s_w[lane * 6 + 4]; v5 = s_w[lane * 6 + 5];
+      }
 #pragma unroll
       for (int o = 8; o > 0; o >>= 1) {
         v0 += __shfl_xor_sync(0xffffffffu, v0, o);
         v1 += __shfl_xor_sync(0xffffffffu, v1, o);
         v2 += __shfl_xor_sync(0xffffffffu, v2, o);
         v3 = pmax_bits(v3, __shfl_xor_sync(0xffffffffu, v3, o));
+        v4 += __shfl_xor_sync(0xffffffffu, v4, o);
+        v5 += __shfl_xor_sync(0xffffffffu, v5, o);
       }
-      if (lane == 0) { slots[par * 8 + 0] = v3; slots[par * 8 + 1] = v0; slots[par * 8 + 2] = v1; slots[par * 8 + 3] = v2; }
+      if (lane == 0) {
+        slots[par * 8 + 0] = v3; slots[par * 8 + 1] = v0; slots[par * 8 + 2] = v1; slots[par * 8 + 3] = v2;
+        slots[par * 8 + 5] = v4; slots[par * 8 + 6] = v5;
+      }
     }
     for (int idx = tid; idx < nc * 2 * L; idx += PERSIST_THREADS) {
       const int jl = idx / (2 * L), q = idx - jl * 2 * L;
@@ -300,18 +313,19 @@ glp_persist_kernel(const PersistArgs a) {
     // ================= decide (every CTA, identical inputs -> identical decision) ===================
     if (warp == 0) {
       const double rr_tot = tree16_sum(lane < PERSIST_WARPS ? s_one[lane] : 0.0);
-      double v1 = 0.0, v2 = 0.0, v3 = 0.0, v4 = 0.0;
+      double v1 = 0.0, v2 = 0.0, v3 = 0.0, v4 = 0.0, v5 = 0.0, v6 = 0.0;
       if (lane < C) {
         const double* rs_ = cluster.map_shared_rank(slots, lane) + par * 8;
-        v1 = rs_[1]; v2 = rs_[2]; v3 = rs_[3]; v4 = rs_[4];
+        v1 = rs_[1]; v2 = rs_[2]; v3 = rs_[3]; v4 = rs_[4]; v5 = rs_[5]; v6 = rs_[6];
       }
-      double gd = 0.0, dd = 0.0, reg = 0.0, cn = 0.0;
+      double gd = 0.0, dd = 0.0, reg = 0.0, cn = 0.0, sx = 0.0, sy = 0.0;
       for (int c = 0; c < C; ++c) {
         gd += __shfl_sync(0xffffffffu, v1, c); dd += __shfl_sync(0xffffffffu, v2, c);
         reg += __shfl_sync(0xffffffffu, v3, c); cn += __shfl_sync(0xffffffffu, v4, c);
+        sx += __shfl_sync(0xffffffffu, v5, c); sy += __shfl_sync(0xffffffffu, v6, c);
       }
       if (lane == 0) {
-        Reduced red = {rr_tot, gd, dd, reg, cn, r_gy};
+        Reduced red = {rr_tot, gd, dd, reg, cn, r_gy, sx, sy};
         decide_step(a.sc, *s_ctrl, red, double(a.n) * double(L), *s_new, *s_act, rank == 0 ? a.f_hist : nullptr,
                     rank == 0 ? a.f_hist_best : nullptr);
         *s_ctrl = *s_new;

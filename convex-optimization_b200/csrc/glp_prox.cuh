@@ -20,6 +20,7 @@ namespace glp {
 
 struct ProxScal {
   double gd, dd, reg, mx;
+  double sx, sy;  // FGD: smoothed regulariser at the candidate / at the base point
 };
 
 __device__ __forceinline__ double nmax(double a, double b) {
@@ -28,7 +29,7 @@ __device__ __forceinline__ double nmax(double a, double b) {
 
 struct ProxResolved {
   int algo, cur, init;
-  double theta, t, mu, thres;
+  double theta, t, mu, thres, delta;
 };
 
 __device__ __forceinline__ ProxResolved resolve(const ProxArgs& p) {
@@ -36,6 +37,7 @@ __device__ __forceinline__ ProxResolved resolve(const ProxArgs& p) {
   r.algo = p.algo;
   r.init = p.init;
   r.thres = p.thres;
+  r.delta = p.delta;
   if (p.ctrl != nullptr) {
     r.cur = p.ctrl->cur; r.theta = p.ctrl->theta; r.t = p.ctrl->t; r.mu = p.ctrl->mu;
   } else {
@@ -59,7 +61,7 @@ __device__ __forceinline__ void prox_group(const ProxArgs& p, const ProxResolved
   double* xnt = C + int64_t(l) * ldn;
   double* vn = C + 2 * int64_t(l) * ldn;
   T* xop = static_cast<T*>(p.xop);
-  const bool accel = r.algo == 1;
+  const bool accel = r.algo == ALGO_FPROXGD || r.algo == ALGO_FGD;
 
   if (r.init) {
     double nn = 0.0;
@@ -76,6 +78,49 @@ __device__ __forceinline__ void prox_group(const ProxArgs& p, const ProxResolved
   }
 
   const double omt = xsub(1.0, r.theta);
+  if (r.algo >= ALGO_FGD) {
+    // ---- smoothed / subgradient solvers: prox = identity, the regulariser enters
+    // through its gradient at the base point.  Operation order of gl_FGD_primal.py:69-72,139-145,
+    // gl_GD_primal.py:59-63,92-94 and gl_SGD_primal.py:56-61,90-92.
+    double nb = 0.0;
+    for (int c = 0; c < l; ++c) {
+      const double xtc = xt[c * ldn + j];
+      const double base = accel ? xadd(xmul(omt, xtc), xmul(r.theta, v[c * ldn + j])) : xtc;
+      nb = xadd(nb, xmul(base, base));
+    }
+    double den;
+    if (r.algo == ALGO_SGD) {
+      const double rn = __dsqrt_rn(nb);
+      den = xadd(rn < r.thres ? 1.0 : 0.0, rn);
+    } else {
+      den = __dsqrt_rn(xadd(nb, xmul(r.delta, r.delta)));
+    }
+    double n2 = 0.0;
+    for (int c = 0; c < l; ++c) {
+      const double xtc = xt[c * ldn + j];
+      const double base = accel ? xadd(xmul(omt, xtc), xmul(r.theta, v[c * ldn + j])) : xtc;
+      const double gr = SMEM ? p.grad[c * ldn + j] : __ldcg(&p.grad[c * ldn + j]);
+      const double gtot = xadd(gr, xmul(r.mu, xdiv(base, den)));
+      const double o = xsub(base, xmul(r.t, gtot));
+      const double oz = fabs(o) < r.thres ? 0.0 : o;
+      xn[c * ldn + j] = o;
+      xnt[c * ldn + j] = oz;
+      if (xop != nullptr) { xop[c * ldn + j] = T(o); xop[(l + c) * ldn + j] = T(oz); }
+      if (accel) vn[c * ldn + j] = xadd(xtc, xdiv(xsub(o, xtc), r.theta));
+      const double d = xsub(o, base);
+      sc.gd = xadd(sc.gd, xmul(gtot, d));
+      sc.dd = xadd(sc.dd, xmul(d, d));
+      n2 = xadd(n2, xmul(o, o));
+      sc.mx = nmax(sc.mx, fabs(o));
+    }
+    sc.reg = xadd(sc.reg, __dsqrt_rn(n2));
+    if (r.algo == ALGO_FGD) {
+      const double d2 = xmul(r.delta, r.delta);
+      sc.sx = xadd(sc.sx, xsub(__dsqrt_rn(xadd(n2, d2)), r.delta));
+      sc.sy = xadd(sc.sy, xsub(__dsqrt_rn(xadd(nb, d2)), r.delta));
+    }
+    return;
+  }
   const double tmu = xmul(r.t, r.mu);
   double nn = 0.0;
   for (int c = 0; c < l; ++c) {
@@ -118,9 +163,9 @@ __device__ __forceinline__ void prox_group(const ProxArgs& p, const ProxResolved
 // all call this function; the scalar partials land in scal_partial[cb][0..3] in a fixed order.
 template <typename T>
 __device__ __forceinline__ void prox_block(const ProxArgs& p, const ProxResolved& r, const Geom& g,
-                                           int64_t cb, int tid, double (*s_red)[4]) {
+                                           int64_t cb, int tid, double (*s_red)[6]) {
   constexpr int TC = Elem<T>::TILE_COLS;
-  ProxScal sc = {0.0, 0.0, 0.0, 0.0};
+  ProxScal sc = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   for (int jj = tid; jj < TC; jj += CONSUMER_THREADS) {
     const int64_t j = cb * TC + jj;
     if (j < g.n) prox_group<T>(p, r, g, j, sc);
@@ -128,19 +173,25 @@ __device__ __forceinline__ void prox_block(const ProxArgs& p, const ProxResolved
   sc.gd = warp_sum(sc.gd);
   sc.dd = warp_sum(sc.dd);
   sc.reg = warp_sum(sc.reg);
+  sc.sx = warp_sum(sc.sx);
+  sc.sy = warp_sum(sc.sy);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) sc.mx = nmax(sc.mx, __shfl_xor_sync(0xffffffffu, sc.mx, o));
   const int warp = tid >> 5, lane = tid & 31;
-  if (lane == 0) { s_red[warp][0] = sc.gd; s_red[warp][1] = sc.dd; s_red[warp][2] = sc.reg; s_red[warp][3] = sc.mx; }
+  if (lane == 0) {
+    s_red[warp][0] = sc.gd; s_red[warp][1] = sc.dd; s_red[warp][2] = sc.reg; s_red[warp][3] = sc.mx;
+    s_red[warp][4] = sc.sx; s_red[warp][5] = sc.sy;
+  }
   consumer_bar();
   if (tid == 0) {
-    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, a4 = 0.0, a5 = 0.0;
 #pragma unroll
     for (int w = 0; w < NUM_CONSUMER_WARPS; ++w) {
       a0 += s_red[w][0]; a1 += s_red[w][1]; a2 += s_red[w][2]; a3 = nmax(a3, s_red[w][3]);
+      a4 += s_red[w][4]; a5 += s_red[w][5];
     }
-    double* out = p.scal_partial + 4 * cb;
-    out[0] = a0; out[1] = a1; out[2] = a2; out[3] = a3;
+    double* out = p.scal_partial + SCAL_STRIDE * cb;
+    out[0] = a0; out[1] = a1; out[2] = a2; out[3] = a3; out[4] = a4; out[5] = a5;
   }
   consumer_bar();
 }
@@ -150,7 +201,7 @@ __device__ __forceinline__ void prox_block(const ProxArgs& p, const ProxResolved
 template <typename T>
 __global__ void __launch_bounds__(CONSUMER_THREADS)
 glp_prox_kernel(const ProxArgs p, const Geom g, const int only_if_retry) {
-  __shared__ double s_red[NUM_CONSUMER_WARPS][4];
+  __shared__ double s_red[NUM_CONSUMER_WARPS][6];
   if (p.ctrl != nullptr) {
     if (p.ctrl->done) return;
     if (only_if_retry && !p.ctrl->retry) return;

@@ -48,7 +48,7 @@ glp_tpass_kernel(const __grid_constant__ CUtensorMap tmapA, const TpassArgs a, c
   uint64_t* empty = full + NUM_STAGES;
   T* red = reinterpret_cast<T*>(empty + NUM_STAGES);  // [8 warps][LC][TC]
   __shared__ int s_last;
-  __shared__ double s_red[NUM_CONSUMER_WARPS][4];
+  __shared__ double s_red[NUM_CONSUMER_WARPS][6];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 

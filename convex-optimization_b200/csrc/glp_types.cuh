@@ -34,14 +34,20 @@ struct Ctrl {
   int64_t n_fwd, n_tpass;
 };
 
+// Per-column-block scalar record written by the prox epilogue: {gd, dd, reg, max|xn|, sx, sy, -, -}
+// (sx / sy: smoothed regulariser at the candidate / base point, FGD only).
+constexpr int SCAL_STRIDE = 8;
+enum { ALGO_PROXGD = 0, ALGO_FPROXGD = 1, ALGO_FGD = 2, ALGO_GD = 3, ALGO_SGD = 4 };
+
 struct SolveConst {
-  int32_t algo;          // GLP_PROXGD / GLP_FPROXGD
+  int32_t algo;          // ALGO_*
   int32_t step_type;
   int32_t maxit;
   int32_t stable_cap;
   int32_t ls_cap;
   int32_t hist_cap;
   double thres, alpha0, ftol, atten, mu0;
+  double delta;          // smoothing parameter of FGD / GD (gl_FGD_primal.py:20, gl_GD_primal.py:18)
 };
 
 // Geometry of one problem shard on one device.
@@ -86,7 +92,7 @@ struct FwdArgs {
   double* partial;       // [(grid + nrb)][TILE_ROWS][RC]
   unsigned* counter;     // [nrb], zero between launches
   double* rr_partial;    // [nrb]  sum over rows of the block of (AX - b)^2
-  const double* scal_partial;  // [ncb][4] from the transposed epilogue (slot 3 = max|xn|)
+  const double* scal_partial;  // [ncb][SCAL_STRIDE] from the transposed epilogue (slot 3 = max|xn|)
   const double* xcand[2];      // candidate x [l][ldn] fp64, selected like X
   double* cnt_partial;   // [grid]
   int32_t* fault;
@@ -126,13 +132,14 @@ struct ProxArgs {
   double* state[2];      // each: [3][l][ldn] = {x, xt, v}; committed = state[cur], candidates = state[1-cur]
   void* xop;             // fp32 mode: operand copy [2l][ldn] float {xn | xnt}; fp64 mode: nullptr
   const double* grad;    // [l][ldn]
-  double* scal_partial;  // [ncb][4] = {gd, dd, reg, max}
+  double* scal_partial;  // [ncb][SCAL_STRIDE] = {gd, dd, reg, max, sx, sy}
   const Ctrl* ctrl;      // nullable: when null the explicit fields below are used
   int32_t algo;
   int32_t cur;
   int32_t init;          // 1: candidate = x0 already stored in state[1-cur][0]; only threshold + scalars
   int32_t pad;
   double theta, t, mu, thres;
+  double delta;
   ProxPost post;
 };
 

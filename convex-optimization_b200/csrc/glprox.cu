@@ -24,7 +24,7 @@
 
 using namespace glp;
 
-static_assert(sizeof(glp_opts) == 56 && sizeof(glp_result) == 80 && sizeof(glp_step_params) == 40,
+static_assert(sizeof(glp_opts) == 64 && sizeof(glp_result) == 80 && sizeof(glp_step_params) == 40,
               "ABI structs changed: update glprox/_lib.py and tests/test_abi.py");
 
 // ------------------------------------------------------------------------------------------------
@@ -73,17 +73,20 @@ extern "C" int glp_device_count(void) {
 }
 
 extern "C" int glp_default_opts(int algo, glp_opts* o) {
-  if (o == nullptr || (algo != GLP_PROXGD && algo != GLP_FPROXGD)) return fail(GLP_ERR_ARG, "bad algo/opts");
+  if (o == nullptr || algo < GLP_PROXGD || algo > GLP_SGD) return fail(GLP_ERR_ARG, "bad algo/opts");
   memset(o, 0, sizeof(*o));
-  // gl_ProxGD_primal.py:10-19 / gl_FProxGD_primal.py:10-19
-  o->maxit = algo == GLP_PROXGD ? 2500 : 1500;
+  // gl_ProxGD_primal.py:10-19 / gl_FProxGD_primal.py:10-19 / gl_FGD_primal.py:10-21 / gl_GD_primal.py:10-19 /
+  // gl_SGD_primal.py:10-18
+  const bool plain = algo == GLP_GD || algo == GLP_SGD;
+  o->maxit = algo == GLP_PROXGD ? 2500 : (algo == GLP_GD ? 2500 : (algo == GLP_SGD ? 2100 : 1500));
   o->thres = 1e-3;
-  o->step_type = GLP_STEP_LINE_SEARCH;
+  o->step_type = plain ? GLP_STEP_DIMINISHING : GLP_STEP_LINE_SEARCH;
   o->alpha0 = algo == GLP_PROXGD ? 2e-3 : 1e-3;
-  o->ftol = 1e-6;
-  o->stable_len_threshold = 70;
-  o->line_search_attenuation_coeffi = algo == GLP_PROXGD ? 0.9 : 0.98;
-  o->maxit_line_search_iter = 5;
+  o->ftol = plain ? 1e-5 : 1e-6;
+  o->stable_len_threshold = plain ? 100 : 70;
+  o->line_search_attenuation_coeffi = algo == GLP_PROXGD ? 0.9 : (plain ? 1.0 : 0.98);
+  o->maxit_line_search_iter = plain ? 0 : 5;
+  o->delta = algo == GLP_FGD ? 1e-6 : (algo == GLP_GD ? 1e-3 : 0.0);
   o->backend = GLP_BACKEND_AUTO;
   o->poll_interval = 0;
   return GLP_OK;
@@ -424,7 +427,7 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
   const size_t o_r = carve(lm * esz);
   const size_t o_s0 = carve(3 * ln * 8), o_s1 = carve(3 * ln * 8), o_grad = carve(ln * 8);
   const size_t o_xop = carve(dtype == GLP_F32 ? 2 * ln * 4 : 0);
-  const size_t o_scal = carve(size_t(g.ncb) * 4 * 8), o_cnt = carve(size_t(g.grid) * 8);
+  const size_t o_scal = carve(size_t(g.ncb) * SCAL_STRIDE * 8), o_cnt = carve(size_t(g.grid) * 8);
   const size_t o_rr = carve(size_t(h->n_fchunks) * g.nrb * 8);
   const size_t o_gy0 = carve(size_t(h->decide_grid) * 8), o_gy1 = carve(size_t(h->decide_grid) * 8);
   const size_t o_fp = carve(size_t(g.grid + g.nrb) * TILE_ROWS * 4 * 8);
@@ -432,7 +435,7 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
   const size_t o_fc = carve(size_t(g.nrb) * 4), o_tc = carve(size_t(g.ncb) * 4);
   const size_t o_ctrl = carve(2 * sizeof(Ctrl)), o_fault = carve(16);
   h->gather_grid = int(std::max<int64_t>(1, std::min<int64_t>(num_sms, (int64_t(2) * lm + GATHER_THREADS - 1) / GATHER_THREADS)));
-  const size_t o_fin = carve(16), o_rrg = carve(size_t(h->gather_grid) * 8), o_sred = carve(4 * 8), o_cred = carve(8);
+  const size_t o_fin = carve(16), o_rrg = carve(size_t(h->gather_grid) * 8), o_sred = carve(SCAL_STRIDE * 8), o_cred = carve(8);
   cudaError_t e = cudaMalloc(&h->arena, off);
   if (e != cudaSuccess) { glp_destroy(h); return fail(GLP_ERR_CUDA, "cudaMalloc(%zu) failed: %s", off, cudaGetErrorString(e)); }
   e = cudaMemsetAsync(h->arena, 0, off, h->stream);
@@ -659,6 +662,7 @@ static ProxArgs solver_prox_args(glp_handle* h, const Ctrl* ctrl) {
   p.ctrl = ctrl;
   p.algo = h->sc.algo;
   p.thres = h->sc.thres;
+  p.delta = h->sc.delta;
   return p;
 }
 
@@ -699,16 +703,18 @@ static int enqueue_gather(glp_handle* h, const Ctrl* ctrl) {
 // ------------------------------------------------------------------------------------------------
 static int phase_prepare(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o) {
   if (h == nullptr || x0_dev == nullptr || o == nullptr) return fail(GLP_ERR_ARG, "null argument");
-  if (algo != GLP_PROXGD && algo != GLP_FPROXGD) return fail(GLP_ERR_ARG, "unknown algo %d", algo);
+  if (algo < GLP_PROXGD || algo > GLP_SGD) return fail(GLP_ERR_ARG, "unknown algo %d", algo);
   if (o->step_type < GLP_STEP_LINE_SEARCH || o->step_type > GLP_STEP_DIMINISHING2)
     return fail(GLP_ERR_ARG, "unsupported step_type %d", o->step_type);
+  if ((algo == GLP_GD || algo == GLP_SGD) && o->step_type == GLP_STEP_LINE_SEARCH)
+    return fail(GLP_ERR_ARG, "gl_GD_primal / gl_SGD_primal have no line search (step_type fixed | diminishing | diminishing2)");
   if (o->maxit < 0 || o->maxit > (1 << 26)) return fail(GLP_ERR_ARG, "maxit out of range");
   CU_TRY(cudaSetDevice(h->device));
   const Geom& g = h->g;
   SolveConst& sc = h->sc;
   sc.algo = algo; sc.step_type = o->step_type; sc.maxit = o->maxit; sc.stable_cap = o->stable_len_threshold;
   sc.ls_cap = o->maxit_line_search_iter; sc.thres = o->thres; sc.alpha0 = o->alpha0; sc.ftol = o->ftol;
-  sc.atten = o->line_search_attenuation_coeffi; sc.mu0 = mu0;
+  sc.atten = o->line_search_attenuation_coeffi; sc.mu0 = mu0; sc.delta = o->delta;
   sc.hist_cap = 3 * o->maxit + 8;
   if (h->hist_cap < sc.hist_cap) {
     if (h->f_hist) CU_TRY(cudaFree(h->f_hist));
@@ -891,7 +897,7 @@ extern "C" int glp_solve_end(glp_handle* h, void* x_out_dev, glp_result* res, do
   prof_collect(h);
   fill_result(h, c, res);
   if (res) res->device_ms = ms;
-  if (h->sc.algo == GLP_FPROXGD && !c.ran_any) {
+  if ((h->sc.algo == GLP_FPROXGD || h->sc.algo == GLP_FGD) && !c.ran_any) {
     if (res) res->status = GLP_ERR_UNBOUND;
     return fail(GLP_ERR_UNBOUND, "FProxGD ran no iteration (maxit == 0): the reference raises UnboundLocalError");
   }
@@ -1216,7 +1222,7 @@ extern "C" int glp_tpass_prox(glp_handle* h, const glp_step_params* sp, const do
     if (v_dev) CU_TRY(to_planar(h->stream, v_dev, h->state[0] + 2 * ln, g.n, g.l, g.ldn));
     p = solver_prox_args(h, nullptr);
     p.algo = sp->algo; p.cur = 0; p.init = 0;
-    p.theta = sp->theta; p.t = sp->t; p.mu = sp->mu; p.thres = sp->thres;
+    p.theta = sp->theta; p.t = sp->t; p.mu = sp->mu; p.thres = sp->thres; p.delta = 0.0;
   }
   GLP_TRY(enqueue_tpass(h, nullptr, sp ? &p : nullptr, h->grad, false));
   if (G_dev) CU_TRY(from_planar(h->stream, h->grad, G_dev, g.n, g.l, g.ldn));
@@ -1225,7 +1231,7 @@ extern "C" int glp_tpass_prox(glp_handle* h, const glp_step_params* sp, const do
     CU_TRY(from_planar(h->stream, h->state[1] + ln, xnt_dev, g.n, g.l, g.ldn));
     if (vn_dev && sp->algo == GLP_FPROXGD) CU_TRY(from_planar(h->stream, h->state[1] + 2 * ln, vn_dev, g.n, g.l, g.ldn));
     for (int k = 0; k < 4; ++k) {
-      sum_partials_kernel<<<1, 256, 0, h->stream>>>(h->scal_partial, g.ncb, 4, k, k == 3 ? 1 : 0, scalars_dev + k);
+      sum_partials_kernel<<<1, 256, 0, h->stream>>>(h->scal_partial, g.ncb, SCAL_STRIDE, k, k == 3 ? 1 : 0, scalars_dev + k);
       CU_TRY(cudaGetLastError());
     }
   }

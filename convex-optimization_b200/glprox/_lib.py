@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libglprox.so")
 
 GLP_F32, GLP_F64 = 0, 1
-GLP_PROXGD, GLP_FPROXGD = 0, 1
+GLP_PROXGD, GLP_FPROXGD, GLP_FGD, GLP_GD, GLP_SGD = 0, 1, 2, 3, 4
 STEP_TYPES = {"line_search": 0, "fixed": 1, "diminishing": 2, "diminishing2": 3}
 BACKENDS = {"auto": 0, "stream": 1, "persistent": 2}
 
@@ -23,7 +23,7 @@ class GlpOpts(C.Structure):
     _fields_ = [("maxit", C.c_int32), ("step_type", C.c_int32), ("stable_len_threshold", C.c_int32),
                 ("maxit_line_search_iter", C.c_int32), ("thres", C.c_double), ("alpha0", C.c_double),
                 ("ftol", C.c_double), ("line_search_attenuation_coeffi", C.c_double),
-                ("backend", C.c_int32), ("poll_interval", C.c_int32)]
+                ("backend", C.c_int32), ("poll_interval", C.c_int32), ("delta", C.c_double)]
 
 
 class GlpResult(C.Structure):

@@ -24,7 +24,18 @@ DEFAULT_OPTS = {
                 "stable_len_threshold": 70, "line_search_attenuation_coeffi": 0.98,
                 "maxit_line_search_iter": 5},
 }
-ALGO_ID = {"ProxGD": _lib.GLP_PROXGD, "FProxGD": _lib.GLP_FPROXGD}
+# gl_FGD_primal.py:10-21, gl_GD_primal.py:10-19, gl_SGD_primal.py:10-18
+DEFAULT_OPTS.update({
+    "FGD": {"maxit": 1500, "thres": 1e-3, "step_type": "line_search", "alpha0": 1e-3, "ftol": 1e-6,
+            "stable_len_threshold": 70, "line_search_attenuation_coeffi": 0.98, "maxit_line_search_iter": 5,
+            "delta": 1e-6},
+    "GD": {"maxit": 2500, "thres": 1e-3, "step_type": "diminishing", "alpha0": 1e-3, "ftol": 1e-5,
+           "stable_len_threshold": 100, "continuous_subgradient_flag": False, "delta": 1e-3},
+    "SGD": {"maxit": 2100, "thres": 1e-3, "step_type": "diminishing", "alpha0": 1e-3, "ftol": 1e-5,
+            "stable_len_threshold": 100, "continuous_subgradient_flag": False},
+})
+ALGO_ID = {"ProxGD": _lib.GLP_PROXGD, "FProxGD": _lib.GLP_FPROXGD, "FGD": _lib.GLP_FGD, "GD": _lib.GLP_GD,
+           "SGD": _lib.GLP_SGD}
 # additive keys (not in the reference): dtype 'fp32'|'fp64', backend 'auto'|'stream'|'persistent',
 # device (int), poll_interval (int), dist (bool), tensor_cores 'auto'|'off'|'tf32'|'3xtf32' (wide l >= 16 mode)
 TENSOR_MODES = {"auto": 0, "3xtf32": 0, "off": 1, "tf32": 2}
@@ -43,6 +54,14 @@ def pack_opts(algo, merged):
         # the reference logs "Unsupported type." and then dies with TypeError (gl_ProxGD_primal.py:100-101)
         logger.error("Unsupported type.")
         raise ValueError("unsupported step_type %r (expected one of %s)" % (st, sorted(_lib.STEP_TYPES)))
+    if algo in ("GD", "SGD"):
+        if st == "line_search":  # the reference returns None as the step and dies with TypeError (gl_GD_primal.py:75-76)
+            logger.error("Unsupported type.")
+            raise ValueError("gl_%s_primal has no line search: step_type must be fixed, diminishing or diminishing2" % algo)
+        if merged.get("continuous_subgradient_flag"):
+            raise NotImplementedError("continuous_subgradient_flag (alpha0 = 1/lambda_max(A^T A) from a dense n x n "
+                                      "eigendecomposition, gl_GD_primal.py:43-45) is outside the streaming path; "
+                                      "pass alpha0 explicitly")
     backend = merged.get("backend", "auto")
     if backend not in _lib.BACKENDS:
         raise ValueError("unknown backend %r" % (backend,))
@@ -50,11 +69,12 @@ def pack_opts(algo, merged):
     o.maxit = int(merged["maxit"])
     o.step_type = _lib.STEP_TYPES[st]
     o.stable_len_threshold = int(merged["stable_len_threshold"])
-    o.maxit_line_search_iter = int(merged["maxit_line_search_iter"])
+    o.maxit_line_search_iter = int(merged.get("maxit_line_search_iter", 0))
     o.thres = float(merged["thres"])
     o.alpha0 = float(merged["alpha0"])
     o.ftol = float(merged["ftol"])
-    o.line_search_attenuation_coeffi = float(merged["line_search_attenuation_coeffi"])
+    o.line_search_attenuation_coeffi = float(merged.get("line_search_attenuation_coeffi", 1.0))
+    o.delta = float(merged.get("delta", 0.0))
     o.backend = _lib.BACKENDS[backend]
     o.poll_interval = int(merged.get("poll_interval", 0))
     return o

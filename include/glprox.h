@@ -42,7 +42,9 @@ typedef enum glp_status {
 } glp_status;
 
 enum { GLP_F32 = 0, GLP_F64 = 1 };
-enum { GLP_PROXGD = 0, GLP_FPROXGD = 1 };
+/* 0/1: the hot path; 2..4: SURVEY.md 8(f) row 1 -- the smoothed / subgradient solvers on the same two streams
+ * (gl_FGD_primal.py, gl_GD_primal.py, gl_SGD_primal.py) */
+enum { GLP_PROXGD = 0, GLP_FPROXGD = 1, GLP_FGD = 2, GLP_GD = 3, GLP_SGD = 4 };
 /* step_type strings of gl_ProxGD_primal.py:78-101 / gl_FProxGD_primal.py:81-106 */
 enum { GLP_STEP_LINE_SEARCH = 0, GLP_STEP_FIXED = 1, GLP_STEP_DIMINISHING = 2, GLP_STEP_DIMINISHING2 = 3 };
 enum { GLP_BACKEND_AUTO = 0, GLP_BACKEND_STREAM = 1, GLP_BACKEND_PERSISTENT = 2 };
@@ -61,6 +63,7 @@ typedef struct glp_opts {
   double line_search_attenuation_coeffi;
   int32_t backend;                        /* GLP_BACKEND_* (additive key, default AUTO) */
   int32_t poll_interval;                  /* iterations enqueued between host polls (0 = auto) */
+  double delta;                           /* smoothing parameter (FGD 1e-6, GD 1e-3; gl_FGD_primal.py:20, gl_GD_primal.py:18) */
 } glp_opts;
 
 typedef struct glp_result {

@@ -34,6 +34,15 @@ _COMMON = dict(thres=1e-3, step_type="line_search", ftol=1e-6, stable_len_thresh
 DEFAULTS = {
     "ProxGD": dict(_COMMON, maxit=2500, alpha0=2e-3, line_search_attenuation_coeffi=0.9),
     "FProxGD": dict(_COMMON, maxit=1500, alpha0=1e-3, line_search_attenuation_coeffi=0.98),
+    # "next" row f-1 of SURVEY.md 8(f): the smoothed / subgradient solvers on the same two streams
+    # (gl_FGD_primal.py:10-21, gl_GD_primal.py:10-19, gl_SGD_primal.py:10-18)
+    "FGD": dict(_COMMON, maxit=1500, alpha0=1e-3, line_search_attenuation_coeffi=0.98, delta=1e-6),
+    "GD": dict(maxit=2500, thres=1e-3, step_type="diminishing", alpha0=1e-3, ftol=1e-5, stable_len_threshold=100,
+               continuous_subgradient_flag=False, delta=1e-3, line_search_attenuation_coeffi=1.0,
+               maxit_line_search_iter=0),
+    "SGD": dict(maxit=2100, thres=1e-3, step_type="diminishing", alpha0=1e-3, ftol=1e-5, stable_len_threshold=100,
+                continuous_subgradient_flag=False, delta=0.0, line_search_attenuation_coeffi=1.0,
+                maxit_line_search_iter=0),
 }
 CONTINUATION = (100.0, 10.0, 1.0)  # mu stages: gl_ProxGD_primal.py:53 / gl_FProxGD_primal.py:55
 
@@ -83,6 +92,94 @@ def sparsity(x):
 def smooth_part(A, b, z):
     """g(z) = 0.5*||A z - b||^2  (gl_ProxGD_primal.py:60-61 / gl_FProxGD_primal.py:62-63)."""
     return 0.5 * np.sum((A @ z - b) ** 2)
+
+
+def smooth_reg(z, delta):
+    """sum_i sqrt(||z_i||^2 + delta^2) - delta   (gl_FGD_primal.py:64-67)."""
+    return np.sum(np.sqrt(np.sum(z ** 2, axis=1).reshape(-1, 1) + delta * delta) - delta)
+
+
+def smooth_reg_grad(z, delta):
+    """z / sqrt(||z_i||^2 + delta^2)   (gl_FGD_primal.py:69-72, gl_GD_primal.py:59-63)."""
+    return z / np.sqrt(np.sum(z ** 2, axis=1).reshape(-1, 1) + delta * delta)
+
+
+def subgrad_reg(z, thres):
+    """z / ((||z_i|| < thres) + ||z_i||)   (gl_SGD_primal.py:56-61)."""
+    rn = row_norms(z)
+    return z / ((rn < thres) + rn)
+
+
+def solve_smooth(algo, x0, A, b, mu0, opts=None):
+    """Reference-structured restatement of gl_FGD_primal / gl_GD_primal / gl_SGD_primal
+    (code/gl_FGD_primal.py:56-163, code/gl_GD_primal.py:53-112, code/gl_SGD_primal.py:47-109)."""
+    o = dict(DEFAULTS[algo])
+    o.update(opts or {})
+    if o.get("continuous_subgradient_flag"):
+        raise NotImplementedError("continuous_subgradient_flag (alpha0 = 1/lambda_max via eigvals) is out of scope")
+    maxit, ftol, alpha0, thres, rule = o["maxit"], o["ftol"], o["alpha0"], o["thres"], o["step_type"]
+    delta = o["delta"]
+    f_hist, f_best_hist, s_hist = [], [], []
+    f_best = np.inf
+    xk = np.copy(x0)
+    x_last = None if algo == "FGD" else xk
+    k, stable = 0, 0
+    t_begin = time.time_ns()
+    mu = mu0
+    for factor in CONTINUATION:
+        mu = factor * mu0
+        inner = 0
+        if algo == "FGD":
+            vk, tk, stable = np.copy(xk), alpha0, 0
+        while inner < maxit:
+            f_now = objective(A, b, xk, mu if algo == "SGD" else mu0)   # SGD records the stage objective (:50-53)
+            f_hist.append(f_now)
+            f_best = min(f_best, f_now)
+            f_best_hist.append(f_best)
+            s_hist.append(sparsity(xk))
+            k += 1
+            inner += 1
+            if algo == "FGD":
+                with np.errstate(divide="ignore", invalid="ignore"):
+                    ok = (k > 1 and abs(f_hist[k - 1] - f_hist[k - 2]) / abs(f_hist[k - 2]) < ftol
+                          and abs(s_hist[k - 1] - s_hist[k - 2]) / abs(s_hist[k - 2]) < ftol)
+                stable = stable + 1 if ok else 0
+                if stable > o["stable_len_threshold"]:
+                    break
+            xk[np.abs(xk) < thres] = 0
+            if algo == "FGD":
+                theta = 2 / (inner + 1)
+                y = (1 - theta) * xk + theta * vk
+                grad = A.T @ (A @ y - b) + mu * smooth_reg_grad(y, delta)
+                if rule == "line_search":
+                    t = tk
+                    g_y = 0.5 * np.sum((A @ y - b) ** 2) + mu * smooth_reg(y, delta)
+                    for _ in range(o["maxit_line_search_iter"]):
+                        x = y - t * grad
+                        g_x = 0.5 * np.sum((A @ x - b) ** 2) + mu * smooth_reg(x, delta)
+                        if g_x <= g_y + np.sum(grad * (x - y)) + np.sum((x - y) ** 2) / (2 * t):
+                            break
+                        t *= o["line_search_attenuation_coeffi"]
+                else:
+                    t = _open_loop_step(rule, alpha0, inner)
+                x = y - t * grad
+                vk = xk + (x - xk) / theta
+                xk, tk = x, t
+                x_last = x
+            else:
+                reg_g = smooth_reg_grad(xk, delta) if algo == "GD" else subgrad_reg(xk, thres)
+                sub_g = A.T @ (A @ xk - b) + mu * reg_g
+                if rule == "fixed" or mu > mu0:          # gl_GD_primal.py:67-70 / gl_SGD_primal.py:65-68
+                    alpha = alpha0
+                else:
+                    alpha = _open_loop_step(rule, alpha0, inner)
+                xk = xk - alpha * sub_g
+                x_last = xk
+    tt = _round_us(time.time_ns() - t_begin) / 1e6
+    if x_last is None:
+        raise UnboundLocalError("FGD ran no iteration (maxit=0), as in the reference")
+    fval = objective(A, b, x_last, mu if algo == "SGD" else mu0)
+    return x_last, k, {"tt": tt, "fval": fval, "f_hist": f_hist, "f_hist_best": f_best_hist}
 
 
 def _open_loop_step(step_type, alpha0, inner):
@@ -217,29 +314,40 @@ def hard_threshold(x, thres):
     return out
 
 
-def prox_epilogue(algo, grad, xt, v, theta, t, mu, thres):
+def prox_epilogue(algo, grad, xt, v, theta, t, mu, thres, delta=0.0, full=False):
     """What the transposed pass's fused epilogue produces for one trial step t.
 
-    Returns (xn, xnt, vn, gd, dd, reg, mx):  candidate iterate, its thresholded copy, the FProxGD
-    momentum candidate, the two line-search inner products, sum_i||xn_i|| and max|xn|.
-    FProxGD: base y=(1-theta)*xt+theta*v, gd=<grad,xn-y>, dd=||xn-y||^2.
-    ProxGD:  base xt,                     gd=<grad,gt>,   dd=||gt||^2 with gt=(xt-xn)/t.
+    Returns (xn, xnt, vn, gd, dd, reg, mx) [+ (sx, sy) with full=True]:  candidate iterate, its
+    thresholded copy, the momentum candidate, the two line-search inner products, sum_i||xn_i||,
+    max|xn| and the smoothed regulariser at the candidate / base point.
+    FProxGD: base y=(1-theta)*xt+theta*v, xn=prox(y-t*grad), gd=<grad,xn-y>, dd=||xn-y||^2.
+    ProxGD:  base xt, gd=<grad,gt>, dd=||gt||^2 with gt=(xt-xn)/t.
+    FGD:     base y, gtot=grad+mu*y/sqrt(||y_i||^2+delta^2), xn=y-t*gtot, gd=<gtot,xn-y>, dd=||xn-y||^2.
+    GD/SGD:  base xt, gtot=grad+mu*(smoothed | guarded sub)gradient, xn=xt-t*gtot.
     """
-    if algo == "FProxGD":
-        base = (1 - theta) * xt + theta * v
+    accel = algo in ("FProxGD", "FGD")
+    base = (1 - theta) * xt + theta * v if accel else xt
+    sx = sy = 0.0
+    if algo in ("FProxGD", "ProxGD"):
+        xn = group_prox(base - t * grad, t, mu, thres)
+        gtot = grad
     else:
-        base = xt
-    xn = group_prox(base - t * grad, t, mu, thres)
+        reg_g = subgrad_reg(base, thres) if algo == "SGD" else smooth_reg_grad(base, delta)
+        gtot = grad + mu * reg_g
+        xn = base - t * gtot
+        if algo == "FGD":
+            sx, sy = smooth_reg(xn, delta), smooth_reg(base, delta)
     xnt = hard_threshold(xn, thres)
-    if algo == "FProxGD":
-        d = xn - base
-        vn = xt + (xn - xt) / theta
-    else:
+    vn = xt + (xn - xt) / theta if accel else None
+    if algo == "ProxGD":
         d = (base - xn) / t
-        vn = None
-    gd, dd = np.sum(grad * d), np.sum(d ** 2)
+    else:
+        d = xn - base
+    gd, dd = np.sum(gtot * d), np.sum(d ** 2)
     reg = np.sum(row_norms(xn))
     mx = np.max(np.abs(xn))
+    if full:
+        return xn, xnt, vn, gd, dd, reg, mx, sx, sy
     return xn, xnt, vn, gd, dd, reg, mx
 
 

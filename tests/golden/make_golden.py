@@ -19,11 +19,15 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, "/root/reference/code")
 
+from gl_FGD_primal import gl_FGD_primal  # noqa: E402  (reference)
 from gl_FProxGD_primal import gl_FProxGD_primal  # noqa: E402  (reference)
+from gl_GD_primal import gl_GD_primal  # noqa: E402  (reference)
 from gl_ProxGD_primal import gl_ProxGD_primal  # noqa: E402  (reference)
+from gl_SGD_primal import gl_SGD_primal  # noqa: E402  (reference)
 from oracle.glprox_oracle import gen_data, sparsity  # noqa: E402
 
 REF = {"ProxGD": gl_ProxGD_primal, "FProxGD": gl_FProxGD_primal}
+REF_SMOOTH = {"FGD": gl_FGD_primal, "GD": gl_GD_primal, "SGD": gl_SGD_primal}
 
 
 def mp_step(m, n):
@@ -57,15 +61,37 @@ CASES = {
 }
 
 
+# cases for the smoothed / subgradient solvers; per-algorithm opts where the defaults differ too much
+SMOOTH_CASES = {
+    "smooth_fixture": (97006855, 256, 512, 2, "f8", {}),
+    "smooth_maxit40": (97006855, 256, 512, 2, "f8", {"maxit": 40}),
+    "smooth_seed2": (2, 256, 512, 2, "f8", {"maxit": 700}),
+    "smooth_ragged": (5, 193, 391, 2, "f8", {"alpha0": mp_step(193, 391), "maxit": 60}),
+    "smooth_l3": (8, 96, 260, 3, "f8", {"alpha0": mp_step(96, 260), "maxit": 60}),
+    "smooth_fixed": (97006855, 256, 512, 2, "f8", {"step_type": "fixed", "alpha0": 5e-4, "maxit": 400}),
+    "smooth_dim2": (97006855, 256, 512, 2, "f8", {"step_type": "diminishing2", "alpha0": 5e-4, "maxit": 1100}),
+    "smooth_f32in": (97006855, 256, 512, 2, "f4", {"maxit": 200}),
+}
+
+
 def run_case(name):
-    seed, m, n, l, dt, opts = CASES[name]
+    if name in SMOOTH_CASES:
+        seed, m, n, l, dt, opts = SMOOTH_CASES[name]
+        algos = REF_SMOOTH
+    else:
+        seed, m, n, l, dt, opts = CASES[name]
+        algos = REF
+    return _run(name, seed, m, n, l, dt, opts, algos)
+
+
+def _run(name, seed, m, n, l, dt, opts, algos):
     A, b, x0, u, mu = gen_data(seed, m, n, l)
     if dt == "f4":  # round the inputs to fp32, then run the reference in fp64 on them
         A, b, x0 = (z.astype(np.float32).astype(np.float64) for z in (A, b, x0))
     rec = {"seed": seed, "m": m, "n": n, "l": l, "in_dtype": dt, "mu": mu,
            "opts_keys": np.array(sorted(opts.keys())),
            "opts_vals": np.array([str(opts[k]) for k in sorted(opts.keys())])}
-    for algo, fn in REF.items():
+    for algo, fn in algos.items():
         A_keep, b_keep, x0_keep = A.copy(), b.copy(), x0.copy()
         x, k, out = fn(x0, A, b, mu, dict(opts))
         assert np.array_equal(A, A_keep) and np.array_equal(b, b_keep) and np.array_equal(x0, x0_keep)
@@ -83,6 +109,6 @@ def run_case(name):
 
 
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(CASES)
+    names = sys.argv[1:] or list(CASES) + list(SMOOTH_CASES)
     for nm in names:
         np.savez_compressed(os.path.join(HERE, "ref_%s.npz" % nm), **run_case(nm))

@@ -28,11 +28,11 @@ class Ctrl(C.Structure):
 
 class SolveConst(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("algo", "step_type", "maxit", "stable_cap", "ls_cap", "hist_cap")] + \
-               [(n, C.c_double) for n in ("thres", "alpha0", "ftol", "atten", "mu0")]
+               [(n, C.c_double) for n in ("thres", "alpha0", "ftol", "atten", "mu0", "delta")]
 
 
 class Reduced(C.Structure):
-    _fields_ = [(n, C.c_double) for n in ("rr", "gd", "dd", "reg", "cnt", "gbase")]
+    _fields_ = [(n, C.c_double) for n in ("rr", "gd", "dd", "reg", "cnt", "gbase", "sx", "sy")]
 
 
 class DecideOut(C.Structure):
@@ -41,6 +41,7 @@ class DecideOut(C.Structure):
 
 ACT_NONE, ACT_RETRY, ACT_ITERATE, ACT_FINISH = 0, 1, 2, 3
 STEP_ID = {"line_search": 0, "fixed": 1, "diminishing": 2, "diminishing2": 3}
+ALGO_ID = {"ProxGD": 0, "FProxGD": 1, "FGD": 2, "GD": 3, "SGD": 4}
 _shim = None
 
 
@@ -69,10 +70,12 @@ def emulate(algo, x0, A, b, mu0, opts=None, matmul=None, rmatmul=None, n_shards=
     fwd = matmul or (lambda X: A @ X)
     bwd = rmatmul or (lambda R: A.T @ R)
     n, l = x0.shape
-    sc = SolveConst(algo=1 if algo == "FProxGD" else 0, step_type=STEP_ID[o["step_type"]], maxit=o["maxit"],
-                    stable_cap=o["stable_len_threshold"], ls_cap=o["maxit_line_search_iter"],
+    accel = algo in ("FProxGD", "FGD")
+    delta = float(o.get("delta", 0.0))
+    sc = SolveConst(algo=ALGO_ID[algo], step_type=STEP_ID[o["step_type"]], maxit=o["maxit"],
+                    stable_cap=o["stable_len_threshold"], ls_cap=o.get("maxit_line_search_iter", 0),
                     hist_cap=3 * o["maxit"] + 8, thres=o["thres"], alpha0=o["alpha0"], ftol=o["ftol"],
-                    atten=o["line_search_attenuation_coeffi"], mu0=mu0)
+                    atten=o.get("line_search_attenuation_coeffi", 1.0), mu0=mu0, delta=delta)
     f_hist = np.zeros(sc.hist_cap)
     f_best = np.zeros(sc.hist_cap)
     ctrl = [Ctrl(), Ctrl()]
@@ -86,7 +89,8 @@ def emulate(algo, x0, A, b, mu0, opts=None, matmul=None, rmatmul=None, n_shards=
     # init: candidate of cur=0 is slot 1
     st[1]["x"] = np.array(x0, dtype=np.float64)
     st[1]["xt"] = orc.hard_threshold(st[1]["x"], o["thres"])
-    scal = dict(gd=0.0, dd=0.0, reg=float(np.sum(orc.row_norms(st[1]["x"]))), mx=float(np.max(np.abs(st[1]["x"]))))
+    scal = dict(gd=0.0, dd=0.0, reg=float(np.sum(orc.row_norms(st[1]["x"]))), mx=float(np.max(np.abs(st[1]["x"]))),
+                sx=0.0, sy=0.0)
 
     def forward(cand):
         prod = fwd(np.concatenate([st[cand]["x"], st[cand]["xt"]], axis=1))
@@ -100,7 +104,8 @@ def emulate(algo, x0, A, b, mu0, opts=None, matmul=None, rmatmul=None, n_shards=
     n_slots = 0
     while True:
         cin, cout = ctrl[j & 1], ctrl[(j + 1) & 1]
-        red = Reduced(rr=rr, gd=scal["gd"], dd=scal["dd"], reg=scal["reg"], cnt=cnt, gbase=gy[cin.gy_sel])
+        red = Reduced(rr=rr, gd=scal["gd"], dd=scal["dd"], reg=scal["reg"], cnt=cnt, gbase=gy[cin.gy_sel],
+                      sx=scal["sx"], sy=scal["sy"])
         act = DecideOut()
         lib.shim_decide(C.byref(sc), C.byref(cin), C.byref(red), float(n * l), C.byref(cout), C.byref(act),
                         f_hist.ctypes.data, f_best.ctypes.data)
@@ -114,7 +119,7 @@ def emulate(algo, x0, A, b, mu0, opts=None, matmul=None, rmatmul=None, n_shards=
         if act.action == ACT_ITERATE:
             nc = act.new_cur
             Axn, Axnt, Axt_old = AX[nc]["Ax"], AX[nc]["Axt"], AX[1 - nc]["Axt"]
-            if sc.algo == 1:
+            if accel:
                 if act.reset_v:
                     Av = Axn.copy()
                     st[nc]["v"] = st[nc]["x"].copy()
@@ -127,10 +132,10 @@ def emulate(algo, x0, A, b, mu0, opts=None, matmul=None, rmatmul=None, n_shards=
             gy[cout.gy_sel] = float(np.sum(r ** 2))
             grad = bwd(r)
         # transposed epilogue (fresh or retry) writes the candidates of slot 1-cur
-        xn, xnt, vn, gd, dd, reg, mx = orc.prox_epilogue(algo, grad, st[cur]["xt"], st[cur]["v"], cout.theta,
-                                                         cout.t, cout.mu, o["thres"])
+        xn, xnt, vn, gd, dd, reg, mx, sx, sy = orc.prox_epilogue(algo, grad, st[cur]["xt"], st[cur]["v"], cout.theta,
+                                                                 cout.t, cout.mu, o["thres"], delta, full=True)
         st[1 - cur].update(x=xn, xt=xnt, v=vn)
-        scal = dict(gd=float(gd), dd=float(dd), reg=float(reg), mx=float(mx))
+        scal = dict(gd=float(gd), dd=float(dd), reg=float(reg), mx=float(mx), sx=float(sx), sy=float(sy))
         rr, cnt = forward(1 - cur)
     fin = ctrl[j & 1]
     x = st[fin.cur]["x"]

@@ -33,7 +33,7 @@ def test_every_declared_symbol_is_exported_and_bound(lib):
 
 def test_pod_layouts_match_the_header(lib):
     from glprox import _lib
-    assert C.sizeof(_lib.GlpOpts) == 56 and C.sizeof(_lib.GlpStepParams) == 40
+    assert C.sizeof(_lib.GlpOpts) == 64 and C.sizeof(_lib.GlpStepParams) == 40
     assert C.sizeof(_lib.GlpResult) == 80
     for algo, maxit, alpha0, att in ((0, 2500, 2e-3, 0.9), (1, 1500, 1e-3, 0.98)):
         o = _lib.GlpOpts()

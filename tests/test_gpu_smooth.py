@@ -1,0 +1,82 @@
+"""GPU parity tests of SURVEY.md 8(f) row 1: gl_FGD_primal / gl_GD_primal / gl_SGD_primal through the
+drop-in modules, on the streaming and the persistent backend, against golden vectors of the unmodified
+reference.  Same bars as the proximal solvers (fp64: 1e-10, fp32: 1e-5); FGD's long runs are chaotic
+under any re-rounding (see tests/test_smooth_cpu.py) and are held to the final objective."""
+import numpy as np
+import pytest
+
+from conftest import golden_inputs, load_golden
+from oracle import glprox_oracle as orc
+
+pytestmark = pytest.mark.gpu
+FGD_LONG = {"smooth_fixed", "smooth_dim2", "smooth_seed2", "smooth_fixture"}
+
+
+def _fn(algo):
+    import gl_FGD_primal, gl_GD_primal, gl_SGD_primal
+    return {"FGD": gl_FGD_primal.gl_FGD_primal, "GD": gl_GD_primal.gl_GD_primal, "SGD": gl_SGD_primal.gl_SGD_primal}[algo]
+
+
+@pytest.mark.parametrize("backend", ["stream", "persistent"])
+@pytest.mark.parametrize("algo", ["FGD", "GD", "SGD"])
+@pytest.mark.parametrize("name", ["smooth_maxit40", "smooth_ragged", "smooth_l3", "smooth_fixed", "smooth_dim2",
+                                  "smooth_seed2", "smooth_fixture"])
+def test_fp64_smooth_solvers_match_reference(name, algo, backend):
+    if backend == "stream" and name in ("smooth_fixture", "smooth_dim2", "smooth_seed2"):
+        pytest.skip("thousands of launch-bound iterations; the persistent backend covers the long cases")
+    rec = load_golden(name)
+    A, b, x0, u, mu = golden_inputs(rec)
+    keep = (A.copy(), b.copy(), x0.copy())
+    x, k, out = _fn(algo)(x0, A, b, mu, dict(rec["opts"], backend=backend))
+    assert np.array_equal(A, keep[0]) and np.array_equal(b, keep[1]) and np.array_equal(x0, keep[2])
+    assert out["glprox"]["backend"] == backend and isinstance(k, int)
+    fh, ref = np.asarray(out["f_hist"]), rec[algo + "_f_hist"]
+    assert np.array_equal(np.asarray(out["f_hist_best"]), np.minimum.accumulate(fh))
+    if algo == "FGD" and name in FGD_LONG:
+        assert abs(k - int(rec[algo + "_k"])) <= 0.15 * int(rec[algo + "_k"]) and len(fh) == k
+        assert abs(out["fval"] - rec[algo + "_fval"]) <= 1e-6 * abs(rec[algo + "_fval"])
+        assert np.max(np.abs(fh[:100] - ref[:100]) / np.abs(ref[:100])) <= 1e-10
+        return
+    assert k == int(rec[algo + "_k"]) and fh.shape == ref.shape
+    assert np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-10
+    assert abs(out["fval"] - rec[algo + "_fval"]) <= 1e-10 * abs(rec[algo + "_fval"])
+    assert np.max(np.abs(x - rec[algo + "_x"])) <= 1e-8
+    ax = np.abs(x)
+    assert np.array_equal(np.flatnonzero((ax > 1e-6 * ax.max()).any(axis=1)), rec[algo + "_support_rule"])
+    assert out["glprox"]["n_tpass"] <= k
+
+
+@pytest.mark.parametrize("backend", ["stream", "persistent"])
+@pytest.mark.parametrize("algo", ["FGD", "GD", "SGD"])
+def test_fp32_smooth_solvers_match_fp64_reference_on_rounded_inputs(algo, backend):
+    rec = load_golden("smooth_f32in")
+    A, b, x0, u, mu = golden_inputs(rec)
+    x, k, out = _fn(algo)(x0.astype(np.float32), A.astype(np.float32), b.astype(np.float32), mu,
+                          dict(rec["opts"], backend=backend))
+    assert x.dtype == np.float32
+    ref_f = rec[algo + "_fval"]
+    assert abs(out["fval"] - ref_f) <= 1e-5 * abs(ref_f)
+    f_true = orc.objective(A, b, x.astype(np.float64), mu)
+    assert abs(f_true - ref_f) <= 1e-5 * abs(ref_f)
+    if algo != "FGD":
+        assert k == int(rec[algo + "_k"])
+
+
+def test_smooth_edge_cases():
+    A, b, x0, u, mu = orc.gen_data(3, 32, 64, 2)
+    for algo in ("GD", "SGD"):
+        x, k, out = _fn(algo)(x0, A, b, mu, {"maxit": 0})
+        assert k == 0 and np.array_equal(x, x0) and out["f_hist"] == []
+        with pytest.raises(ValueError):
+            _fn(algo)(x0, A, b, mu, {"step_type": "line_search"})
+    with pytest.raises(UnboundLocalError):
+        _fn("FGD")(x0, A, b, mu, {"maxit": 0})
+    # a mid-size problem through the streaming kernels, fp32 and fp64, against the oracle restatement
+    A, b, x0, u, mu = orc.gen_data(11, 600, 2500, 2)
+    opts = {"maxit": 25, "alpha0": float(1.0 / (np.sqrt(600) + np.sqrt(2500)) ** 2)}
+    for algo in ("FGD", "GD", "SGD"):
+        xr, kr, outr = orc.solve_smooth(algo, x0, A, b, mu, opts)
+        x, k, out = _fn(algo)(x0, A, b, mu, opts)
+        assert k == kr and out["glprox"]["backend"] == "stream"
+        assert np.max(np.abs(np.asarray(out["f_hist"]) - np.asarray(outr["f_hist"])) / np.abs(outr["f_hist"])) <= 1e-10
+        assert np.max(np.abs(x - xr)) <= 1e-9

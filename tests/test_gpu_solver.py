@@ -193,3 +193,66 @@ def test_large_size_properties_fp32():
     rhs = (x.double() * G).sum().item()
     assert abs(lhs - rhs) <= 1e-5 * (Ax.abs() * r.abs()).sum().item()
     prob.close()
+
+
+def test_full_size_properties_c4_fp32():
+    """BASELINE.json configs[3] at full size (m=32768 n=131072 l=2 fp32, 17 GB of A): no CPU oracle can run
+    this, so parity rests on size-independent properties -- forward/transposed adjointness, linearity of the
+    forward stream, the solver's reported objective re-evaluated independently through K1, a monotone
+    objective under the 1/L step, and run-to-run bit-reproducibility."""
+    import ctypes as C
+    import torch
+    from glprox import GroupLassoProblem, _lib
+    if torch.cuda.mem_get_info()[0] < 40e9:
+        pytest.skip("needs 40 GB of free HBM")
+    lib = _lib.load()
+    m, n, l = 32768, 131072, 2
+    st = torch.cuda.current_stream().cuda_stream
+    A = torch.empty((m, n), dtype=torch.float32, device="cuda")
+    _lib.check(lib.glp_randn(A.data_ptr(), _lib.GLP_F32, m, n, n, 12345, 0, 0, st))
+    g = torch.Generator(device="cuda").manual_seed(9)
+    u = torch.zeros((n, l), device="cuda")
+    idx = torch.randperm(n, generator=g, device="cuda")[: n // 10]
+    u[idx] = torch.randn((n // 10, l), generator=g, device="cuda")
+    prob = GroupLassoProblem(A, torch.zeros((m, l), device="cuda"))
+    null = C.c_void_p()
+
+    def fwd(x):
+        out = torch.empty((m, x.shape[1]), dtype=torch.float64, device="cuda")
+        _lib.check(lib.glp_fwd(prob.handle, x.contiguous().data_ptr(), x.shape[1], out.data_ptr(), None))
+        return out
+
+    def tps(r):
+        out = torch.empty((n, l), dtype=torch.float64, device="cuda")
+        _lib.check(lib.glp_tpass_prox(prob.handle, None, r.contiguous().data_ptr(), out.data_ptr(), null, null, null, null, null, null))
+        return out
+
+    Au = fwd(u)
+    # linearity: A(2u - w) == 2Au - Aw (fp32 operands, fp64 outputs)
+    w = torch.randn((n, l), generator=g, device="cuda")
+    lin = fwd(2 * u - w) - (2 * Au - fwd(w))
+    assert lin.abs().max().item() <= 2e-5 * (2 * Au).abs().max().item()
+    # adjointness <A u, r> == <u, A^T r>
+    r = torch.randn((m, l), generator=g, device="cuda", dtype=torch.float64)
+    lhs = (Au * r.float().double()).sum().item()
+    rhs = (u.double() * tps(r)).sum().item()
+    assert abs(lhs - rhs) <= 1e-5 * (Au.abs() * r.abs()).sum().item()
+    prob.close()
+    # solver: 2 x 9 iterations, bit-identical reruns, monotone objective, independent re-evaluation
+    b = Au.float()
+    prob = GroupLassoProblem(A, b)
+    x0 = torch.randn((n, l), generator=g, device="cuda")
+    mu, opts = 1e-2, {"maxit": 3, "alpha0": float(1.0 / (np.sqrt(m) + np.sqrt(n)) ** 2)}
+    x1, k1, o1 = prob.solve("FProxGD", x0, mu, opts)
+    x2, k2, o2 = prob.solve("FProxGD", x0, mu, opts)
+    assert k1 == k2 == 9 and torch.equal(x1, x2) and o1["f_hist"] == o2["f_hist"]
+    xp, kp, op_ = prob.solve("ProxGD", x0, mu, opts)
+    fp = np.asarray(op_["f_hist"])
+    assert np.all(np.diff(fp) <= 0) and np.all(np.isfinite(o1["f_hist"]))
+    assert kp + 1 <= op_["glprox"]["n_fwd"] <= kp + 3 and op_["glprox"]["n_tpass"] == kp   # step ~ 1/L: first trials accepted
+    rr = torch.zeros(1, dtype=torch.float64, device="cuda")
+    Ax = torch.empty((m, l), dtype=torch.float64, device="cuda")
+    _lib.check(lib.glp_fwd(prob.handle, x1.data_ptr(), l, Ax.data_ptr(), rr.data_ptr()))
+    f_chk = 0.5 * rr.item() + mu * x1.double().norm(dim=1).sum().item()
+    assert abs(f_chk - o1["fval"]) <= 1e-6 * abs(f_chk)
+    prob.close()
