@@ -70,6 +70,23 @@ GLP_HDI double stage_mu(int stage, double mu0) {
   return stage == 0 ? GLP_XMUL(100.0, mu0) : (stage == 1 ? GLP_XMUL(10.0, mu0) : mu0);
 }
 
+// Opt-in Barzilai-Borwein step (step_type "bb", gl_ProxGD_primal only; the reference has no such rule):
+// first trial step of the next line search = ||d||^2 / ||A d||^2 for the displacement d = xn - x just
+// accepted.  Both norms come from scalars the line search already reduced: ||d||^2 = t^2 ||gt||^2, and
+// since g is quadratic, g(xn) = g(x) + <grad, d> + 0.5 ||A d||^2 with <grad, d> = -t <grad, gt>, i.e.
+// ||A d||^2 = rr_new - rr_base + 2 t <grad, gt>: no extra stream and no extra reduction.
+// Safeguards: a non-positive / non-finite curvature falls back to alpha0; the step is kept within
+// [alpha0 * 1e-3, alpha0 * 1e3]; the usual sufficient-decrease backtracking still runs on it.
+GLP_HDI double bb_step(const SolveConst& sc, double t, const Reduced& red) {
+  const double num = GLP_XMUL(GLP_XMUL(t, t), red.dd);
+  const double den = GLP_XADD(GLP_XSUB(red.rr, red.gbase), GLP_XMUL(GLP_XMUL(2.0, t), red.gd));
+  if (!(den > 0.0) || !(num > 0.0)) return sc.alpha0;
+  const double bb = GLP_XDIV(num, den);
+  const double lo = GLP_XMUL(sc.alpha0, 1e-3), hi = GLP_XMUL(sc.alpha0, 1e3);
+  if (!(bb == bb)) return sc.alpha0;
+  return bb < lo ? lo : (bb > hi ? hi : bb);
+}
+
 // f_hist may be null (then values are not stored).  size_total = n_total * l.
 GLP_HDI void decide_step(const SolveConst& sc, const Ctrl& in, const Reduced& red, double size_total,
                          Ctrl& out, DecideOut& act, double* f_hist, double* f_hist_best) {
@@ -109,6 +126,7 @@ GLP_HDI void decide_step(const SolveConst& sc, const Ctrl& in, const Reduced& re
   out.retry = 0;
   out.first_commit = 0;
   if (accel && !in.first_commit) out.t_k = in.t;
+  if (sc.step_type == STEP_BB && !in.first_commit) out.t_k = bb_step(sc, in.t, red);
   out.f_cur = GLP_XADD(GLP_XMUL(0.5, red.rr), GLP_XMUL(sc.mu0, red.reg));
   out.s_cur = GLP_XDIV(red.cnt, size_total);
 
@@ -161,8 +179,8 @@ GLP_HDI void decide_step(const SolveConst& sc, const Ctrl& in, const Reduced& re
   if (plain && (sc.step_type == 1 || out.mu > sc.mu0)) {   // gl_GD_primal.py:67-70 / gl_SGD_primal.py:65-68
     out.t = sc.alpha0;
     out.tested = 0;
-  } else if (sc.step_type == 0) {  // line_search
-    out.t = accel ? out.t_k : sc.alpha0;
+  } else if (sc.step_type == 0 || sc.step_type == STEP_BB) {  // line_search (ProxGD restarts at alpha0 or the BB step)
+    out.t = (accel || sc.step_type == STEP_BB) ? out.t_k : sc.alpha0;
     out.tested = sc.ls_cap > 0 ? 1 : 0;
   } else {
     const int it = (out.inner > 1000 ? out.inner : 1000) - 999;

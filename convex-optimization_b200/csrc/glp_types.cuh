@@ -38,6 +38,7 @@ struct Ctrl {
 // (sx / sy: smoothed regulariser at the candidate / base point, FGD only).
 constexpr int SCAL_STRIDE = 8;
 enum { ALGO_PROXGD = 0, ALGO_FPROXGD = 1, ALGO_FGD = 2, ALGO_GD = 3, ALGO_SGD = 4 };
+enum { STEP_LINE_SEARCH = 0, STEP_FIXED = 1, STEP_DIMINISHING = 2, STEP_DIMINISHING2 = 3, STEP_BB = 4 };
 
 struct SolveConst {
   int32_t algo;          // ALGO_*

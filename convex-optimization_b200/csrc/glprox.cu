@@ -9,6 +9,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <cmath>
+#include <limits>
 #include <thread>
 #include <vector>
 
@@ -17,6 +19,7 @@
 #include "glp_decide.cuh"
 #include "glp_fwd.cuh"
 #include "glp_gemm.cuh"
+#include "glp_metrics.cuh"
 #include "glp_misc.cuh"
 #include "glp_persist.cuh"
 #include "glp_tpass.cuh"
@@ -704,8 +707,10 @@ static int enqueue_gather(glp_handle* h, const Ctrl* ctrl) {
 static int phase_prepare(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o) {
   if (h == nullptr || x0_dev == nullptr || o == nullptr) return fail(GLP_ERR_ARG, "null argument");
   if (algo < GLP_PROXGD || algo > GLP_SGD) return fail(GLP_ERR_ARG, "unknown algo %d", algo);
-  if (o->step_type < GLP_STEP_LINE_SEARCH || o->step_type > GLP_STEP_DIMINISHING2)
+  if (o->step_type < GLP_STEP_LINE_SEARCH || o->step_type > GLP_STEP_BB)
     return fail(GLP_ERR_ARG, "unsupported step_type %d", o->step_type);
+  if (o->step_type == GLP_STEP_BB && algo != GLP_PROXGD)
+    return fail(GLP_ERR_ARG, "step_type bb is an opt-in of gl_ProxGD_primal only");
   if ((algo == GLP_GD || algo == GLP_SGD) && o->step_type == GLP_STEP_LINE_SEARCH)
     return fail(GLP_ERR_ARG, "gl_GD_primal / gl_SGD_primal have no line search (step_type fixed | diminishing | diminishing2)");
   if (o->maxit < 0 || o->maxit > (1 << 26)) return fail(GLP_ERR_ARG, "maxit out of range");
@@ -1519,6 +1524,57 @@ extern "C" int glp_tf32_split(void* stream, const void* src, int64_t rows, int64
                                                 static_cast<float*>(lo), rows, cols, ld_src, ld_dst);
   }
   CU_TRY(cudaGetLastError());
+  return GLP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// caller-side metrics (code/main.py:30-34,48-50) on the device
+// ------------------------------------------------------------------------------------------------
+extern "C" int glp_metrics_eval(glp_handle* h, const void* x_dev, const void* ref_dev, double mu,
+                                double max_abs_override, glp_metrics* out) {
+  if (h == nullptr || x_dev == nullptr || out == nullptr) return fail(GLP_ERR_ARG, "bad argument");
+  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
+  CU_TRY(cudaSetDevice(h->device));
+  const Geom& g = h->g;
+  const int64_t n = g.n, total = int64_t(g.n) * g.l;
+  const int grid = int(std::max<int64_t>(1, std::min<int64_t>((n + MET_THREADS - 1) / MET_THREADS, 148 * 4)));
+  const bool sharded = h->comm.world > 1;
+  // [grid][MET_STRIDE] records, 8 folded values, rr, then (unsharded) the m x l product
+  const size_t words = size_t(grid) * MET_STRIDE + 16 + (sharded ? 0 : size_t(g.m) * g.l);
+  double* buf = nullptr;
+  CU_TRY(cudaMalloc(&buf, words * sizeof(double)));
+  double* part = buf;
+  double* folded = buf + size_t(grid) * MET_STRIDE;
+  double* rr_dev = folded + 8;
+  double* ax = folded + 16;
+  int rc = GLP_OK;
+  cudaError_t ce = cudaMemsetAsync(buf, 0, (size_t(grid) * MET_STRIDE + 16) * sizeof(double), h->stream);
+  if (ce == cudaSuccess) {
+    if (h->dtype == GLP_F32) {
+      glp_metrics_sums_kernel<float><<<grid, MET_THREADS, 0, h->stream>>>(static_cast<const float*>(x_dev), static_cast<const float*>(ref_dev), n, g.l, part);
+      glp_metrics_count_kernel<float><<<grid, MET_THREADS, 0, h->stream>>>(static_cast<const float*>(x_dev), total, part, grid, max_abs_override);
+    } else {
+      glp_metrics_sums_kernel<double><<<grid, MET_THREADS, 0, h->stream>>>(static_cast<const double*>(x_dev), static_cast<const double*>(ref_dev), n, g.l, part);
+      glp_metrics_count_kernel<double><<<grid, MET_THREADS, 0, h->stream>>>(static_cast<const double*>(x_dev), total, part, grid, max_abs_override);
+    }
+    glp_metrics_fold_kernel<<<1, MET_THREADS, 0, h->stream>>>(part, grid, folded);
+    ce = cudaGetLastError();
+  }
+  if (ce == cudaSuccess && !sharded) rc = glp_fwd(h, x_dev, g.l, ax, rr_dev);
+  double host[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  if (ce == cudaSuccess && rc == GLP_OK) ce = cudaMemcpyAsync(host, folded, 9 * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+  if (ce == cudaSuccess && rc == GLP_OK) ce = cudaStreamSynchronize(h->stream);
+  cudaFree(buf);
+  if (rc != GLP_OK) return rc;
+  CU_TRY(ce);
+  out->sumsq_x = host[0]; out->sumsq_ref = host[1]; out->sumsq_diff = host[2];
+  out->reg = host[3]; out->max_abs = host[4]; out->count = host[5];
+  const double nan = std::numeric_limits<double>::quiet_NaN();
+  out->rr = sharded ? nan : host[8];
+  out->objective = sharded ? nan : 0.5 * host[8] + mu * host[3];
+  out->sparsity = total > 0 ? host[5] / double(total) : nan;
+  out->err_exact = ref_dev ? std::sqrt(host[2]) / (1.0 + std::sqrt(host[0])) : nan;
+  out->err_ref = ref_dev ? std::sqrt(host[2]) / (1.0 + std::sqrt(host[1])) : nan;
   return GLP_OK;
 }
 

@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(_HERE, "libglprox.so")
 
 GLP_F32, GLP_F64 = 0, 1
 GLP_PROXGD, GLP_FPROXGD, GLP_FGD, GLP_GD, GLP_SGD = 0, 1, 2, 3, 4
-STEP_TYPES = {"line_search": 0, "fixed": 1, "diminishing": 2, "diminishing2": 3}
+STEP_TYPES = {"line_search": 0, "fixed": 1, "diminishing": 2, "diminishing2": 3, "bb": 4}
 BACKENDS = {"auto": 0, "stream": 1, "persistent": 2}
 
 GLP_OK = 0
@@ -42,6 +42,11 @@ class GlpProfile(C.Structure):
     _fields_ = [("fwd_launches", C.c_int64), ("tpass_launches", C.c_int64), ("fwd_ms_sum", C.c_double),
                 ("fwd_ms_min", C.c_double), ("tpass_ms_sum", C.c_double), ("tpass_ms_min", C.c_double),
                 ("bytes_per_launch", C.c_double)]
+
+
+class GlpMetrics(C.Structure):
+    _fields_ = [(k, C.c_double) for k in ("sumsq_x", "sumsq_ref", "sumsq_diff", "reg", "max_abs", "count", "rr",
+                                          "objective", "sparsity", "err_exact", "err_ref")]
 
 
 class GlproxError(RuntimeError):
@@ -81,6 +86,7 @@ SIGNATURES = {
     "glp_nccl_unique_id": (_I, [_VP]),
     "glp_nccl_comm_create": (_I, [C.POINTER(_VP), _VP, _I, _I, _I]),
     "glp_nccl_comm_destroy": (_I, [_VP]),
+    "glp_metrics_eval": (_I, [_VP, _VP, _VP, _D, _D, C.POINTER(GlpMetrics)]),
     "glp_randn": (_I, [_VP, _I, _I64, _I64, _I64, C.c_uint64, _I64, _I64, _VP]),
 }
 

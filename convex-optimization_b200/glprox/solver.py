@@ -54,6 +54,8 @@ def pack_opts(algo, merged):
         # the reference logs "Unsupported type." and then dies with TypeError (gl_ProxGD_primal.py:100-101)
         logger.error("Unsupported type.")
         raise ValueError("unsupported step_type %r (expected one of %s)" % (st, sorted(_lib.STEP_TYPES)))
+    if st == "bb" and algo != "ProxGD":
+        raise ValueError("step_type 'bb' (Barzilai-Borwein first trial step, an additive opt-in) exists for gl_ProxGD_primal only")
     if algo in ("GD", "SGD"):
         if st == "line_search":  # the reference returns None as the step and dies with TypeError (gl_GD_primal.py:75-76)
             logger.error("Unsupported type.")
@@ -315,6 +317,55 @@ class GroupLassoProblem:
         fh = f_hist[:res.iters]
         _log_history(fh, res)
         return x, int(res.iters), _format_out(res, fh, tt)
+
+
+    def metrics(self, x, ref=None, mu=0.0, group=None):
+        """Driver metrics of code/main.py:30-34,48-50 for an iterate that stays on the device.
+
+        x, ref: (n_local, l) CUDA tensors (ref = the ground truth u, or another solver's solution).
+        Returns {"objective", "sparsity", "err_exact", "err_ref", "norm_x", ...}.  On a handle attached
+        to peers the shard sums are combined over `group` (sum / max of a dozen doubles; the count
+        is taken against the global max) and the objective is left to the solve's out["fval"]."""
+        import torch
+        lib = _lib.load()
+        xd = x.to(device=self.device, dtype=self.dtype).contiguous()
+        rd = None if ref is None else ref.to(device=self.device, dtype=self.dtype).contiguous()
+        if xd.shape != (self.n, self.l) or (rd is not None and rd.shape != xd.shape):
+            raise ValueError("x / ref must be (%d, %d)" % (self.n, self.l))
+        met = _lib.GlpMetrics()
+        call = lambda mx: _lib.check(lib.glp_metrics_eval(self._h, xd.data_ptr(), rd.data_ptr() if rd is not None else None,
+                                                          float(mu), float(mx), C.byref(met)))
+        with torch.cuda.device(self.device):
+            call(-1.0)
+            size = float(self.n * self.l)
+            sums = [met.sumsq_x, met.sumsq_ref, met.sumsq_diff, met.reg, met.count, size]
+            if getattr(self, "world", 1) > 1:
+                import torch.distributed as dist
+                on = self.device if dist.get_backend(group) == "nccl" else "cpu"
+                mx = torch.tensor([met.max_abs], dtype=torch.float64, device=on)
+                dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
+                call(float(mx.item()))
+                t = torch.tensor([met.sumsq_x, met.sumsq_ref, met.sumsq_diff, met.reg, met.count, size],
+                                 dtype=torch.float64, device=on)
+                dist.all_reduce(t, group=group)
+                sums = [float(v) for v in t.cpu()]
+                max_abs = float(mx.item())
+            else:
+                max_abs = met.max_abs
+        return combine_metrics(sums, max_abs, None if getattr(self, "world", 1) > 1 else met.rr, mu, ref is not None)
+
+
+def combine_metrics(sums, max_abs, rr, mu, has_ref):
+    """Finish the metrics from (sumsq_x, sumsq_ref, sumsq_diff, reg, count, size) totals."""
+    sx, sr, sd, reg, cnt, size = sums
+    nan = float("nan")
+    nx, nr, nd = np.sqrt(sx), np.sqrt(sr), np.sqrt(sd)
+    return {"objective": nan if rr is None else 0.5 * rr + mu * reg,
+            "sparsity": cnt / size if size else nan,
+            "err_exact": nd / (1.0 + nx) if has_ref else nan,   # main.py:49
+            "err_ref": nd / (1.0 + nr) if has_ref else nan,     # main.py:48 errfun(ref, x)
+            "norm_x": float(nx), "norm_ref": float(nr), "norm_diff": float(nd), "reg": reg,
+            "max_abs": max_abs, "count": int(cnt)}
 
 
 def shard_bounds(n, world, align=128):

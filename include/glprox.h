@@ -46,7 +46,11 @@ enum { GLP_F32 = 0, GLP_F64 = 1 };
  * (gl_FGD_primal.py, gl_GD_primal.py, gl_SGD_primal.py) */
 enum { GLP_PROXGD = 0, GLP_FPROXGD = 1, GLP_FGD = 2, GLP_GD = 3, GLP_SGD = 4 };
 /* step_type strings of gl_ProxGD_primal.py:78-101 / gl_FProxGD_primal.py:81-106 */
-enum { GLP_STEP_LINE_SEARCH = 0, GLP_STEP_FIXED = 1, GLP_STEP_DIMINISHING = 2, GLP_STEP_DIMINISHING2 = 3 };
+enum { GLP_STEP_LINE_SEARCH = 0, GLP_STEP_FIXED = 1, GLP_STEP_DIMINISHING = 2, GLP_STEP_DIMINISHING2 = 3,
+       /* additive opt-in (the reference has no such rule), gl_ProxGD_primal only: the line search of each
+        * iteration starts from the Barzilai-Borwein step ||d||^2/||A d||^2 of the displacement just
+        * accepted instead of alpha0; both norms come from the line-search scalars already on the device */
+       GLP_STEP_BB = 4 };
 enum { GLP_BACKEND_AUTO = 0, GLP_BACKEND_STREAM = 1, GLP_BACKEND_PERSISTENT = 2 };
 
 /* POD mirror of the reference's `opts` dict after the merge with default_opts
@@ -213,6 +217,31 @@ int glp_set_tensor_mode(glp_handle* h, int mode);
  * (hi[j][i], lo[j][i]) -- the resident A^T of the transposed pass. */
 int glp_tf32_split(void* stream, const void* src, int64_t rows, int64_t cols, int64_t ld_src, void* hi,
                    void* lo, int64_t ld_dst, int transpose);
+
+/* ---- caller-side metrics of the reference driver, evaluated on the device ----------------------
+ * Replaces, for an iterate that stays in HBM, the host lambdas of code/main.py:48-50 and obj_func
+ * (code/main.py:30-34); these are the columns of the per-solver log line / Markdown row
+ * (code/main.py:113-125, doc/report.md:439-447):
+ *   sparsity     = #{ |x| > 1e-6 max|x| } / (n l)                      main.py:50
+ *   err_exact    = ||x - ref||_F / (1 + ||x||_F)                        main.py:49  (ref = u)
+ *   err_ref      = ||ref - x||_F / (1 + ||ref||_F)                      main.py:48  errfun(ref, x)
+ *   objective    = 0.5 ||A x - b||_F^2 + mu sum_i ||x(i,:)||_2          main.py:30-34
+ * x_dev / ref_dev: n_local x l row-major arrays of the handle's dtype (ref_dev may be NULL).
+ * The raw sums are returned too so that column shards can be combined across ranks (sum / max);
+ * for a shard, pass the cross-rank max|x| as max_abs_override (>= 0) to get the global count, and
+ * leave the objective to the solve result (it is NaN here when the handle is attached to peers). */
+typedef struct glp_metrics {
+  double sumsq_x;    /* ||x||_F^2 of this shard */
+  double sumsq_ref;  /* ||ref||_F^2 */
+  double sumsq_diff; /* ||x - ref||_F^2 */
+  double reg;        /* sum_i ||x(i,:)||_2 */
+  double max_abs;    /* max |x| of this shard */
+  double count;      /* #{ |x| > 1e-6 * max } (max = max_abs_override if >= 0) */
+  double rr;         /* ||A x - b||_F^2 (NaN for a shard) */
+  double objective, sparsity, err_exact, err_ref; /* finished values for an unsharded handle */
+} glp_metrics;
+int glp_metrics_eval(glp_handle* h, const void* x_dev, const void* ref_dev, double mu,
+                     double max_abs_override, glp_metrics* out);
 
 /* ---- synthetic data: counter-based N(0,1) generator (bench / large fixtures) --------------------
  * Fills dst_dev[rows][ld] (dtype T) with value(seed, global_row, global_col) so that any

@@ -233,6 +233,9 @@ def solve(algo, x0, A, b, mu0, opts=None, trace=None):
     shrink_c, ls_cap, rule = (o["line_search_attenuation_coeffi"], o["maxit_line_search_iter"],
                               o["step_type"])
     accel = algo == "FProxGD"
+    if rule == "bb" and accel:
+        raise ValueError("step_type 'bb' exists for ProxGD only")
+    bb_t = alpha0   # opt-in BB rule (NOT in the reference): first trial step of the next line search
     hist = _History(ftol, o["stable_len_threshold"])
     steps = []
     xk = np.copy(x0)
@@ -256,9 +259,9 @@ def solve(algo, x0, A, b, mu0, opts=None, trace=None):
             else:
                 base = xk
             grad = A.T @ (A @ base - b)           # :129 / :140
-            if rule == "line_search":
+            if rule in ("line_search", "bb"):
                 g_base = smooth_part(A, b, base)
-                t = tk if accel else alpha0       # FProxGD carries t, ProxGD restarts (:91 / :94)
+                t = tk if accel else (bb_t if rule == "bb" else alpha0)   # FProxGD carries t, ProxGD restarts (:91 / :94)
                 for _ in range(ls_cap):
                     cand = group_prox(base - t * grad, t, mu, thres)
                     if accel:                     # gl_FProxGD_primal.py:96-99
@@ -275,6 +278,10 @@ def solve(algo, x0, A, b, mu0, opts=None, trace=None):
                 t = _open_loop_step(rule, alpha0, inner)
             x_new = group_prox(base - t * grad, t, mu, thres)   # :132 / :144
             steps.append(t)
+            if rule == "bb":                      # BB1 = ||d||^2 / ||A d||^2, by its definition (extra product)
+                d = x_new - base
+                num, den = float(np.sum(d * d)), float(np.sum((A @ d) ** 2))
+                bb_t = min(max(num / den, alpha0 * 1e-3), alpha0 * 1e3) if den > 0.0 and num > 0.0 else alpha0
             if accel:
                 vk = xk + (x_new - xk) / theta    # :145 (xk is the thresholded iterate)
                 tk = t

@@ -40,7 +40,7 @@ class DecideOut(C.Structure):
 
 
 ACT_NONE, ACT_RETRY, ACT_ITERATE, ACT_FINISH = 0, 1, 2, 3
-STEP_ID = {"line_search": 0, "fixed": 1, "diminishing": 2, "diminishing2": 3}
+STEP_ID = {"line_search": 0, "fixed": 1, "diminishing": 2, "diminishing2": 3, "bb": 4}
 ALGO_ID = {"ProxGD": 0, "FProxGD": 1, "FGD": 2, "GD": 3, "SGD": 4}
 _shim = None
 
