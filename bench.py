@@ -38,9 +38,10 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--m", type=int, default=32768)
-    ap.add_argument("--n", type=int, default=131072)
-    ap.add_argument("--l", type=int, default=2)
+    # --rows / --cols: spellings to use under torchrun, whose own parser claims the prefix "--m"
+    ap.add_argument("--m", "--rows", dest="m", type=int, default=32768)
+    ap.add_argument("--n", "--cols", dest="n", type=int, default=131072)
+    ap.add_argument("--l", "--rhs", dest="l", type=int, default=2)
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
     ap.add_argument("--algo", default="FProxGD", choices=["FProxGD", "ProxGD"])
     ap.add_argument("--maxit", type=int, default=50, help="iterations per continuation stage in one step")
@@ -229,11 +230,11 @@ def run_ours(args):
                 "bytes_per_launch": prof.bytes_per_launch,
                 "whole_iteration_GBps": 2.0 * prof.bytes_per_launch * value / 1e9}
 
-    if args.l >= 16 and args.dtype == "f32" and world == 1:
+    if args.l >= 16 and args.dtype == "f32":
         # wide multi-RHS mode: both products run on tcgen05 (3xTF32); the bounding roofline is the tensor pipe
         passes = 3
         n_it = max(int(prof.tpass_launches), 1)
-        flops = passes * 2.0 * args.m * args.n * 3 * args.l * n_it
+        flops = passes * 2.0 * args.m * A.shape[1] * 3 * args.l * n_it   # this rank's column shard
         t_s = (prof.fwd_ms_sum + prof.tpass_ms_sum) * 1e-3
         tf = flops / max(t_s, 1e-12) / 1e12
         tpeak = float(peaks.get("bf16_tflops", 1590.0)) / 2.0
@@ -252,8 +253,11 @@ def run_ours(args):
                                        args.algo, args.m, args.n, args.l, args.dtype, args.maxit, 3 * args.maxit),
                        "sharding": "column groups of A / row groups of x over %d rank(s)" % world,
                        "exchange": "none (1 GPU)" if world == 1 else
-                                   "m x 2l partial products + 5 scalars pushed into peer mailboxes over NVLink from "
-                                   "inside the forward kernel; rank-ordered sum on every rank; no NCCL on the data path",
+                                   ("reduce-scatter + all-gather of the m x 2l partial products over row slices, pushed "
+                                    "through peer mailboxes over NVLink (3 small kernels per forward product); no NCCL on "
+                                    "the data path" if args.l >= 16 and args.dtype == "f32" else
+                                    "m x 2l partial products + 5 scalars pushed into peer mailboxes over NVLink from "
+                                    "inside the forward kernel; rank-ordered sum on every rank; no NCCL on the data path"),
                        "l2_policy": "A (%.1f GB per rank) is far larger than the 126 MB L2; no flush needed" % (
                            A.numel() * A.element_size() / 1e9)},
             "iterations_per_step": iters // max(args.steps, 1), "final_objective": fval,

@@ -15,6 +15,9 @@
 //   warps2-9 epilogue: tcgen05.ld 32 lanes x 16 columns at a time into fp64 REGISTER accumulators (64 per
 //            thread) that live across the K chunks of a tile; the chunk accumulator is double buffered in
 //            TMEM so the drain of chunk i overlaps the MMAs of chunk i+1; coalesced planar fp64 stores
+// Work decomposition: items = column groups (NT columns each) x K splits x M tiles, dealt round-robin to
+// the persistent CTAs.  148 SMs rarely divide the tile count (128 tiles -> 86 % of the SMs busy), so K
+// is split until the item count fills whole waves; partial products are summed in split order afterwards.
 // Precision: kind::tf32 keeps 10 mantissa bits of each operand and the tensor core accumulates in fp32
 // with truncation (measured: a relative bias of ~(K/8)*2^-24 on the result).  PASSES = 3 runs the
 // error-compensated product  P.Q ~= Ph.Qh + (Ph.Ql + Pl.Qh)  on hi/lo fp32 splits resident in HBM; the
@@ -43,7 +46,10 @@ struct GemmArgs {
   const Ctrl* ctrl;                         // nullable
   double* D_alt;                            // role 1: D = ctrl->cur ? D : D_alt  (candidate product buffer 1 - cur)
   int32_t role;                             // 0 plain, 1 forward (skip when done), 2 transposed (skip when done or retry)
-  int32_t pad;
+  // split-K: work item = (column group, K split, M tile); split s writes its partial product to
+  // D + s * split_stride (the caller sums the partials in split order: glp_sum_splits_kernel)
+  int32_t splits;                           // >= 1
+  int64_t split_stride;                     // doubles between the partial outputs
 };
 
 template <int NT, int PASSES> constexpr int gemm_stage_bytes() {
@@ -145,6 +151,42 @@ __global__ void glp_transpose_split_kernel(const float* __restrict__ src, float*
   }
 }
 
+// work item w -> (K split, M tile, column group), column group fastest: the CTAs that take the column
+// groups of one P tile run side by side, so P is read from HBM once and from L2 by the others (with
+// N = 2l = 256 the product would otherwise stream A twice and turn HBM-bound); neighbouring CTAs also
+// share the Q slices of their K range.  Split s covers the chunks [s*nchunks/S, (s+1)*nchunks/S).
+struct GemmItem { int64_t group, split, tile, ch0, ch1, kb0, kb1; };
+__device__ __forceinline__ GemmItem gemm_item(int64_t w, int64_t tiles, int64_t G, int64_t S, int64_t nchunks, int64_t kc,
+                                              int64_t nkb) {
+  GemmItem it;
+  const int64_t ts = w / G;
+  it.group = w - ts * G;
+  it.split = ts / tiles;
+  it.tile = ts - it.split * tiles;
+  it.ch0 = it.split * nchunks / S;
+  it.ch1 = (it.split + 1) * nchunks / S;
+  it.kb0 = it.ch0 * kc;
+  it.kb1 = it.ch1 * kc < nkb ? it.ch1 * kc : nkb;
+  return it;
+}
+
+// out[i] = sum_s part[s * stride + i] in split order (fixed, deterministic); solver launches pick the
+// destination / skip from the control block exactly like the product kernel.
+__global__ void glp_sum_splits_kernel(const double* __restrict__ part, int splits, int64_t stride, int64_t M, int N,
+                                      int64_t ldd, double* out, double* out_alt, const Ctrl* ctrl, int role) {
+  if (ctrl != nullptr) {
+    if (ctrl->done || (role == 2 && ctrl->retry)) return;
+    if (role == 1 && ctrl->cur == 0) out = out_alt;
+  }
+  const int64_t total = M * N;
+  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t col = e / M, i = col * ldd + (e - col * M);
+    double v = part[i];
+    for (int s = 1; s < splits; ++s) v += part[s * stride + i];
+    out[i] = v;
+  }
+}
+
 template <int NT, int PASSES>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_constant__ CUtensorMap tmPl,
@@ -179,6 +221,9 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
   const int64_t nkb = (a.K + GEMM_BK - 1) / GEMM_BK;
   const int64_t kc = a.k_chunk_blocks > 0 ? a.k_chunk_blocks : nkb;
   const int64_t nchunks = (nkb + kc - 1) / kc;
+  const int64_t S = a.splits > 1 ? a.splits : 1;
+  const int64_t G = (a.N + NT - 1) / NT;
+  const int64_t items = G * S * tiles;
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
@@ -199,17 +244,18 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
       prefetch_tensormap(&tmPh); prefetch_tensormap(&tmQh);
       const uint64_t pol_stream = policy_evict_first(), pol_keep = policy_evict_normal();
       int stage = 0; uint32_t phase = 0;
-      for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-        for (int64_t kb = 0; kb < nkb; ++kb) {
+      for (int64_t w = blockIdx.x; w < items; w += gridDim.x) {
+        const GemmItem it = gemm_item(w, tiles, G, S, nchunks, kc, nkb);
+        for (int64_t kb = it.kb0; kb < it.kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1u, a.fault);
           mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
           uint8_t* s = smem + stage * STAGE_BYTES;
-          const int32_t k0 = int32_t(kb * GEMM_BK), r0 = int32_t(tile * GEMM_BM);
+          const int32_t k0 = int32_t(kb * GEMM_BK), r0 = int32_t(it.tile * GEMM_BM), q0 = int32_t(it.group * NT);
           tma_load_2d(s, &tmPh, &full[stage], k0, r0, pol_stream);
-          tma_load_2d(s + P_BYTES, &tmQh, &full[stage], k0, 0, pol_keep);
+          tma_load_2d(s + P_BYTES, &tmQh, &full[stage], k0, q0, pol_keep);
           if (PASSES == 3) {
             tma_load_2d(s + P_BYTES + Q_BYTES, &tmPl, &full[stage], k0, r0, pol_stream);
-            tma_load_2d(s + 2 * P_BYTES + Q_BYTES, &tmQl, &full[stage], k0, 0, pol_keep);
+            tma_load_2d(s + 2 * P_BYTES + Q_BYTES, &tmQl, &full[stage], k0, q0, pol_keep);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
@@ -222,13 +268,14 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0, c_phase = 0;
       const uint32_t c_tmem = tmem_base + uint32_t(2 * NT);
-      for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+      for (int64_t w = blockIdx.x; w < items; w += gridDim.x) {
+        const GemmItem it = gemm_item(w, tiles, G, S, nchunks, kc, nkb);
         if (PASSES == 3) {
-          mbar_wait(cempty, c_phase ^ 1u, a.fault);  // epilogue has read the previous tile's corrections
+          mbar_wait(cempty, c_phase ^ 1u, a.fault);  // epilogue has read the previous item's corrections
           c_phase ^= 1u;
         }
         uint32_t c_accumulate = 0;
-        for (int64_t ch = 0; ch < nchunks; ++ch) {
+        for (int64_t ch = it.ch0; ch < it.ch1; ++ch) {
           mbar_wait(&tempty[acc], acc_phase ^ 1u, a.fault);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + uint32_t(acc * NT);
@@ -268,13 +315,14 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
     // across the K chunks of a tile, so the tensor core's fp32 accumulation never spans more than one chunk
     const int quarter = warp & 3, half = (warp - 2) >> 2;
     int acc = 0; uint32_t acc_phase = 0;
-    for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-      const int64_t row = tile * GEMM_BM + quarter * 32 + lane;
+    for (int64_t w = blockIdx.x; w < items; w += gridDim.x) {
+      const GemmItem it = gemm_item(w, tiles, G, S, nchunks, kc, nkb);
+      const int64_t row = it.tile * GEMM_BM + quarter * 32 + lane;
       double sum[HC];
 #pragma unroll
       for (int j = 0; j < HC; ++j) sum[j] = 0.0;
       const uint32_t lane_off = uint32_t(quarter * 32) << 16;
-      for (int64_t ch = 0; ch < nchunks; ++ch) {
+      for (int64_t ch = it.ch0; ch < it.ch1; ++ch) {
         mbar_wait(&tfull[acc], acc_phase, a.fault);
         tc_fence_after();
         const uint32_t t0 = tmem_base + uint32_t(acc * NT + half * HC) + lane_off;
@@ -306,10 +354,11 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
         if (lane == 0) mbar_arrive(cempty);
       }
       if (row < a.M) {
+        double* dst = Dout + it.split * a.split_stride;
 #pragma unroll
         for (int j = 0; j < HC; ++j) {
-          const int col = half * HC + j;
-          if (col < a.N) Dout[int64_t(col) * a.ldd + row] = sum[j];
+          const int col = int(it.group) * NT + half * HC + j;
+          if (col < a.N) dst[int64_t(col) * a.ldd + row] = sum[j];
         }
       }
     }

@@ -24,6 +24,7 @@
 #include "glp_persist.cuh"
 #include "glp_tpass.cuh"
 #include "glp_types.cuh"
+#include "glp_wide_comm.cuh"
 
 using namespace glp;
 
@@ -147,6 +148,8 @@ struct glp_handle {
   float *A_hi = nullptr, *A_lo = nullptr, *At_hi = nullptr, *At_lo = nullptr;
   float *xop_lo = nullptr, *r_lo = nullptr;
   double* cnt_g = nullptr;
+  double* gemm_ws = nullptr;   // split-K partial products of K5
+  size_t gemm_ws_bytes = 0;
   int64_t n_gemm = 0;              // tensor-core launches of the current solve
 
   // step-level scratch (lazily sized)
@@ -366,6 +369,7 @@ extern "C" int glp_destroy(glp_handle* h) {
   if (h->xop_lo) cudaFree(h->xop_lo);
   if (h->r_lo) cudaFree(h->r_lo);
   if (h->cnt_g) cudaFree(h->cnt_g);
+  if (h->gemm_ws) cudaFree(h->gemm_ws);
   if (h->arena) cudaFree(h->arena);
   if (h->scratch) cudaFree(h->scratch);
   if (h->f_hist) cudaFree(h->f_hist);
@@ -417,7 +421,8 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
   h->evict_first = (double(m) * double(lda) * esz > 64.0 * 1024 * 1024) ? 1 : 0;
   h->n_fchunks = count_fchunks(2 * l);
   const int64_t vec_len = int64_t(l) * std::max(g.ldm, g.ldn);
-  h->decide_grid = int(std::max<int64_t>(1, std::min<int64_t>(num_sms, (vec_len + 4 * DECIDE_THREADS - 1) / (4 * DECIDE_THREADS))));
+  // latency-bound element loops: up to 4 CTAs per SM once the vectors are long (wide multi-RHS mode)
+  h->decide_grid = int(std::max<int64_t>(1, std::min<int64_t>(int64_t(num_sms) * 4, (vec_len + 4 * DECIDE_THREADS - 1) / (4 * DECIDE_THREADS))));
 
   int rc = make_tensor_map(h);
   if (rc != GLP_OK) { glp_destroy(h); return rc; }
@@ -437,7 +442,7 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
   const size_t o_tp = carve(size_t(g.grid + g.ncb) * 2 * tc * 8);
   const size_t o_fc = carve(size_t(g.nrb) * 4), o_tc = carve(size_t(g.ncb) * 4);
   const size_t o_ctrl = carve(2 * sizeof(Ctrl)), o_fault = carve(16);
-  h->gather_grid = int(std::max<int64_t>(1, std::min<int64_t>(num_sms, (int64_t(2) * lm + GATHER_THREADS - 1) / GATHER_THREADS)));
+  h->gather_grid = int(std::max<int64_t>(1, std::min<int64_t>(int64_t(num_sms) * 8, (int64_t(2) * lm + GATHER_THREADS - 1) / GATHER_THREADS)));
   const size_t o_fin = carve(16), o_rrg = carve(size_t(h->gather_grid) * 8), o_sred = carve(SCAL_STRIDE * 8), o_cred = carve(8);
   cudaError_t e = cudaMalloc(&h->arena, off);
   if (e != cudaSuccess) { glp_destroy(h); return fail(GLP_ERR_CUDA, "cudaMalloc(%zu) failed: %s", off, cudaGetErrorString(e)); }
@@ -491,9 +496,10 @@ static bool multi(const glp_handle* h) { return h->comm.world > 1; }
 
 // ---- wide multi-RHS mode: both products of an iteration run on the tensor cores (K5) ---------------
 static bool wide_active(const glp_handle* h) {
-  return h->dtype == GLP_F32 && h->g.l >= 16 && 2 * h->g.l <= 256 && !multi(h) && h->tensor_mode != 1;
+  return h->dtype == GLP_F32 && h->g.l >= 16 && 2 * h->g.l <= 256 && h->tensor_mode != 1;
 }
 static int wide_passes(const glp_handle* h) { return h->tensor_mode == 2 ? 1 : 3; }
+static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms);
 constexpr int WIDE_K_CHUNK = 8;  // the tensor core's fp32 accumulator spans 8 x 32 = 256 elements of K, then fp64
 
 static int split_f32(cudaStream_t st, const float* src, int64_t rows, int64_t cols, int64_t ld_src, float* hi, float* lo,
@@ -523,6 +529,12 @@ static int ensure_wide(glp_handle* h) {
   CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->xop_lo), size_t(2) * g.l * g.ldn * 4));
   CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->r_lo), size_t(g.l) * g.ldm * 4));
   CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->cnt_g), size_t(h->gather_grid) * 8));
+  {  // split-K workspace for the larger of the two products
+    const size_t fwd = size_t(gemm_splits(g.m, g.n, 2 * g.l, WIDE_K_CHUNK, h->num_sms)) * 2 * g.l * g.ldm * 8;
+    const size_t tps = size_t(gemm_splits(g.n, g.m, g.l, WIDE_K_CHUNK, h->num_sms)) * g.l * g.ldn * 8;
+    h->gemm_ws_bytes = std::max(fwd, tps);
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->gemm_ws), h->gemm_ws_bytes));
+  }
   CU_TRY(cudaMemsetAsync(h->A_hi, 0, a_bytes, h->stream));
   CU_TRY(cudaMemsetAsync(h->A_lo, 0, a_bytes, h->stream));
   CU_TRY(cudaMemsetAsync(h->At_hi, 0, at_bytes, h->stream));
@@ -535,26 +547,59 @@ static int ensure_wide(glp_handle* h) {
   return GLP_OK;
 }
 
+struct GemmWs { double* buf; size_t bytes; };  // split-K partial products (nullptr: no splitting)
+static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms);
 static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
                         const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
                         int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl = nullptr, double* D_alt = nullptr,
-                        int role = 0);
+                        int role = 0, GemmWs ws = GemmWs{nullptr, 0});
+
+static uint64_t seq_base(const glp_handle* h);
+
+// Multi-GPU wide mode (glp_wide_comm.cuh): stage 0 push (right after the local product), 1 reduce, 2 finish.
+// One device-wide stage per phase, so that a multi-rank job on ONE device can enqueue each stage for all
+// of its logical ranks before the next.
+static int enqueue_wide_exchange(glp_handle* h, const Ctrl* ctrl, int stage) {
+  const Geom& g = h->g;
+  WideXArgs a{};
+  a.comm = h->comm;
+  a.ctrl = ctrl;
+  a.sel = 0;
+  a.par = h->group & 1;
+  a.ncols = 2 * g.l;
+  a.slice_rows = int32_t(((g.ldm + h->comm.world - 1) / h->comm.world + 31) / 32 * 32);
+  if (stage == 0) ++h->idx_f;
+  a.seq_f = seq_base(h) | h->idx_f;
+  a.seq_t = h->seq_t_cur;
+  a.AX[0] = h->AX[0]; a.AX[1] = h->AX[1];
+  a.b = h->b;
+  a.xcand[0] = h->state[0]; a.xcand[1] = h->state[1];
+  a.cnt_partial = h->cnt_g;
+  a.rr_partial = h->rr_g;
+  a.scal_red = h->scal_red;
+  a.cnt_red = h->cnt_red;
+  a.fin = h->fin_f;
+  a.fault = h->fault;
+  if (stage == 0) glp_wide_push_kernel<<<h->gather_grid, WIDEX_THREADS, 0, h->stream>>>(a, g);
+  else if (stage == 1) glp_wide_reduce_kernel<<<h->gather_grid, WIDEX_THREADS, 0, h->stream>>>(a, g);
+  else glp_wide_finish_kernel<<<h->gather_grid, WIDEX_THREADS, 0, h->stream>>>(a, g);
+  CU_TRY(cudaGetLastError());
+  h->n_launches++;
+  return GLP_OK;
+}
 
 // forward product of the solver on the tensor cores: AX[1-cur] = A . [xn | xnt], then ||r||^2 and the count
 static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
   const Geom& g = h->g;
   float* xop = static_cast<float*>(h->xop);
   GLP_TRY(split_f32(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_lo, g.ldn, false));  // hi in place
-  for (int c0 = 0; c0 < 2 * g.l; c0 += 128) {  // up to 128 operand columns per launch
-    const int nc = std::min(128, 2 * g.l - c0);
-    prof_mark(h, 0, 0);
-    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, nc, h->A_hi, h->A_lo, g.ldn,
-                         xop + int64_t(c0) * g.ldn, h->xop_lo + int64_t(c0) * g.ldn, g.ldn,
-                         h->AX[0] + int64_t(c0) * g.ldm, g.ldm, WIDE_K_CHUNK, h->fault, ctrl,
-                         h->AX[1] + int64_t(c0) * g.ldm, 1));
-    prof_mark(h, 0, 1);
-    h->n_launches++;
-  }
+  prof_mark(h, 0, 0);
+  GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, 2 * g.l, h->A_hi, h->A_lo, g.ldn, xop, h->xop_lo,
+                       g.ldn, h->AX[0], g.ldm, WIDE_K_CHUNK, h->fault, ctrl, h->AX[1], 1,
+                       GemmWs{h->gemm_ws, h->gemm_ws_bytes}));
+  prof_mark(h, 0, 1);
+  h->n_launches += 2;
+  if (multi(h)) return enqueue_wide_exchange(h, ctrl, 0);
   PostFwdArgs pa{};
   pa.ctrl = ctrl;
   pa.AX[0] = h->AX[0]; pa.AX[1] = h->AX[1];
@@ -577,7 +622,8 @@ static int enqueue_wide_tpass(glp_handle* h, const Ctrl* ctrl) {
   GLP_TRY(split_f32(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_lo, g.ldm, false));
   prof_mark(h, 1, 0);
   GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.n, g.m, g.l, h->At_hi, h->At_lo, g.ldm, r, h->r_lo,
-                       g.ldm, h->grad, g.ldn, WIDE_K_CHUNK, h->fault, ctrl, nullptr, 2));
+                       g.ldm, h->grad, g.ldn, WIDE_K_CHUNK, h->fault, ctrl, nullptr, 2,
+                       GemmWs{h->gemm_ws, h->gemm_ws_bytes}));
   prof_mark(h, 1, 1);
   h->n_launches += 2;
   h->n_gemm++;
@@ -681,6 +727,7 @@ static int enqueue_solver_fwd(glp_handle* h, const Ctrl* ctrl) {
 // candidate product buffers, with the residual norm and the exchanged scalars.
 static int enqueue_gather(glp_handle* h, const Ctrl* ctrl) {
   if (!multi(h)) return GLP_OK;
+  if (wide_active(h)) return enqueue_wide_exchange(h, ctrl, 1);
   GatherArgs a{};
   a.comm = h->comm;
   a.ctrl = ctrl;
@@ -812,6 +859,12 @@ static int phase_tpass(glp_handle* h) {
   ProxArgs p = solver_prox_args(h, h->cur_ctrl);
   if (wide_active(h)) {
     GLP_TRY(enqueue_wide_tpass(h, h->cur_ctrl));
+    if (multi(h)) {   // the prox tail posts this rank's scalars to every peer (as enqueue_tpass does)
+      p.post.comm = h->comm;
+      p.post.seq_t = h->seq_t_cur = seq_base(h) | ++h->idx_t;
+      p.post.par = h->group & 1;
+      p.post.fin = h->fin_t;
+    }
     CU_TRY(launch_prox(h, p, 0));
     return GLP_OK;
   }
@@ -819,6 +872,9 @@ static int phase_tpass(glp_handle* h) {
 }
 static int phase_fwd(glp_handle* h) { return enqueue_solver_fwd(h, h->cur_ctrl); }
 static int phase_gather(glp_handle* h) { return enqueue_gather(h, h->cur_ctrl); }
+static int phase_finish(glp_handle* h) {   // third exchange stage of the wide multi-GPU mode, otherwise nothing
+  return (multi(h) && wide_active(h)) ? enqueue_wide_exchange(h, h->cur_ctrl, 2) : GLP_OK;
+}
 
 extern "C" int glp_solve_begin(glp_handle* h, int algo, const void* x0_dev, double mu0, const glp_opts* o) {
   GLP_TRY(phase_prepare(h, algo, x0_dev, mu0, o));
@@ -826,6 +882,7 @@ extern "C" int glp_solve_begin(glp_handle* h, int algo, const void* x0_dev, doub
   GLP_TRY(phase_init_prox(h));
   GLP_TRY(phase_fwd(h));
   GLP_TRY(phase_gather(h));
+  GLP_TRY(phase_finish(h));
   return GLP_OK;
 }
 
@@ -837,6 +894,7 @@ extern "C" int glp_solve_step(glp_handle* h, int slots) {
     GLP_TRY(phase_tpass(h));
     GLP_TRY(phase_fwd(h));
     GLP_TRY(phase_gather(h));
+    GLP_TRY(phase_finish(h));
   }
   return GLP_OK;
 }
@@ -994,6 +1052,7 @@ static int drive_until_done(glp_handle** hs, int G, const glp_opts* o) {
       for (int i = 0; i < G; ++i) { CU_TRY(cudaSetDevice(hs[i]->device)); GLP_TRY(phase_tpass(hs[i])); }
       for (int i = 0; i < G; ++i) { CU_TRY(cudaSetDevice(hs[i]->device)); GLP_TRY(phase_fwd(hs[i])); }
       for (int i = 0; i < G; ++i) { CU_TRY(cudaSetDevice(hs[i]->device)); GLP_TRY(phase_gather(hs[i])); }
+      for (int i = 0; i < G; ++i) { CU_TRY(cudaSetDevice(hs[i]->device)); GLP_TRY(phase_finish(hs[i])); }
     }
     issued += batch;
     CU_TRY(cudaSetDevice(h0->device));
@@ -1101,6 +1160,7 @@ extern "C" int glp_solve(glp_handle* h, int algo, const void* x0_dev, double mu0
     rc = phase_init_prox(h);
     if (rc == GLP_OK) rc = phase_fwd(h);
     if (rc == GLP_OK) rc = phase_gather(h);
+    if (rc == GLP_OK) rc = phase_finish(h);
     if (rc == GLP_OK) rc = drive_until_done(&h, 1, o);
   }
   if (rc != GLP_OK) { h->solving = false; return rc; }
@@ -1126,6 +1186,7 @@ extern "C" int glp_group_solve(glp_handle** hs, int G, int algo, const void* con
   for (int i = 0; i < G && rc == GLP_OK; ++i) { cudaSetDevice(hs[i]->device); rc = phase_init_prox(hs[i]); }
   for (int i = 0; i < G && rc == GLP_OK; ++i) { cudaSetDevice(hs[i]->device); rc = phase_fwd(hs[i]); }
   for (int i = 0; i < G && rc == GLP_OK; ++i) { cudaSetDevice(hs[i]->device); rc = phase_gather(hs[i]); }
+  for (int i = 0; i < G && rc == GLP_OK; ++i) { cudaSetDevice(hs[i]->device); rc = phase_finish(hs[i]); }
   if (rc == GLP_OK) rc = drive_until_done(hs, G, o);
   if (rc != GLP_OK) {
     for (int i = 0; i < G; ++i) hs[i]->solving = false;
@@ -1455,11 +1516,32 @@ static cudaError_t launch_gemm_t(cudaStream_t st, int grid, const CUtensorMap& p
   return cudaGetLastError();
 }
 
-// D[N][ldd] = P[M x K] . Q[N x K]^T ; passes 1 (TF32) or 3 (hi/lo compensated)
+// Number of K splits.  Measured on B200 (tests/bench_gemm_probe.py split): the kernel runs under the
+// board's power cap, so filling the SMs left idle by the tail wave buys nothing at 128+ items (3.15 ms
+// unsplit vs 3.56 ms with 4 splits at M=16384 K=65536 N=256) and fine splits cost epilogue + workspace
+// traffic.  K is therefore split only when the items cover less than half of the SMs (column shards of a
+// multi-GPU job), and then just enough to occupy them, keeping >= 8 accumulation chunks per item.
+static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms) {
+  const int NT = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
+  const int64_t base = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + NT - 1) / NT);
+  const int64_t nkb = (K + GEMM_BK - 1) / GEMM_BK;
+  const int64_t kc = k_chunk > 0 ? k_chunk : nkb;
+  const int64_t nchunks = (nkb + kc - 1) / kc;
+  if (const char* e = getenv("GLPROX_GEMM_SPLITS")) {   // measurement override
+    const int64_t S = atoi(e);
+    return int(std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(S, 16), nchunks)));
+  }
+  if (base * 2 > num_sms) return 1;
+  int64_t S = num_sms / base;
+  S = std::min<int64_t>(S, std::max<int64_t>(1, nchunks / 8));
+  return int(std::max<int64_t>(1, std::min<int64_t>(S, 16)));
+}
+
+// D[N][ldd] = P[M x K] . Q[N x K]^T ; passes 1 (TF32) or 3 (hi/lo compensated); N <= 256 (groups of <= 128 columns)
 static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
                         const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
-                        int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl, double* D_alt, int role) {
-  if (N < 1 || N > 128) return fail(GLP_ERR_ARG, "gemm: N must be 1..128 per launch (got %d)", N);
+                        int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl, double* D_alt, int role, GemmWs ws) {
+  if (N < 1 || N > 256) return fail(GLP_ERR_ARG, "gemm: N must be 1..256 per launch (got %d)", N);
   if (passes != 1 && passes != 3) return fail(GLP_ERR_ARG, "gemm: passes must be 1 or 3");
   if ((ldp * 4) % 16 || (ldq * 4) % 16 || (reinterpret_cast<uintptr_t>(Ph) % 16) || (reinterpret_cast<uintptr_t>(Qh) % 16))
     return fail(GLP_ERR_ARG, "gemm: operands must be 16-byte aligned with 16-byte aligned pitches");
@@ -1474,11 +1556,16 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   } else {
     mpl = mph; mql = mqh;
   }
+  int S = ws.buf != nullptr ? gemm_splits(M, K, N, k_chunk, num_sms) : 1;
+  const int64_t stride = int64_t(N) * ldd;
+  while (S > 1 && size_t(S) * stride * 8 > ws.bytes) --S;
   GemmArgs a{};
   a.M = M; a.K = K; a.N = N; a.k_chunk_blocks = k_chunk; a.D = D; a.ldd = ldd; a.fault = fault;
   a.ctrl = ctrl; a.D_alt = D_alt; a.role = role;
-  const int64_t tiles = (M + GEMM_BM - 1) / GEMM_BM;
-  const int grid = int(std::min<int64_t>(num_sms, tiles));
+  a.splits = S; a.split_stride = stride;
+  if (S > 1) { a.D = ws.buf; a.D_alt = ws.buf; }   // partials first; the sum below picks the real destination
+  const int64_t items = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + NT - 1) / NT) * S;
+  const int grid = int(std::min<int64_t>(num_sms, items));
   cudaError_t e;
   if (passes == 1) e = NT == 32 ? launch_gemm_t<32, 1>(st, grid, mph, mpl, mqh, mql, a)
                    : NT == 64 ? launch_gemm_t<64, 1>(st, grid, mph, mpl, mqh, mql, a)
@@ -1487,6 +1574,11 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
          : NT == 64 ? launch_gemm_t<64, 3>(st, grid, mph, mpl, mqh, mql, a)
                     : launch_gemm_t<128, 3>(st, grid, mph, mpl, mqh, mql, a);
   if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "gemm launch failed: %s", cudaGetErrorString(e));
+  if (S > 1) {
+    const int sgrid = int(std::min<int64_t>((M * N + 255) / 256, int64_t(num_sms) * 8));
+    glp_sum_splits_kernel<<<sgrid, 256, 0, st>>>(ws.buf, S, stride, M, N, ldd, D, D_alt, ctrl, role);
+    CU_TRY(cudaGetLastError());
+  }
   return GLP_OK;
 }
 
@@ -1498,15 +1590,20 @@ extern "C" int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, in
   GLP_TRY(check_device(device, &sms));
   CU_TRY(cudaSetDevice(device));
   if (N < 1 || N > 256) return fail(GLP_ERR_ARG, "gemm: N must be 1..256 (got %d)", N);
-  for (int c0 = 0; c0 < N; c0 += 128) {  // the kernel takes up to 128 columns per launch
-    const int nc = std::min(128, N - c0);
-    const float* qh = static_cast<const float*>(Q_hi) + int64_t(c0) * ldq;
-    const float* ql = Q_lo ? static_cast<const float*>(Q_lo) + int64_t(c0) * ldq : nullptr;
-    GLP_TRY(gemm_enqueue(static_cast<cudaStream_t>(stream), sms, passes, M, K, nc, static_cast<const float*>(P_hi),
-                         static_cast<const float*>(P_lo), ldp, qh, ql, ldq, D_dev + int64_t(c0) * ldd, ldd,
-                         k_chunk_blocks, nullptr, nullptr, nullptr, 0));
+  // k_chunk_blocks < 0: also exercise the split-K path (|k_chunk_blocks| blocks per chunk, partials in a
+  // stream-ordered temporary)
+  const int kc = k_chunk_blocks < 0 ? -k_chunk_blocks : k_chunk_blocks;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  GemmWs ws{nullptr, 0};
+  if (k_chunk_blocks < 0) {
+    ws.bytes = size_t(gemm_splits(M, K, N, kc, sms)) * N * ldd * 8;
+    CU_TRY(cudaMallocAsync(reinterpret_cast<void**>(&ws.buf), ws.bytes, st));
   }
-  return GLP_OK;
+  int rc = gemm_enqueue(st, sms, passes, M, K, N, static_cast<const float*>(P_hi), static_cast<const float*>(P_lo), ldp,
+                        static_cast<const float*>(Q_hi), static_cast<const float*>(Q_lo), ldq, D_dev, ldd, kc, nullptr,
+                        nullptr, nullptr, 0, ws);
+  if (ws.buf != nullptr) cudaFreeAsync(ws.buf, st);
+  return rc;
 }
 
 extern "C" int glp_tf32_split(void* stream, const void* src, int64_t rows, int64_t cols, int64_t ld_src, void* hi,

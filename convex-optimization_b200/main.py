@@ -65,7 +65,7 @@ def parse_args(argv=None):
     # (--rows / --cols are the spellings to use under torchrun, whose own parser claims the prefix "--m")
     p.add_argument("--m", "--rows", dest="m", type=int, default=0, help="rows of A (0 = the reference fixture 256 x 512)")
     p.add_argument("--n", "--cols", dest="n", type=int, default=0, help="columns of A = row groups of x")
-    p.add_argument("--l", type=int, default=2)
+    p.add_argument("--l", "--rhs", dest="l", type=int, default=2, help="right-hand sides = columns of x")
     p.add_argument("--mu", type=float, default=1e-2)
     p.add_argument("--dtype", choices=["f32", "f64"], default="f64")
     p.add_argument("--solvers", default="SGD,GD,FGD,ProxGD,FProxGD")

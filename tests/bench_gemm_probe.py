@@ -25,6 +25,11 @@ def run(M, K, N, passes, chunk, reps=5):
 if len(sys.argv) > 1 and sys.argv[1] == "one":   # the launch profiled with ncu (profiles/)
     run(16384, 65536, 128, 3, 8, reps=2)
     sys.exit(0)
+if len(sys.argv) > 1 and sys.argv[1] == "split":  # unsplit vs split-K schedule, 1-GPU and 8-GPU shard shapes
+    for (M, K, N) in [(16384, 65536, 256), (65536, 16384, 128), (16384, 8192, 256), (8192, 16384, 128)]:
+        for chunk in (8, -8):
+            run(M, K, N, 3, chunk)
+    sys.exit(0)
 for (M, K, N) in [(16384, 65536, 256), (65536, 16384, 128)]:
     for passes in (1, 3):
         for chunk in (0, 8, 32):

@@ -42,6 +42,23 @@ def main():
             lst = [torch.empty_like(t) for _ in range(world)]
             dist.all_gather(lst, t)
             assert all(torch.equal(lst[0], z) for z in lst)
+    # wide multi-RHS mode (l = 32, fp32): tcgen05 products per shard, reduce-scatter + all-gather over NVLink
+    from oracle import glprox_oracle as orc
+    m, n, l = 512, 1024 * world, 32
+    A, b, x0, u, mu = orc.gen_data(7, m, n, l)
+    A, b, x0 = (z.astype(np.float32) for z in (A, b, x0))
+    wopts = {"maxit": 15, "alpha0": float(1.0 / (np.sqrt(m) + np.sqrt(n)) ** 2)}
+    xr, kr, outr = orc.solve("FProxGD", x0.astype(np.float64), A.astype(np.float64), b.astype(np.float64), mu, wopts)
+    c0, c1 = shard_bounds(n, world, 128)[rank]
+    x, k, out = gl_FProxGD_primal(x0[c0:c1].copy(), np.ascontiguousarray(A[:, c0:c1]), b, mu, dict(wopts, dist=True))
+    assert k == kr == 45, k
+    fh, fr = np.asarray(out["f_hist"]), np.asarray(outr["f_hist"])
+    assert np.max(np.abs(fh - fr) / np.abs(fr)) <= 1e-5
+    assert abs(out["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
+    t = torch.tensor([out["fval"], float(k)], device="cuda", dtype=torch.float64)
+    lst = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(lst, t)
+    assert all(torch.equal(lst[0], z) for z in lst)
     dist.barrier()
     if rank == 0:
         print("DIST_PARITY_OK %d" % world, flush=True)

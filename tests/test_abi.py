@@ -66,7 +66,7 @@ def test_option_semantics_mirror_the_reference():
         o = solver.pack_opts(algo, m)
         assert o.maxit == 7 and o.step_type == 0
         with pytest.raises(ValueError):
-            solver.pack_opts(algo, solver.merge_opts(algo, {"step_type": "bb"}))
+            solver.pack_opts(algo, solver.merge_opts(algo, {"step_type": "no_such_rule"}))
 
 
 def test_product_path_never_imports_the_oracle():

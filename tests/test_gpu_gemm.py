@@ -66,6 +66,26 @@ def test_compensated_3xtf32_reaches_fp32_class_accuracy(shape, k_chunk):
     assert err <= (5e-7 if k_chunk else 2e-5), err   # unchunked: the tensor core's fp32 accumulation spans all of K
 
 
+@pytest.mark.parametrize("passes", [1, 3])
+@pytest.mark.parametrize("shape", [(2048, 8192, 128), (16384, 4096, 256), (8192, 16384, 128), (300, 4096, 200), (128, 640, 16)])
+def test_split_k_partials_sum_to_the_unsplit_product(shape, passes, monkeypatch):
+    """k_chunk_blocks < 0 selects the split-K schedule (items = column groups x K splits x M tiles, partial
+    products summed in split order).  The chunk sums are the same fp32 tensor-core sums either way, added
+    in fp64, so the result matches the unsplit launch to fp64 rounding and is run-to-run identical."""
+    import torch
+    M, K, N = shape
+    D0 = _run(M, K, N, passes, 8)[-1]
+    monkeypatch.setenv("GLPROX_GEMM_SPLITS", "4")   # the heuristic only splits small shards; force it here
+    D1 = _run(M, K, N, passes, -8)[-1]
+    D2 = _run(M, K, N, passes, -8)[-1]
+    assert torch.equal(D1, D2)
+    assert not torch.isnan(D1).any()
+    # passes = 3: the small correction terms (2^-11 of the result) are accumulated in fp32 over the whole K range
+    # of an item, so their truncation bias ((K/8) 2^-24 of THEM) changes with the split: fp32-class differences
+    err = ((D1 - D0).abs().max() / D0.abs().max()).item()
+    assert err <= (1e-13 if passes == 1 else 2e-7), err
+
+
 def test_transposing_split():
     import torch
     from glprox import _lib

@@ -127,7 +127,7 @@ def test_edge_cases_follow_the_reference():
     with pytest.raises(UnboundLocalError):
         _fn("FProxGD")(x0, A, b, mu, {"maxit": 0})
     with pytest.raises(ValueError):
-        _fn("ProxGD")(x0, A, b, mu, {"step_type": "bb"})
+        _fn("ProxGD")(x0, A, b, mu, {"step_type": "no_such_rule"})
     # unknown keys are ignored, like {**default_opts, **opts}
     x2, k2, _ = _fn("FProxGD")(x0, A, b, mu, {"maxit": 5, "alpha0": 1e-3, "no_such_key": 1})
     xr, kr, _ = orc.solve("FProxGD", x0, A, b, mu, {"maxit": 5, "alpha0": 1e-3})

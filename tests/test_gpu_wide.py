@@ -51,3 +51,42 @@ def test_wide_mode_streams_A_twice_per_iteration():
     assert out["glprox"]["n_launches"] < out2["glprox"]["n_launches"] / 2
     assert abs(out["fval"] - out2["fval"]) <= 1e-5 * abs(out2["fval"])
     prob.close()
+
+
+@pytest.mark.parametrize("algo", ["FProxGD", "ProxGD"])
+@pytest.mark.parametrize("G,shape", [(2, (256, 1024, 16)), (4, (300, 2048, 24)), (8, (512, 4096, 128)), (3, (1024, 4096, 64))])
+def test_wide_mode_sharded_matches_single_handle_and_oracle(G, shape, algo):
+    """Wide mode over G column shards on ONE device (phase-ordered launches): tcgen05 products per shard,
+    reduce-scatter + all-gather of the m x 2l partial products through the peer mailboxes
+    (csrc/glp_wide_comm.cuh).  Same bar as the single-GPU wide mode (1e-5 vs the fp64 oracle)."""
+    import torch
+    from glprox import GroupLassoProblem, shard_bounds, solve_group
+    m, n, l = shape
+    A, b, x0, mu, opts = _case(m, n, l, 7, 15)
+    Ad, bd = torch.from_numpy(A).cuda(), torch.from_numpy(b).cuda()
+    bounds = shard_bounds(n, G, 128)
+    probs = [GroupLassoProblem(Ad[:, c0:c1], bd) for c0, c1 in bounds]
+    ptrs = [p.export_mailbox(G)[1] for p in probs]
+    for r, p in enumerate(probs):
+        p.attach_peers(r, G, n, ptrs, kind=1)
+    x0s = [torch.from_numpy(x0[c0:c1].copy()).cuda() for c0, c1 in bounds]
+    single = GroupLassoProblem(Ad, bd)
+    x1, k1, out1 = single.solve(algo, torch.from_numpy(x0).cuda(), mu, opts)
+    xr, kr, outr = orc.solve(algo, x0.astype(np.float64), A.astype(np.float64), b.astype(np.float64), mu, opts)
+    for rep in range(2):   # the mailboxes and slab parities are reused by the second solve
+        xs, k, out = solve_group(probs, algo, x0s, mu, opts)
+        assert k == k1 == kr == 45
+        fh, f1, fr = (np.asarray(o["f_hist"]) for o in (out, out1, outr))
+        assert np.max(np.abs(fh - fr) / np.abs(fr)) <= 1e-5
+        assert np.max(np.abs(fh - f1) / np.abs(f1)) <= 1e-5
+        assert abs(out["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
+        x = torch.cat(xs, 0).cpu().numpy().astype(np.float64)
+        f_true = orc.objective(A.astype(np.float64), b.astype(np.float64), x, mu)
+        assert abs(f_true - outr["fval"]) <= 1e-5 * abs(outr["fval"])
+        pr = out["glprox"]["per_rank"]   # every rank took bit-identical decisions
+        assert all(r["iters"] == k and r["fval"] == pr[0]["fval"] and r["n_fwd"] == pr[0]["n_fwd"] for r in pr)
+        # 1 product + 3 exchange kernels per forward instead of 2l/4 CUDA-core streams
+        assert out["glprox"]["n_launches"] < 45 * 24
+    single.close()
+    for p in probs:
+        p.close()

@@ -81,4 +81,4 @@ def test_edge_cases_match_reference_behaviour():
     x2, k2, _ = orc.solve_two_stream("ProxGD", x0, A, b, mu, {"maxit": 0})
     assert k2 == 0 and np.array_equal(x2, x0)
     with pytest.raises(ValueError):
-        orc.solve("ProxGD", x0, A, b, mu, {"step_type": "bb"})
+        orc.solve("ProxGD", x0, A, b, mu, {"step_type": "no_such_rule"})
