@@ -402,15 +402,15 @@ glp_post_fwd_kernel(const PostFwdArgs a, const Geom g) {
   const double cut = xmul(1e-6, s_mx);
   const int64_t stride = int64_t(gridDim.x) * 256, first = int64_t(blockIdx.x) * 256 + tid;
   double cnt = 0.0, rr = 0.0;
+  // flat loops over the planar arrays (padding rows / row groups are zero and contribute nothing)
   const double* xc = a.xcand[sel];
-  for (int c = 0; c < g.l; ++c)
-    for (int64_t j = first; j < g.n; j += stride) cnt += fabs(xc[c * g.ldn + j]) > cut ? 1.0 : 0.0;
+  const int64_t lenn = int64_t(g.l) * g.ldn, lenm = int64_t(g.l) * g.ldm;
+  for (int64_t j = first; j < lenn; j += stride) cnt += fabs(xc[j]) > cut ? 1.0 : 0.0;
   const double* ax = a.AX[sel];
-  for (int c = 0; c < g.l; ++c)
-    for (int64_t i = first; i < g.m; i += stride) {
-      const double d = ax[c * g.ldm + i] - a.b[c * g.ldm + i];
-      rr += d * d;
-    }
+  for (int64_t i = first; i < lenm; i += stride) {
+    const double d = ax[i] - a.b[i];
+    rr += d * d;
+  }
   cnt = warp_sum(cnt); rr = warp_sum(rr);
   __syncthreads();
   if (lane == 0) s_red[warp] = rr;

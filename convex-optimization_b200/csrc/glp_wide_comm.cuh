@@ -69,8 +69,8 @@ glp_wide_push_kernel(const WideXArgs a, const Geom g) {
   const int64_t stride = int64_t(gridDim.x) * WIDEX_THREADS, first = int64_t(blockIdx.x) * WIDEX_THREADS + tid;
   double cnt = 0.0;
   const double* xc = a.xcand[sel];
-  for (int c = 0; c < g.l; ++c)
-    for (int64_t j = first; j < g.n; j += stride) cnt += fabs(xc[c * g.ldn + j]) > cut ? 1.0 : 0.0;
+  const int64_t lenn = int64_t(g.l) * g.ldn;   // flat: padding row groups are zero and never counted
+  for (int64_t j = first; j < lenn; j += stride) cnt += fabs(xc[j]) > cut ? 1.0 : 0.0;
   cnt = warp_sum(cnt);
   if (lane == 0) s_red[warp] = cnt;
   __syncthreads();
