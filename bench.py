@@ -495,9 +495,9 @@ def main():
                 host = (A.cpu().numpy(), b.cpu().numpy(), x0.cpu().numpy())
         if host is not None:
             An, bn, x0n = host
-            k, tt, fval = cpu_reference_solve(args, An, bn, x0n, mu, opts, 1)
+            k, tt, fval = cpu_reference_solve(args, An, bn, x0n, mu, opts, 2)
             line["cpu_baseline"] = {"value": k / tt, "unit": UNIT, "cores": blas_threads(), "kind": "port",
-                                    "sample": "%d iterations (maxit=1 per stage) of the full-size workload, "
+                                    "sample": "%d iterations (maxit=2 per stage) of the full-size workload, "
                                               "oracle port of the reference on NumPy/BLAS" % k,
                                     "seconds": tt}
         else:

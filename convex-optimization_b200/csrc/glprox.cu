@@ -177,18 +177,29 @@ typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency);
+// looked up once per process (K5 encodes four maps per product launch).
+static PFN_encodeTiled encode_tiled_fn() {
+  static PFN_encodeTiled cached = []() -> PFN_encodeTiled {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return reinterpret_cast<PFN_encodeTiled>(fn);
+  }();
+  return cached;
+}
+
 static int make_tensor_map(glp_handle* h) {
-  void* fn = nullptr;
-  cudaDriverEntryPointQueryResult qres;
-  CU_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
-  if (fn == nullptr || qres != cudaDriverEntryPointSuccess)
-    return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  PFN_encodeTiled fn = encode_tiled_fn();
+  if (fn == nullptr) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
   const int esz = h->dtype == GLP_F32 ? 4 : 8;
   const cuuint64_t dims[2] = {cuuint64_t(h->g.n), cuuint64_t(h->g.m)};
   const cuuint64_t strides[1] = {cuuint64_t(h->lda) * esz};
   const cuuint32_t box[2] = {cuuint32_t(TILE_ROW_BYTES / esz), cuuint32_t(TILE_ROWS)};
   const cuuint32_t estr[2] = {1, 1};
-  CUresult r = reinterpret_cast<PFN_encodeTiled>(fn)(
+  CUresult r = fn(
       &h->tmap, h->dtype == GLP_F32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2,
       const_cast<void*>(h->A), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -1489,16 +1500,13 @@ extern "C" int glp_solve_host(int device, int algo, int dtype, int m, int n, int
 // ------------------------------------------------------------------------------------------------
 static int make_map_f32_k128(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t stride_bytes,
                              uint32_t box_outer) {
-  void* fn = nullptr;
-  cudaDriverEntryPointQueryResult qres;
-  CU_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
-  if (fn == nullptr || qres != cudaDriverEntryPointSuccess)
-    return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  PFN_encodeTiled fn = encode_tiled_fn();
+  if (fn == nullptr) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
   const cuuint64_t dims[2] = {inner, outer};
   const cuuint64_t strides[1] = {stride_bytes};
   const cuuint32_t box[2] = {cuuint32_t(GEMM_BK), box_outer};
   const cuuint32_t estr[2] = {1, 1};
-  CUresult r = reinterpret_cast<PFN_encodeTiled>(fn)(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims,
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims,
                                                      strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                                                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
