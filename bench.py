@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=97006855)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--tensor-cores", default="auto", choices=["auto", "3xtf32", "tf32+bf16", "tf32", "off"],
+                    help="wide multi-RHS mode (l >= 16): product scheme on the tensor cores")
     ap.add_argument("--no-converge", action="store_true", help="skip the run-to-convergence / time-to-1e-8 report")
     return ap.parse_args()
 
@@ -145,7 +147,10 @@ def make_problem(args, rank, world):
 
 
 def solver_opts(args):
-    return {"maxit": args.maxit, "alpha0": mp_step(args.m, args.n)}
+    o = {"maxit": args.maxit, "alpha0": mp_step(args.m, args.n)}
+    if args.tensor_cores != "auto":
+        o["tensor_cores"] = args.tensor_cores
+    return o
 
 
 def run_ours(args):
@@ -232,7 +237,9 @@ def run_ours(args):
 
     if args.l >= 16 and args.dtype == "f32":
         # wide multi-RHS mode: both products run on tcgen05 (3xTF32); the bounding roofline is the tensor pipe
-        passes = 3
+        # tensor time in TF32-product units: 3xTF32 issues 3 TF32 products; tf32+bf16 one TF32 product and two
+        # bf16 products at twice the rate (= 2 units); plain TF32 one
+        passes = {"tf32": 1.0, "tf32+bf16": 2.0}.get(args.tensor_cores, 3.0)
         n_it = max(int(prof.tpass_launches), 1)
         flops = passes * 2.0 * args.m * A.shape[1] * 3 * args.l * n_it   # this rank's column shard
         t_s = (prof.fwd_ms_sum + prof.tpass_ms_sum) * 1e-3
@@ -241,7 +248,10 @@ def run_ours(args):
         hbm_stream = 2.0 * prof.bytes_per_launch * (prof.fwd_launches + prof.tpass_launches) / max(t_s, 1e-12) / 1e9
         roofline = {"bound": "tensor", "achieved": tf, "peak": tpeak, "unit": "TFLOP/s", "frac": tf / tpeak, "traffic": None,
                     "peak_source": "MEASURED_PEAKS.json bf16_tflops / 2 (kind::tf32 runs at half the bf16 rate)",
-                    "work": "3 compensated TF32 products per stream: Ah.Xh + Ah.Xl + Al.Xh, issued flops counted",
+                    "work": {"tf32": "1 TF32 product per stream (approximate mode)",
+                             "tf32+bf16": "Ah.Xh on TF32 + (Ah.Xl + Al.Xh) on bf16 at twice the rate: 2 TF32-product "
+                                          "units of tensor time per stream, counted as such"}.get(
+                                 args.tensor_cores, "3 compensated TF32 products per stream: Ah.Xh + Ah.Xl + Al.Xh, issued flops counted"),
                     "hbm_GBps_of_hi_lo_streams": hbm_stream, "hbm_peak": peak,
                     "kernels": {"glp_gemm_tf32_kernel<fwd>": {"launches": int(prof.fwd_launches), "avg_ms": prof.fwd_ms_sum / max(prof.fwd_launches, 1)},
                                 "glp_gemm_tf32_kernel<tpass>": {"launches": int(prof.tpass_launches), "avg_ms": prof.tpass_ms_sum / max(prof.tpass_launches, 1)}}}

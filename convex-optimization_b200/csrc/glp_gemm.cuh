@@ -24,6 +24,8 @@
 // main term is accumulated in TMEM over short K chunks only (k_chunk_blocks*32 elements) and summed in
 // fp64 by the epilogue, the two small correction terms in a third TMEM accumulator over the whole tile.
 #pragma once
+#include <cuda_bf16.h>
+
 #include "glp_device.cuh"
 #include "glp_types.cuh"
 
@@ -53,7 +55,7 @@ struct GemmArgs {
 };
 
 template <int NT, int PASSES> constexpr int gemm_stage_bytes() {
-  return (PASSES == 3 ? 2 : 1) * (GEMM_BM * 128 + NT * 128);
+  return (PASSES >= 2 ? 2 : 1) * (GEMM_BM * 128 + NT * 128);
 }
 template <int NT, int PASSES> constexpr int gemm_stages() {
   return (200 * 1024) / gemm_stage_bytes<NT, PASSES>() > 8 ? 8 : (200 * 1024) / gemm_stage_bytes<NT, PASSES>();
@@ -82,6 +84,15 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// same with bf16 operands (kind::f16, K = 16 per instruction, twice the tf32 rate)
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // mbarrier arrive when all previously issued MMAs of this thread have completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -105,6 +116,20 @@ __device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
   d |= uint64_t(1) << 46;
   d |= uint64_t(2) << 61;
   return d;
+}
+// K-major bf16 tile [rows][32 bf16 = 64 bytes] written by TMA with CU_TENSOR_MAP_SWIZZLE_64B: 8-row groups are
+// 512 bytes apart, layout type 4 (SWIZZLE_64B)
+__device__ __forceinline__ uint64_t umma_desc_k_sw64(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= uint64_t((smem_addr >> 4) & 0x3fffu);
+  d |= uint64_t(512u >> 4) << 32;
+  d |= uint64_t(1) << 46;
+  d |= uint64_t(4) << 61;
+  return d;
+}
+// kind::f16 with bf16 operands (format 1), fp32 accumulate, both K-major, M = 128
+template <int NT> __device__ __forceinline__ constexpr uint32_t umma_idesc_bf16() {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (uint32_t(NT >> 3) << 17) | (uint32_t(GEMM_BM >> 4) << 24);
 }
 // kind::tf32, fp32 accumulate, both operands K-major, M = 128
 template <int NT> __device__ __forceinline__ constexpr uint32_t umma_idesc_tf32() {
@@ -151,6 +176,55 @@ __global__ void glp_transpose_split_kernel(const float* __restrict__ src, float*
   }
 }
 
+// PASSES = 2 operands: hi as above (fp32 storage, TF32-exact), plus bf16 copies of hi and of lo = a - hi for
+// the two correction products (their result is 2^-11 of the main term, so 8 mantissa bits suffice).
+__device__ __forceinline__ void split_bf16_one(float a, float& h, __nv_bfloat16& hb, __nv_bfloat16& lb) {
+  uint32_t u = __float_as_uint(a);
+  u = (u + 0x00000fffu + ((u >> 13) & 1u)) & 0xffffe000u;
+  h = __uint_as_float(u);
+  if (!(fabsf(h) <= 3.0e38f)) h = a;
+  hb = __float2bfloat16_rn(h);
+  lb = __float2bfloat16_rn(a - h);
+}
+__global__ void glp_split_bf16_kernel(const float* src, float* hi, __nv_bfloat16* hb, __nv_bfloat16* lb,  // hi may alias src
+                                      int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst) {
+  const int64_t total = rows * cols;
+  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t i = e / cols, j = e - i * cols;
+    float h; __nv_bfloat16 b0, b1;
+    split_bf16_one(src[i * ld_src + j], h, b0, b1);
+    hi[i * ld_dst + j] = h;
+    hb[i * ld_dst + j] = b0;
+    lb[i * ld_dst + j] = b1;
+  }
+}
+__global__ void glp_transpose_split_bf16_kernel(const float* __restrict__ src, float* __restrict__ hi,
+                                                __nv_bfloat16* __restrict__ hb, __nv_bfloat16* __restrict__ lb,
+                                                int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst) {
+  __shared__ float t[32][33];
+  const int64_t bi = int64_t(blockIdx.y) * 32, bj = int64_t(blockIdx.x) * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int64_t i = bi + r, j = bj + threadIdx.x;
+    t[r][threadIdx.x] = (i < rows && j < cols) ? src[i * ld_src + j] : 0.f;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int64_t j = bj + r, i = bi + threadIdx.x;
+    if (j < cols && i < rows) {
+      float h; __nv_bfloat16 b0, b1;
+      split_bf16_one(t[threadIdx.x][r], h, b0, b1);
+      hi[j * ld_dst + i] = h;
+      hb[j * ld_dst + i] = b0;
+      lb[j * ld_dst + i] = b1;
+    }
+  }
+}
+
+__global__ void glp_to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t total) {
+  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x)
+    dst[e] = __float2bfloat16_rn(src[e]);
+}
+
 // work item w -> (K split, M tile, column group), column group fastest: the CTAs that take the column
 // groups of one P tile run side by side, so P is read from HBM once and from L2 by the others (with
 // N = 2l = 256 the product would otherwise stream A twice and turn HBM-bound); neighbouring CTAs also
@@ -191,13 +265,19 @@ template <int NT, int PASSES>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_constant__ CUtensorMap tmPl,
                      const __grid_constant__ CUtensorMap tmQh, const __grid_constant__ CUtensorMap tmQl,
+                     const __grid_constant__ CUtensorMap tmPx, const __grid_constant__ CUtensorMap tmQx,
                      const GemmArgs a) {
+  // PASSES = 1: Ph.Qh (plain TF32).  PASSES = 3: + Ph.Ql + Pl.Qh on TF32 hi/lo splits (tmPl / tmQl = fp32 lo).
+  // PASSES = 2: the same two corrections on bf16 operands (kind::f16): tmPx / tmQx = bf16(hi), tmPl / tmQl = bf16(lo);
+  //             stage = Ph | Qh | bf16 Ph | bf16 Pl | bf16 Qh | bf16 Ql  (same bytes as PASSES = 3)
+  constexpr bool CORR = PASSES >= 2;
+  constexpr int PB_BYTES = GEMM_BM * 64, QB_BYTES = NT * 64;   // bf16 tiles
   constexpr int STAGES = gemm_stages<NT, PASSES>();
   constexpr int STAGE_BYTES = gemm_stage_bytes<NT, PASSES>();
   constexpr int P_BYTES = GEMM_BM * 128, Q_BYTES = NT * 128;
   // TMEM: two chunk accumulators (main term, double buffered) + one whole-tile accumulator of the two
   // correction terms (their magnitude is 2^-11 of the main term, so their rounding is harmless)
-  constexpr uint32_t TMEM_NEED = (PASSES == 3 ? 3 : 2) * NT;
+  constexpr uint32_t TMEM_NEED = (CORR ? 3 : 2) * NT;
   constexpr uint32_t TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
   constexpr int HC = NT / 2;  // columns per epilogue thread
   static_assert(NT == 32 || NT == 64 || NT == 128, "NT");
@@ -242,6 +322,7 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       prefetch_tensormap(&tmPh); prefetch_tensormap(&tmQh);
+      if (PASSES == 2) { prefetch_tensormap(&tmPx); prefetch_tensormap(&tmQx); }
       const uint64_t pol_stream = policy_evict_first(), pol_keep = policy_evict_normal();
       int stage = 0; uint32_t phase = 0;
       for (int64_t w = blockIdx.x; w < items; w += gridDim.x) {
@@ -257,6 +338,13 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
             tma_load_2d(s + P_BYTES + Q_BYTES, &tmPl, &full[stage], k0, r0, pol_stream);
             tma_load_2d(s + 2 * P_BYTES + Q_BYTES, &tmQl, &full[stage], k0, q0, pol_keep);
           }
+          if (PASSES == 2) {
+            uint8_t* x = s + P_BYTES + Q_BYTES;
+            tma_load_2d(x, &tmPx, &full[stage], k0, r0, pol_stream);
+            tma_load_2d(x + PB_BYTES, &tmPl, &full[stage], k0, r0, pol_stream);
+            tma_load_2d(x + 2 * PB_BYTES, &tmQx, &full[stage], k0, q0, pol_keep);
+            tma_load_2d(x + 2 * PB_BYTES + QB_BYTES, &tmQl, &full[stage], k0, q0, pol_keep);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
@@ -270,7 +358,7 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
       const uint32_t c_tmem = tmem_base + uint32_t(2 * NT);
       for (int64_t w = blockIdx.x; w < items; w += gridDim.x) {
         const GemmItem it = gemm_item(w, tiles, G, S, nchunks, kc, nkb);
-        if (PASSES == 3) {
+        if (CORR) {
           mbar_wait(cempty, c_phase ^ 1u, a.fault);  // epilogue has read the previous item's corrections
           c_phase ^= 1u;
         }
@@ -299,6 +387,18 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
                 umma_tf32(c_tmem, dPh + uint64_t(2 * k4), dQl + uint64_t(2 * k4), idesc, c_accumulate);
                 c_accumulate = 1;
                 umma_tf32(c_tmem, dPl + uint64_t(2 * k4), dQh + uint64_t(2 * k4), idesc, 1u);
+              }
+            }
+            if (PASSES == 2) {
+              constexpr uint32_t idesc_b = umma_idesc_bf16<NT>();
+              const uint32_t xb = sbase + P_BYTES + Q_BYTES;
+              const uint64_t dPhb = umma_desc_k_sw64(xb), dPlb = umma_desc_k_sw64(xb + PB_BYTES);
+              const uint64_t dQhb = umma_desc_k_sw64(xb + 2 * PB_BYTES), dQlb = umma_desc_k_sw64(xb + 2 * PB_BYTES + QB_BYTES);
+#pragma unroll
+              for (int k2 = 0; k2 < GEMM_BK / 16; ++k2) {
+                umma_bf16(c_tmem, dPhb + uint64_t(2 * k2), dQlb + uint64_t(2 * k2), idesc_b, c_accumulate);
+                c_accumulate = 1;
+                umma_bf16(c_tmem, dPlb + uint64_t(2 * k2), dQhb + uint64_t(2 * k2), idesc_b, 1u);
               }
             }
             umma_commit(&empty[stage]);  // frees the smem stage when these MMAs have read it
@@ -339,7 +439,7 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
         if (lane == 0) mbar_arrive(&tempty[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
-      if (PASSES == 3) {
+      if (CORR) {
         const uint32_t t0 = tmem_base + uint32_t(2 * NT + half * HC) + lane_off;
 #pragma unroll
         for (int c0 = 0; c0 < HC; c0 += 16) {

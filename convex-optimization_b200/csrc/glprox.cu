@@ -148,6 +148,10 @@ struct glp_handle {
   float *A_hi = nullptr, *A_lo = nullptr, *At_hi = nullptr, *At_lo = nullptr;
   float *xop_lo = nullptr, *r_lo = nullptr;
   double* cnt_g = nullptr;
+  // tensor mode 3 (tf32 main term + bf16 corrections): bf16 copies of hi and lo instead of the fp32 lo arrays
+  __nv_bfloat16 *A_hb = nullptr, *A_lb = nullptr, *At_hb = nullptr, *At_lb = nullptr;
+  __nv_bfloat16 *xop_hb = nullptr, *xop_lb = nullptr, *r_hb = nullptr, *r_lb = nullptr;
+  int wide_built = -1;         // which operand set (wide_passes) is resident
   double* gemm_ws = nullptr;   // split-K partial products of K5
   size_t gemm_ws_bytes = 0;
   int64_t n_gemm = 0;              // tensor-core launches of the current solve
@@ -381,6 +385,8 @@ extern "C" int glp_destroy(glp_handle* h) {
   if (h->r_lo) cudaFree(h->r_lo);
   if (h->cnt_g) cudaFree(h->cnt_g);
   if (h->gemm_ws) cudaFree(h->gemm_ws);
+  for (__nv_bfloat16* q : {h->A_hb, h->A_lb, h->At_hb, h->At_lb, h->xop_hb, h->xop_lb, h->r_hb, h->r_lb})
+    if (q) cudaFree(q);
   if (h->arena) cudaFree(h->arena);
   if (h->scratch) cudaFree(h->scratch);
   if (h->f_hist) cudaFree(h->f_hist);
@@ -509,7 +515,7 @@ static bool multi(const glp_handle* h) { return h->comm.world > 1; }
 static bool wide_active(const glp_handle* h) {
   return h->dtype == GLP_F32 && h->g.l >= 16 && 2 * h->g.l <= 256 && h->tensor_mode != 1;
 }
-static int wide_passes(const glp_handle* h) { return h->tensor_mode == 2 ? 1 : 3; }
+static int wide_passes(const glp_handle* h) { return h->tensor_mode == 2 ? 1 : (h->tensor_mode == 3 ? 2 : 3); }
 static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms);
 constexpr int WIDE_K_CHUNK = 8;  // the tensor core's fp32 accumulator spans 8 x 32 = 256 elements of K, then fp64
 
@@ -527,43 +533,77 @@ static int split_f32(cudaStream_t st, const float* src, int64_t rows, int64_t co
   return GLP_OK;
 }
 
-// One-time set-up: A = A_hi + A_lo and A^T = At_hi + At_lo resident in HBM (4 x |A|; "memory laid out for
-// 180 GB"), plus the lo halves of the two small operands.
+static int split_bf16(cudaStream_t st, const float* src, int64_t rows, int64_t cols, int64_t ld_src, float* hi,
+                      __nv_bfloat16* hb, __nv_bfloat16* lb, int64_t ld_dst, bool transpose) {
+  if (transpose) {
+    dim3 grid(unsigned((cols + 31) / 32), unsigned((rows + 31) / 32));
+    if (grid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
+    glp_transpose_split_bf16_kernel<<<grid, dim3(32, 8), 0, st>>>(src, hi, hb, lb, rows, cols, ld_src, ld_dst);
+  } else {
+    const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
+    glp_split_bf16_kernel<<<grid, 256, 0, st>>>(src, hi, hb, lb, rows, cols, ld_src, ld_dst);
+  }
+  CU_TRY(cudaGetLastError());
+  return GLP_OK;
+}
+
+template <typename Q>
+static int alloc_zero(Q** p, size_t bytes, cudaStream_t st) {
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(p), bytes));
+  CU_TRY(cudaMemsetAsync(*p, 0, bytes, st));
+  return GLP_OK;
+}
+
+// One-time set-up per operand set: A = A_hi + A_lo and A^T = At_hi + At_lo resident in HBM (fp32 hi always;
+// the lo parts as fp32 for the 3xTF32 mode or hi/lo as bf16 for the TF32 + bf16-corrections mode: 4 x |A|
+// either way, "memory laid out for 180 GB"), plus the matching halves of the two small operands.
 static int ensure_wide(glp_handle* h) {
-  if (h->A_hi != nullptr) return GLP_OK;
   const Geom& g = h->g;
-  const size_t a_bytes = size_t(g.m) * g.ldn * 4, at_bytes = size_t(g.n) * g.ldm * 4;
-  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->A_hi), a_bytes));
-  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->A_lo), a_bytes));
-  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->At_hi), at_bytes));
-  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->At_lo), at_bytes));
-  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->xop_lo), size_t(2) * g.l * g.ldn * 4));
-  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->r_lo), size_t(g.l) * g.ldm * 4));
-  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->cnt_g), size_t(h->gather_grid) * 8));
-  {  // split-K workspace for the larger of the two products
+  const size_t a_el = size_t(g.m) * g.ldn, at_el = size_t(g.n) * g.ldm;
+  const size_t x_el = size_t(2) * g.l * g.ldn, r_el = size_t(g.l) * g.ldm;
+  const float* A = static_cast<const float*>(h->A);
+  if (h->A_hi == nullptr) {
+    GLP_TRY(alloc_zero(&h->A_hi, a_el * 4, h->stream));
+    GLP_TRY(alloc_zero(&h->At_hi, at_el * 4, h->stream));
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->cnt_g), size_t(h->gather_grid) * 8));
+    // split-K workspace for the larger of the two products
     const size_t fwd = size_t(gemm_splits(g.m, g.n, 2 * g.l, WIDE_K_CHUNK, h->num_sms)) * 2 * g.l * g.ldm * 8;
     const size_t tps = size_t(gemm_splits(g.n, g.m, g.l, WIDE_K_CHUNK, h->num_sms)) * g.l * g.ldn * 8;
     h->gemm_ws_bytes = std::max(fwd, tps);
     CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->gemm_ws), h->gemm_ws_bytes));
   }
-  CU_TRY(cudaMemsetAsync(h->A_hi, 0, a_bytes, h->stream));
-  CU_TRY(cudaMemsetAsync(h->A_lo, 0, a_bytes, h->stream));
-  CU_TRY(cudaMemsetAsync(h->At_hi, 0, at_bytes, h->stream));
-  CU_TRY(cudaMemsetAsync(h->At_lo, 0, at_bytes, h->stream));
-  CU_TRY(cudaMemsetAsync(h->xop_lo, 0, size_t(2) * g.l * g.ldn * 4, h->stream));
-  CU_TRY(cudaMemsetAsync(h->r_lo, 0, size_t(g.l) * g.ldm * 4, h->stream));
-  const float* A = static_cast<const float*>(h->A);
-  GLP_TRY(split_f32(h->stream, A, g.m, g.n, h->lda, h->A_hi, h->A_lo, g.ldn, false));
-  GLP_TRY(split_f32(h->stream, A, g.m, g.n, h->lda, h->At_hi, h->At_lo, g.ldm, true));
+  if (wide_passes(h) == 2) {
+    if (h->A_hb == nullptr) {
+      GLP_TRY(alloc_zero(&h->A_hb, a_el * 2, h->stream));
+      GLP_TRY(alloc_zero(&h->A_lb, a_el * 2, h->stream));
+      GLP_TRY(alloc_zero(&h->At_hb, at_el * 2, h->stream));
+      GLP_TRY(alloc_zero(&h->At_lb, at_el * 2, h->stream));
+      GLP_TRY(alloc_zero(&h->xop_hb, x_el * 2, h->stream));
+      GLP_TRY(alloc_zero(&h->xop_lb, x_el * 2, h->stream));
+      GLP_TRY(alloc_zero(&h->r_hb, r_el * 2, h->stream));
+      GLP_TRY(alloc_zero(&h->r_lb, r_el * 2, h->stream));
+      GLP_TRY(split_bf16(h->stream, A, g.m, g.n, h->lda, h->A_hi, h->A_hb, h->A_lb, g.ldn, false));
+      GLP_TRY(split_bf16(h->stream, A, g.m, g.n, h->lda, h->At_hi, h->At_hb, h->At_lb, g.ldm, true));
+    }
+  } else if (h->A_lo == nullptr) {
+    GLP_TRY(alloc_zero(&h->A_lo, a_el * 4, h->stream));
+    GLP_TRY(alloc_zero(&h->At_lo, at_el * 4, h->stream));
+    GLP_TRY(alloc_zero(&h->xop_lo, x_el * 4, h->stream));
+    GLP_TRY(alloc_zero(&h->r_lo, r_el * 4, h->stream));
+    GLP_TRY(split_f32(h->stream, A, g.m, g.n, h->lda, h->A_hi, h->A_lo, g.ldn, false));
+    GLP_TRY(split_f32(h->stream, A, g.m, g.n, h->lda, h->At_hi, h->At_lo, g.ldm, true));
+  }
   return GLP_OK;
 }
 
 struct GemmWs { double* buf; size_t bytes; };  // split-K partial products (nullptr: no splitting)
+struct GemmBf16 { const __nv_bfloat16 *Phb, *Plb, *Qhb, *Qlb; };  // passes = 2: bf16 copies of hi / lo, same pitches
 static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms);
 static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
                         const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
                         int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl = nullptr, double* D_alt = nullptr,
-                        int role = 0, GemmWs ws = GemmWs{nullptr, 0});
+                        int role = 0, GemmWs ws = GemmWs{nullptr, 0},
+                        GemmBf16 bf = GemmBf16{nullptr, nullptr, nullptr, nullptr});
 
 static uint64_t seq_base(const glp_handle* h);
 
@@ -603,11 +643,13 @@ static int enqueue_wide_exchange(glp_handle* h, const Ctrl* ctrl, int stage) {
 static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
   const Geom& g = h->g;
   float* xop = static_cast<float*>(h->xop);
-  GLP_TRY(split_f32(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_lo, g.ldn, false));  // hi in place
+  const bool bf = wide_passes(h) == 2;
+  if (bf) GLP_TRY(split_bf16(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_hb, h->xop_lb, g.ldn, false));
+  else GLP_TRY(split_f32(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_lo, g.ldn, false));  // hi in place
   prof_mark(h, 0, 0);
   GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, 2 * g.l, h->A_hi, h->A_lo, g.ldn, xop, h->xop_lo,
                        g.ldn, h->AX[0], g.ldm, WIDE_K_CHUNK, h->fault, ctrl, h->AX[1], 1,
-                       GemmWs{h->gemm_ws, h->gemm_ws_bytes}));
+                       GemmWs{h->gemm_ws, h->gemm_ws_bytes}, GemmBf16{h->A_hb, h->A_lb, h->xop_hb, h->xop_lb}));
   prof_mark(h, 0, 1);
   h->n_launches += 2;
   if (multi(h)) return enqueue_wide_exchange(h, ctrl, 0);
@@ -630,11 +672,12 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
 static int enqueue_wide_tpass(glp_handle* h, const Ctrl* ctrl) {
   const Geom& g = h->g;
   float* r = static_cast<float*>(h->r);
-  GLP_TRY(split_f32(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_lo, g.ldm, false));
+  if (wide_passes(h) == 2) GLP_TRY(split_bf16(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_hb, h->r_lb, g.ldm, false));
+  else GLP_TRY(split_f32(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_lo, g.ldm, false));
   prof_mark(h, 1, 0);
   GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.n, g.m, g.l, h->At_hi, h->At_lo, g.ldm, r, h->r_lo,
                        g.ldm, h->grad, g.ldn, WIDE_K_CHUNK, h->fault, ctrl, nullptr, 2,
-                       GemmWs{h->gemm_ws, h->gemm_ws_bytes}));
+                       GemmWs{h->gemm_ws, h->gemm_ws_bytes}, GemmBf16{h->At_hb, h->At_lb, h->r_hb, h->r_lb}));
   prof_mark(h, 1, 1);
   h->n_launches += 2;
   h->n_gemm++;
@@ -1317,7 +1360,8 @@ extern "C" int glp_tpass_prox(glp_handle* h, const glp_step_params* sp, const do
 
 extern "C" int glp_set_tensor_mode(glp_handle* h, int mode) {
   if (h == nullptr) return fail(GLP_ERR_ARG, "null handle");
-  if (mode < 0 || mode > 2) return fail(GLP_ERR_ARG, "tensor mode must be 0 (auto: 3xTF32), 1 (off) or 2 (plain TF32)");
+  if (mode < 0 || mode > 3)
+    return fail(GLP_ERR_ARG, "tensor mode must be 0 (auto: 3xTF32), 1 (off), 2 (plain TF32) or 3 (TF32 + bf16 corrections)");
   if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
   h->tensor_mode = mode;
   return GLP_OK;
@@ -1514,13 +1558,30 @@ static int make_map_f32_k128(CUtensorMap* map, const void* base, uint64_t inner,
   return GLP_OK;
 }
 
+// bf16 operand tile: 32 elements = 64 bytes of K per row, 64-byte swizzle
+static int make_map_bf16_k64(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t stride_bytes,
+                             uint32_t box_outer) {
+  PFN_encodeTiled fn = encode_tiled_fn();
+  if (fn == nullptr) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  const cuuint64_t dims[2] = {inner, outer};
+  const cuuint64_t strides[1] = {stride_bytes};
+  const cuuint32_t box[2] = {cuuint32_t(GEMM_BK), box_outer};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled (bf16 operand) failed with CUresult %d", int(r));
+  return GLP_OK;
+}
+
 template <int NT, int PASSES>
 static cudaError_t launch_gemm_t(cudaStream_t st, int grid, const CUtensorMap& ph, const CUtensorMap& pl,
-                                 const CUtensorMap& qh, const CUtensorMap& ql, const GemmArgs& a) {
+                                 const CUtensorMap& qh, const CUtensorMap& ql, const CUtensorMap& px,
+                                 const CUtensorMap& qx, const GemmArgs& a) {
   auto kfn = glp_gemm_tf32_kernel<NT, PASSES>;
   cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes<NT, PASSES>());
   if (e != cudaSuccess) return e;
-  kfn<<<grid, GEMM_THREADS, gemm_smem_bytes<NT, PASSES>(), st>>>(ph, pl, qh, ql, a);
+  kfn<<<grid, GEMM_THREADS, gemm_smem_bytes<NT, PASSES>(), st>>>(ph, pl, qh, ql, px, qx, a);
   return cudaGetLastError();
 }
 
@@ -1548,16 +1609,25 @@ static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms) {
 // D[N][ldd] = P[M x K] . Q[N x K]^T ; passes 1 (TF32) or 3 (hi/lo compensated); N <= 256 (groups of <= 128 columns)
 static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
                         const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
-                        int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl, double* D_alt, int role, GemmWs ws) {
+                        int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl, double* D_alt, int role, GemmWs ws,
+                        GemmBf16 bf) {
   if (N < 1 || N > 256) return fail(GLP_ERR_ARG, "gemm: N must be 1..256 per launch (got %d)", N);
-  if (passes != 1 && passes != 3) return fail(GLP_ERR_ARG, "gemm: passes must be 1 or 3");
+  if (passes < 1 || passes > 3) return fail(GLP_ERR_ARG, "gemm: passes must be 1, 2 or 3");
   if ((ldp * 4) % 16 || (ldq * 4) % 16 || (reinterpret_cast<uintptr_t>(Ph) % 16) || (reinterpret_cast<uintptr_t>(Qh) % 16))
     return fail(GLP_ERR_ARG, "gemm: operands must be 16-byte aligned with 16-byte aligned pitches");
   const int NT = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
-  CUtensorMap mph, mpl, mqh, mql;
+  CUtensorMap mph, mpl, mqh, mql, mpx, mqx;
   GLP_TRY(make_map_f32_k128(&mph, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, GEMM_BM));
   GLP_TRY(make_map_f32_k128(&mqh, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, uint32_t(NT)));
-  if (passes == 3) {
+  mpx = mph; mqx = mqh;
+  if (passes == 2) {
+    if (bf.Phb == nullptr || bf.Plb == nullptr || bf.Qhb == nullptr || bf.Qlb == nullptr)
+      return fail(GLP_ERR_ARG, "gemm: passes = 2 needs the bf16 operands");
+    GLP_TRY(make_map_bf16_k64(&mpx, bf.Phb, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
+    GLP_TRY(make_map_bf16_k64(&mpl, bf.Plb, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
+    GLP_TRY(make_map_bf16_k64(&mqx, bf.Qhb, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, uint32_t(NT)));
+    GLP_TRY(make_map_bf16_k64(&mql, bf.Qlb, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, uint32_t(NT)));
+  } else if (passes == 3) {
     if (Pl == nullptr || Ql == nullptr) return fail(GLP_ERR_ARG, "gemm: passes = 3 needs the lo operands");
     GLP_TRY(make_map_f32_k128(&mpl, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, GEMM_BM));
     GLP_TRY(make_map_f32_k128(&mql, Ql, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, uint32_t(NT)));
@@ -1575,12 +1645,15 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   const int64_t items = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + NT - 1) / NT) * S;
   const int grid = int(std::min<int64_t>(num_sms, items));
   cudaError_t e;
-  if (passes == 1) e = NT == 32 ? launch_gemm_t<32, 1>(st, grid, mph, mpl, mqh, mql, a)
-                   : NT == 64 ? launch_gemm_t<64, 1>(st, grid, mph, mpl, mqh, mql, a)
-                              : launch_gemm_t<128, 1>(st, grid, mph, mpl, mqh, mql, a);
-  else e = NT == 32 ? launch_gemm_t<32, 3>(st, grid, mph, mpl, mqh, mql, a)
-         : NT == 64 ? launch_gemm_t<64, 3>(st, grid, mph, mpl, mqh, mql, a)
-                    : launch_gemm_t<128, 3>(st, grid, mph, mpl, mqh, mql, a);
+  if (passes == 1) e = NT == 32 ? launch_gemm_t<32, 1>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
+                   : NT == 64 ? launch_gemm_t<64, 1>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
+                              : launch_gemm_t<128, 1>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a);
+  else if (passes == 2) e = NT == 32 ? launch_gemm_t<32, 2>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
+                        : NT == 64 ? launch_gemm_t<64, 2>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
+                                   : launch_gemm_t<128, 2>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a);
+  else e = NT == 32 ? launch_gemm_t<32, 3>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
+         : NT == 64 ? launch_gemm_t<64, 3>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
+                    : launch_gemm_t<128, 3>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a);
   if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "gemm launch failed: %s", cudaGetErrorString(e));
   if (S > 1) {
     const int sgrid = int(std::min<int64_t>((M * N + 255) / 256, int64_t(num_sms) * 8));
@@ -1607,10 +1680,25 @@ extern "C" int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, in
     ws.bytes = size_t(gemm_splits(M, K, N, kc, sms)) * N * ldd * 8;
     CU_TRY(cudaMallocAsync(reinterpret_cast<void**>(&ws.buf), ws.bytes, st));
   }
+  GemmBf16 bf{nullptr, nullptr, nullptr, nullptr};
+  __nv_bfloat16* tmp = nullptr;
+  if (passes == 2) {  // bf16 copies of the caller's hi / lo arrays (stream-ordered temporaries; test / probe entry point)
+    if (P_lo == nullptr || Q_lo == nullptr) return fail(GLP_ERR_ARG, "gemm: passes = 2 needs the lo operands");
+    const size_t pe = size_t(M) * ldp, qe = size_t(N) * ldq;
+    CU_TRY(cudaMallocAsync(reinterpret_cast<void**>(&tmp), (2 * pe + 2 * qe) * 2, st));
+    __nv_bfloat16 *phb = tmp, *plb = tmp + pe, *qhb = tmp + 2 * pe, *qlb = tmp + 2 * pe + qe;
+    const int g1 = int(std::min<size_t>((pe + 255) / 256, 148 * 16)), g2 = int(std::min<size_t>((qe + 255) / 256, 148 * 16));
+    glp_to_bf16_kernel<<<g1, 256, 0, st>>>(static_cast<const float*>(P_hi), phb, int64_t(pe));
+    glp_to_bf16_kernel<<<g1, 256, 0, st>>>(static_cast<const float*>(P_lo), plb, int64_t(pe));
+    glp_to_bf16_kernel<<<g2, 256, 0, st>>>(static_cast<const float*>(Q_hi), qhb, int64_t(qe));
+    glp_to_bf16_kernel<<<g2, 256, 0, st>>>(static_cast<const float*>(Q_lo), qlb, int64_t(qe));
+    bf = GemmBf16{phb, plb, qhb, qlb};
+  }
   int rc = gemm_enqueue(st, sms, passes, M, K, N, static_cast<const float*>(P_hi), static_cast<const float*>(P_lo), ldp,
                         static_cast<const float*>(Q_hi), static_cast<const float*>(Q_lo), ldq, D_dev, ldd, kc, nullptr,
-                        nullptr, nullptr, 0, ws);
+                        nullptr, nullptr, 0, ws, bf);
   if (ws.buf != nullptr) cudaFreeAsync(ws.buf, st);
+  if (tmp != nullptr) cudaFreeAsync(tmp, st);
   return rc;
 }
 

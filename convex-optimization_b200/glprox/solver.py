@@ -37,8 +37,8 @@ DEFAULT_OPTS.update({
 ALGO_ID = {"ProxGD": _lib.GLP_PROXGD, "FProxGD": _lib.GLP_FPROXGD, "FGD": _lib.GLP_FGD, "GD": _lib.GLP_GD,
            "SGD": _lib.GLP_SGD}
 # additive keys (not in the reference): dtype 'fp32'|'fp64', backend 'auto'|'stream'|'persistent',
-# device (int), poll_interval (int), dist (bool), tensor_cores 'auto'|'off'|'tf32'|'3xtf32' (wide l >= 16 mode)
-TENSOR_MODES = {"auto": 0, "3xtf32": 0, "off": 1, "tf32": 2}
+# device (int), poll_interval (int), dist (bool), tensor_cores 'auto'|'off'|'tf32'|'3xtf32'|'tf32+bf16' (wide l >= 16 mode)
+TENSOR_MODES = {"auto": 0, "3xtf32": 0, "off": 1, "tf32": 2, "tf32+bf16": 3}
 
 
 def merge_opts(algo, opts):

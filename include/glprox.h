@@ -204,14 +204,18 @@ int glp_nccl_comm_destroy(void* comm);
  * D[N][ldd] (fp64, planar) = P[M x K] . Q[N x K]^T with P row-major (pitch ldp) and Q planar (pitch ldq),
  * both fp32 device arrays, N <= 256.  Batched form of `A @ x` / `A.T @ r` (gl_*_primal.py:25,61,129 / :63,66)
  * for l >= 16 right-hand sides.  passes = 1: plain TF32 operands; passes = 3: error-compensated
- * Ph.Qh + Ph.Ql + Pl.Qh with the hi/lo splits of glp_tf32_split (fp32-class accuracy).
+ * Ph.Qh + Ph.Ql + Pl.Qh with the hi/lo splits of glp_tf32_split (fp32-class accuracy); passes = 2: the same
+ * two corrections computed on bf16 copies of hi / lo (kind::f16 at twice the TF32 rate; the corrections are
+ * 2^-11 of the result, so their 8-bit mantissas cost ~1e-7 of scale).
+ * k_chunk_blocks < 0: |k_chunk_blocks| with the split-K schedule (partial products summed in split order).
  * k_chunk_blocks > 0: flush the fp32 accumulator to fp64 every k_chunk_blocks*32 elements of K. */
 int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, int64_t K, int N, const void* P_hi,
                   const void* P_lo, int64_t ldp, const void* Q_hi, const void* Q_lo, int64_t ldq,
                   double* D_dev, int64_t ldd, int k_chunk_blocks);
 /* Wide multi-RHS mode of the solvers (fp32 data, 16 <= l <= 128, single GPU): both products of an
  * iteration run on glp_gemm_tf32 with A and A^T resident as TF32 hi/lo splits (4 x |A| of HBM).
- * mode 0 (default): on, error-compensated 3xTF32;  1: off (CUDA-core streams);  2: on, plain TF32. */
+ * mode 0 (default): on, error-compensated 3xTF32;  1: off (CUDA-core streams);  2: on, plain TF32;
+ * 3: on, TF32 main term + bf16 correction products (passes = 2 above). */
 int glp_set_tensor_mode(glp_handle* h, int mode);
 /* hi = src rounded to TF32 (10 mantissa bits), lo = src - hi; transpose != 0 writes the transposes
  * (hi[j][i], lo[j][i]) -- the resident A^T of the transposed pass. */

@@ -8,8 +8,8 @@ lib = _lib.load()
 st = torch.cuda.current_stream().cuda_stream
 def run(M, K, N, passes, chunk, reps=5):
     P = torch.randn((M, K), device="cuda"); Q = torch.randn((N, K), device="cuda")
-    Pl = torch.randn((M, K), device="cuda") * 1e-4 if passes == 3 else P
-    Ql = torch.randn((N, K), device="cuda") * 1e-4 if passes == 3 else Q
+    Pl = torch.randn((M, K), device="cuda") * 1e-4 if passes >= 2 else P
+    Ql = torch.randn((N, K), device="cuda") * 1e-4 if passes >= 2 else Q
     D = torch.empty((N, M), device="cuda", dtype=torch.float64)
     def go():
         _lib.check(lib.glp_gemm_tf32(0, st, passes, M, K, N, P.data_ptr(), Pl.data_ptr(), K, Q.data_ptr(), Ql.data_ptr(), K, D.data_ptr(), M, chunk))
@@ -24,6 +24,11 @@ def run(M, K, N, passes, chunk, reps=5):
     print("M=%d K=%d N=%d passes=%d chunk=%d: %.3f ms  %.1f TFLOP/s (tensor work)  %.0f GB/s (P stream)" % (M, K, N, passes, chunk, ms, flops / ms / 1e9, byts / ms / 1e6), flush=True)
 if len(sys.argv) > 1 and sys.argv[1] == "one":   # the launch profiled with ncu (profiles/)
     run(16384, 65536, 128, 3, 8, reps=2)
+    sys.exit(0)
+if len(sys.argv) > 1 and sys.argv[1] == "bf16":   # 3xTF32 vs TF32 + bf16 corrections
+    for (M, K, N) in [(16384, 65536, 256), (65536, 16384, 128), (16384, 8192, 256), (8192, 16384, 128)]:
+        for passes in (3, 2, 1):
+            run(M, K, N, passes, 8)
     sys.exit(0)
 if len(sys.argv) > 1 and sys.argv[1] == "split":  # unsplit vs split-K schedule, 1-GPU and 8-GPU shard shapes
     for (M, K, N) in [(16384, 65536, 256), (65536, 16384, 128), (16384, 8192, 256), (8192, 16384, 128)]:

@@ -86,6 +86,20 @@ def test_split_k_partials_sum_to_the_unsplit_product(shape, passes, monkeypatch)
     assert err <= (1e-13 if passes == 1 else 2e-7), err
 
 
+@pytest.mark.parametrize("shape", [(128, 256, 64), (300, 4096, 256), (1000, 333, 200), (2048, 8192, 128), (128, 64, 16)])
+def test_bf16_corrections_stay_fp32_class(shape):
+    """passes = 2: Ph.Qh on TF32 + (bf16(Ph).bf16(Ql) + bf16(Pl).bf16(Qh)) on kind::f16.  The corrections are 2^-11
+    of the result and carry 8-bit mantissas: error ~2^-19/sqrt(K) of scale, still far below plain TF32 (5e-5)."""
+    M, K, N = shape
+    P, Q, Ph, Pl, Qh, Ql, D = _run(M, K, N, 2, 8)
+    full = P.double() @ Q.double().t()
+    scale = P.double().abs() @ Q.double().abs().t() + 1e-300
+    err = ((D - full).abs() / scale).max().item()
+    assert err <= 1e-6, err
+    D3 = _run(M, K, N, 3, 8)[-1]
+    assert ((D - D3).abs() / scale).max().item() <= 1e-6
+
+
 def test_transposing_split():
     import torch
     from glprox import _lib

@@ -28,7 +28,7 @@ def test_wide_mode_matches_fp64_oracle(shape, algo):
     A, b, x0, mu, opts = _case(m, n, l, 7, 15)
     xr, kr, outr = orc.solve(algo, x0.astype(np.float64), A.astype(np.float64), b.astype(np.float64), mu, opts)
     ref_h = np.asarray(outr["f_hist"])
-    for mode, tol, tol_hist in (("3xtf32", 1e-5, 1e-5), ("tf32", 5e-2, 1e-1), ("off", 1e-5, 1e-5)):
+    for mode, tol, tol_hist in (("3xtf32", 1e-5, 1e-5), ("tf32+bf16", 1e-5, 1e-5), ("tf32", 5e-2, 1e-1), ("off", 1e-5, 1e-5)):
         x, k, out = fn(x0, A, b, mu, dict(opts, tensor_cores=mode))
         assert k == kr == 45 and x.dtype == np.float32
         fh = np.asarray(out["f_hist"])
