@@ -52,6 +52,10 @@ struct GemmArgs {
   // D + s * split_stride (the caller sums the partials in split order: glp_sum_splits_kernel)
   int32_t splits;                           // >= 1
   int64_t split_stride;                     // doubles between the partial outputs
+  // thread-block cluster of ct x cg CTAs working on ct neighbouring M tiles x cg column groups of the same K
+  // range: every P tile is loaded once per cluster row (each of the cg CTAs fetches 1/cg of its rows and TMA
+  // multicasts them to the others), every Q tile once per cluster column.  1 x 1 = no cluster.
+  int32_t ct, cg;
 };
 
 template <int NT, int PASSES> constexpr int gemm_stage_bytes() {
@@ -92,6 +96,11 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
+}
+// the same arrive delivered to the mbarrier at this offset in every CTA of the cluster named in cta_mask
+__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t cta_mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(cta_mask) : "memory");
 }
 // mbarrier arrive when all previously issued MMAs of this thread have completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
@@ -303,10 +312,20 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
   const int64_t nchunks = (nkb + kc - 1) / kc;
   const int64_t S = a.splits > 1 ? a.splits : 1;
   const int64_t G = (a.N + NT - 1) / NT;
-  const int64_t items = G * S * tiles;
+  // cluster geometry: this CTA is (dt, dg) of a ct x cg cluster; clusters are the scheduling unit
+  const int CT = a.ct > 1 ? a.ct : 1, CG = a.cg > 1 ? a.cg : 1, CS = CT * CG;
+  const int crank = CS > 1 ? int(cluster_ctarank()) : 0;
+  const int dt = crank % CT, dg = crank / CT;
+  const int64_t cl_id = blockIdx.x / CS, ncl = gridDim.x / CS;
+  const int64_t tblocks = (tiles + CT - 1) / CT, gblocks = (G + CG - 1) / CG;
+  const int64_t items = gblocks * S * tblocks;
+  uint16_t mask_p = 0, mask_q = 0;   // CTAs that share my P tile (same dt) / my Q tile (same dg)
+  for (int q = 0; q < CG; ++q) mask_p |= uint16_t(1u << (dt + CT * q));
+  for (int q = 0; q < CT; ++q) mask_q |= uint16_t(1u << (q + CT * dg));
+  const uint16_t mask_all = uint16_t((1u << CS) - 1u);
 
   if (tid == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], uint32_t(CS)); }
     for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], GEMM_EPI_WARPS); }
     mbar_init(cempty, GEMM_EPI_WARPS);
     fence_mbar_init();
@@ -317,6 +336,7 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (CS > 1) cluster_sync_all();   // every CTA's barriers exist before a peer multicasts into them
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -325,25 +345,36 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
       if (PASSES == 2) { prefetch_tensormap(&tmPx); prefetch_tensormap(&tmQx); }
       const uint64_t pol_stream = policy_evict_first(), pol_keep = policy_evict_normal();
       int stage = 0; uint32_t phase = 0;
-      for (int64_t w = blockIdx.x; w < items; w += gridDim.x) {
-        const GemmItem it = gemm_item(w, tiles, G, S, nchunks, kc, nkb);
+      // my share of each shared tile: rows [dg*BM/CG, ...) of P, rows [dt*NT/CT, ...) of Q (box sizes of the maps)
+      const int pr = dg * (GEMM_BM / CG), qr = dt * (NT / CT);
+      auto load_p = [&](uint8_t* tile, const CUtensorMap* m, uint64_t* bar, int32_t k0, int32_t r0, int row_bytes) {
+        if (CG > 1) tma_load_2d_mc(tile + pr * row_bytes, m, bar, k0, r0 + pr, mask_p, pol_stream);
+        else tma_load_2d(tile, m, bar, k0, r0, pol_stream);
+      };
+      auto load_q = [&](uint8_t* tile, const CUtensorMap* m, uint64_t* bar, int32_t k0, int32_t q0, int row_bytes) {
+        if (CT > 1) tma_load_2d_mc(tile + qr * row_bytes, m, bar, k0, q0 + qr, mask_q, pol_keep);
+        else tma_load_2d(tile, m, bar, k0, q0, pol_keep);
+      };
+      for (int64_t w = cl_id; w < items; w += ncl) {
+        const GemmItem it = gemm_item(w, tblocks, gblocks, S, nchunks, kc, nkb);
+        const int32_t r0 = int32_t((it.tile * CT + dt) * GEMM_BM), q0 = int32_t((it.group * CG + dg) * NT);
         for (int64_t kb = it.kb0; kb < it.kb1; ++kb) {
-          mbar_wait(&empty[stage], phase ^ 1u, a.fault);
+          mbar_wait(&empty[stage], phase ^ 1u, a.fault);   // the slot is free in EVERY CTA I multicast into
           mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
           uint8_t* s = smem + stage * STAGE_BYTES;
-          const int32_t k0 = int32_t(kb * GEMM_BK), r0 = int32_t(it.tile * GEMM_BM), q0 = int32_t(it.group * NT);
-          tma_load_2d(s, &tmPh, &full[stage], k0, r0, pol_stream);
-          tma_load_2d(s + P_BYTES, &tmQh, &full[stage], k0, q0, pol_keep);
+          const int32_t k0 = int32_t(kb * GEMM_BK);
+          load_p(s, &tmPh, &full[stage], k0, r0, 128);
+          load_q(s + P_BYTES, &tmQh, &full[stage], k0, q0, 128);
           if (PASSES == 3) {
-            tma_load_2d(s + P_BYTES + Q_BYTES, &tmPl, &full[stage], k0, r0, pol_stream);
-            tma_load_2d(s + 2 * P_BYTES + Q_BYTES, &tmQl, &full[stage], k0, q0, pol_keep);
+            load_p(s + P_BYTES + Q_BYTES, &tmPl, &full[stage], k0, r0, 128);
+            load_q(s + 2 * P_BYTES + Q_BYTES, &tmQl, &full[stage], k0, q0, 128);
           }
           if (PASSES == 2) {
             uint8_t* x = s + P_BYTES + Q_BYTES;
-            tma_load_2d(x, &tmPx, &full[stage], k0, r0, pol_stream);
-            tma_load_2d(x + PB_BYTES, &tmPl, &full[stage], k0, r0, pol_stream);
-            tma_load_2d(x + 2 * PB_BYTES, &tmQx, &full[stage], k0, q0, pol_keep);
-            tma_load_2d(x + 2 * PB_BYTES + QB_BYTES, &tmQl, &full[stage], k0, q0, pol_keep);
+            load_p(x, &tmPx, &full[stage], k0, r0, 64);
+            load_p(x + PB_BYTES, &tmPl, &full[stage], k0, r0, 64);
+            load_q(x + 2 * PB_BYTES, &tmQx, &full[stage], k0, q0, 64);
+            load_q(x + 2 * PB_BYTES + QB_BYTES, &tmQl, &full[stage], k0, q0, 64);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
@@ -356,8 +387,8 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0, c_phase = 0;
       const uint32_t c_tmem = tmem_base + uint32_t(2 * NT);
-      for (int64_t w = blockIdx.x; w < items; w += gridDim.x) {
-        const GemmItem it = gemm_item(w, tiles, G, S, nchunks, kc, nkb);
+      for (int64_t w = cl_id; w < items; w += ncl) {
+        const GemmItem it = gemm_item(w, tblocks, gblocks, S, nchunks, kc, nkb);
         if (CORR) {
           mbar_wait(cempty, c_phase ^ 1u, a.fault);  // epilogue has read the previous item's corrections
           c_phase ^= 1u;
@@ -401,7 +432,10 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
                 umma_bf16(c_tmem, dPlb + uint64_t(2 * k2), dQhb + uint64_t(2 * k2), idesc_b, 1u);
               }
             }
-            umma_commit(&empty[stage]);  // frees the smem stage when these MMAs have read it
+            // frees the smem stage when these MMAs have read it -- in every CTA of the cluster, whose producers
+            // multicast into this slot
+            if (CS > 1) umma_commit_mc(&empty[stage], mask_all);
+            else umma_commit(&empty[stage]);
             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           }
           umma_commit(&tfull[acc]);      // chunk accumulator (and, after the last chunk, the corrections) complete
@@ -415,9 +449,9 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
     // across the K chunks of a tile, so the tensor core's fp32 accumulation never spans more than one chunk
     const int quarter = warp & 3, half = (warp - 2) >> 2;
     int acc = 0; uint32_t acc_phase = 0;
-    for (int64_t w = blockIdx.x; w < items; w += gridDim.x) {
-      const GemmItem it = gemm_item(w, tiles, G, S, nchunks, kc, nkb);
-      const int64_t row = it.tile * GEMM_BM + quarter * 32 + lane;
+    for (int64_t w = cl_id; w < items; w += ncl) {
+      const GemmItem it = gemm_item(w, tblocks, gblocks, S, nchunks, kc, nkb);
+      const int64_t row = (it.tile * CT + dt) * GEMM_BM + quarter * 32 + lane;
       double sum[HC];
 #pragma unroll
       for (int j = 0; j < HC; ++j) sum[j] = 0.0;
@@ -457,7 +491,7 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
         double* dst = Dout + it.split * a.split_stride;
 #pragma unroll
         for (int j = 0; j < HC; ++j) {
-          const int col = int(it.group) * NT + half * HC + j;
+          const int col = int(it.group * CG + dg) * NT + half * HC + j;
           if (col < a.N) dst[int64_t(col) * a.ldd + row] = sum[j];
         }
       }
@@ -465,6 +499,7 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
   }
   tc_fence_before();
   __syncthreads();
+  if (CS > 1) cluster_sync_all();   // no CTA leaves while a peer may still multicast into it or arrive on its barriers
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
 }
 

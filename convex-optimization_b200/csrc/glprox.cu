@@ -1575,14 +1575,37 @@ static int make_map_bf16_k64(CUtensorMap* map, const void* base, uint64_t inner,
 }
 
 template <int NT, int PASSES>
-static cudaError_t launch_gemm_t(cudaStream_t st, int grid, const CUtensorMap& ph, const CUtensorMap& pl,
-                                 const CUtensorMap& qh, const CUtensorMap& ql, const CUtensorMap& px,
-                                 const CUtensorMap& qx, const GemmArgs& a) {
+static cudaError_t launch_gemm_t(cudaStream_t st, int num_sms, int64_t cluster_items, const CUtensorMap& ph,
+                                 const CUtensorMap& pl, const CUtensorMap& qh, const CUtensorMap& ql,
+                                 const CUtensorMap& px, const CUtensorMap& qx, const GemmArgs& a) {
   auto kfn = glp_gemm_tf32_kernel<NT, PASSES>;
-  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes<NT, PASSES>());
+  constexpr int smem = gemm_smem_bytes<NT, PASSES>();
+  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  kfn<<<grid, GEMM_THREADS, gemm_smem_bytes<NT, PASSES>(), st>>>(ph, pl, qh, ql, px, qx, a);
-  return cudaGetLastError();
+  const int cs = std::max(1, a.ct) * std::max(1, a.cg);
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(GEMM_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = unsigned(cs);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = cs > 1 ? 1 : 0;
+  int64_t ncl = num_sms / cs;
+  if (cs > 1) {  // clusters must fit inside a GPC: ask how many can be resident at once
+    cfg.gridDim = dim3(unsigned(ncl * cs), 1, 1);
+    int max_cl = 0;
+    e = cudaOccupancyMaxActiveClusters(&max_cl, kfn, &cfg);
+    if (e != cudaSuccess) return e;
+    if (max_cl < 1) return cudaErrorInvalidConfiguration;
+    ncl = std::min<int64_t>(ncl, max_cl);
+  }
+  ncl = std::max<int64_t>(1, std::min<int64_t>(ncl, cluster_items));
+  cfg.gridDim = dim3(unsigned(ncl * cs), 1, 1);
+  return cudaLaunchKernelEx(&cfg, kfn, ph, pl, qh, ql, px, qx, a);
 }
 
 // Number of K splits.  Measured on B200 (tests/bench_gemm_probe.py split): the kernel runs under the
@@ -1616,21 +1639,38 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   if ((ldp * 4) % 16 || (ldq * 4) % 16 || (reinterpret_cast<uintptr_t>(Ph) % 16) || (reinterpret_cast<uintptr_t>(Qh) % 16))
     return fail(GLP_ERR_ARG, "gemm: operands must be 16-byte aligned with 16-byte aligned pitches");
   const int NT = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
+  const int64_t tiles = (M + GEMM_BM - 1) / GEMM_BM, groups = (N + NT - 1) / NT;
+  // cluster geometry (TMA multicast of the shared operand tiles): neighbouring M tiles share every Q tile,
+  // the 2 column groups of N = 256 share every P tile.  Measured in the solver at C5 (it/s, fwd / tpass ms):
+  // 1x1 171.6 (3.45 / 1.78), 2x2 176.0 (3.34 / 1.76), 4 tiles 154.7 (4.28 with 8-CTA clusters / 1.61): 2 x 2 for
+  // the two-group forward product, 4 x 1 for the one-group transposed product.
+  // GLPROX_GEMM_CLUSTER=ct,cg overrides (1,1 = off).
+  int cg = groups == 2 ? 2 : 1;
+  int ct = cg == 2 ? (tiles >= 2 ? 2 : 1) : (tiles >= 4 ? 4 : (tiles >= 2 ? 2 : 1));
+  if (const char* e = getenv("GLPROX_GEMM_CLUSTER")) {
+    int a1 = 0, a2 = 0;
+    if (sscanf(e, "%d,%d", &a1, &a2) == 2 && (a1 == 1 || a1 == 2 || a1 == 4) && (a2 == 1 || a2 == 2)) {
+      ct = std::min<int64_t>(a1, tiles >= a1 ? a1 : 1);
+      cg = groups == 2 ? a2 : 1;
+    }
+  }
+  if (NT / ct < 8) ct = 1;
+  const uint32_t pbox = uint32_t(GEMM_BM / cg), qbox = uint32_t(NT / ct);
   CUtensorMap mph, mpl, mqh, mql, mpx, mqx;
-  GLP_TRY(make_map_f32_k128(&mph, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, GEMM_BM));
-  GLP_TRY(make_map_f32_k128(&mqh, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, uint32_t(NT)));
+  GLP_TRY(make_map_f32_k128(&mph, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, pbox));
+  GLP_TRY(make_map_f32_k128(&mqh, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, qbox));
   mpx = mph; mqx = mqh;
   if (passes == 2) {
     if (bf.Phb == nullptr || bf.Plb == nullptr || bf.Qhb == nullptr || bf.Qlb == nullptr)
       return fail(GLP_ERR_ARG, "gemm: passes = 2 needs the bf16 operands");
-    GLP_TRY(make_map_bf16_k64(&mpx, bf.Phb, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
-    GLP_TRY(make_map_bf16_k64(&mpl, bf.Plb, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
-    GLP_TRY(make_map_bf16_k64(&mqx, bf.Qhb, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, uint32_t(NT)));
-    GLP_TRY(make_map_bf16_k64(&mql, bf.Qlb, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, uint32_t(NT)));
+    GLP_TRY(make_map_bf16_k64(&mpx, bf.Phb, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, pbox));
+    GLP_TRY(make_map_bf16_k64(&mpl, bf.Plb, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, pbox));
+    GLP_TRY(make_map_bf16_k64(&mqx, bf.Qhb, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, qbox));
+    GLP_TRY(make_map_bf16_k64(&mql, bf.Qlb, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, qbox));
   } else if (passes == 3) {
     if (Pl == nullptr || Ql == nullptr) return fail(GLP_ERR_ARG, "gemm: passes = 3 needs the lo operands");
-    GLP_TRY(make_map_f32_k128(&mpl, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, GEMM_BM));
-    GLP_TRY(make_map_f32_k128(&mql, Ql, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, uint32_t(NT)));
+    GLP_TRY(make_map_f32_k128(&mpl, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, pbox));
+    GLP_TRY(make_map_f32_k128(&mql, Ql, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, qbox));
   } else {
     mpl = mph; mql = mqh;
   }
@@ -1642,18 +1682,14 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   a.ctrl = ctrl; a.D_alt = D_alt; a.role = role;
   a.splits = S; a.split_stride = stride;
   if (S > 1) { a.D = ws.buf; a.D_alt = ws.buf; }   // partials first; the sum below picks the real destination
-  const int64_t items = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + NT - 1) / NT) * S;
-  const int grid = int(std::min<int64_t>(num_sms, items));
+  a.ct = ct; a.cg = cg;
+  const int64_t items = ((tiles + ct - 1) / ct) * ((groups + cg - 1) / cg) * S;   // cluster items
   cudaError_t e;
-  if (passes == 1) e = NT == 32 ? launch_gemm_t<32, 1>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
-                   : NT == 64 ? launch_gemm_t<64, 1>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
-                              : launch_gemm_t<128, 1>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a);
-  else if (passes == 2) e = NT == 32 ? launch_gemm_t<32, 2>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
-                        : NT == 64 ? launch_gemm_t<64, 2>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
-                                   : launch_gemm_t<128, 2>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a);
-  else e = NT == 32 ? launch_gemm_t<32, 3>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
-         : NT == 64 ? launch_gemm_t<64, 3>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a)
-                    : launch_gemm_t<128, 3>(st, grid, mph, mpl, mqh, mql, mpx, mqx, a);
+#define GLP_GEMM_LAUNCH(NTV, PV) launch_gemm_t<NTV, PV>(st, num_sms, items, mph, mpl, mqh, mql, mpx, mqx, a)
+  if (passes == 1) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 1) : NT == 64 ? GLP_GEMM_LAUNCH(64, 1) : GLP_GEMM_LAUNCH(128, 1);
+  else if (passes == 2) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 2) : NT == 64 ? GLP_GEMM_LAUNCH(64, 2) : GLP_GEMM_LAUNCH(128, 2);
+  else e = NT == 32 ? GLP_GEMM_LAUNCH(32, 3) : NT == 64 ? GLP_GEMM_LAUNCH(64, 3) : GLP_GEMM_LAUNCH(128, 3);
+#undef GLP_GEMM_LAUNCH
   if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "gemm launch failed: %s", cudaGetErrorString(e));
   if (S > 1) {
     const int sgrid = int(std::min<int64_t>((M * N + 255) / 256, int64_t(num_sms) * 8));
