@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=97006855)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="multi-GPU exchange: peer-mailbox push fused into the kernels (product) or the ncclAllReduce baseline")
     ap.add_argument("--tensor-cores", default="auto", choices=["auto", "3xtf32", "tf32+bf16", "tf32", "off"],
                     help="wide multi-RHS mode (l >= 16): product scheme on the tensor cores")
     ap.add_argument("--no-converge", action="store_true", help="skip the run-to-convergence / time-to-1e-8 report")
@@ -165,7 +167,7 @@ def run_ours(args):
     prob = GroupLassoProblem(A, b)
     if world > 1:
         from glprox import attach_distributed
-        attach_distributed(prob, args.n)
+        attach_distributed(prob, args.n, exchange=args.exchange)
 
     def barrier():
         if world > 1:
@@ -263,7 +265,9 @@ def run_ours(args):
                                        args.algo, args.m, args.n, args.l, args.dtype, args.maxit, 3 * args.maxit),
                        "sharding": "column groups of A / row groups of x over %d rank(s)" % world,
                        "exchange": "none (1 GPU)" if world == 1 else
-                                   ("reduce-scatter + all-gather of the m x 2l partial products over row slices, pushed "
+                                   ("BASELINE: two ncclAllReduce calls per forward stream (MAX of one double, SUM of the m x 2l "
+                                    "partial product + 8 scalars) on the solver stream" if args.exchange == "nccl" else
+                                    "reduce-scatter + all-gather of the m x 2l partial products over row slices, pushed "
                                     "through peer mailboxes over NVLink (3 small kernels per forward product); no NCCL on "
                                     "the data path" if args.l >= 16 and args.dtype == "f32" else
                                     "m x 2l partial products + 5 scalars pushed into peer mailboxes over NVLink from "

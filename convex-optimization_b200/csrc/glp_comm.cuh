@@ -177,3 +177,100 @@ glp_gather_kernel(const GatherArgs a, const Geom g) {
 }
 
 }  // namespace glp
+
+// ---- NCCL baseline exchange (A/B measurement only; the product path is the peer-mailbox push above) ----------
+// The same sums taken with two ncclAllReduce calls per forward stream on the solver's stream: MAX of max|xn|
+// (one double, after the prox) and SUM of this rank's partial product with the scalar partials appended
+// (2 l ldm + 8 doubles, after the forward stream).  The kernels below only pack / unpack the staging buffer;
+// the destination buffer of the product is chosen on the device (1 - ctrl->cur), which a host-side
+// collective cannot see, hence the staging copy.
+namespace glp {
+
+struct NcclXArgs {
+  const Ctrl* ctrl;
+  double* stage;               // [2l*ldm] partial product, then tail[8] = {gd, dd, reg, sx, sy, count, -, -}
+  double* stage_m;             // [1] max|xn| (MAX-reduced)
+  int64_t slab_words;          // 2l*ldm
+  const double* scal_partial;  // [ncb][SCAL_STRIDE]
+  int32_t ncb, pad;
+  const double* xcand[2];
+  double* AX[2];
+  const double* b;
+  double* rr_partial;          // [gridDim of the post kernel]
+  double* scal_red;
+  double* cnt_red;
+};
+
+__global__ void __launch_bounds__(256) glp_nccl_fold_kernel(const NcclXArgs a) {
+  __shared__ double s[8][6];
+  if (a.ctrl != nullptr && a.ctrl->done) return;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  double gd = 0.0, dd = 0.0, reg = 0.0, mx = 0.0, sx = 0.0, sy = 0.0;
+  for (int i = tid; i < a.ncb; i += 256) {
+    const double* p = a.scal_partial + SCAL_STRIDE * i;
+    gd += __ldcg(p + 0); dd += __ldcg(p + 1); reg += __ldcg(p + 2); mx = comm_nmax(mx, __ldcg(p + 3));
+    sx += __ldcg(p + 4); sy += __ldcg(p + 5);
+  }
+  gd = warp_sum(gd); dd = warp_sum(dd); reg = warp_sum(reg); sx = warp_sum(sx); sy = warp_sum(sy);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = comm_nmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0) { s[warp][0] = gd; s[warp][1] = dd; s[warp][2] = reg; s[warp][3] = mx; s[warp][4] = sx; s[warp][5] = sy; }
+  __syncthreads();
+  if (tid == 0) {
+    double t[6] = {0, 0, 0, 0, 0, 0};
+    for (int w = 0; w < 8; ++w) {
+      t[0] += s[w][0]; t[1] += s[w][1]; t[2] += s[w][2]; t[3] = comm_nmax(t[3], s[w][3]); t[4] += s[w][4]; t[5] += s[w][5];
+    }
+    double* tail = a.stage + a.slab_words;
+    tail[0] = t[0]; tail[1] = t[1]; tail[2] = t[2]; tail[3] = t[4]; tail[4] = t[5]; tail[5] = 0.0; tail[6] = 0.0; tail[7] = 0.0;
+    a.stage_m[0] = t[3];
+  }
+}
+
+// local sparsity count against the MAX-reduced max|xn| (counts are integers: the atomic sum is exact)
+__global__ void __launch_bounds__(256) glp_nccl_count_kernel(const NcclXArgs a, const Geom g) {
+  if (a.ctrl != nullptr && a.ctrl->done) return;
+  const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : 0;
+  const double cut = xmul(1e-6, a.stage_m[0]);
+  const double* xc = a.xcand[sel];
+  const int64_t lenn = int64_t(g.l) * g.ldn;
+  double cnt = 0.0;
+  for (int64_t j = int64_t(blockIdx.x) * 256 + threadIdx.x; j < lenn; j += int64_t(gridDim.x) * 256)
+    cnt += fabs(xc[j]) > cut ? 1.0 : 0.0;
+  cnt = warp_sum(cnt);
+  if ((threadIdx.x & 31) == 0 && cnt != 0.0) atomicAdd(a.stage + a.slab_words + 5, cnt);
+}
+
+__global__ void __launch_bounds__(GATHER_THREADS) glp_nccl_post_kernel(const NcclXArgs a, const Geom g) {
+  __shared__ double s_red[GATHER_THREADS / 32];
+  if (a.ctrl != nullptr && a.ctrl->done) return;
+  const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : 0;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  double* out = a.AX[sel];
+  const int64_t lenb = int64_t(g.l) * g.ldm;
+  double rr = 0.0;
+  for (int64_t i = int64_t(blockIdx.x) * GATHER_THREADS + tid; i < a.slab_words; i += int64_t(gridDim.x) * GATHER_THREADS) {
+    const double v = a.stage[i];
+    out[i] = v;
+    if (i < lenb) {
+      const double d = v - a.b[i];
+      rr += d * d;
+    }
+  }
+  rr = warp_sum(rr);
+  if (lane == 0) s_red[warp] = rr;
+  __syncthreads();
+  if (tid == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < GATHER_THREADS / 32; ++w) tot += s_red[w];
+    a.rr_partial[blockIdx.x] = tot;
+    if (blockIdx.x == 0) {
+      const double* tail = a.stage + a.slab_words;
+      a.scal_red[0] = tail[0]; a.scal_red[1] = tail[1]; a.scal_red[2] = tail[2]; a.scal_red[3] = a.stage_m[0];
+      a.scal_red[4] = tail[3]; a.scal_red[5] = tail[4];
+      a.cnt_red[0] = tail[5];
+    }
+  }
+}
+
+}  // namespace glp

@@ -110,6 +110,8 @@ struct glp_handle {
   int evict_first = 1;
   int num_sms = 0;
   void* nccl_comm = nullptr;
+  bool xch_nccl = false;        // baseline exchange: ncclAllReduce instead of the peer-mailbox push (A/B measurements)
+  double* nccl_stage = nullptr; // [2l*ldm + 8] partial product + scalar tail, [8] max
 
   // device arena
   void* arena = nullptr;
@@ -385,6 +387,7 @@ extern "C" int glp_destroy(glp_handle* h) {
   if (h->r_lo) cudaFree(h->r_lo);
   if (h->cnt_g) cudaFree(h->cnt_g);
   if (h->gemm_ws) cudaFree(h->gemm_ws);
+  if (h->nccl_stage) cudaFree(h->nccl_stage);
   for (__nv_bfloat16* q : {h->A_hb, h->A_lb, h->At_hb, h->At_lb, h->xop_hb, h->xop_lb, h->r_hb, h->r_lb})
     if (q) cudaFree(q);
   if (h->arena) cudaFree(h->arena);
@@ -510,10 +513,12 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
 static int esize(const glp_handle* h) { return h->dtype == GLP_F32 ? 4 : 8; }
 
 static bool multi(const glp_handle* h) { return h->comm.world > 1; }
+static bool peer_push(const glp_handle* h) { return h->comm.world > 1 && !h->xch_nccl; }   // mailbox exchange
+static int glp_allreduce_f64(glp_handle* h, double* buf, size_t count, bool is_max);
 
 // ---- wide multi-RHS mode: both products of an iteration run on the tensor cores (K5) ---------------
 static bool wide_active(const glp_handle* h) {
-  return h->dtype == GLP_F32 && h->g.l >= 16 && 2 * h->g.l <= 256 && h->tensor_mode != 1;
+  return h->dtype == GLP_F32 && h->g.l >= 16 && 2 * h->g.l <= 256 && h->tensor_mode != 1 && !h->xch_nccl;
 }
 static int wide_passes(const glp_handle* h) { return h->tensor_mode == 2 ? 1 : (h->tensor_mode == 3 ? 2 : 3); }
 static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms);
@@ -711,7 +716,7 @@ static int enqueue_fwd(glp_handle* h, const Ctrl* ctrl, int sel, const void* con
     a.scal_partial = h->scal_partial;
     a.cnt_partial = h->cnt_partial;
     a.fault = h->fault;
-    if (exchange && multi(h)) {
+    if (exchange && peer_push(h)) {
       a.comm = h->comm;
       a.seq_f = seq_base(h) | ++h->idx_f;
       a.seq_t = h->seq_t_cur;
@@ -731,7 +736,7 @@ static int enqueue_tpass(glp_handle* h, const Ctrl* ctrl, const ProxArgs* p, dou
   ProxArgs pa{};
   if (p) pa = *p;
   const bool fuse = p != nullptr && g.l <= 2;
-  if (p != nullptr && exchange && multi(h)) {
+  if (p != nullptr && exchange && peer_push(h)) {
     pa.post.comm = h->comm;
     pa.post.seq_t = h->seq_t_cur = seq_base(h) | ++h->idx_t;
     pa.post.par = h->group & 1;
@@ -769,11 +774,45 @@ static ProxArgs solver_prox_args(glp_handle* h, const Ctrl* ctrl) {
   return p;
 }
 
+// NCCL baseline exchange (glp_comm.cuh, bottom): packing kernels + two collectives per forward stream
+static NcclXArgs nccl_args(glp_handle* h, const Ctrl* ctrl) {
+  NcclXArgs a{};
+  a.ctrl = ctrl;
+  a.slab_words = int64_t(2) * h->g.l * h->g.ldm;
+  a.stage = h->nccl_stage;
+  a.stage_m = h->nccl_stage + a.slab_words + 8;
+  a.scal_partial = h->scal_partial;
+  a.ncb = h->g.ncb;
+  a.xcand[0] = h->state[0]; a.xcand[1] = h->state[1];
+  a.AX[0] = h->AX[0]; a.AX[1] = h->AX[1];
+  a.b = h->b;
+  a.rr_partial = h->rr_g;
+  a.scal_red = h->scal_red;
+  a.cnt_red = h->cnt_red;
+  return a;
+}
+static int nccl_after_prox(glp_handle* h, const Ctrl* ctrl) {   // local scalar partials -> staging; MAX of max|xn|
+  const NcclXArgs a = nccl_args(h, ctrl);
+  glp_nccl_fold_kernel<<<1, 256, 0, h->stream>>>(a);
+  CU_TRY(cudaGetLastError());
+  h->n_launches++;
+  return glp_allreduce_f64(h, a.stage_m, 1, true);
+}
+
 static int enqueue_solver_fwd(glp_handle* h, const Ctrl* ctrl) {
   if (wide_active(h)) return enqueue_wide_fwd(h, ctrl);
   const void* Xb[2];
   const double* xc[2] = {h->state[0], h->state[1]};
   for (int s = 0; s < 2; ++s) Xb[s] = h->dtype == GLP_F32 ? h->xop : static_cast<const void*>(h->state[s]);
+  if (h->xch_nccl) {   // partial product into the staging buffer, count against the global max, one SUM all-reduce
+    const NcclXArgs a = nccl_args(h, ctrl);
+    double* stage2[2] = {a.stage, a.stage};
+    GLP_TRY(enqueue_fwd(h, ctrl, 0, Xb, stage2, xc, 2 * h->g.l, 0, false));
+    glp_nccl_count_kernel<<<h->gather_grid, 256, 0, h->stream>>>(a, h->g);
+    CU_TRY(cudaGetLastError());
+    h->n_launches++;
+    return glp_allreduce_f64(h, a.stage, size_t(a.slab_words) + 8, false);
+  }
   return enqueue_fwd(h, ctrl, 0, Xb, h->AX, xc, 2 * h->g.l, 1, true);
 }
 
@@ -781,6 +820,12 @@ static int enqueue_solver_fwd(glp_handle* h, const Ctrl* ctrl) {
 // candidate product buffers, with the residual norm and the exchanged scalars.
 static int enqueue_gather(glp_handle* h, const Ctrl* ctrl) {
   if (!multi(h)) return GLP_OK;
+  if (h->xch_nccl) {
+    glp_nccl_post_kernel<<<h->gather_grid, GATHER_THREADS, 0, h->stream>>>(nccl_args(h, ctrl), h->g);
+    CU_TRY(cudaGetLastError());
+    h->n_launches++;
+    return GLP_OK;
+  }
   if (wide_active(h)) return enqueue_wide_exchange(h, ctrl, 1);
   GatherArgs a{};
   a.comm = h->comm;
@@ -849,7 +894,7 @@ static int phase_prepare(glp_handle* h, int algo, const void* x0_dev, double mu0
   // x0 -> candidate slot of cur = 0
   if (h->dtype == GLP_F32) CU_TRY(to_planar(h->stream, static_cast<const float*>(x0_dev), h->state[1], g.n, g.l, g.ldn));
   else CU_TRY(to_planar(h->stream, static_cast<const double*>(x0_dev), h->state[1], g.n, g.l, g.ldn));
-  if (multi(h)) {
+  if (peer_push(h)) {
     // every rank has drained its previous solve before it gets here: after the epoch barrier the
     // mailboxes may be reused from parity 0
     glp_epoch_post_kernel<<<1, 32, 0, h->stream>>>(h->comm, h->epoch);
@@ -861,22 +906,24 @@ static int phase_prepare(glp_handle* h, int algo, const void* x0_dev, double mu0
   return GLP_OK;
 }
 
+static int nccl_after_prox(glp_handle* h, const Ctrl* ctrl);
 // threshold + scalars of x0 (init epilogue)
 static int phase_init_prox(glp_handle* h) {
-  if (multi(h)) {
+  if (peer_push(h)) {
     glp_epoch_wait_kernel<<<1, 32, 0, h->stream>>>(h->comm, h->epoch, h->fault);
     CU_TRY(cudaGetLastError());
   }
   ProxArgs p = solver_prox_args(h, nullptr);
   p.cur = 0;
   p.init = 1;
-  if (multi(h)) {
+  if (peer_push(h)) {
     p.post.comm = h->comm;
     p.post.seq_t = h->seq_t_cur = seq_base(h) | ++h->idx_t;
     p.post.par = h->group & 1;
     p.post.fin = h->fin_t;
   }
   CU_TRY(launch_prox(h, p, 0));
+  if (h->xch_nccl) GLP_TRY(nccl_after_prox(h, nullptr));
   return GLP_OK;
 }
 
@@ -922,7 +969,9 @@ static int phase_tpass(glp_handle* h) {
     CU_TRY(launch_prox(h, p, 0));
     return GLP_OK;
   }
-  return enqueue_tpass(h, h->cur_ctrl, &p, h->grad, true);
+  GLP_TRY(enqueue_tpass(h, h->cur_ctrl, &p, h->grad, true));
+  if (h->xch_nccl) GLP_TRY(nccl_after_prox(h, h->cur_ctrl));
+  return GLP_OK;
 }
 static int phase_fwd(glp_handle* h) { return enqueue_solver_fwd(h, h->cur_ctrl); }
 static int phase_gather(glp_handle* h) { return enqueue_gather(h, h->cur_ctrl); }
@@ -1085,6 +1134,29 @@ extern "C" int glp_comm_attach(glp_handle* h, int rank, int world, int64_t n_tot
     c.mail[r] = static_cast<unsigned long long*>(ptr);
   }
   h->comm = c;
+  h->g.world = world;
+  h->g.n_total = n_total;
+  return GLP_OK;
+}
+
+extern "C" int glp_comm_attach_nccl(glp_handle* h, void* nccl_comm, int rank, int world, int64_t n_total) {
+  if (h == nullptr || nccl_comm == nullptr) return fail(GLP_ERR_ARG, "null argument");
+  if (world < 1 || world > MAX_WORLD || rank < 0 || rank >= world) return fail(GLP_ERR_ARG, "bad rank/world %d/%d", rank, world);
+  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
+  if (n_total < h->g.n) return fail(GLP_ERR_ARG, "n_total (%lld) < local n (%d)", (long long)n_total, h->g.n);
+  CU_TRY(cudaSetDevice(h->device));
+  if (h->nccl_stage == nullptr) {
+    const size_t words = size_t(2) * h->g.l * h->g.ldm + 16;
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->nccl_stage), words * 8));
+    CU_TRY(cudaMemsetAsync(h->nccl_stage, 0, words * 8, h->stream));
+  }
+  Comm c{};
+  c.world = world;
+  c.rank = rank;
+  c.slab_words = int64_t(2) * h->g.l * h->g.ldm;
+  h->comm = c;
+  h->nccl_comm = nccl_comm;
+  h->xch_nccl = true;
   h->g.world = world;
   h->g.n_total = n_total;
   return GLP_OK;

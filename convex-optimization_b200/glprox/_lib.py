@@ -86,6 +86,7 @@ SIGNATURES = {
     "glp_nccl_unique_id": (_I, [_VP]),
     "glp_nccl_comm_create": (_I, [C.POINTER(_VP), _VP, _I, _I, _I]),
     "glp_nccl_comm_destroy": (_I, [_VP]),
+    "glp_comm_attach_nccl": (_I, [_VP, _VP, _I, _I, _I64]),
     "glp_metrics_eval": (_I, [_VP, _VP, _VP, _D, _D, C.POINTER(GlpMetrics)]),
     "glp_randn": (_I, [_VP, _I, _I64, _I64, _I64, C.c_uint64, _I64, _I64, _VP]),
 }

@@ -290,6 +290,10 @@ class GroupLassoProblem:
         if self._h:
             _lib.load().glp_destroy(self._h)
             self._h = C.c_void_p()
+        comm = getattr(self, "_nccl_comm", None)
+        if comm:
+            _lib.load().glp_nccl_comm_destroy(comm)
+            self._nccl_comm = None
 
     def __del__(self):
         try:
@@ -394,13 +398,41 @@ def exchange_handles(mine, group=None):
     return b"".join(bytes(o.cpu().numpy().tobytes()) for o in out)
 
 
-def attach_distributed(prob, n_total, group=None):
-    """One process per GPU: export this rank's mailbox, all-gather the IPC handles, map the peers."""
+def attach_distributed(prob, n_total, group=None, exchange="peer"):
+    """One process per GPU: export this rank's mailbox, all-gather the IPC handles, map the peers.
+
+    exchange="nccl" selects the baseline exchange instead (two ncclAllReduce calls per forward stream on a
+    communicator created here from an id broadcast over `group`); it exists for A/B measurements."""
     import torch.distributed as dist
     rank, world = dist.get_rank(group), dist.get_world_size(group)
+    if exchange == "nccl":
+        return _attach_nccl(prob, n_total, rank, world, group)
+    if exchange != "peer":
+        raise ValueError("exchange must be 'peer' or 'nccl'")
     blob, _ = prob.export_mailbox(world)
     prob.attach_peers(rank, world, n_total, exchange_handles(blob, group), kind=0)
     dist.barrier(group)  # every mailbox is mapped everywhere before the first push
+    return prob
+
+
+def _attach_nccl(prob, n_total, rank, world, group):
+    import torch
+    import torch.distributed as dist
+    lib = _lib.load()
+    ident = (C.c_char * 128)()
+    if rank == 0:
+        _lib.check(lib.glp_nccl_unique_id(ident))
+    on = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+    t = torch.tensor(list(ident.raw), dtype=torch.uint8, device=on)
+    dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    ident = (C.c_char * 128).from_buffer_copy(bytes(t.cpu().numpy().tobytes()))
+    comm = C.c_void_p()
+    with prob._device_ctx():
+        _lib.check(lib.glp_nccl_comm_create(C.byref(comm), ident, int(rank), int(world), prob.device.index))
+        _lib.check(lib.glp_comm_attach_nccl(prob.handle, comm, int(rank), int(world), int(n_total)))
+    prob.rank, prob.world, prob.n_total = int(rank), int(world), int(n_total)
+    prob._nccl_comm = comm
+    dist.barrier(group)
     return prob
 
 

@@ -199,6 +199,10 @@ int glp_group_solve(glp_handle** hs, int G, int algo, const void* const* x0_dev,
 int glp_nccl_unique_id(void* id128 /* 128 bytes out */);
 int glp_nccl_comm_create(void** comm_out, const void* id128, int rank, int world, int device);
 int glp_nccl_comm_destroy(void* comm);
+/* Baseline exchange for A/B measurements: shard sums with two ncclAllReduce calls per forward stream on the
+ * solver's stream instead of the peer-mailbox push (l <= 8 streaming path only; bit-identical on all ranks like
+ * the product path, slower: see DESIGN.md section 5). */
+int glp_comm_attach_nccl(glp_handle* h, void* nccl_comm, int rank, int world, int64_t n_total);
 
 /* ---- K5: tensor-core products of the wide multi-RHS mode (tcgen05 / TMEM, kind::tf32) -------------
  * D[N][ldd] (fp64, planar) = P[M x K] . Q[N x K]^T with P row-major (pitch ldp) and Q planar (pitch ldq),

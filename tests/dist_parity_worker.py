@@ -42,6 +42,26 @@ def main():
             lst = [torch.empty_like(t) for _ in range(world)]
             dist.all_gather(lst, t)
             assert all(torch.equal(lst[0], z) for z in lst)
+    # baseline exchange (two ncclAllReduce calls per forward stream instead of the peer-mailbox push): same bar
+    from glprox import GroupLassoProblem, attach_distributed
+    for name in ("fixture_maxit40", "harsh_ls"):
+        rec = load_golden(name)
+        A, b, x0, u, mu = golden_inputs(rec)
+        c0, c1 = shard_bounds(A.shape[1], world, 64)[rank]
+        prob = GroupLassoProblem(torch.from_numpy(np.ascontiguousarray(A[:, c0:c1])).cuda(), torch.from_numpy(b).cuda())
+        attach_distributed(prob, A.shape[1], exchange="nccl")
+        for algo in ("FProxGD", "ProxGD"):
+            for rep in range(2):
+                x, k, out = prob.solve(algo, torch.from_numpy(x0[c0:c1].copy()).cuda(), mu, dict(rec["opts"]))
+                assert k == int(rec[algo + "_k"]), (name, algo, k)
+                fh, ref = np.asarray(out["f_hist"]), rec[algo + "_f_hist"]
+                assert np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-10, (name, algo)
+                assert np.max(np.abs(x.cpu().numpy() - rec[algo + "_x"][c0:c1])) <= 1e-8
+                t = torch.tensor([out["fval"], float(k)], device="cuda", dtype=torch.float64)
+                lst = [torch.empty_like(t) for _ in range(world)]
+                dist.all_gather(lst, t)
+                assert all(torch.equal(lst[0], z) for z in lst)
+        prob.close()
     # wide multi-RHS mode (l = 32, fp32): tcgen05 products per shard, reduce-scatter + all-gather over NVLink
     from oracle import glprox_oracle as orc
     m, n, l = 512, 1024 * world, 32
