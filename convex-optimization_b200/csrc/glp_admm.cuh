@@ -1,0 +1,327 @@
+// glp_admm.cuh -- SURVEY.md 8(f) row 4: gl_Admm_dual (code/gl_ADMM_dual.py:10-103) on the two stream kernels.
+//
+// One iteration of the reference is
+//   z = (I + rho A A^T)^-1 (A (x - rho u) - b)      :63   Cholesky factor L computed once (:57)
+//   u' = P_mu(x / rho - A^T z)                      :64   row-wise projection onto the mu-ball (:45-47)
+//   x' = x - tau rho (u' + A^T z)                   :65
+//   r = u' + A^T z ,  s = A (u - u')                :67-68  residuals, judged by their matrix 2-norms (:87-88)
+//   f = 0.5 ||A x' - b||^2 + mu sum_i ||x'_i||      :72
+// Here: ONE forward stream (K1) over the 2l operand columns [x - rho u | u] gives A(x - rho u) and A u; by
+// linearity A x = A(x - rho u) + rho A u and s = A u_prev - A u, so the objective, the sparsity and both
+// residual norms of iteration k are evaluated after the forward stream of iteration k+1 (kernel `mid`,
+// which also does the two triangular solves with L in one CTA); ONE transposed stream (K2) gives A^T z and
+// `update` applies the row-local projection / multiplier step.  A is streamed exactly twice per iteration,
+// the control (k, the converge_len counter, histories) lives on the device.
+// Scope: homework-sized systems -- the m x m factor is built and applied by single-CTA kernels (m <= 2048),
+// l <= 2 (the residual 2-norms are taken from the l x l Gram matrices in closed form).
+#pragma once
+#include "glp_decide.h"
+#include "glp_device.cuh"
+#include "glp_types.cuh"
+
+namespace glp {
+
+constexpr int ADMM_MAX_M = 2048;
+constexpr int ADMM_THREADS = 1024;
+
+struct AdmmConst {
+  int32_t maxit, converge_len, hist_cap, pad;
+  double thres, tau, rho, mu;
+};
+
+// ---- G = I + rho A A^T (lower triangle and diagonal), one 32 x 32 tile per CTA ------------------------------
+template <typename T>
+__global__ void __launch_bounds__(1024) glp_admm_gram_kernel(const T* __restrict__ A, int64_t lda, int m, int n,
+                                                             double rho, double* __restrict__ G) {
+  __shared__ double sa[32][33], sb[32][33];
+  const int bi = blockIdx.y, bj = blockIdx.x;
+  if (bj > bi) return;
+  const int ty = threadIdx.y, tx = threadIdx.x;
+  const int i = bi * 32 + ty, j = bj * 32 + tx;
+  double acc = 0.0;
+  for (int k0 = 0; k0 < n; k0 += 32) {
+    const int k = k0 + tx;
+    sa[ty][tx] = (bi * 32 + ty < m && k < n) ? double(A[int64_t(bi * 32 + ty) * lda + k]) : 0.0;
+    sb[ty][tx] = (bj * 32 + ty < m && k < n) ? double(A[int64_t(bj * 32 + ty) * lda + k]) : 0.0;
+    __syncthreads();
+#pragma unroll 8
+    for (int q = 0; q < 32; ++q) acc = fma(sa[ty][q], sb[tx][q], acc);
+    __syncthreads();
+  }
+  if (i < m && j < m && j <= i) G[int64_t(i) * m + j] = rho * acc + (i == j ? 1.0 : 0.0);
+}
+
+// ---- in-place lower Cholesky G = L L^T, one CTA, right-looking by columns ---------------------------------
+__global__ void __launch_bounds__(ADMM_THREADS) glp_admm_chol_kernel(double* __restrict__ G, int m, int32_t* fault) {
+  const int tid = threadIdx.x;
+  for (int j = 0; j < m; ++j) {
+    const double d = G[int64_t(j) * m + j];
+    if (!(d > 0.0)) {  // not positive definite (NaN input): report instead of spinning on garbage
+      if (tid == 0 && fault) atomicExch(fault, 3);
+      return;
+    }
+    const double ljj = sqrt(d);
+    __syncthreads();
+    for (int i = j + tid; i < m; i += ADMM_THREADS) G[int64_t(i) * m + j] = (i == j) ? ljj : G[int64_t(i) * m + j] / ljj;
+    __syncthreads();
+    // trailing update of the lower triangle: G[i][k] -= L[i][j] L[k][j], j < k <= i
+    const int r = m - j - 1;
+    for (int64_t e = tid; e < int64_t(r) * r; e += ADMM_THREADS) {
+      const int ii = int(e / r), kk = int(e - int64_t(ii) * r);
+      if (kk <= ii) {
+        const int i = j + 1 + ii, k = j + 1 + kk;
+        G[int64_t(i) * m + k] -= G[int64_t(i) * m + j] * G[int64_t(k) * m + j];
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- row-local update (also the initial pass): u' , x' , operands, partial sums per column block -----------
+struct AdmmUpdArgs {
+  const Ctrl* ctrl;        // done => no-op
+  int32_t init;            // 1: x = x0, u = 0: only operands and partials
+  int32_t pad;
+  double* x;               // [l][ldn]
+  double* u;               // [l][ldn]
+  const double* grad;      // [l][ldn] = A^T z
+  void* xop;               // [2l][ldn] dtype T: [x - rho u | u]
+  double* scal_partial;    // [ncb][SCAL_STRIDE]: {r00, r01, reg, max|x|, r11, -, -, -}
+  AdmmConst c;
+};
+
+template <typename T>
+__global__ void glp_admm_update_kernel(const AdmmUpdArgs a, const Geom g) {
+  __shared__ double s_red[8][5];
+  if (a.ctrl != nullptr && a.ctrl->done) return;
+  constexpr int TC = Elem<T>::TILE_COLS;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t j = int64_t(blockIdx.x) * TC + tid;
+  const int l = g.l;
+  const int64_t ldn = g.ldn;
+  T* xop = static_cast<T*>(a.xop);
+  double r00 = 0.0, r01 = 0.0, r11 = 0.0, reg = 0.0, mx = 0.0;
+  if (tid < TC && j < g.n) {
+    const double taurho = xmul(a.c.tau, a.c.rho);
+    double nn = 0.0, xv[2], gv[2] = {0.0, 0.0}, vv[2];
+    for (int c = 0; c < l; ++c) {
+      xv[c] = a.x[c * ldn + j];
+      if (!a.init) {
+        gv[c] = __ldcg(&a.grad[c * ldn + j]);
+        vv[c] = xsub(xdiv(xv[c], a.c.rho), gv[c]);   // x_k / rho - A.T @ z                   :64
+        nn = xadd(nn, xmul(vv[c], vv[c]));
+      }
+    }
+    double n2 = 0.0, rr[2] = {0.0, 0.0};
+    if (!a.init) {
+      const double rn = __dsqrt_rn(nn);
+      const double den = rn < a.c.mu ? a.c.mu : rn;    // np.clip(row_norms, a_min=mu)              :47
+      for (int c = 0; c < l; ++c) {
+        const double un = xdiv(xmul(a.c.mu, vv[c]), den);
+        rr[c] = xadd(un, gv[c]);                       // r_k = u + A.T @ z                        :67
+        const double xn = xsub(xv[c], xmul(taurho, rr[c]));   // x_k - tau * rho * (u + A.T @ z)   :65
+        a.x[c * ldn + j] = xn;
+        a.u[c * ldn + j] = un;
+        xop[c * ldn + j] = T(xsub(xn, xmul(a.c.rho, un)));
+        xop[(l + c) * ldn + j] = T(un);
+        n2 = xadd(n2, xmul(xn, xn));
+        mx = fmax(mx, fabs(xn));
+      }
+    } else {
+      for (int c = 0; c < l; ++c) {
+        a.u[c * ldn + j] = 0.0;
+        xop[c * ldn + j] = T(xv[c]);
+        xop[(l + c) * ldn + j] = T(0.0);
+        n2 = xadd(n2, xmul(xv[c], xv[c]));
+        mx = fmax(mx, fabs(xv[c]));
+      }
+    }
+    reg = __dsqrt_rn(n2);
+    r00 = rr[0] * rr[0]; r01 = rr[0] * rr[1]; r11 = rr[1] * rr[1];
+  }
+  r00 = warp_sum(r00); r01 = warp_sum(r01); r11 = warp_sum(r11); reg = warp_sum(reg);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0) { s_red[warp][0] = r00; s_red[warp][1] = r01; s_red[warp][2] = reg; s_red[warp][3] = mx; s_red[warp][4] = r11; }
+  __syncthreads();
+  if (tid == 0) {
+    double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0, t4 = 0.0;
+    for (int w = 0; w < int(blockDim.x >> 5); ++w) {
+      t0 += s_red[w][0]; t1 += s_red[w][1]; t2 += s_red[w][2]; t3 = fmax(t3, s_red[w][3]); t4 += s_red[w][4];
+    }
+    double* out = a.scal_partial + SCAL_STRIDE * int64_t(blockIdx.x);
+    out[0] = t0; out[1] = t1; out[2] = t2; out[3] = t3; out[4] = t4; out[5] = 0.0;
+  }
+}
+
+// ---- mid: evaluate the iteration whose products just arrived, advance the control, z = L^-T L^-1 (P1 - b) ----
+struct AdmmMidArgs {
+  const Ctrl* cin;
+  Ctrl* cout;
+  AdmmConst c;
+  const double* P;            // [2l][ldm] = A [x - rho u | u]
+  const double* b;            // [l][ldm]
+  double* Au_prev;            // [l][ldm]
+  const double* L;            // [m][m] lower Cholesky factor
+  const double* scal_partial; int32_t n_scal;
+  const double* cnt_partial;  int32_t n_cnt;
+  void* r;                    // [l][ldm] dtype T: z, the operand of the transposed stream
+  double* f_hist;
+  double* f_hist_best;
+  double size_total;          // n_total * l
+};
+
+// largest singular value of a matrix with Gram matrix [[a, b], [b, c]] (l = 2) or [[a]] (l = 1)
+__device__ __forceinline__ double admm_norm2(double a, double b, double c, int l) {
+  if (l == 1) return sqrt(a);
+  const double h = 0.5 * (a - c);
+  return sqrt(0.5 * (a + c) + sqrt(h * h + b * b));
+}
+
+template <typename T>
+__global__ void __launch_bounds__(ADMM_THREADS) glp_admm_mid_kernel(const AdmmMidArgs a, const Geom g) {
+  extern __shared__ double s_w[];                 // [l][m] right-hand sides / solution
+  __shared__ double s_red[ADMM_THREADS / 32][8];
+  __shared__ Ctrl s_out;
+  __shared__ double s_z[2][32];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const Ctrl cin = *a.cin;
+  if (cin.done) {
+    if (tid == 0) *a.cout = cin;
+    return;
+  }
+  const int l = g.l, m = g.m;
+  const int64_t ldm = g.ldm;
+  const double* P1 = a.P;
+  const double* P2 = a.P + int64_t(l) * ldm;
+  // ---- reductions: ||A x - b||^2 with A x = P1 + rho P2, Gram of s = A u_prev - A u, scalar partials
+  double v[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // rr, s00, s01, s11, r00, r01, r11, reg
+  double mx = 0.0, cnt = 0.0;
+  for (int i = tid; i < m; i += ADMM_THREADS) {
+    double sv[2] = {0.0, 0.0};
+    for (int c = 0; c < l; ++c) {
+      const double p2 = P2[c * ldm + i];
+      const double d = xsub(xadd(P1[c * ldm + i], xmul(a.c.rho, p2)), a.b[c * ldm + i]);
+      v[0] += d * d;
+      sv[c] = xsub(a.Au_prev[c * ldm + i], p2);
+    }
+    v[1] += sv[0] * sv[0]; v[2] += sv[0] * sv[1]; v[3] += sv[1] * sv[1];
+  }
+  for (int i = tid; i < a.n_scal; i += ADMM_THREADS) {
+    const double* p = a.scal_partial + SCAL_STRIDE * int64_t(i);
+    v[4] += __ldcg(p + 0); v[5] += __ldcg(p + 1); v[7] += __ldcg(p + 2); mx = fmax(mx, __ldcg(p + 3)); v[6] += __ldcg(p + 4);
+  }
+  for (int i = tid; i < a.n_cnt; i += ADMM_THREADS) cnt += __ldcg(&a.cnt_partial[i]);
+#pragma unroll
+  for (int q = 0; q < 8; ++q) v[q] = warp_sum(v[q]);
+  cnt = warp_sum(cnt);
+  if (lane == 0) {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) s_red[warp][q] = v[q];
+  }
+  __syncthreads();
+  if (tid == 0) {
+    double t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int w = 0; w < ADMM_THREADS / 32; ++w)
+      for (int q = 0; q < 8; ++q) t[q] += s_red[w][q];
+    s_red[0][0] = t[0]; s_red[0][1] = t[1]; s_red[0][2] = t[2]; s_red[0][3] = t[3];
+    s_red[0][4] = t[4]; s_red[0][5] = t[5]; s_red[0][6] = t[6]; s_red[0][7] = t[7];
+  }
+  __syncthreads();
+  __shared__ double s_cnt[ADMM_THREADS / 32];
+  if (lane == 0) s_cnt[warp] = cnt;
+  __syncthreads();
+  if (tid == 0) {
+    double ctot = 0.0;
+    for (int w = 0; w < ADMM_THREADS / 32; ++w) ctot += s_cnt[w];
+    Ctrl out = cin;
+    const double f_now = xadd(xmul(0.5, s_red[0][0]), xmul(a.c.mu, s_red[0][7]));
+    out.f_cur = f_now;
+    out.s_cur = ctot / a.size_total;
+    if (cin.k > 0) {   // iteration cin.k has just been completed by the forward stream: record and test it (:72-99)
+      if (a.f_hist != nullptr && cin.k - 1 < a.c.hist_cap) a.f_hist[cin.k - 1] = f_now;
+      out.f_best = f_now < cin.f_best ? f_now : cin.f_best;
+      if (a.f_hist_best != nullptr && cin.k - 1 < a.c.hist_cap) a.f_hist_best[cin.k - 1] = out.f_best;
+      const double rn = admm_norm2(s_red[0][4], s_red[0][5], s_red[0][6], l);
+      const double sn = admm_norm2(s_red[0][1], s_red[0][2], s_red[0][3], l);
+      out.stable = (rn < a.c.thres && sn < a.c.thres) ? cin.stable + 1 : 0;
+      if (out.stable >= a.c.converge_len) out.done = 1;
+    }
+    if (!out.done) {
+      if (cin.k < a.c.maxit) { out.k = cin.k + 1; out.n_fwd = cin.n_fwd + 1; out.n_tpass = cin.n_tpass + 1; }
+      else out.done = 1;
+    }
+    s_out = out;
+    *a.cout = out;
+  }
+  __syncthreads();
+  if (s_out.done) return;
+
+  // ---- w = P1 - b ; A u_prev <- A u ; then the two triangular solves in shared memory
+  for (int i = tid; i < m; i += ADMM_THREADS)
+    for (int c = 0; c < l; ++c) {
+      s_w[c * m + i] = xsub(P1[c * ldm + i], a.b[c * ldm + i]);
+      a.Au_prev[c * ldm + i] = P2[c * ldm + i];
+    }
+  __syncthreads();
+  const double* L = a.L;
+  // forward substitution  L y = w, 32 columns at a time: warp c solves the diagonal block of RHS c with
+  // shuffles, then every thread subtracts the panel's contribution from the rows below
+  for (int j0 = 0; j0 < m; j0 += 32) {
+    const int pw = m - j0 < 32 ? m - j0 : 32;
+    if (warp < l) {
+      const int c = warp;
+      double wi = lane < pw ? s_w[c * m + j0 + lane] : 0.0;
+      for (int jj = 0; jj < pw; ++jj) {
+        const double zj = __shfl_sync(0xffffffffu, wi, jj) / L[int64_t(j0 + jj) * m + j0 + jj];
+        if (lane == jj) wi = zj;
+        else if (lane > jj && lane < pw) wi -= L[int64_t(j0 + lane) * m + j0 + jj] * zj;
+      }
+      if (lane < pw) { s_w[c * m + j0 + lane] = wi; s_z[c][lane] = wi; }
+    }
+    __syncthreads();
+    for (int i = j0 + pw + tid; i < m; i += ADMM_THREADS) {
+      double acc0 = 0.0, acc1 = 0.0;
+      const double* Li = L + int64_t(i) * m + j0;
+      for (int jj = 0; jj < pw; ++jj) {
+        const double lij = Li[jj];
+        acc0 += lij * s_z[0][jj];
+        if (l > 1) acc1 += lij * s_z[1][jj];
+      }
+      s_w[i] -= acc0;
+      if (l > 1) s_w[m + i] -= acc1;
+    }
+    __syncthreads();
+  }
+  // back substitution  L^T z = y, panels from the bottom
+  for (int j1 = m; j1 > 0; j1 -= 32) {
+    const int j0 = j1 - 32 > 0 ? j1 - 32 : 0, pw = j1 - j0;
+    if (warp < l) {
+      const int c = warp;
+      double wi = lane < pw ? s_w[c * m + j0 + lane] : 0.0;
+      for (int jj = pw - 1; jj >= 0; --jj) {
+        const double zj = __shfl_sync(0xffffffffu, wi, jj) / L[int64_t(j0 + jj) * m + j0 + jj];
+        if (lane == jj) wi = zj;
+        else if (lane < jj) wi -= L[int64_t(j0 + jj) * m + j0 + lane] * zj;   // (L^T)[lane][jj] = L[jj][lane]
+      }
+      if (lane < pw) { s_w[c * m + j0 + lane] = wi; s_z[c][lane] = wi; }
+    }
+    __syncthreads();
+    for (int i = tid; i < j0; i += ADMM_THREADS) {
+      double acc0 = 0.0, acc1 = 0.0;
+      for (int jj = 0; jj < pw; ++jj) {
+        const double lji = L[int64_t(j0 + jj) * m + i];   // coalesced over i
+        acc0 += lji * s_z[0][jj];
+        if (l > 1) acc1 += lji * s_z[1][jj];
+      }
+      s_w[i] -= acc0;
+      if (l > 1) s_w[m + i] -= acc1;
+    }
+    __syncthreads();
+  }
+  T* r = static_cast<T*>(a.r);
+  for (int i = tid; i < m; i += ADMM_THREADS)
+    for (int c = 0; c < l; ++c) r[c * ldm + i] = T(s_w[c * m + i]);
+}
+
+}  // namespace glp

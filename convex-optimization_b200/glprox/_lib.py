@@ -44,6 +44,11 @@ class GlpProfile(C.Structure):
                 ("bytes_per_launch", C.c_double)]
 
 
+class GlpAdmmOpts(C.Structure):
+    _fields_ = [("maxit", C.c_int32), ("converge_len", C.c_int32), ("thres", C.c_double), ("tau", C.c_double),
+                ("rho", C.c_double)]
+
+
 class GlpMetrics(C.Structure):
     _fields_ = [(k, C.c_double) for k in ("sumsq_x", "sumsq_ref", "sumsq_diff", "reg", "max_abs", "count", "rr",
                                           "objective", "sparsity", "err_exact", "err_ref")]
@@ -87,6 +92,8 @@ SIGNATURES = {
     "glp_nccl_comm_create": (_I, [C.POINTER(_VP), _VP, _I, _I, _I]),
     "glp_nccl_comm_destroy": (_I, [_VP]),
     "glp_comm_attach_nccl": (_I, [_VP, _VP, _I, _I, _I64]),
+    "glp_admm_default_opts": (_I, [C.POINTER(GlpAdmmOpts)]),
+    "glp_admm_dual": (_I, [_VP, _VP, _D, C.POINTER(GlpAdmmOpts), _VP, C.POINTER(GlpResult), _VP, _I]),
     "glp_metrics_eval": (_I, [_VP, _VP, _VP, _D, _D, C.POINTER(GlpMetrics)]),
     "glp_randn": (_I, [_VP, _I, _I64, _I64, _I64, C.c_uint64, _I64, _I64, _VP]),
 }

@@ -34,6 +34,8 @@ DEFAULT_OPTS.update({
     "SGD": {"maxit": 2100, "thres": 1e-3, "step_type": "diminishing", "alpha0": 1e-3, "ftol": 1e-5,
             "stable_len_threshold": 100, "continuous_subgradient_flag": False},
 })
+# gl_ADMM_dual.py:11-17
+ADMM_DUAL_DEFAULT_OPTS = {"maxit": 100, "thres": 1e-3, "tau": (1 + 5 ** 0.5) * 0.5, "rho": 1e2, "converge_len": 20}
 ALGO_ID = {"ProxGD": _lib.GLP_PROXGD, "FProxGD": _lib.GLP_FPROXGD, "FGD": _lib.GLP_FGD, "GD": _lib.GLP_GD,
            "SGD": _lib.GLP_SGD}
 # additive keys (not in the reference): dtype 'fp32'|'fp64', backend 'auto'|'stream'|'persistent',
@@ -359,6 +361,27 @@ class GroupLassoProblem:
         return combine_metrics(sums, max_abs, None if getattr(self, "world", 1) > 1 else met.rr, mu, ref is not None)
 
 
+    def solve_admm_dual(self, x0, mu, opts=None):
+        """gl_Admm_dual (code/gl_ADMM_dual.py) on this problem; x0 a CUDA tensor, returns (x, k, out)."""
+        import torch
+        lib = _lib.load()
+        merged = dict(ADMM_DUAL_DEFAULT_OPTS)
+        merged.update(opts or {})
+        o = _lib.GlpAdmmOpts(maxit=int(merged["maxit"]), converge_len=int(merged["converge_len"]),
+                             thres=float(merged["thres"]), tau=float(merged["tau"]), rho=float(merged["rho"]))
+        x0d = x0.to(device=self.device, dtype=self.dtype).contiguous()
+        x = torch.empty_like(x0d)
+        cap = int(o.maxit) + 8
+        f_hist = np.empty(cap, dtype=np.float64)
+        res = _lib.GlpResult()
+        t0 = time.perf_counter()
+        with torch.cuda.device(self.device):
+            _lib.check(lib.glp_admm_dual(self._h, x0d.data_ptr(), float(mu), C.byref(o), x.data_ptr(), C.byref(res),
+                                         f_hist.ctypes.data, cap))
+        tt = time.perf_counter() - t0
+        return x, int(res.iters), _format_out(res, f_hist[:res.iters], tt)
+
+
 def combine_metrics(sums, max_abs, rr, mu, has_ref):
     """Finish the metrics from (sumsq_x, sumsq_ref, sumsq_diff, reg, count, size) totals."""
     sx, sr, sd, reg, cnt, size = sums
@@ -370,6 +393,37 @@ def combine_metrics(sums, max_abs, rr, mu, has_ref):
             "err_ref": nd / (1.0 + nr) if has_ref else nan,     # main.py:48 errfun(ref, x)
             "norm_x": float(nx), "norm_ref": float(nr), "norm_diff": float(nd), "reg": reg,
             "max_abs": max_abs, "count": int(cnt)}
+
+
+def solve_admm_dual(x0, A, b, mu, opts):
+    """Drop-in body of gl_Admm_dual: NumPy arrays (uploaded for the call) or CUDA tensors."""
+    merged = dict(ADMM_DUAL_DEFAULT_OPTS)
+    merged.update(opts or {})
+    import torch
+    if isinstance(A, torch.Tensor):
+        if not A.is_cuda:
+            raise ValueError("torch tensors must live on a CUDA device (NumPy arrays take the host path)")
+        prob = GroupLassoProblem(A, b)
+        try:
+            return prob.solve_admm_dual(x0, mu, merged)
+        finally:
+            prob.close()
+    A = np.asarray(A)
+    x0, b = np.asarray(x0), np.asarray(b)
+    if A.ndim != 2 or x0.ndim != 2 or b.ndim != 2 or x0.shape[0] != A.shape[1] or b.shape[0] != A.shape[0] or x0.shape[1] != b.shape[1]:
+        raise ValueError("shape mismatch: A %s, x0 %s, b %s" % (A.shape, x0.shape, b.shape))
+    dt = _mode_dtype(A.dtype, merged)
+    dev = torch.device("cuda", int(merged.get("device", 0)))
+    t0 = time.perf_counter()
+    to = lambda z: torch.from_numpy(np.ascontiguousarray(z, dtype=dt)).to(dev)
+    prob = GroupLassoProblem(to(A), to(b))
+    try:
+        x, k, out = prob.solve_admm_dual(to(x0), mu, merged)
+        xh = x.cpu().numpy()
+    finally:
+        prob.close()
+    out["tt"] = time.perf_counter() - t0
+    return xh, k, out
 
 
 def shard_bounds(n, world, align=128):

@@ -31,6 +31,7 @@ SOLVERS = {  # name -> (row label of doc/report.md:439-447, algo key)
     "FGD": ("FGD Primal", "FGD"),
     "ProxGD": ("ProxGD Primal", "ProxGD"),
     "FProxGD": ("FProxGD Primal", "FProxGD"),
+    "ADMM_dual": ("ADMM Dual", "ADMM_dual"),   # doc/report.md:571 (m <= 2048, l <= 2)
 }
 HEADERS = ["solver", "cpu", "iter", "optval", "sparsity", "err-to-exact", "err-to-best"]
 
@@ -131,7 +132,10 @@ def main(argv=None):
         if key not in SOLVERS:
             raise SystemExit("unknown solver %r (choose from %s)" % (key, ", ".join(SOLVERS)))
         label, algo = SOLVERS[key]
-        x, iters, out = prob.solve(algo, x0, mu, opts)      # x stays in HBM
+        if algo == "ADMM_dual":
+            x, iters, out = prob.solve_admm_dual(x0, mu, {"maxit": args.maxit} if args.maxit else {})
+        else:
+            x, iters, out = prob.solve(algo, x0, mu, opts)      # x stays in HBM
         met = prob.metrics(x, u, mu)
         runs.append((label, out["tt"], iters, float(out["fval"]), met, x))
     best = min(runs, key=lambda r: r[3])[5] if runs else None

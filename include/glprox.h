@@ -216,7 +216,7 @@ int glp_comm_attach_nccl(glp_handle* h, void* nccl_comm, int rank, int world, in
 int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, int64_t K, int N, const void* P_hi,
                   const void* P_lo, int64_t ldp, const void* Q_hi, const void* Q_lo, int64_t ldq,
                   double* D_dev, int64_t ldd, int k_chunk_blocks);
-/* Wide multi-RHS mode of the solvers (fp32 data, 16 <= l <= 128, single GPU): both products of an
+/* Wide multi-RHS mode of the solvers (fp32 data, 16 <= l <= 128, one GPU or column shards over several): both products of an
  * iteration run on glp_gemm_tf32 with A and A^T resident as TF32 hi/lo splits (4 x |A| of HBM).
  * mode 0 (default): on, error-compensated 3xTF32;  1: off (CUDA-core streams);  2: on, plain TF32;
  * 3: on, TF32 main term + bf16 correction products (passes = 2 above). */
@@ -225,6 +225,24 @@ int glp_set_tensor_mode(glp_handle* h, int mode);
  * (hi[j][i], lo[j][i]) -- the resident A^T of the transposed pass. */
 int glp_tf32_split(void* stream, const void* src, int64_t rows, int64_t cols, int64_t ld_src, void* hi,
                    void* lo, int64_t ld_dst, int transpose);
+
+/* ---- gl_Admm_dual (code/gl_ADMM_dual.py:10-103) ------------------------------------
+ * ADMM on the dual problem, no mu-continuation.  Option semantics of default_opts (:11-17): maxit 100,
+ * thres 1e-3 (residual test), tau (1+sqrt(5))/2, rho 1e2, converge_len 20.  Replaces the whole function body:
+ * the Cholesky factor of I + rho A A^T (:57) is built once on the device, every iteration is one forward and
+ * one transposed stream of A plus two triangular solves; objective history, residual norms and the
+ * converge_len stop rule (:87-99) are evaluated on the device.  Scope: m <= 2048, l <= 2, one GPU.
+ * res->iters = k, res->fval = out["fval"]; f_hist_host receives min(k, hist_cap) values. */
+typedef struct glp_admm_opts {
+  int32_t maxit;
+  int32_t converge_len;
+  double thres;
+  double tau;
+  double rho;
+} glp_admm_opts;
+int glp_admm_default_opts(glp_admm_opts* out);
+int glp_admm_dual(glp_handle* h, const void* x0_dev, double mu, const glp_admm_opts* opts, void* x_out_dev,
+                  glp_result* res, double* f_hist_host, int hist_cap);
 
 /* ---- caller-side metrics of the reference driver, evaluated on the device ----------------------
  * Replaces, for an iterate that stays in HBM, the host lambdas of code/main.py:48-50 and obj_func

@@ -182,6 +182,50 @@ def solve_smooth(algo, x0, A, b, mu0, opts=None):
     return x_last, k, {"tt": tt, "fval": fval, "f_hist": f_hist, "f_hist_best": f_best_hist}
 
 
+ADMM_DUAL_DEFAULTS = dict(maxit=100, thres=1e-3, tau=(1 + math.sqrt(5)) * 0.5, rho=1e2, converge_len=20)
+
+
+def solve_admm_dual(x0, A, b, mu, opts=None):
+    """Reference-structured restatement of gl_Admm_dual (code/gl_ADMM_dual.py:10-103): ADMM on the dual,
+    no mu-continuation; the z-update solves (I + rho A A^T) z = A(x - rho u) - b through a Cholesky factor
+    computed once (:57, :63), u is the projection onto the row-wise mu-ball (:45-47, :64), x the multiplier
+    update (:65); the loop stops after converge_len consecutive iterations whose primal / dual residuals
+    (matrix 2-norms = largest singular values, :87-88) are both below thres."""
+    o = dict(ADMM_DUAL_DEFAULTS)
+    o.update(opts or {})
+    maxit, thres, rho, tau, converge_len = o["maxit"], o["thres"], o["rho"], o["tau"], o["converge_len"]
+    f_hist, f_best_hist = [], []
+    f_best = np.inf
+    x_k = np.copy(x0)
+    u_k = np.zeros_like(x_k)
+    t_begin = time.time_ns()
+    k = 0
+    L = np.linalg.cholesky(np.identity(A.shape[0]) + rho * A @ A.T)
+    length = 0
+    while k < maxit:
+        k += 1
+        z = np.linalg.solve(L.T, np.linalg.solve(L, A @ (x_k - rho * u_k) - b))
+        v = x_k / rho - A.T @ z
+        rn = np.linalg.norm(v, axis=1, ord=2).reshape(-1, 1)
+        u = mu * v / np.clip(rn, a_min=mu, a_max=None)
+        x = x_k - tau * rho * (u + A.T @ z)
+        r_k = u + A.T @ z
+        s_k = A @ (u_k - u)
+        u_k, x_k = u, x
+        f_now = objective(A, b, x_k, mu)
+        f_hist.append(f_now)
+        f_best = min(f_best, f_now)
+        f_best_hist.append(f_best)
+        if np.linalg.norm(r_k, ord=2) < thres and np.linalg.norm(s_k, ord=2) < thres:
+            length += 1
+        else:
+            length = 0
+        if length >= converge_len:
+            break
+    tt = _round_us(time.time_ns() - t_begin) / 1e6
+    return x_k, k, {"tt": tt, "fval": objective(A, b, x_k, mu), "f_hist": f_hist, "f_hist_best": f_best_hist}
+
+
 def _open_loop_step(step_type, alpha0, inner):
     """Non-adaptive step rules, gl_ProxGD_primal.py:79-85 / gl_FProxGD_primal.py:82-88."""
     it_hat = max(inner, 1000) - 999

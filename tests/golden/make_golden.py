@@ -19,6 +19,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, "/root/reference/code")
 
+from gl_ADMM_dual import gl_Admm_dual  # noqa: E402  (reference)
 from gl_FGD_primal import gl_FGD_primal  # noqa: E402  (reference)
 from gl_FProxGD_primal import gl_FProxGD_primal  # noqa: E402  (reference)
 from gl_GD_primal import gl_GD_primal  # noqa: E402  (reference)
@@ -74,7 +75,25 @@ SMOOTH_CASES = {
 }
 
 
+# gl_Admm_dual (no continuation; its own option set)
+ADMM_CASES = {
+    "admm_fixture": (97006855, 256, 512, 2, "f8", {}),
+    "admm_seed1": (1, 256, 512, 2, "f8", {}),
+    "admm_seed2": (2, 256, 512, 2, "f8", {}),
+    "admm_maxit7": (97006855, 256, 512, 2, "f8", {"maxit": 7}),
+    "admm_ragged": (5, 193, 391, 2, "f8", {"maxit": 60}),
+    "admm_l1": (6, 128, 300, 1, "f8", {"maxit": 60}),
+    "admm_rho10": (97006855, 256, 512, 2, "f8", {"rho": 10.0, "tau": 1.0, "maxit": 150, "converge_len": 5}),
+    "admm_loose": (3, 96, 300, 2, "f8", {"thres": 1e-1, "converge_len": 3}),
+    "admm_f32in": (97006855, 256, 512, 2, "f4", {}),
+}
+REF_ADMM = {"ADMM_dual": gl_Admm_dual}
+
+
 def run_case(name):
+    if name in ADMM_CASES:
+        seed, m, n, l, dt, opts = ADMM_CASES[name]
+        return _run(name, seed, m, n, l, dt, opts, REF_ADMM)
     if name in SMOOTH_CASES:
         seed, m, n, l, dt, opts = SMOOTH_CASES[name]
         algos = REF_SMOOTH
@@ -109,6 +128,6 @@ def _run(name, seed, m, n, l, dt, opts, algos):
 
 
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(CASES) + list(SMOOTH_CASES)
+    names = sys.argv[1:] or list(CASES) + list(SMOOTH_CASES) + list(ADMM_CASES)
     for nm in names:
         np.savez_compressed(os.path.join(HERE, "ref_%s.npz" % nm), **run_case(nm))
