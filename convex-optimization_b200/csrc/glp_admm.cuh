@@ -184,6 +184,7 @@ __global__ void __launch_bounds__(ADMM_THREADS) glp_admm_mid_kernel(const AdmmMi
   __shared__ double s_red[ADMM_THREADS / 32][8];
   __shared__ Ctrl s_out;
   __shared__ double s_z[2][32];
+  __shared__ double s_blk[32][33];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const Ctrl cin = *a.cin;
   if (cin.done) {
@@ -269,13 +270,21 @@ __global__ void __launch_bounds__(ADMM_THREADS) glp_admm_mid_kernel(const AdmmMi
   // shuffles, then every thread subtracts the panel's contribution from the rows below
   for (int j0 = 0; j0 < m; j0 += 32) {
     const int pw = m - j0 < 32 ? m - j0 : 32;
+    // the 32 x 32 diagonal block goes to shared memory first (one element per thread), so that the 32 dependent
+    // steps below are shuffles, shared loads and FMAs only; a global load inside the chain costs ~0.7 us a step
+    {
+      const int bi = tid >> 5, bj = tid & 31;
+      s_blk[bi][bj] = (bi < pw && bj <= bi) ? L[int64_t(j0 + bi) * m + j0 + bj] : 0.0;
+    }
+    __syncthreads();
     if (warp < l) {
       const int c = warp;
+      const double dg = lane < pw ? s_blk[lane][lane] : 1.0;
       double wi = lane < pw ? s_w[c * m + j0 + lane] : 0.0;
       for (int jj = 0; jj < pw; ++jj) {
-        const double zj = __shfl_sync(0xffffffffu, wi, jj) / L[int64_t(j0 + jj) * m + j0 + jj];
+        const double zj = __shfl_sync(0xffffffffu, wi, jj) / __shfl_sync(0xffffffffu, dg, jj);
         if (lane == jj) wi = zj;
-        else if (lane > jj && lane < pw) wi -= L[int64_t(j0 + lane) * m + j0 + jj] * zj;
+        else if (lane > jj && lane < pw) wi -= s_blk[lane][jj] * zj;
       }
       if (lane < pw) { s_w[c * m + j0 + lane] = wi; s_z[c][lane] = wi; }
     }
@@ -296,13 +305,19 @@ __global__ void __launch_bounds__(ADMM_THREADS) glp_admm_mid_kernel(const AdmmMi
   // back substitution  L^T z = y, panels from the bottom
   for (int j1 = m; j1 > 0; j1 -= 32) {
     const int j0 = j1 - 32 > 0 ? j1 - 32 : 0, pw = j1 - j0;
+    {
+      const int bi = tid >> 5, bj = tid & 31;   // s_blk[bi][bj] = L[j0+bi][j0+bj], lower triangle
+      s_blk[bi][bj] = (bi < pw && bj <= bi) ? L[int64_t(j0 + bi) * m + j0 + bj] : 0.0;
+    }
+    __syncthreads();
     if (warp < l) {
       const int c = warp;
+      const double dg = lane < pw ? s_blk[lane][lane] : 1.0;
       double wi = lane < pw ? s_w[c * m + j0 + lane] : 0.0;
       for (int jj = pw - 1; jj >= 0; --jj) {
-        const double zj = __shfl_sync(0xffffffffu, wi, jj) / L[int64_t(j0 + jj) * m + j0 + jj];
+        const double zj = __shfl_sync(0xffffffffu, wi, jj) / __shfl_sync(0xffffffffu, dg, jj);
         if (lane == jj) wi = zj;
-        else if (lane < jj) wi -= L[int64_t(j0 + jj) * m + j0 + lane] * zj;   // (L^T)[lane][jj] = L[jj][lane]
+        else if (lane < jj) wi -= s_blk[jj][lane] * zj;   // (L^T)[lane][jj]
       }
       if (lane < pw) { s_w[c * m + j0 + lane] = wi; s_z[c][lane] = wi; }
     }
