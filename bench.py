@@ -243,7 +243,12 @@ def run_ours(args):
         # bf16 products at twice the rate (= 2 units); plain TF32 one
         passes = {"tf32": 1.0, "tf32+bf16": 2.0}.get(args.tensor_cores, 3.0)
         n_it = max(int(prof.tpass_launches), 1)
-        flops = passes * 2.0 * args.m * A.shape[1] * 3 * args.l * n_it   # this rank's column shard
+        # operand columns on the tensor cores per iteration: l (A.xn) + l (A^T r); the product of the thresholded
+        # iterate comes from A.xn by a sparse CUDA-core correction (csrc/glp_thrfix.cuh) unless switched off,
+        # in which case the forward product has 2l columns.  The correction's time is inside the fwd window.
+        thrfix = os.environ.get("GLPROX_WIDE_THRFIX", "1") != "0"
+        op_cols = (2 if thrfix else 3) * args.l
+        flops = passes * 2.0 * args.m * A.shape[1] * op_cols * n_it   # this rank's column shard
         t_s = (prof.fwd_ms_sum + prof.tpass_ms_sum) * 1e-3
         tf = flops / max(t_s, 1e-12) / 1e12
         tpeak = float(peaks.get("bf16_tflops", 1590.0)) / 2.0
@@ -254,6 +259,9 @@ def run_ours(args):
                              "tf32+bf16": "Ah.Xh on TF32 + (Ah.Xl + Al.Xh) on bf16 at twice the rate: 2 TF32-product "
                                           "units of tensor time per stream, counted as such"}.get(
                                  args.tensor_cores, "3 compensated TF32 products per stream: Ah.Xh + Ah.Xl + Al.Xh, issued flops counted"),
+                    "tensor_operand_columns_per_iteration": op_cols,
+                    "forward_product": ("A.xn on tcgen05 (l columns) + sparse fp64 correction for A.thr(xn), both inside the "
+                                        "fwd window" if thrfix else "A.[xn | thr(xn)] on tcgen05 (2l columns)"),
                     "hbm_GBps_of_hi_lo_streams": hbm_stream, "hbm_peak": peak,
                     "kernels": {"glp_gemm_tf32_kernel<fwd>": {"launches": int(prof.fwd_launches), "avg_ms": prof.fwd_ms_sum / max(prof.fwd_launches, 1)},
                                 "glp_gemm_tf32_kernel<tpass>": {"launches": int(prof.tpass_launches), "avg_ms": prof.tpass_ms_sum / max(prof.tpass_launches, 1)}}}

@@ -56,6 +56,9 @@ struct GemmArgs {
   // range: every P tile is loaded once per cluster row (each of the cg CTAs fetches 1/cg of its rows and TMA
   // multicasts them to the others), every Q tile once per cluster column.  1 x 1 = no cluster.
   int32_t ct, cg;
+  // device-side gate (glp_thrfix.cuh): when set, the launch does nothing unless *gate > gate_cap
+  const int32_t* gate;
+  int32_t gate_cap;
 };
 
 template <int NT, int PASSES> constexpr int gemm_stage_bytes() {
@@ -256,7 +259,9 @@ __device__ __forceinline__ GemmItem gemm_item(int64_t w, int64_t tiles, int64_t 
 // out[i] = sum_s part[s * stride + i] in split order (fixed, deterministic); solver launches pick the
 // destination / skip from the control block exactly like the product kernel.
 __global__ void glp_sum_splits_kernel(const double* __restrict__ part, int splits, int64_t stride, int64_t M, int N,
-                                      int64_t ldd, double* out, double* out_alt, const Ctrl* ctrl, int role) {
+                                      int64_t ldd, double* out, double* out_alt, const Ctrl* ctrl, int role,
+                                      const int32_t* gate, int gate_cap) {
+  if (gate != nullptr && *gate <= gate_cap) return;
   if (ctrl != nullptr) {
     if (ctrl->done || (role == 2 && ctrl->retry)) return;
     if (role == 1 && ctrl->cur == 0) out = out_alt;
@@ -306,6 +311,7 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
     if (a.ctrl->done || (a.role == 2 && a.ctrl->retry)) return;
     if (a.role == 1 && a.ctrl->cur == 0) Dout = a.D_alt;
   }
+  if (a.gate != nullptr && *a.gate <= a.gate_cap) return;   // grid-uniform, before any barrier or cluster traffic
   const int64_t tiles = (a.M + GEMM_BM - 1) / GEMM_BM;
   const int64_t nkb = (a.K + GEMM_BK - 1) / GEMM_BK;
   const int64_t kc = a.k_chunk_blocks > 0 ? a.k_chunk_blocks : nkb;

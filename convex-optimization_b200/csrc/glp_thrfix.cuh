@@ -1,0 +1,172 @@
+// Wide (tensor-core) mode: the forward product of the thresholded iterate from the product of the iterate.
+//
+// The reference thresholds the iterate element-wise AFTER the objective is recorded (gl_*_primal.py:
+// x[abs(x) < thres] = 0), so every iteration needs A.xn (objective) and A.xnt (next gradient base point).
+// On the CUDA-core path the two ride in one stream over A at no extra HBM cost.  On the tensor cores the product
+// is compute-bound and the second operand doubles its price, although xnt differs from xn only where
+// 0 < |xn| < thres: E := xn - xnt has |E_jc| < thres and (thres = 1e-3, entries of order 1) about one non-zero
+// entry in a thousand.  So here
+//     A.xnt = A.xn - A.E,        column c:  (A.E)(:, c) = sum over the entries (j, c) of E:  A(:, j) E_jc
+// The entries are listed per operand column in ascending row order by one block per column (fixed order ->
+// run-to-run identical bits) and applied by a CUDA-core kernel in fp64.  A(:, j) is read from the resident
+// transposed split (row j of At_hi + At_lo: coalesced over the output rows); |E| < thres makes the 2^-22 relative
+// gap between hi + lo and A irrelevant next to the rounding of the TF32 product itself.  Cost: entries x m x 8
+// bytes of L2/HBM traffic instead of a second product.
+// When a column holds more entries than the list has room for, the lists are abandoned and a second,
+// device-gated launch of the product kernel computes A.xnt directly, as before (GemmArgs::gate).
+#pragma once
+#include <cuda_bf16.h>
+
+#include "glp_device.cuh"
+#include "glp_types.cuh"
+
+namespace glp {
+
+constexpr int THRLIST_THREADS = 1024;
+constexpr int THRFIX_THREADS = 128;
+
+// count[0] = entries listed (all columns), count[1] = columns whose list overflowed (> 0: lists unusable),
+// count[2] = arrival counter of the list blocks (zero between launches)
+struct ThrListArgs {
+  const Ctrl* ctrl;              // nullable; done -> nothing to do
+  const float* xop;              // [2l][ldn] operand copy {xn | xnt}, BEFORE the hi/lo split overwrites it
+  int32_t* rows;                 // [l][cap] out: rows of the entries of column c, ascending
+  float* vals;                   // [l][cap] out: xn - xnt there (exact: xnt is xn or 0)
+  int32_t* col_count;            // [l] out
+  int32_t* count;                // [3], see above
+  int32_t cap;                   // list entries per column
+};
+
+__global__ void __launch_bounds__(THRLIST_THREADS)
+glp_thr_list_kernel(const ThrListArgs a, const Geom g) {
+  __shared__ int s_warp[THRLIST_THREADS / 32];
+  __shared__ int s_carry;
+  __shared__ bool s_last;
+  if (a.ctrl != nullptr && a.ctrl->done) return;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int c = blockIdx.x, l = g.l;
+  const float* x = a.xop + int64_t(c) * g.ldn;
+  const float* xz = a.xop + int64_t(l + c) * g.ldn;
+  int32_t* rows = a.rows + int64_t(c) * a.cap;
+  float* vals = a.vals + int64_t(c) * a.cap;
+  if (tid == 0) s_carry = 0;
+  __syncthreads();
+  // ordered compaction, 4 consecutive rows per thread and 4096 rows per round (padding rows are zero in both)
+  for (int64_t j0 = 0; j0 < g.ldn; j0 += 4 * THRLIST_THREADS) {
+    const int64_t j = j0 + 4 * tid;
+    float4 u = make_float4(0.f, 0.f, 0.f, 0.f), v = u;
+    if (j + 3 < g.ldn) {
+      u = *reinterpret_cast<const float4*>(x + j);
+      v = *reinterpret_cast<const float4*>(xz + j);
+    } else {
+      float* up = &u.x; float* vp = &v.x;
+      for (int q = 0; q < 4; ++q) if (j + q < g.ldn) { up[q] = x[j + q]; vp[q] = xz[j + q]; }
+    }
+    const float d[4] = {u.x - v.x, u.y - v.y, u.z - v.z, u.w - v.w};
+    const int mine = (d[0] != 0.f) + (d[1] != 0.f) + (d[2] != 0.f) + (d[3] != 0.f);
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    int base = s_carry;
+    for (int w = 0; w < warp; ++w) base += s_warp[w];
+    int pos = base + incl - mine;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (d[q] != 0.f) {
+        if (pos < a.cap) { rows[pos] = int32_t(j + q); vals[pos] = d[q]; }
+        ++pos;
+      }
+    __syncthreads();
+    if (tid == THRLIST_THREADS - 1) s_carry = base + incl;
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const int R = s_carry;
+    a.col_count[c] = R;
+    __threadfence();
+    s_last = atomicAdd(reinterpret_cast<unsigned*>(&a.count[2]), 1u) == unsigned(l - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  // the last block to arrive totals the columns (fixed order) and re-arms the counter
+  __threadfence();
+  if (warp == 0) {
+    int tot = 0, over = 0;
+    for (int q = lane; q < l; q += 32) {
+      const int r = __ldcg(&a.col_count[q]);
+      tot += r;
+      over += r > a.cap ? 1 : 0;
+    }
+    tot = __reduce_add_sync(0xffffffffu, tot);
+    over = __reduce_add_sync(0xffffffffu, over);
+    if (lane == 0) { a.count[0] = tot; a.count[1] = over; a.count[2] = 0; }
+  }
+}
+
+struct ThrFixArgs {
+  const Ctrl* ctrl;
+  const int32_t* count;             // count[1] > 0: lists unusable, the gated product has computed A.xnt
+  const int32_t* col_count;
+  const int32_t* rows;
+  const float* vals;
+  int32_t cap;
+  int32_t pad;
+  const float* At_hi;               // [n][ldm] transposed A, TF32 part
+  const float* At_lo;               // fp32 remainder (3xTF32 operand set) or nullptr
+  const __nv_bfloat16* At_lb;       // bf16 remainder (TF32 + bf16 operand set) or nullptr
+  double* AX[2];                    // [2l][ldm]: column l + c := column c - sum_r At[rows_r][:] * vals_r
+};
+
+// grid (ceil(ldm / 128), l): block (ib, c) owns 128 output rows of column c
+__global__ void __launch_bounds__(THRFIX_THREADS)
+glp_thr_fix_kernel(const ThrFixArgs a, const Geom g) {
+  __shared__ int32_t s_j[THRFIX_THREADS];
+  __shared__ float s_v[THRFIX_THREADS];
+  if (a.ctrl != nullptr && a.ctrl->done) return;
+  if (a.count[1] > 0) return;
+  const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : 0;
+  const int tid = threadIdx.x, c = blockIdx.y, l = g.l;
+  const int R = a.col_count[c];
+  const int64_t i = int64_t(blockIdx.x) * THRFIX_THREADS + tid;
+  const bool live = i < g.ldm;
+  const int32_t* rows = a.rows + int64_t(c) * a.cap;
+  const float* vals = a.vals + int64_t(c) * a.cap;
+  double acc = 0.0;
+  for (int r0 = 0; r0 < R; r0 += THRFIX_THREADS) {
+    const int nr = R - r0 < THRFIX_THREADS ? R - r0 : THRFIX_THREADS;
+    __syncthreads();
+    if (tid < nr) { s_j[tid] = rows[r0 + tid]; s_v[tid] = vals[r0 + tid]; }
+    __syncthreads();
+    if (!live) continue;
+    int r = 0;
+    for (; r + 4 <= nr; r += 4) {   // four independent row loads in flight
+      double av[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int64_t at = int64_t(s_j[r + q]) * g.ldm + i;
+        av[q] = double(a.At_hi[at]);
+        if (a.At_lo != nullptr) av[q] += double(a.At_lo[at]);
+        else if (a.At_lb != nullptr) av[q] += double(__bfloat162float(a.At_lb[at]));
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc = fma(av[q], double(s_v[r + q]), acc);
+    }
+    for (; r < nr; ++r) {
+      const int64_t at = int64_t(s_j[r]) * g.ldm + i;
+      double av = double(a.At_hi[at]);
+      if (a.At_lo != nullptr) av += double(a.At_lo[at]);
+      else if (a.At_lb != nullptr) av += double(__bfloat162float(a.At_lb[at]));
+      acc = fma(av, double(s_v[r]), acc);
+    }
+  }
+  if (!live) return;
+  double* ax = a.AX[sel];
+  ax[int64_t(l + c) * g.ldm + i] = ax[int64_t(c) * g.ldm + i] - acc;
+}
+
+}  // namespace glp

@@ -23,6 +23,7 @@
 #include "glp_metrics.cuh"
 #include "glp_misc.cuh"
 #include "glp_persist.cuh"
+#include "glp_thrfix.cuh"
 #include "glp_tpass.cuh"
 #include "glp_types.cuh"
 #include "glp_wide_comm.cuh"
@@ -155,6 +156,10 @@ struct glp_handle {
   __nv_bfloat16 *A_hb = nullptr, *A_lb = nullptr, *At_hb = nullptr, *At_lb = nullptr;
   __nv_bfloat16 *xop_hb = nullptr, *xop_lb = nullptr, *r_hb = nullptr, *r_lb = nullptr;
   int wide_built = -1;         // which operand set (wide_passes) is resident
+  // A.xnt from A.xn by a sparse correction (glp_thrfix.cuh); thr_cap < 0: off (GLPROX_WIDE_THRFIX=0)
+  int32_t *thr_rows = nullptr, *thr_col_count = nullptr, *thr_count = nullptr;
+  float* thr_vals = nullptr;
+  int32_t thr_cap = -1;            // list entries per operand column
   double* admm_L = nullptr;    // gl_Admm_dual: m x m Cholesky factor of I + rho A A^T
   double* gemm_ws = nullptr;   // split-K partial products of K5
   size_t gemm_ws_bytes = 0;
@@ -388,6 +393,10 @@ extern "C" int glp_destroy(glp_handle* h) {
   if (h->xop_lo) cudaFree(h->xop_lo);
   if (h->r_lo) cudaFree(h->r_lo);
   if (h->cnt_g) cudaFree(h->cnt_g);
+  if (h->thr_rows) cudaFree(h->thr_rows);
+  if (h->thr_vals) cudaFree(h->thr_vals);
+  if (h->thr_col_count) cudaFree(h->thr_col_count);
+  if (h->thr_count) cudaFree(h->thr_count);
   if (h->gemm_ws) cudaFree(h->gemm_ws);
   if (h->admm_L) cudaFree(h->admm_L);
   if (h->nccl_stage) cudaFree(h->nccl_stage);
@@ -574,8 +583,23 @@ static int ensure_wide(glp_handle* h) {
     GLP_TRY(alloc_zero(&h->A_hi, a_el * 4, h->stream));
     GLP_TRY(alloc_zero(&h->At_hi, at_el * 4, h->stream));
     CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->cnt_g), size_t(h->gather_grid) * 8));
-    // split-K workspace for the larger of the two products
-    const size_t fwd = size_t(gemm_splits(g.m, g.n, 2 * g.l, WIDE_K_CHUNK, h->num_sms)) * 2 * g.l * g.ldm * 8;
+    // A.xnt by sparse correction: on unless GLPROX_WIDE_THRFIX=0.  Room for n/32 entries per operand column
+    // (>= 64): ~30 x the expected load at thres = 1e-3, and at that load the correction still costs well under
+    // half of the product it replaces.  GLPROX_WIDE_THRFIX_CAP overrides (tests).
+    const char* e_fix = getenv("GLPROX_WIDE_THRFIX");
+    if (e_fix == nullptr || atoi(e_fix) != 0) {
+      int64_t cap = std::max<int64_t>(64, g.n / 32);
+      if (const char* e_cap = getenv("GLPROX_WIDE_THRFIX_CAP")) cap = std::max(0, atoi(e_cap));
+      const size_t el = size_t(std::max<int64_t>(cap, 1)) * g.l;
+      GLP_TRY(alloc_zero(&h->thr_rows, el * 4, h->stream));
+      GLP_TRY(alloc_zero(&h->thr_vals, el * 4, h->stream));
+      GLP_TRY(alloc_zero(&h->thr_col_count, size_t(g.l) * 4, h->stream));
+      GLP_TRY(alloc_zero(&h->thr_count, 4 * 4, h->stream));
+      h->thr_cap = int32_t(cap);
+    }
+    // split-K workspace for the larger of the products
+    size_t fwd = size_t(gemm_splits(g.m, g.n, 2 * g.l, WIDE_K_CHUNK, h->num_sms)) * 2 * g.l * g.ldm * 8;
+    fwd = std::max(fwd, size_t(gemm_splits(g.m, g.n, g.l, WIDE_K_CHUNK, h->num_sms)) * g.l * g.ldm * 8);
     const size_t tps = size_t(gemm_splits(g.n, g.m, g.l, WIDE_K_CHUNK, h->num_sms)) * g.l * g.ldn * 8;
     h->gemm_ws_bytes = std::max(fwd, tps);
     CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->gemm_ws), h->gemm_ws_bytes));
@@ -606,12 +630,13 @@ static int ensure_wide(glp_handle* h) {
 
 struct GemmWs { double* buf; size_t bytes; };  // split-K partial products (nullptr: no splitting)
 struct GemmBf16 { const __nv_bfloat16 *Phb, *Plb, *Qhb, *Qlb; };  // passes = 2: bf16 copies of hi / lo, same pitches
+struct GemmGate { const int32_t* count; int32_t cap; };            // run only when *count > cap (nullptr: always)
 static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms);
 static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
                         const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
                         int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl = nullptr, double* D_alt = nullptr,
                         int role = 0, GemmWs ws = GemmWs{nullptr, 0},
-                        GemmBf16 bf = GemmBf16{nullptr, nullptr, nullptr, nullptr});
+                        GemmBf16 bf = GemmBf16{nullptr, nullptr, nullptr, nullptr}, GemmGate gate = GemmGate{nullptr, 0});
 
 static uint64_t seq_base(const glp_handle* h);
 
@@ -652,12 +677,47 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
   const Geom& g = h->g;
   float* xop = static_cast<float*>(h->xop);
   const bool bf = wide_passes(h) == 2;
+  if (h->thr_cap >= 0) {   // list the rows the hard threshold changed, before the split overwrites the operand
+    ThrListArgs la{};
+    la.ctrl = ctrl;
+    la.xop = xop;
+    la.rows = h->thr_rows; la.vals = h->thr_vals; la.col_count = h->thr_col_count; la.count = h->thr_count;
+    la.cap = h->thr_cap;
+    glp_thr_list_kernel<<<g.l, THRLIST_THREADS, 0, h->stream>>>(la, g);
+    CU_TRY(cudaGetLastError());
+    h->n_launches++;
+  }
   if (bf) GLP_TRY(split_bf16(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_hb, h->xop_lb, g.ldn, false));
   else GLP_TRY(split_f32(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_lo, g.ldn, false));  // hi in place
   prof_mark(h, 0, 0);
-  GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, 2 * g.l, h->A_hi, h->A_lo, g.ldn, xop, h->xop_lo,
-                       g.ldn, h->AX[0], g.ldm, WIDE_K_CHUNK, h->fault, ctrl, h->AX[1], 1,
-                       GemmWs{h->gemm_ws, h->gemm_ws_bytes}, GemmBf16{h->A_hb, h->A_lb, h->xop_hb, h->xop_lb}));
+  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes};
+  if (h->thr_cap < 0) {   // one product over both operand halves
+    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, 2 * g.l, h->A_hi, h->A_lo, g.ldn, xop, h->xop_lo,
+                         g.ldn, h->AX[0], g.ldm, WIDE_K_CHUNK, h->fault, ctrl, h->AX[1], 1, ws,
+                         GemmBf16{h->A_hb, h->A_lb, h->xop_hb, h->xop_lb}));
+  } else {
+    // A.xn on the tensor cores; A.xnt = A.xn - A.(xn - xnt) on the CUDA cores from the listed entries, or, when
+    // a list overflowed, by a second product launch that the device gates on the overflow count
+    const int64_t q2 = int64_t(g.l) * g.ldn, d2 = int64_t(g.l) * g.ldm;
+    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, g.l, h->A_hi, h->A_lo, g.ldn, xop, h->xop_lo,
+                         g.ldn, h->AX[0], g.ldm, WIDE_K_CHUNK, h->fault, ctrl, h->AX[1], 1, ws,
+                         GemmBf16{h->A_hb, h->A_lb, h->xop_hb, h->xop_lb}));
+    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, g.l, h->A_hi, h->A_lo, g.ldn, xop + q2,
+                         bf ? nullptr : h->xop_lo + q2, g.ldn, h->AX[0] + d2, g.ldm, WIDE_K_CHUNK, h->fault, ctrl,
+                         h->AX[1] + d2, 1, ws,
+                         GemmBf16{h->A_hb, h->A_lb, bf ? h->xop_hb + q2 : nullptr, bf ? h->xop_lb + q2 : nullptr},
+                         GemmGate{h->thr_count + 1, 0}));
+    ThrFixArgs fa{};
+    fa.ctrl = ctrl;
+    fa.count = h->thr_count; fa.col_count = h->thr_col_count;
+    fa.rows = h->thr_rows; fa.vals = h->thr_vals; fa.cap = h->thr_cap;
+    fa.At_hi = h->At_hi; fa.At_lo = bf ? nullptr : h->At_lo; fa.At_lb = bf ? h->At_lb : nullptr;
+    fa.AX[0] = h->AX[0]; fa.AX[1] = h->AX[1];
+    const dim3 fgrid(unsigned((g.ldm + THRFIX_THREADS - 1) / THRFIX_THREADS), unsigned(g.l));
+    glp_thr_fix_kernel<<<fgrid, THRFIX_THREADS, 0, h->stream>>>(fa, g);
+    CU_TRY(cudaGetLastError());
+    h->n_launches += 2;
+  }
   prof_mark(h, 0, 1);
   h->n_launches += 2;
   if (multi(h)) return enqueue_wide_exchange(h, ctrl, 0);
@@ -1708,7 +1768,7 @@ static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms) {
 static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
                         const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
                         int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl, double* D_alt, int role, GemmWs ws,
-                        GemmBf16 bf) {
+                        GemmBf16 bf, GemmGate gate) {
   if (N < 1 || N > 256) return fail(GLP_ERR_ARG, "gemm: N must be 1..256 per launch (got %d)", N);
   if (passes < 1 || passes > 3) return fail(GLP_ERR_ARG, "gemm: passes must be 1, 2 or 3");
   if ((ldp * 4) % 16 || (ldq * 4) % 16 || (reinterpret_cast<uintptr_t>(Ph) % 16) || (reinterpret_cast<uintptr_t>(Qh) % 16))
@@ -1758,6 +1818,7 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   a.splits = S; a.split_stride = stride;
   if (S > 1) { a.D = ws.buf; a.D_alt = ws.buf; }   // partials first; the sum below picks the real destination
   a.ct = ct; a.cg = cg;
+  a.gate = gate.count; a.gate_cap = gate.cap;
   const int64_t items = ((tiles + ct - 1) / ct) * ((groups + cg - 1) / cg) * S;   // cluster items
   cudaError_t e;
 #define GLP_GEMM_LAUNCH(NTV, PV) launch_gemm_t<NTV, PV>(st, num_sms, items, mph, mpl, mqh, mql, mpx, mqx, a)
@@ -1768,7 +1829,7 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "gemm launch failed: %s", cudaGetErrorString(e));
   if (S > 1) {
     const int sgrid = int(std::min<int64_t>((M * N + 255) / 256, int64_t(num_sms) * 8));
-    glp_sum_splits_kernel<<<sgrid, 256, 0, st>>>(ws.buf, S, stride, M, N, ldd, D, D_alt, ctrl, role);
+    glp_sum_splits_kernel<<<sgrid, 256, 0, st>>>(ws.buf, S, stride, M, N, ldd, D, D_alt, ctrl, role, gate.count, gate.cap);
     CU_TRY(cudaGetLastError());
   }
   return GLP_OK;

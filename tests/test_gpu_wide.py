@@ -85,8 +85,56 @@ def test_wide_mode_sharded_matches_single_handle_and_oracle(G, shape, algo):
         assert abs(f_true - outr["fval"]) <= 1e-5 * abs(outr["fval"])
         pr = out["glprox"]["per_rank"]   # every rank took bit-identical decisions
         assert all(r["iters"] == k and r["fval"] == pr[0]["fval"] and r["n_fwd"] == pr[0]["n_fwd"] for r in pr)
-        # 1 product + 3 exchange kernels per forward instead of 2l/4 CUDA-core streams
-        assert out["glprox"]["n_launches"] < 45 * 24
+        # 2 product launches (one gated off on the device) + entry lists / correction + 3 exchange kernels per
+        # forward instead of 2l/4 CUDA-core streams
+        assert out["glprox"]["n_launches"] < 45 * 32
     single.close()
     for p in probs:
         p.close()
+
+
+def _solve_with_env(monkeypatch, env, algo, A, b, x0, mu, opts):
+    """One solve on a fresh handle (the wide operand set and the threshold-correction switches are read when
+    the handle first goes wide)."""
+    import torch
+    from glprox import GroupLassoProblem
+    for k_, v_ in env.items():
+        monkeypatch.setenv(k_, v_)
+    prob = GroupLassoProblem(torch.from_numpy(A).cuda(), torch.from_numpy(b).cuda())
+    x, k, out = prob.solve(algo, torch.from_numpy(x0).cuda(), mu, opts)
+    prob.close()
+    for k_ in env:
+        monkeypatch.delenv(k_)
+    return x.cpu().numpy(), k, out
+
+
+@pytest.mark.parametrize("algo", ["FProxGD", "ProxGD"])
+@pytest.mark.parametrize("mode", ["3xtf32", "tf32+bf16"])
+@pytest.mark.parametrize("shape", [(256, 1024, 16), (300, 1100, 24), (512, 2048, 128)])
+def test_wide_threshold_correction_equals_direct_product(monkeypatch, shape, algo, mode):
+    """A.thr(x) = A.x - A.(x - thr(x)) (csrc/glp_thrfix.cuh) against the direct product over both operand halves.
+    thres = 2e-2 makes the hard threshold bite in every iteration (x0 ~ N(0,1): ~1.6 % of the entries), so the
+    per-column entry lists, their overflow fallback (cap = 0: device-gated second product, bit-identical to the
+    direct product) and the default capacity (which some columns exceed at this thres) are all exercised."""
+    m, n, l = shape
+    A, b, x0, mu, opts = _case(m, n, l, 11, 8)
+    x0[5, 3] = 3e-3   # a row that is certainly hit
+    opts = dict(opts, thres=2e-2, tensor_cores=mode)
+    xd, kd, outd = _solve_with_env(monkeypatch, {"GLPROX_WIDE_THRFIX": "0"}, algo, A, b, x0, mu, opts)
+    xg, kg, outg = _solve_with_env(monkeypatch, {"GLPROX_WIDE_THRFIX_CAP": "0"}, algo, A, b, x0, mu, opts)
+    xl, kl, outl = _solve_with_env(monkeypatch, {"GLPROX_WIDE_THRFIX_CAP": str(n)}, algo, A, b, x0, mu, opts)
+    xa, ka, outa = _solve_with_env(monkeypatch, {}, algo, A, b, x0, mu, opts)   # default cap: mixes both
+    assert kd == kg == kl == ka
+    fd, fg, fl, fa = (np.asarray(o["f_hist"]) for o in (outd, outg, outl, outa))
+    assert np.array_equal(fd, fg) and np.array_equal(xd, xg)          # gated product = direct product, bit for bit
+    # the correction is exact in fp64 where the direct product rounds A.E through the TF32 splits; the objective
+    # falls by 5 orders of magnitude over the run (cancellation in r = Ax - b), so the two agree to ~1e-7
+    for f, x in ((fl, xl), (fa, xa)):
+        assert np.max(np.abs(f - fd) / np.abs(fd)) <= 2e-6, np.max(np.abs(f - fd) / np.abs(fd))
+        assert np.max(np.abs(x - xd)) <= 1e-5 * max(1.0, np.max(np.abs(xd)))
+    xr, kr, outr = orc.solve(algo, x0.astype(np.float64), A.astype(np.float64), b.astype(np.float64), mu,
+                             {k_: v_ for k_, v_ in opts.items() if k_ != "tensor_cores"})
+    assert kl == kr
+    assert abs(outl["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
+    # the correction replaces half of the forward product: fewer tensor-core column groups, a few small launches
+    assert outl["glprox"]["n_launches"] >= outd["glprox"]["n_launches"]
