@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="multi-GPU exchange: peer-mailbox push fused into the kernels (product) or the ncclAllReduce baseline")
-    ap.add_argument("--tensor-cores", default="auto", choices=["auto", "3xtf32", "tf32+bf16", "tf32", "off"],
+    ap.add_argument("--tensor-cores", default="auto", choices=["auto", "3xtf32", "tf32+bf16", "f16x2", "tf32", "off"],
                     help="wide multi-RHS mode (l >= 16): product scheme on the tensor cores")
     ap.add_argument("--no-converge", action="store_true", help="skip the run-to-convergence / time-to-1e-8 report")
     return ap.parse_args()
@@ -241,7 +241,7 @@ def run_ours(args):
         # wide multi-RHS mode: both products run on tcgen05 (3xTF32); the bounding roofline is the tensor pipe
         # tensor time in TF32-product units: 3xTF32 issues 3 TF32 products; tf32+bf16 one TF32 product and two
         # bf16 products at twice the rate (= 2 units); plain TF32 one
-        passes = {"tf32": 1.0, "tf32+bf16": 2.0}.get(args.tensor_cores, 3.0)
+        passes = {"tf32": 1.0, "tf32+bf16": 2.0, "f16x2": 1.5}.get(args.tensor_cores, 3.0)
         n_it = max(int(prof.tpass_launches), 1)
         # operand columns on the tensor cores per iteration: l (A.xn) + l (A^T r); the product of the thresholded
         # iterate comes from A.xn by a sparse CUDA-core correction (csrc/glp_thrfix.cuh) unless switched off,
@@ -252,17 +252,33 @@ def run_ours(args):
         t_s = (prof.fwd_ms_sum + prof.tpass_ms_sum) * 1e-3
         tf = flops / max(t_s, 1e-12) / 1e12
         tpeak = float(peaks.get("bf16_tflops", 1590.0)) / 2.0
-        hbm_stream = 2.0 * prof.bytes_per_launch * (prof.fwd_launches + prof.tpass_launches) / max(t_s, 1e-12) / 1e9
-        roofline = {"bound": "tensor", "achieved": tf, "peak": tpeak, "unit": "TFLOP/s", "frac": tf / tpeak, "traffic": None,
-                    "peak_source": "MEASURED_PEAKS.json bf16_tflops / 2 (kind::tf32 runs at half the bf16 rate)",
+        # bytes of the resident operand per product: 8 per element (fp32 hi + fp32 lo, or fp32 hi + 2 bf16), 4 for
+        # plain TF32 and for the fp16 pairs
+        stream_x = 1.0 if args.tensor_cores in ("tf32", "f16x2") else 2.0
+        stream_bytes = stream_x * prof.bytes_per_launch * (prof.fwd_launches + prof.tpass_launches)
+        hbm_stream = stream_bytes / max(t_s, 1e-12) / 1e9
+        # the binding roofline is the one with the larger minimum time for this work
+        t_min_tensor, t_min_hbm = flops / (tpeak * 1e12), stream_bytes / (peak * 1e9)
+        tensor_part = {"achieved": tf, "peak": tpeak, "unit": "TFLOP/s", "frac": tf / tpeak,
+                       "peak_source": "MEASURED_PEAKS.json bf16_tflops / 2 (kind::tf32 runs at half the bf16 rate)"}
+        hbm_part = {"achieved": hbm_stream, "peak": peak, "unit": "GB/s", "frac": hbm_stream / peak,
+                    "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write)" if peaks else "fallback 6650 GB/s"}
+        bound = "hbm" if t_min_hbm > t_min_tensor else "tensor"
+        roofline = {"bound": bound, **(hbm_part if bound == "hbm" else tensor_part), "traffic": None,
+                    "other_roofline": {"bound": "tensor" if bound == "hbm" else "hbm",
+                                       **(tensor_part if bound == "hbm" else hbm_part)},
+                    "min_ms_per_iteration": {"tensor": 1e3 * t_min_tensor / n_it, "hbm": 1e3 * t_min_hbm / n_it,
+                                             "measured_products": 1e3 * t_s / n_it},
                     "work": {"tf32": "1 TF32 product per stream (approximate mode)",
+                             "f16x2": "3 kind::f16 products of fp16 pairs (P0.Q0 + P0.Q1 + P1.Q0) at twice the TF32 rate: "
+                                      "1.5 TF32-product units of tensor time per stream, counted as such; the resident "
+                                      "operand streams 4 bytes per element",
                              "tf32+bf16": "Ah.Xh on TF32 + (Ah.Xl + Al.Xh) on bf16 at twice the rate: 2 TF32-product "
                                           "units of tensor time per stream, counted as such"}.get(
                                  args.tensor_cores, "3 compensated TF32 products per stream: Ah.Xh + Ah.Xl + Al.Xh, issued flops counted"),
                     "tensor_operand_columns_per_iteration": op_cols,
                     "forward_product": ("A.xn on tcgen05 (l columns) + sparse fp64 correction for A.thr(xn), both inside the "
                                         "fwd window" if thrfix else "A.[xn | thr(xn)] on tcgen05 (2l columns)"),
-                    "hbm_GBps_of_hi_lo_streams": hbm_stream, "hbm_peak": peak,
                     "kernels": {"glp_gemm_tf32_kernel<fwd>": {"launches": int(prof.fwd_launches), "avg_ms": prof.fwd_ms_sum / max(prof.fwd_launches, 1)},
                                 "glp_gemm_tf32_kernel<tpass>": {"launches": int(prof.tpass_launches), "avg_ms": prof.tpass_ms_sum / max(prof.tpass_launches, 1)}}}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

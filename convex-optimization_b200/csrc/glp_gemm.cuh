@@ -27,6 +27,8 @@
 #include <cuda_bf16.h>
 
 #include "glp_device.cuh"
+#include <cuda_fp16.h>
+
 #include "glp_types.cuh"
 
 namespace glp {
@@ -59,6 +61,8 @@ struct GemmArgs {
   // device-side gate (glp_thrfix.cuh): when set, the launch does nothing unless *gate > gate_cap
   const int32_t* gate;
   int32_t gate_cap;
+  // PASSES = 4 (fp16 pairs): the operands were scaled by powers of two; the epilogue multiplies by *scale
+  const double* scale;
 };
 
 template <int NT, int PASSES> constexpr int gemm_stage_bytes() {
@@ -143,28 +147,53 @@ __device__ __forceinline__ uint64_t umma_desc_k_sw64(uint32_t smem_addr) {
 template <int NT> __device__ __forceinline__ constexpr uint32_t umma_idesc_bf16() {
   return (1u << 4) | (1u << 7) | (1u << 10) | (uint32_t(NT >> 3) << 17) | (uint32_t(GEMM_BM >> 4) << 24);
 }
+// kind::f16 with fp16 operands (format 0), fp32 accumulate, both K-major, M = 128
+template <int NT> __device__ __forceinline__ constexpr uint32_t umma_idesc_f16() {
+  return (1u << 4) | (uint32_t(NT >> 3) << 17) | (uint32_t(GEMM_BM >> 4) << 24);
+}
 // kind::tf32, fp32 accumulate, both operands K-major, M = 128
 template <int NT> __device__ __forceinline__ constexpr uint32_t umma_idesc_tf32() {
   return (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(NT >> 3) << 17) | (uint32_t(GEMM_BM >> 4) << 24);
 }
 
 // hi = a with the 13 low mantissa bits cleared after rounding to nearest (what kind::tf32 keeps), lo = a - hi
+__device__ __forceinline__ void split_tf32_one(float a, float& h, float& lo) {
+  uint32_t u = __float_as_uint(a);
+  u = (u + 0x00000fffu + ((u >> 13) & 1u)) & 0xffffe000u;  // round to nearest even on bit 13
+  h = __uint_as_float(u);
+  if (!(fabsf(h) <= 3.0e38f)) h = a;                        // inf / nan / overflow of the rounding: keep a
+  lo = a - h;
+}
+// gate (nullable): the launch does nothing unless *gate > gate_cap (glp_thrfix.cuh)
 __global__ void glp_split_tf32_kernel(const float* src, float* hi, float* lo,  // hi may alias src (in place)
-                                      int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst) {
+                                      int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst,
+                                      const int32_t* gate, int gate_cap) {
+  if (gate != nullptr && *gate <= gate_cap) return;
   const int64_t total = rows * cols;
-  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x) {
+  const int64_t step = int64_t(gridDim.x) * blockDim.x, first = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (ld_src == cols && ld_dst == cols && (total & 3) == 0 &&
+      ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(hi) | reinterpret_cast<uintptr_t>(lo)) & 15) == 0) {
+    // contiguous operand (the solver's small operands): 128-bit accesses, no index arithmetic
+    for (int64_t e = first; e < total / 4; e += step) {
+      const float4 a = reinterpret_cast<const float4*>(src)[e];
+      float4 h, l;
+      split_tf32_one(a.x, h.x, l.x); split_tf32_one(a.y, h.y, l.y);
+      split_tf32_one(a.z, h.z, l.z); split_tf32_one(a.w, h.w, l.w);
+      reinterpret_cast<float4*>(hi)[e] = h;
+      reinterpret_cast<float4*>(lo)[e] = l;
+    }
+    return;
+  }
+  for (int64_t e = first; e < total; e += step) {
     const int64_t i = e / cols, j = e - i * cols;
-    const float a = src[i * ld_src + j];
-    uint32_t u = __float_as_uint(a);
-    u = (u + 0x00000fffu + ((u >> 13) & 1u)) & 0xffffe000u;  // round to nearest even on bit 13
-    float h = __uint_as_float(u);
-    if (!(fabsf(h) <= 3.0e38f)) h = a;                        // inf / nan / overflow of the rounding: keep a
+    float h, l;
+    split_tf32_one(src[i * ld_src + j], h, l);
     hi[i * ld_dst + j] = h;
-    lo[i * ld_dst + j] = a - h;
+    lo[i * ld_dst + j] = l;
   }
 }
 
-// dst[j][i] = src[i][j]  (32 x 32 tiles through shared memory), optionally split into hi / lo
+// dst[j][i] = src[i][j]  (32 x 32 tiles through shared memory), split into hi / lo
 __global__ void glp_transpose_split_kernel(const float* __restrict__ src, float* __restrict__ hi, float* __restrict__ lo,
                                            int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst) {
   __shared__ float t[32][33];
@@ -177,13 +206,10 @@ __global__ void glp_transpose_split_kernel(const float* __restrict__ src, float*
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
     const int64_t j = bj + r, i = bi + threadIdx.x;
     if (j < cols && i < rows) {
-      const float a = t[threadIdx.x][r];
-      uint32_t u = __float_as_uint(a);
-      u = (u + 0x00000fffu + ((u >> 13) & 1u)) & 0xffffe000u;
-      float h = __uint_as_float(u);
-      if (!(fabsf(h) <= 3.0e38f)) h = a;
+      float h, l;
+      split_tf32_one(t[threadIdx.x][r], h, l);
       hi[j * ld_dst + i] = h;
-      lo[j * ld_dst + i] = a - h;
+      lo[j * ld_dst + i] = l;
     }
   }
 }
@@ -199,9 +225,27 @@ __device__ __forceinline__ void split_bf16_one(float a, float& h, __nv_bfloat16&
   lb = __float2bfloat16_rn(a - h);
 }
 __global__ void glp_split_bf16_kernel(const float* src, float* hi, __nv_bfloat16* hb, __nv_bfloat16* lb,  // hi may alias src
-                                      int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst) {
+                                      int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst,
+                                      const int32_t* gate, int gate_cap) {
+  if (gate != nullptr && *gate <= gate_cap) return;
   const int64_t total = rows * cols;
-  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x) {
+  const int64_t step = int64_t(gridDim.x) * blockDim.x, first = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (ld_src == cols && ld_dst == cols && (total & 3) == 0 &&
+      ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(hi)) & 15) == 0 &&
+      ((reinterpret_cast<uintptr_t>(hb) | reinterpret_cast<uintptr_t>(lb)) & 7) == 0) {
+    for (int64_t e = first; e < total / 4; e += step) {
+      const float4 a = reinterpret_cast<const float4*>(src)[e];
+      float4 h;
+      __nv_bfloat16 b0[4], b1[4];
+      split_bf16_one(a.x, h.x, b0[0], b1[0]); split_bf16_one(a.y, h.y, b0[1], b1[1]);
+      split_bf16_one(a.z, h.z, b0[2], b1[2]); split_bf16_one(a.w, h.w, b0[3], b1[3]);
+      reinterpret_cast<float4*>(hi)[e] = h;
+      reinterpret_cast<uint2*>(hb)[e] = *reinterpret_cast<const uint2*>(b0);
+      reinterpret_cast<uint2*>(lb)[e] = *reinterpret_cast<const uint2*>(b1);
+    }
+    return;
+  }
+  for (int64_t e = first; e < total; e += step) {
     const int64_t i = e / cols, j = e - i * cols;
     float h; __nv_bfloat16 b0, b1;
     split_bf16_one(src[i * ld_src + j], h, b0, b1);
@@ -235,6 +279,86 @@ __global__ void glp_transpose_split_bf16_kernel(const float* __restrict__ src, f
 __global__ void glp_to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t total) {
   for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x)
     dst[e] = __float2bfloat16_rn(src[e]);
+}
+
+// ---- PASSES = 4 operands: fp16 pairs of the scaled value ---------------------------------------------------
+// v = a * s (s a power of two chosen so that max|v| < 2^15): v0 = fp16(v), v1 = fp16(v - v0); v0 + v1 carries 22
+// significant bits of v while v1 is a normal number (|v| >= 2^-3), and is within 2^-25 of v below that.
+__device__ __forceinline__ void split_f16_one(float a, float s, __half& v0, __half& v1) {
+  const float v = a * s;
+  v0 = __float2half_rn(v);
+  v1 = __float2half_rn(v - __half2float(v0));
+}
+// power-of-two scale that brings max|.| = mx into [2^14, 2^15); 1 for zero / non-finite input
+__device__ __host__ __forceinline__ float f16_scale_for(float mx) {
+  if (!(mx > 0.0f) || !(mx < 3.0e38f)) return 1.0f;
+  int e = 0;
+  frexpf(mx, &e);            // mx = f * 2^e, f in [0.5, 1)  ->  mx * 2^(15 - e) in [2^14, 2^15)
+  int k = 15 - e;
+  k = k > 126 ? 126 : (k < -126 ? -126 : k);
+  return ldexpf(1.0f, k);
+}
+// max |src| as float bits (non-negative floats order like unsigned integers); *out zeroed by the caller
+__global__ void glp_absmax_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int64_t ld, unsigned* out) {
+  unsigned mx = 0u;
+  const int64_t total = rows * cols;
+  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t i = e / cols, j = e - i * cols;
+    const unsigned u = __float_as_uint(fabsf(src[i * ld + j]));
+    mx = u > mx ? u : mx;
+  }
+  mx = __reduce_max_sync(0xffffffffu, mx);
+  if ((threadIdx.x & 31) == 0 && mx != 0u) atomicMax(out, mx);
+}
+// contiguous small operand (x or r) with the scale taken from its own max on the device; block 0 publishes
+// inv_scale_out = 1 / (s * s_other) for the product's epilogue.  gate as in glp_split_tf32_kernel.
+__global__ void glp_split_f16_kernel(const float* __restrict__ src, __half* __restrict__ o0, __half* __restrict__ o1,
+                                     int64_t total, const unsigned* amax_bits, float s_other,
+                                     const unsigned* other_amax_bits, double* inv_scale_out,
+                                     const int32_t* gate, int gate_cap) {
+  if (gate != nullptr && *gate <= gate_cap) return;
+  const float s = f16_scale_for(__uint_as_float(*amax_bits));
+  if (inv_scale_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    const float so = other_amax_bits != nullptr ? f16_scale_for(__uint_as_float(*other_amax_bits)) : s_other;
+    *inv_scale_out = 1.0 / (double(s) * double(so));
+  }
+  const int64_t step = int64_t(gridDim.x) * blockDim.x, first = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if ((total & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0 &&
+      ((reinterpret_cast<uintptr_t>(o0) | reinterpret_cast<uintptr_t>(o1)) & 7) == 0) {
+    for (int64_t e = first; e < total / 4; e += step) {
+      const float4 a = reinterpret_cast<const float4*>(src)[e];
+      __half h0[4], h1[4];
+      split_f16_one(a.x, s, h0[0], h1[0]); split_f16_one(a.y, s, h0[1], h1[1]);
+      split_f16_one(a.z, s, h0[2], h1[2]); split_f16_one(a.w, s, h0[3], h1[3]);
+      reinterpret_cast<uint2*>(o0)[e] = *reinterpret_cast<const uint2*>(h0);
+      reinterpret_cast<uint2*>(o1)[e] = *reinterpret_cast<const uint2*>(h1);
+    }
+    return;
+  }
+  for (int64_t e = first; e < total; e += step) split_f16_one(src[e], s, o0[e], o1[e]);
+}
+// resident operand (A or its transpose) with a fixed scale
+__global__ void glp_split_f16_2d_kernel(const float* __restrict__ src, __half* __restrict__ o0, __half* __restrict__ o1,
+                                        int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst, float s) {
+  const int64_t total = rows * cols;
+  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t i = e / cols, j = e - i * cols;
+    split_f16_one(src[i * ld_src + j], s, o0[i * ld_dst + j], o1[i * ld_dst + j]);
+  }
+}
+__global__ void glp_transpose_split_f16_kernel(const float* __restrict__ src, __half* __restrict__ o0, __half* __restrict__ o1,
+                                               int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst, float s) {
+  __shared__ float t[32][33];
+  const int64_t bi = int64_t(blockIdx.y) * 32, bj = int64_t(blockIdx.x) * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int64_t i = bi + r, j = bj + threadIdx.x;
+    t[r][threadIdx.x] = (i < rows && j < cols) ? src[i * ld_src + j] : 0.f;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int64_t j = bj + r, i = bi + threadIdx.x;
+    if (j < cols && i < rows) split_f16_one(t[threadIdx.x][r], s, o0[j * ld_dst + i], o1[j * ld_dst + i]);
+  }
 }
 
 // work item w -> (K split, M tile, column group), column group fastest: the CTAs that take the column
@@ -284,7 +408,12 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
   // PASSES = 1: Ph.Qh (plain TF32).  PASSES = 3: + Ph.Ql + Pl.Qh on TF32 hi/lo splits (tmPl / tmQl = fp32 lo).
   // PASSES = 2: the same two corrections on bf16 operands (kind::f16): tmPx / tmQx = bf16(hi), tmPl / tmQl = bf16(lo);
   //             stage = Ph | Qh | bf16 Ph | bf16 Pl | bf16 Qh | bf16 Ql  (same bytes as PASSES = 3)
+  // PASSES = 4: fp16 pairs, P = (P0 + P1) / sP and Q = (Q0 + Q1) / sQ with power-of-two scales: P0.Q0 + P0.Q1 + P1.Q0 on
+  //             kind::f16 (same 11-bit significands as TF32, twice the rate, half the bytes); tmPh / tmPl = P0 / P1,
+  //             tmQh / tmQl = Q0 / Q1; a K block is 64 elements (128-byte rows, same stage layout as PASSES = 3)
   constexpr bool CORR = PASSES >= 2;
+  constexpr bool F16X2 = PASSES == 4;
+  constexpr int BK = F16X2 ? 2 * GEMM_BK : GEMM_BK;
   constexpr int PB_BYTES = GEMM_BM * 64, QB_BYTES = NT * 64;   // bf16 tiles
   constexpr int STAGES = gemm_stages<NT, PASSES>();
   constexpr int STAGE_BYTES = gemm_stage_bytes<NT, PASSES>();
@@ -313,7 +442,7 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
   }
   if (a.gate != nullptr && *a.gate <= a.gate_cap) return;   // grid-uniform, before any barrier or cluster traffic
   const int64_t tiles = (a.M + GEMM_BM - 1) / GEMM_BM;
-  const int64_t nkb = (a.K + GEMM_BK - 1) / GEMM_BK;
+  const int64_t nkb = (a.K + BK - 1) / BK;
   const int64_t kc = a.k_chunk_blocks > 0 ? a.k_chunk_blocks : nkb;
   const int64_t nchunks = (nkb + kc - 1) / kc;
   const int64_t S = a.splits > 1 ? a.splits : 1;
@@ -368,10 +497,10 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
           mbar_wait(&empty[stage], phase ^ 1u, a.fault);   // the slot is free in EVERY CTA I multicast into
           mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
           uint8_t* s = smem + stage * STAGE_BYTES;
-          const int32_t k0 = int32_t(kb * GEMM_BK);
+          const int32_t k0 = int32_t(kb * BK);
           load_p(s, &tmPh, &full[stage], k0, r0, 128);
           load_q(s + P_BYTES, &tmQh, &full[stage], k0, q0, 128);
-          if (PASSES == 3) {
+          if (PASSES == 3 || F16X2) {
             load_p(s + P_BYTES + Q_BYTES, &tmPl, &full[stage], k0, r0, 128);
             load_q(s + 2 * P_BYTES + Q_BYTES, &tmQl, &full[stage], k0, q0, 128);
           }
@@ -411,10 +540,28 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
             tc_fence_after();
             const uint32_t sbase = smem_u32(smem + stage * STAGE_BYTES);
             const uint64_t dPh = umma_desc_k_sw128(sbase), dQh = umma_desc_k_sw128(sbase + P_BYTES);
+            if (F16X2) {
+              // 4 instructions of K = 16 fp16 (32 bytes) per 128-byte row, like the 4 x 8 fp32 of the TF32 tile
+              constexpr uint32_t idesc_h = umma_idesc_f16<NT>();
+              const uint64_t dPl = umma_desc_k_sw128(sbase + P_BYTES + Q_BYTES);
+              const uint64_t dQl = umma_desc_k_sw128(sbase + 2 * P_BYTES + Q_BYTES);
 #pragma unroll
-            for (int k4 = 0; k4 < GEMM_BK / GEMM_UMMA_K; ++k4) {
-              umma_tf32(d_tmem, dPh + uint64_t(2 * k4), dQh + uint64_t(2 * k4), idesc, accumulate);
-              accumulate = 1;
+              for (int k4 = 0; k4 < 4; ++k4) {
+                umma_bf16(d_tmem, dPh + uint64_t(2 * k4), dQh + uint64_t(2 * k4), idesc_h, accumulate);
+                accumulate = 1;
+              }
+#pragma unroll
+              for (int k4 = 0; k4 < 4; ++k4) {
+                umma_bf16(c_tmem, dPh + uint64_t(2 * k4), dQl + uint64_t(2 * k4), idesc_h, c_accumulate);
+                c_accumulate = 1;
+                umma_bf16(c_tmem, dPl + uint64_t(2 * k4), dQh + uint64_t(2 * k4), idesc_h, 1u);
+              }
+            } else {
+#pragma unroll
+              for (int k4 = 0; k4 < GEMM_BK / GEMM_UMMA_K; ++k4) {
+                umma_tf32(d_tmem, dPh + uint64_t(2 * k4), dQh + uint64_t(2 * k4), idesc, accumulate);
+                accumulate = 1;
+              }
             }
             if (PASSES == 3) {
               const uint64_t dPl = umma_desc_k_sw128(sbase + P_BYTES + Q_BYTES);
@@ -495,10 +642,11 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
       }
       if (row < a.M) {
         double* dst = Dout + it.split * a.split_stride;
+        const double sc = (F16X2 && a.scale != nullptr) ? *a.scale : 1.0;   // a power of two: exact
 #pragma unroll
         for (int j = 0; j < HC; ++j) {
           const int col = int(it.group * CG + dg) * NT + half * HC + j;
-          if (col < a.N) dst[int64_t(col) * a.ldd + row] = sum[j];
+          if (col < a.N) dst[int64_t(col) * a.ldd + row] = F16X2 ? sum[j] * sc : sum[j];
         }
       }
     }

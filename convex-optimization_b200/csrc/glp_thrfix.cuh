@@ -16,6 +16,7 @@
 // device-gated launch of the product kernel computes A.xnt directly, as before (GemmArgs::gate).
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include "glp_device.cuh"
 #include "glp_types.cuh"
@@ -119,6 +120,10 @@ struct ThrFixArgs {
   const float* At_hi;               // [n][ldm] transposed A, TF32 part
   const float* At_lo;               // fp32 remainder (3xTF32 operand set) or nullptr
   const __nv_bfloat16* At_lb;       // bf16 remainder (TF32 + bf16 operand set) or nullptr
+  const __half* At_f0;              // fp16-pair operand set: A^T s = f0 + f1 (then At_hi is nullptr)
+  const __half* At_f1;
+  float inv_s;                      // 1 / s
+  float pad2;
   double* AX[2];                    // [2l][ldm]: column l + c := column c - sum_r At[rows_r][:] * vals_r
 };
 
@@ -143,26 +148,23 @@ glp_thr_fix_kernel(const ThrFixArgs a, const Geom g) {
     if (tid < nr) { s_j[tid] = rows[r0 + tid]; s_v[tid] = vals[r0 + tid]; }
     __syncthreads();
     if (!live) continue;
+    auto at_value = [&](int64_t at) {
+      if (a.At_f0 != nullptr)
+        return (double(__half2float(a.At_f0[at])) + double(__half2float(a.At_f1[at]))) * double(a.inv_s);
+      double v = double(a.At_hi[at]);
+      if (a.At_lo != nullptr) v += double(a.At_lo[at]);
+      else if (a.At_lb != nullptr) v += double(__bfloat162float(a.At_lb[at]));
+      return v;
+    };
     int r = 0;
     for (; r + 4 <= nr; r += 4) {   // four independent row loads in flight
       double av[4];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int64_t at = int64_t(s_j[r + q]) * g.ldm + i;
-        av[q] = double(a.At_hi[at]);
-        if (a.At_lo != nullptr) av[q] += double(a.At_lo[at]);
-        else if (a.At_lb != nullptr) av[q] += double(__bfloat162float(a.At_lb[at]));
-      }
+      for (int q = 0; q < 4; ++q) av[q] = at_value(int64_t(s_j[r + q]) * g.ldm + i);
 #pragma unroll
       for (int q = 0; q < 4; ++q) acc = fma(av[q], double(s_v[r + q]), acc);
     }
-    for (; r < nr; ++r) {
-      const int64_t at = int64_t(s_j[r]) * g.ldm + i;
-      double av = double(a.At_hi[at]);
-      if (a.At_lo != nullptr) av += double(a.At_lo[at]);
-      else if (a.At_lb != nullptr) av += double(__bfloat162float(a.At_lb[at]));
-      acc = fma(av, double(s_v[r]), acc);
-    }
+    for (; r < nr; ++r) acc = fma(at_value(int64_t(s_j[r]) * g.ldm + i), double(s_v[r]), acc);
   }
   if (!live) return;
   double* ax = a.AX[sel];

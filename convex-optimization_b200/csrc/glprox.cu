@@ -155,7 +155,13 @@ struct glp_handle {
   // tensor mode 3 (tf32 main term + bf16 corrections): bf16 copies of hi and lo instead of the fp32 lo arrays
   __nv_bfloat16 *A_hb = nullptr, *A_lb = nullptr, *At_hb = nullptr, *At_lb = nullptr;
   __nv_bfloat16 *xop_hb = nullptr, *xop_lb = nullptr, *r_hb = nullptr, *r_lb = nullptr;
-  int wide_built = -1;         // which operand set (wide_passes) is resident
+  // tensor mode 4 (fp16 pairs): A s and A^T s as v0 + v1 (2 x |A| of HBM in all), the small operands likewise
+  __half *A_f0 = nullptr, *A_f1 = nullptr, *At_f0 = nullptr, *At_f1 = nullptr;
+  __half *xop_f0 = nullptr, *xop_f1 = nullptr, *r_f0 = nullptr, *r_f1 = nullptr;
+  unsigned* f16_amax = nullptr;    // [2] float bits of max|xn| / max|r| of the current operands
+  double* f16_inv = nullptr;       // [2] 1 / (s_A s_x), 1 / (s_A s_r): what the product epilogues multiply by
+  float f16_sA = 1.0f;             // power-of-two scale of the resident A
+  bool f16_unusable = false;       // auto mode found non-finite entries in A: 3xTF32 instead
   // A.xnt from A.xn by a sparse correction (glp_thrfix.cuh); thr_cap < 0: off (GLPROX_WIDE_THRFIX=0)
   int32_t *thr_rows = nullptr, *thr_col_count = nullptr, *thr_count = nullptr;
   float* thr_vals = nullptr;
@@ -400,6 +406,10 @@ extern "C" int glp_destroy(glp_handle* h) {
   if (h->gemm_ws) cudaFree(h->gemm_ws);
   if (h->admm_L) cudaFree(h->admm_L);
   if (h->nccl_stage) cudaFree(h->nccl_stage);
+  for (__half* q : {h->A_f0, h->A_f1, h->At_f0, h->At_f1, h->xop_f0, h->xop_f1, h->r_f0, h->r_f1})
+    if (q) cudaFree(q);
+  if (h->f16_amax) cudaFree(h->f16_amax);
+  if (h->f16_inv) cudaFree(h->f16_inv);
   for (__nv_bfloat16* q : {h->A_hb, h->A_lb, h->At_hb, h->At_lb, h->xop_hb, h->xop_lb, h->r_hb, h->r_lb})
     if (q) cudaFree(q);
   if (h->arena) cudaFree(h->arena);
@@ -532,33 +542,43 @@ static int glp_allreduce_f64(glp_handle* h, double* buf, size_t count, bool is_m
 static bool wide_active(const glp_handle* h) {
   return h->dtype == GLP_F32 && h->g.l >= 16 && 2 * h->g.l <= 256 && h->tensor_mode != 1 && !h->xch_nccl;
 }
-static int wide_passes(const glp_handle* h) { return h->tensor_mode == 2 ? 1 : (h->tensor_mode == 3 ? 2 : 3); }
-static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms);
+static int wide_passes(const glp_handle* h) {   // the PASSES of glp_gemm_tf32_kernel
+  switch (h->tensor_mode) {
+    case 2: return 1;
+    case 3: return 2;
+    case 4: return 4;
+    case 5: return 3;
+    default: return h->f16_unusable ? 3 : 4;   // auto: fp16 pairs unless A cannot be scaled (non-finite entries)
+  }
+}
+static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms, int bk = GEMM_BK);
 constexpr int WIDE_K_CHUNK = 8;  // the tensor core's fp32 accumulator spans 8 x 32 = 256 elements of K, then fp64
 
+struct GemmGate { const int32_t* count; int32_t cap; };            // run only when *count > cap (nullptr: always)
 static int split_f32(cudaStream_t st, const float* src, int64_t rows, int64_t cols, int64_t ld_src, float* hi, float* lo,
-                     int64_t ld_dst, bool transpose) {
+                     int64_t ld_dst, bool transpose, GemmGate gate = GemmGate{nullptr, 0}) {
   if (transpose) {
     dim3 grid(unsigned((cols + 31) / 32), unsigned((rows + 31) / 32));
     if (grid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
     glp_transpose_split_kernel<<<grid, dim3(32, 8), 0, st>>>(src, hi, lo, rows, cols, ld_src, ld_dst);
   } else {
     const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
-    glp_split_tf32_kernel<<<grid, 256, 0, st>>>(src, hi, lo, rows, cols, ld_src, ld_dst);
+    glp_split_tf32_kernel<<<grid, 256, 0, st>>>(src, hi, lo, rows, cols, ld_src, ld_dst, gate.count, gate.cap);
   }
   CU_TRY(cudaGetLastError());
   return GLP_OK;
 }
 
 static int split_bf16(cudaStream_t st, const float* src, int64_t rows, int64_t cols, int64_t ld_src, float* hi,
-                      __nv_bfloat16* hb, __nv_bfloat16* lb, int64_t ld_dst, bool transpose) {
+                      __nv_bfloat16* hb, __nv_bfloat16* lb, int64_t ld_dst, bool transpose,
+                      GemmGate gate = GemmGate{nullptr, 0}) {
   if (transpose) {
     dim3 grid(unsigned((cols + 31) / 32), unsigned((rows + 31) / 32));
     if (grid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
     glp_transpose_split_bf16_kernel<<<grid, dim3(32, 8), 0, st>>>(src, hi, hb, lb, rows, cols, ld_src, ld_dst);
   } else {
     const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
-    glp_split_bf16_kernel<<<grid, 256, 0, st>>>(src, hi, hb, lb, rows, cols, ld_src, ld_dst);
+    glp_split_bf16_kernel<<<grid, 256, 0, st>>>(src, hi, hb, lb, rows, cols, ld_src, ld_dst, gate.count, gate.cap);
   }
   CU_TRY(cudaGetLastError());
   return GLP_OK;
@@ -579,9 +599,7 @@ static int ensure_wide(glp_handle* h) {
   const size_t a_el = size_t(g.m) * g.ldn, at_el = size_t(g.n) * g.ldm;
   const size_t x_el = size_t(2) * g.l * g.ldn, r_el = size_t(g.l) * g.ldm;
   const float* A = static_cast<const float*>(h->A);
-  if (h->A_hi == nullptr) {
-    GLP_TRY(alloc_zero(&h->A_hi, a_el * 4, h->stream));
-    GLP_TRY(alloc_zero(&h->At_hi, at_el * 4, h->stream));
+  if (h->cnt_g == nullptr) {   // shared by all operand sets
     CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->cnt_g), size_t(h->gather_grid) * 8));
     // A.xnt by sparse correction: on unless GLPROX_WIDE_THRFIX=0.  Room for n/32 entries per operand column
     // (>= 64): ~30 x the expected load at thres = 1e-3, and at that load the correction still costs well under
@@ -603,6 +621,47 @@ static int ensure_wide(glp_handle* h) {
     const size_t tps = size_t(gemm_splits(g.n, g.m, g.l, WIDE_K_CHUNK, h->num_sms)) * g.l * g.ldn * 8;
     h->gemm_ws_bytes = std::max(fwd, tps);
     CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->gemm_ws), h->gemm_ws_bytes));
+  }
+  if (wide_passes(h) == 4) {
+    if (h->A_f0 != nullptr) return GLP_OK;
+    // scale of the resident operand from max|A| (one synchronous read-back at set-up)
+    if (h->f16_amax == nullptr) {
+      GLP_TRY(alloc_zero(&h->f16_amax, 4 * sizeof(unsigned), h->stream));
+      GLP_TRY(alloc_zero(&h->f16_inv, 2 * sizeof(double), h->stream));
+    }
+    CU_TRY(cudaMemsetAsync(h->f16_amax + 2, 0, sizeof(unsigned), h->stream));
+    const int ag = int(std::min<int64_t>((int64_t(g.m) * g.n + 255) / 256, int64_t(h->num_sms) * 16));
+    glp_absmax_kernel<<<ag, 256, 0, h->stream>>>(A, g.m, g.n, h->lda, h->f16_amax + 2);
+    CU_TRY(cudaGetLastError());
+    unsigned bits = 0;
+    CU_TRY(cudaMemcpyAsync(&bits, h->f16_amax + 2, sizeof(bits), cudaMemcpyDeviceToHost, h->stream));
+    CU_TRY(cudaStreamSynchronize(h->stream));
+    float amax;
+    memcpy(&amax, &bits, sizeof(amax));
+    if (!(amax < 3.0e38f)) {
+      if (h->tensor_mode != 0) return fail(GLP_ERR_ARG, "A holds non-finite values: the fp16-pair operand set cannot be scaled");
+      h->f16_unusable = true;   // auto: propagate them through the 3xTF32 operand set like any fp32 product would
+      return ensure_wide(h);
+    }
+    h->f16_sA = f16_scale_for(amax);
+    GLP_TRY(alloc_zero(&h->A_f0, a_el * 2, h->stream));
+    GLP_TRY(alloc_zero(&h->A_f1, a_el * 2, h->stream));
+    GLP_TRY(alloc_zero(&h->At_f0, at_el * 2, h->stream));
+    GLP_TRY(alloc_zero(&h->At_f1, at_el * 2, h->stream));
+    GLP_TRY(alloc_zero(&h->xop_f0, x_el * 2, h->stream));
+    GLP_TRY(alloc_zero(&h->xop_f1, x_el * 2, h->stream));
+    GLP_TRY(alloc_zero(&h->r_f0, r_el * 2, h->stream));
+    GLP_TRY(alloc_zero(&h->r_f1, r_el * 2, h->stream));
+    glp_split_f16_2d_kernel<<<ag, 256, 0, h->stream>>>(A, h->A_f0, h->A_f1, g.m, g.n, h->lda, g.ldn, h->f16_sA);
+    dim3 tgrid(unsigned((g.n + 31) / 32), unsigned((g.m + 31) / 32));
+    if (tgrid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
+    glp_transpose_split_f16_kernel<<<tgrid, dim3(32, 8), 0, h->stream>>>(A, h->At_f0, h->At_f1, g.m, g.n, h->lda, g.ldm, h->f16_sA);
+    CU_TRY(cudaGetLastError());
+    return GLP_OK;
+  }
+  if (h->A_hi == nullptr) {
+    GLP_TRY(alloc_zero(&h->A_hi, a_el * 4, h->stream));
+    GLP_TRY(alloc_zero(&h->At_hi, at_el * 4, h->stream));
   }
   if (wide_passes(h) == 2) {
     if (h->A_hb == nullptr) {
@@ -630,13 +689,13 @@ static int ensure_wide(glp_handle* h) {
 
 struct GemmWs { double* buf; size_t bytes; };  // split-K partial products (nullptr: no splitting)
 struct GemmBf16 { const __nv_bfloat16 *Phb, *Plb, *Qhb, *Qlb; };  // passes = 2: bf16 copies of hi / lo, same pitches
-struct GemmGate { const int32_t* count; int32_t cap; };            // run only when *count > cap (nullptr: always)
-static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms);
+static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms, int bk);
 static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
                         const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
                         int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl = nullptr, double* D_alt = nullptr,
                         int role = 0, GemmWs ws = GemmWs{nullptr, 0},
-                        GemmBf16 bf = GemmBf16{nullptr, nullptr, nullptr, nullptr}, GemmGate gate = GemmGate{nullptr, 0});
+                        GemmBf16 bf = GemmBf16{nullptr, nullptr, nullptr, nullptr}, GemmGate gate = GemmGate{nullptr, 0},
+                        const double* scale = nullptr);
 
 static uint64_t seq_base(const glp_handle* h);
 
@@ -687,31 +746,73 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
     CU_TRY(cudaGetLastError());
     h->n_launches++;
   }
-  if (bf) GLP_TRY(split_bf16(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_hb, h->xop_lb, g.ldn, false));
-  else GLP_TRY(split_f32(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_lo, g.ldn, false));  // hi in place
+  const bool f16 = wide_passes(h) == 4;
+  const int64_t q2 = int64_t(g.l) * g.ldn;
+  const GemmGate xnt_gate{h->thr_count + 1, 0};
+  if (f16) {
+    // fp16 pairs of xn s_x, s_x from max|xn| on the device (max|xnt| <= max|xn|: one scale for both halves)
+    CU_TRY(cudaMemsetAsync(h->f16_amax, 0, sizeof(unsigned), h->stream));
+    const int sg = int(std::min<int64_t>((q2 + 1023) / 1024, int64_t(h->num_sms) * 16));
+    glp_absmax_kernel<<<sg, 256, 0, h->stream>>>(xop, g.l, g.ldn, g.ldn, h->f16_amax);
+    if (h->thr_cap < 0) {
+      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop, h->xop_f0, h->xop_f1, 2 * q2, h->f16_amax, h->f16_sA, nullptr,
+                                                      h->f16_inv, nullptr, 0);
+    } else {
+      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop, h->xop_f0, h->xop_f1, q2, h->f16_amax, h->f16_sA, nullptr,
+                                                      h->f16_inv, nullptr, 0);
+      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop + q2, h->xop_f0 + q2, h->xop_f1 + q2, q2, h->f16_amax, h->f16_sA,
+                                                      nullptr, nullptr, xnt_gate.count, xnt_gate.cap);
+      h->n_launches++;
+    }
+    CU_TRY(cudaGetLastError());
+    h->n_launches++;
+  } else if (h->thr_cap < 0) {
+    if (bf) GLP_TRY(split_bf16(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_hb, h->xop_lb, g.ldn, false));
+    else GLP_TRY(split_f32(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_lo, g.ldn, false));  // hi in place
+  } else {   // the xnt half is only needed by the gated fallback product
+    if (bf) {
+      GLP_TRY(split_bf16(h->stream, xop, g.l, g.ldn, g.ldn, xop, h->xop_hb, h->xop_lb, g.ldn, false));
+      GLP_TRY(split_bf16(h->stream, xop + q2, g.l, g.ldn, g.ldn, xop + q2, h->xop_hb + q2, h->xop_lb + q2, g.ldn, false, xnt_gate));
+    } else {
+      GLP_TRY(split_f32(h->stream, xop, g.l, g.ldn, g.ldn, xop, h->xop_lo, g.ldn, false));
+      GLP_TRY(split_f32(h->stream, xop + q2, g.l, g.ldn, g.ldn, xop + q2, h->xop_lo + q2, g.ldn, false, xnt_gate));
+    }
+    h->n_launches++;
+  }
   prof_mark(h, 0, 0);
   const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes};
+  // operand pointers of the selected set (fp16 pairs travel as float* through gemm_enqueue, pitches in elements)
+  const float* Ph = f16 ? reinterpret_cast<const float*>(h->A_f0) : h->A_hi;
+  const float* Pl = f16 ? reinterpret_cast<const float*>(h->A_f1) : h->A_lo;
+  auto qh = [&](int64_t off) { return f16 ? reinterpret_cast<const float*>(h->xop_f0 + off) : xop + off; };
+  auto ql = [&](int64_t off) {
+    return f16 ? reinterpret_cast<const float*>(h->xop_f1 + off) : (bf ? static_cast<const float*>(nullptr) : h->xop_lo + off);
+  };
+  auto qb = [&](int64_t off) {
+    return GemmBf16{h->A_hb, h->A_lb, bf ? h->xop_hb + off : nullptr, bf ? h->xop_lb + off : nullptr};
+  };
+  const double* sc = f16 ? h->f16_inv : nullptr;
+  const int kch = f16 ? WIDE_K_CHUNK / 2 : WIDE_K_CHUNK;   // 256 elements of K per fp32 accumulation either way
   if (h->thr_cap < 0) {   // one product over both operand halves
-    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, 2 * g.l, h->A_hi, h->A_lo, g.ldn, xop, h->xop_lo,
-                         g.ldn, h->AX[0], g.ldm, WIDE_K_CHUNK, h->fault, ctrl, h->AX[1], 1, ws,
-                         GemmBf16{h->A_hb, h->A_lb, h->xop_hb, h->xop_lb}));
+    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, 2 * g.l, Ph, Pl, g.ldn, qh(0), ql(0),
+                         g.ldn, h->AX[0], g.ldm, kch, h->fault, ctrl, h->AX[1], 1, ws, qb(0), GemmGate{nullptr, 0}, sc));
   } else {
     // A.xn on the tensor cores; A.xnt = A.xn - A.(xn - xnt) on the CUDA cores from the listed entries, or, when
     // a list overflowed, by a second product launch that the device gates on the overflow count
-    const int64_t q2 = int64_t(g.l) * g.ldn, d2 = int64_t(g.l) * g.ldm;
-    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, g.l, h->A_hi, h->A_lo, g.ldn, xop, h->xop_lo,
-                         g.ldn, h->AX[0], g.ldm, WIDE_K_CHUNK, h->fault, ctrl, h->AX[1], 1, ws,
-                         GemmBf16{h->A_hb, h->A_lb, h->xop_hb, h->xop_lb}));
-    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, g.l, h->A_hi, h->A_lo, g.ldn, xop + q2,
-                         bf ? nullptr : h->xop_lo + q2, g.ldn, h->AX[0] + d2, g.ldm, WIDE_K_CHUNK, h->fault, ctrl,
-                         h->AX[1] + d2, 1, ws,
-                         GemmBf16{h->A_hb, h->A_lb, bf ? h->xop_hb + q2 : nullptr, bf ? h->xop_lb + q2 : nullptr},
-                         GemmGate{h->thr_count + 1, 0}));
+    const int64_t d2 = int64_t(g.l) * g.ldm;
+    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, g.l, Ph, Pl, g.ldn, qh(0), ql(0),
+                         g.ldn, h->AX[0], g.ldm, kch, h->fault, ctrl, h->AX[1], 1, ws, qb(0), GemmGate{nullptr, 0}, sc));
+    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, g.l, Ph, Pl, g.ldn, qh(q2), ql(q2),
+                         g.ldn, h->AX[0] + d2, g.ldm, kch, h->fault, ctrl, h->AX[1] + d2, 1, ws, qb(q2), xnt_gate, sc));
     ThrFixArgs fa{};
     fa.ctrl = ctrl;
     fa.count = h->thr_count; fa.col_count = h->thr_col_count;
     fa.rows = h->thr_rows; fa.vals = h->thr_vals; fa.cap = h->thr_cap;
     fa.At_hi = h->At_hi; fa.At_lo = bf ? nullptr : h->At_lo; fa.At_lb = bf ? h->At_lb : nullptr;
+    if (f16) {
+      fa.At_hi = nullptr; fa.At_lo = nullptr; fa.At_lb = nullptr;
+      fa.At_f0 = h->At_f0; fa.At_f1 = h->At_f1; fa.inv_s = 1.0f / h->f16_sA;
+    }
     fa.AX[0] = h->AX[0]; fa.AX[1] = h->AX[1];
     const dim3 fgrid(unsigned((g.ldm + THRFIX_THREADS - 1) / THRFIX_THREADS), unsigned(g.l));
     glp_thr_fix_kernel<<<fgrid, THRFIX_THREADS, 0, h->stream>>>(fa, g);
@@ -740,12 +841,29 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
 static int enqueue_wide_tpass(glp_handle* h, const Ctrl* ctrl) {
   const Geom& g = h->g;
   float* r = static_cast<float*>(h->r);
-  if (wide_passes(h) == 2) GLP_TRY(split_bf16(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_hb, h->r_lb, g.ldm, false));
-  else GLP_TRY(split_f32(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_lo, g.ldm, false));
-  prof_mark(h, 1, 0);
-  GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.n, g.m, g.l, h->At_hi, h->At_lo, g.ldm, r, h->r_lo,
-                       g.ldm, h->grad, g.ldn, WIDE_K_CHUNK, h->fault, ctrl, nullptr, 2,
-                       GemmWs{h->gemm_ws, h->gemm_ws_bytes}, GemmBf16{h->At_hb, h->At_lb, h->r_hb, h->r_lb}));
+  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes};
+  if (wide_passes(h) == 4) {
+    const int64_t tot = int64_t(g.l) * g.ldm;
+    CU_TRY(cudaMemsetAsync(h->f16_amax + 1, 0, sizeof(unsigned), h->stream));
+    const int sg = int(std::min<int64_t>((tot + 1023) / 1024, int64_t(h->num_sms) * 16));
+    glp_absmax_kernel<<<sg, 256, 0, h->stream>>>(r, g.l, g.ldm, g.ldm, h->f16_amax + 1);
+    glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(r, h->r_f0, h->r_f1, tot, h->f16_amax + 1, h->f16_sA, nullptr,
+                                                    h->f16_inv + 1, nullptr, 0);
+    CU_TRY(cudaGetLastError());
+    h->n_launches++;
+    prof_mark(h, 1, 0);
+    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, 4, g.n, g.m, g.l, reinterpret_cast<const float*>(h->At_f0),
+                         reinterpret_cast<const float*>(h->At_f1), g.ldm, reinterpret_cast<const float*>(h->r_f0),
+                         reinterpret_cast<const float*>(h->r_f1), g.ldm, h->grad, g.ldn, WIDE_K_CHUNK / 2, h->fault, ctrl,
+                         nullptr, 2, ws, GemmBf16{nullptr, nullptr, nullptr, nullptr}, GemmGate{nullptr, 0}, h->f16_inv + 1));
+  } else {
+    if (wide_passes(h) == 2) GLP_TRY(split_bf16(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_hb, h->r_lb, g.ldm, false));
+    else GLP_TRY(split_f32(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_lo, g.ldm, false));
+    prof_mark(h, 1, 0);
+    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.n, g.m, g.l, h->At_hi, h->At_lo, g.ldm, r, h->r_lo,
+                         g.ldm, h->grad, g.ldn, WIDE_K_CHUNK, h->fault, ctrl, nullptr, 2, ws,
+                         GemmBf16{h->At_hb, h->At_lb, h->r_hb, h->r_lb}));
+  }
   prof_mark(h, 1, 1);
   h->n_launches += 2;
   h->n_gemm++;
@@ -1495,8 +1613,9 @@ extern "C" int glp_tpass_prox(glp_handle* h, const glp_step_params* sp, const do
 
 extern "C" int glp_set_tensor_mode(glp_handle* h, int mode) {
   if (h == nullptr) return fail(GLP_ERR_ARG, "null handle");
-  if (mode < 0 || mode > 3)
-    return fail(GLP_ERR_ARG, "tensor mode must be 0 (auto: 3xTF32), 1 (off), 2 (plain TF32) or 3 (TF32 + bf16 corrections)");
+  if (mode < 0 || mode > 5)
+    return fail(GLP_ERR_ARG, "tensor mode must be 0 (auto: fp16 pairs), 1 (off), 2 (plain TF32), 3 (TF32 + bf16 corrections), "
+                             "4 (fp16 pairs) or 5 (3xTF32)");
   if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
   h->tensor_mode = mode;
   return GLP_OK;
@@ -1693,6 +1812,22 @@ static int make_map_f32_k128(CUtensorMap* map, const void* base, uint64_t inner,
   return GLP_OK;
 }
 
+// fp16 operand tile of the fp16-pair mode: 64 elements = 128 bytes of K per row, 128-byte swizzle
+static int make_map_f16_k128(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t stride_bytes,
+                             uint32_t box_outer) {
+  PFN_encodeTiled fn = encode_tiled_fn();
+  if (fn == nullptr) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  const cuuint64_t dims[2] = {inner, outer};
+  const cuuint64_t strides[1] = {stride_bytes};
+  const cuuint32_t box[2] = {cuuint32_t(2 * GEMM_BK), box_outer};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled (fp16 operand) failed with CUresult %d", int(r));
+  return GLP_OK;
+}
+
 // bf16 operand tile: 32 elements = 64 bytes of K per row, 64-byte swizzle
 static int make_map_bf16_k64(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t stride_bytes,
                              uint32_t box_outer) {
@@ -1748,10 +1883,10 @@ static cudaError_t launch_gemm_t(cudaStream_t st, int num_sms, int64_t cluster_i
 // unsplit vs 3.56 ms with 4 splits at M=16384 K=65536 N=256) and fine splits cost epilogue + workspace
 // traffic.  K is therefore split only when the items cover less than half of the SMs (column shards of a
 // multi-GPU job), and then just enough to occupy them, keeping >= 8 accumulation chunks per item.
-static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms) {
+static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms, int bk) {
   const int NT = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
   const int64_t base = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + NT - 1) / NT);
-  const int64_t nkb = (K + GEMM_BK - 1) / GEMM_BK;
+  const int64_t nkb = (K + bk - 1) / bk;
   const int64_t kc = k_chunk > 0 ? k_chunk : nkb;
   const int64_t nchunks = (nkb + kc - 1) / kc;
   if (const char* e = getenv("GLPROX_GEMM_SPLITS")) {   // measurement override
@@ -1764,14 +1899,17 @@ static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms) {
   return int(std::max<int64_t>(1, std::min<int64_t>(S, 16)));
 }
 
-// D[N][ldd] = P[M x K] . Q[N x K]^T ; passes 1 (TF32) or 3 (hi/lo compensated); N <= 256 (groups of <= 128 columns)
+// D[N][ldd] = P[M x K] . Q[N x K]^T ; passes 1 (TF32), 3 (hi/lo compensated), 2 (bf16 corrections) or 4 (fp16 pairs:
+// Ph / Pl / Qh / Ql then point at __half arrays v0 / v1 with pitches in fp16 elements, and the product is multiplied
+// by *scale); N <= 256 (groups of <= 128 columns)
 static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
                         const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
                         int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl, double* D_alt, int role, GemmWs ws,
-                        GemmBf16 bf, GemmGate gate) {
+                        GemmBf16 bf, GemmGate gate, const double* scale) {
   if (N < 1 || N > 256) return fail(GLP_ERR_ARG, "gemm: N must be 1..256 per launch (got %d)", N);
-  if (passes < 1 || passes > 3) return fail(GLP_ERR_ARG, "gemm: passes must be 1, 2 or 3");
-  if ((ldp * 4) % 16 || (ldq * 4) % 16 || (reinterpret_cast<uintptr_t>(Ph) % 16) || (reinterpret_cast<uintptr_t>(Qh) % 16))
+  if (passes < 1 || passes > 4) return fail(GLP_ERR_ARG, "gemm: passes must be 1, 2, 3 or 4");
+  const int es = passes == 4 ? 2 : 4, bk = passes == 4 ? 2 * GEMM_BK : GEMM_BK;
+  if ((ldp * es) % 16 || (ldq * es) % 16 || (reinterpret_cast<uintptr_t>(Ph) % 16) || (reinterpret_cast<uintptr_t>(Qh) % 16))
     return fail(GLP_ERR_ARG, "gemm: operands must be 16-byte aligned with 16-byte aligned pitches");
   const int NT = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
   const int64_t tiles = (M + GEMM_BM - 1) / GEMM_BM, groups = (N + NT - 1) / NT;
@@ -1792,10 +1930,19 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   if (NT / ct < 8) ct = 1;
   const uint32_t pbox = uint32_t(GEMM_BM / cg), qbox = uint32_t(NT / ct);
   CUtensorMap mph, mpl, mqh, mql, mpx, mqx;
-  GLP_TRY(make_map_f32_k128(&mph, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, pbox));
-  GLP_TRY(make_map_f32_k128(&mqh, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, qbox));
+  if (passes == 4) {
+    if (Pl == nullptr || Ql == nullptr) return fail(GLP_ERR_ARG, "gemm: passes = 4 needs both halves of the fp16 pairs");
+    GLP_TRY(make_map_f16_k128(&mph, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, pbox));
+    GLP_TRY(make_map_f16_k128(&mqh, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, qbox));
+    GLP_TRY(make_map_f16_k128(&mpl, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, pbox));
+    GLP_TRY(make_map_f16_k128(&mql, Ql, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, qbox));
+  } else {
+    GLP_TRY(make_map_f32_k128(&mph, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, pbox));
+    GLP_TRY(make_map_f32_k128(&mqh, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, qbox));
+  }
   mpx = mph; mqx = mqh;
-  if (passes == 2) {
+  if (passes == 4) {
+  } else if (passes == 2) {
     if (bf.Phb == nullptr || bf.Plb == nullptr || bf.Qhb == nullptr || bf.Qlb == nullptr)
       return fail(GLP_ERR_ARG, "gemm: passes = 2 needs the bf16 operands");
     GLP_TRY(make_map_bf16_k64(&mpx, bf.Phb, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, pbox));
@@ -1809,7 +1956,7 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   } else {
     mpl = mph; mql = mqh;
   }
-  int S = ws.buf != nullptr ? gemm_splits(M, K, N, k_chunk, num_sms) : 1;
+  int S = ws.buf != nullptr ? gemm_splits(M, K, N, k_chunk, num_sms, bk) : 1;
   const int64_t stride = int64_t(N) * ldd;
   while (S > 1 && size_t(S) * stride * 8 > ws.bytes) --S;
   GemmArgs a{};
@@ -1819,11 +1966,13 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   if (S > 1) { a.D = ws.buf; a.D_alt = ws.buf; }   // partials first; the sum below picks the real destination
   a.ct = ct; a.cg = cg;
   a.gate = gate.count; a.gate_cap = gate.cap;
+  a.scale = scale;
   const int64_t items = ((tiles + ct - 1) / ct) * ((groups + cg - 1) / cg) * S;   // cluster items
   cudaError_t e;
 #define GLP_GEMM_LAUNCH(NTV, PV) launch_gemm_t<NTV, PV>(st, num_sms, items, mph, mpl, mqh, mql, mpx, mqx, a)
   if (passes == 1) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 1) : NT == 64 ? GLP_GEMM_LAUNCH(64, 1) : GLP_GEMM_LAUNCH(128, 1);
   else if (passes == 2) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 2) : NT == 64 ? GLP_GEMM_LAUNCH(64, 2) : GLP_GEMM_LAUNCH(128, 2);
+  else if (passes == 4) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 4) : NT == 64 ? GLP_GEMM_LAUNCH(64, 4) : GLP_GEMM_LAUNCH(128, 4);
   else e = NT == 32 ? GLP_GEMM_LAUNCH(32, 3) : NT == 64 ? GLP_GEMM_LAUNCH(64, 3) : GLP_GEMM_LAUNCH(128, 3);
 #undef GLP_GEMM_LAUNCH
   if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "gemm launch failed: %s", cudaGetErrorString(e));
@@ -1849,7 +1998,7 @@ extern "C" int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, in
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   GemmWs ws{nullptr, 0};
   if (k_chunk_blocks < 0) {
-    ws.bytes = size_t(gemm_splits(M, K, N, kc, sms)) * N * ldd * 8;
+    ws.bytes = size_t(gemm_splits(M, K, N, kc, sms, passes == 4 ? 2 * GEMM_BK : GEMM_BK)) * N * ldd * 8;
     CU_TRY(cudaMallocAsync(reinterpret_cast<void**>(&ws.buf), ws.bytes, st));
   }
   GemmBf16 bf{nullptr, nullptr, nullptr, nullptr};
@@ -1866,9 +2015,33 @@ extern "C" int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, in
     glp_to_bf16_kernel<<<g2, 256, 0, st>>>(static_cast<const float*>(Q_lo), qlb, int64_t(qe));
     bf = GemmBf16{phb, plb, qhb, qlb};
   }
-  int rc = gemm_enqueue(st, sms, passes, M, K, N, static_cast<const float*>(P_hi), static_cast<const float*>(P_lo), ldp,
-                        static_cast<const float*>(Q_hi), static_cast<const float*>(Q_lo), ldq, D_dev, ldd, kc, nullptr,
-                        nullptr, nullptr, 0, ws, bf);
+  int rc;
+  if (passes == 4) {
+    // fp16 pairs of P_hi and Q_hi themselves (the lo arguments are not used): scales from the operands' maxima,
+    // all on the device in stream-ordered temporaries (test / probe entry point)
+    const size_t pe = size_t(M) * ldp, qe = size_t(N) * ldq;
+    uint8_t* t4 = nullptr;
+    CU_TRY(cudaMallocAsync(reinterpret_cast<void**>(&t4), (2 * pe + 2 * qe) * 2 + 64, st));
+    __half *p0 = reinterpret_cast<__half*>(t4 + 64), *p1 = p0 + pe, *q0 = p1 + pe, *q1 = q0 + qe;
+    unsigned* amax = reinterpret_cast<unsigned*>(t4);
+    double* inv = reinterpret_cast<double*>(t4 + 16);
+    CU_TRY(cudaMemsetAsync(t4, 0, 64, st));
+    const float *Pf = static_cast<const float*>(P_hi), *Qf = static_cast<const float*>(Q_hi);
+    const int g1 = int(std::min<size_t>((pe + 255) / 256, 148 * 16)), g2 = int(std::min<size_t>((qe + 255) / 256, 148 * 16));
+    glp_absmax_kernel<<<g1, 256, 0, st>>>(Pf, M, K, ldp, amax);
+    glp_absmax_kernel<<<g2, 256, 0, st>>>(Qf, N, K, ldq, amax + 1);
+    glp_split_f16_kernel<<<g1, 256, 0, st>>>(Pf, p0, p1, int64_t(pe), amax, 1.0f, nullptr, nullptr, nullptr, 0);
+    glp_split_f16_kernel<<<g2, 256, 0, st>>>(Qf, q0, q1, int64_t(qe), amax + 1, 1.0f, amax, inv, nullptr, 0);
+    CU_TRY(cudaGetLastError());
+    rc = gemm_enqueue(st, sms, 4, M, K, N, reinterpret_cast<const float*>(p0), reinterpret_cast<const float*>(p1), ldp,
+                      reinterpret_cast<const float*>(q0), reinterpret_cast<const float*>(q1), ldq, D_dev, ldd, kc, nullptr,
+                      nullptr, nullptr, 0, ws, bf, GemmGate{nullptr, 0}, inv);
+    cudaFreeAsync(t4, st);
+  } else {
+    rc = gemm_enqueue(st, sms, passes, M, K, N, static_cast<const float*>(P_hi), static_cast<const float*>(P_lo), ldp,
+                      static_cast<const float*>(Q_hi), static_cast<const float*>(Q_lo), ldq, D_dev, ldd, kc, nullptr,
+                      nullptr, nullptr, 0, ws, bf);
+  }
   if (ws.buf != nullptr) cudaFreeAsync(ws.buf, st);
   if (tmp != nullptr) cudaFreeAsync(tmp, st);
   return rc;
@@ -1886,7 +2059,7 @@ extern "C" int glp_tf32_split(void* stream, const void* src, int64_t rows, int64
   } else {
     const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
     glp_split_tf32_kernel<<<grid, 256, 0, st>>>(static_cast<const float*>(src), static_cast<float*>(hi),
-                                                static_cast<float*>(lo), rows, cols, ld_src, ld_dst);
+                                                static_cast<float*>(lo), rows, cols, ld_src, ld_dst, nullptr, 0);
   }
   CU_TRY(cudaGetLastError());
   return GLP_OK;

@@ -40,7 +40,7 @@ ALGO_ID = {"ProxGD": _lib.GLP_PROXGD, "FProxGD": _lib.GLP_FPROXGD, "FGD": _lib.G
            "SGD": _lib.GLP_SGD}
 # additive keys (not in the reference): dtype 'fp32'|'fp64', backend 'auto'|'stream'|'persistent',
 # device (int), poll_interval (int), dist (bool), tensor_cores 'auto'|'off'|'tf32'|'3xtf32'|'tf32+bf16' (wide l >= 16 mode)
-TENSOR_MODES = {"auto": 0, "3xtf32": 0, "off": 1, "tf32": 2, "tf32+bf16": 3}
+TENSOR_MODES = {"auto": 0, "off": 1, "tf32": 2, "tf32+bf16": 3, "f16x2": 4, "3xtf32": 5}
 
 
 def merge_opts(algo, opts):

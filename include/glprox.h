@@ -210,16 +210,21 @@ int glp_comm_attach_nccl(glp_handle* h, void* nccl_comm, int rank, int world, in
  * for l >= 16 right-hand sides.  passes = 1: plain TF32 operands; passes = 3: error-compensated
  * Ph.Qh + Ph.Ql + Pl.Qh with the hi/lo splits of glp_tf32_split (fp32-class accuracy); passes = 2: the same
  * two corrections computed on bf16 copies of hi / lo (kind::f16 at twice the TF32 rate; the corrections are
- * 2^-11 of the result, so their 8-bit mantissas cost ~1e-7 of scale).
+ * 2^-11 of the result, so their 8-bit mantissas cost ~1e-7 of scale); passes = 4: P_hi and Q_hi are the fp32
+ * operands themselves (the lo arguments are ignored): each is scaled by a power of two taken from its largest
+ * magnitude and held as a pair of fp16 numbers v0 + v1 (the same 11-bit significands as TF32 hi/lo at half the
+ * bytes), P0.Q0 + P0.Q1 + P1.Q0 run on kind::f16 at twice the TF32 rate and the epilogue undoes the scales.
  * k_chunk_blocks < 0: |k_chunk_blocks| with the split-K schedule (partial products summed in split order).
  * k_chunk_blocks > 0: flush the fp32 accumulator to fp64 every k_chunk_blocks*32 elements of K. */
 int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, int64_t K, int N, const void* P_hi,
                   const void* P_lo, int64_t ldp, const void* Q_hi, const void* Q_lo, int64_t ldq,
                   double* D_dev, int64_t ldd, int k_chunk_blocks);
 /* Wide multi-RHS mode of the solvers (fp32 data, 16 <= l <= 128, one GPU or column shards over several): both products of an
- * iteration run on glp_gemm_tf32 with A and A^T resident as TF32 hi/lo splits (4 x |A| of HBM).
- * mode 0 (default): on, error-compensated 3xTF32;  1: off (CUDA-core streams);  2: on, plain TF32;
- * 3: on, TF32 main term + bf16 correction products (passes = 2 above). */
+ * iteration run on glp_gemm_tf32 with A and A^T resident as fp16 pairs (2 x |A| of HBM) or TF32 hi/lo splits (4 x |A|).
+ * mode 0 (default): on, fp16 pairs (passes = 4 above; measured 2x closer to the fp64 oracle than 3xTF32 and 1.55x
+ *   faster at m=16384 n=65536 l=128); falls back to 3xTF32 when A holds non-finite entries, which cannot be scaled;
+ * 1: off (CUDA-core streams);  2: on, plain TF32;  3: on, TF32 main term + bf16 correction products (passes = 2);
+ * 4: on, fp16 pairs, an error instead of the fallback;  5: on, error-compensated 3xTF32 (passes = 3). */
 int glp_set_tensor_mode(glp_handle* h, int mode);
 /* hi = src rounded to TF32 (10 mantissa bits), lo = src - hi; transpose != 0 writes the transposes
  * (hi[j][i], lo[j][i]) -- the resident A^T of the transposed pass. */

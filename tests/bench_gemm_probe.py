@@ -6,9 +6,10 @@ import torch
 from glprox import _lib
 lib = _lib.load()
 st = torch.cuda.current_stream().cuda_stream
-def run(M, K, N, passes, chunk, reps=5):
+def run(M, K, N, passes, chunk, reps=5, alias=False):
     P = torch.randn((M, K), device="cuda"); Q = torch.randn((N, K), device="cuda")
-    Pl = torch.randn((M, K), device="cuda") * 1e-4 if passes >= 2 else P
+    # alias: P_lo = P_hi, same tensor work at half the DRAM bytes (the second load of a tile hits L2)
+    Pl = torch.randn((M, K), device="cuda") * 1e-4 if (passes >= 2 and not alias) else P
     Ql = torch.randn((N, K), device="cuda") * 1e-4 if passes >= 2 else Q
     D = torch.empty((N, M), device="cuda", dtype=torch.float64)
     def go():
@@ -20,10 +21,16 @@ def run(M, K, N, passes, chunk, reps=5):
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
     flops = 2.0 * M * K * N * passes
-    byts = M * K * 4.0 * (2 if passes == 3 else 1)
-    print("M=%d K=%d N=%d passes=%d chunk=%d: %.3f ms  %.1f TFLOP/s (tensor work)  %.0f GB/s (P stream)" % (M, K, N, passes, chunk, ms, flops / ms / 1e9, byts / ms / 1e6), flush=True)
+    byts = M * K * 4.0 * (2 if (passes == 3 and not alias) else 1)
+    print(("alias " if alias else "") + "M=%d K=%d N=%d passes=%d chunk=%d: %.3f ms  %.1f TFLOP/s (tensor work)  %.0f GB/s (P stream)" % (M, K, N, passes, chunk, ms, flops / ms / 1e9, byts / ms / 1e6), flush=True)
 if len(sys.argv) > 1 and sys.argv[1] == "one":   # the launch profiled with ncu (profiles/)
     run(16384, 65536, 128, 3, 8, reps=2)
+    sys.exit(0)
+if len(sys.argv) > 1 and sys.argv[1] == "alias":   # is the 3-pass product bound by the P stream from HBM?
+    for (M, K, N) in [(16384, 65536, 128), (65536, 16384, 128), (16384, 65536, 256)]:
+        for al in (False, True):
+            run(M, K, N, 3, 8, alias=al)
+        run(M, K, N, 1, 8)
     sys.exit(0)
 if len(sys.argv) > 1 and sys.argv[1] == "bf16":   # 3xTF32 vs TF32 + bf16 corrections
     for (M, K, N) in [(16384, 65536, 256), (65536, 16384, 128), (16384, 8192, 256), (8192, 16384, 128)]:

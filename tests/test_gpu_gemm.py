@@ -14,14 +14,14 @@ def _tf32_trunc(t):
     return (t.view(torch.int32) & -8192).view(torch.float32)
 
 
-def _run(M, K, N, passes, k_chunk=0, seed=0):
+def _run(M, K, N, passes, k_chunk=0, seed=0, p_scale=1.0, q_scale=1.0):
     import torch
     from glprox import _lib
     lib = _lib.load()
     g = torch.Generator(device="cuda").manual_seed(seed)
-    ldp = (K + 3) // 4 * 4
-    P = torch.randn((M, ldp), generator=g, device="cuda", dtype=torch.float32)[:, :K]
-    Q = torch.randn((N, ldp), generator=g, device="cuda", dtype=torch.float32)[:, :K]
+    ldp = (K + 7) // 8 * 8
+    P = (torch.randn((M, ldp), generator=g, device="cuda", dtype=torch.float32) * p_scale)[:, :K]
+    Q = (torch.randn((N, ldp), generator=g, device="cuda", dtype=torch.float32) * q_scale)[:, :K]
     Ph, Pl = torch.zeros((M, ldp), device="cuda"), torch.zeros((M, ldp), device="cuda")
     Qh, Ql = torch.zeros((N, ldp), device="cuda"), torch.zeros((N, ldp), device="cuda")
     st = torch.cuda.current_stream().cuda_stream
@@ -29,8 +29,11 @@ def _run(M, K, N, passes, k_chunk=0, seed=0):
     _lib.check(lib.glp_tf32_split(st, Q.data_ptr(), N, K, ldp, Qh.data_ptr(), Ql.data_ptr(), ldp, 0))
     ldd = (M + 7) // 8 * 8
     D = torch.full((N, ldd), float("nan"), device="cuda", dtype=torch.float64)
-    _lib.check(lib.glp_gemm_tf32(0, st, passes, M, K, N, Ph.data_ptr(), Pl.data_ptr(), ldp, Qh.data_ptr(), Ql.data_ptr(),
-                                 ldp, D.data_ptr(), ldd, k_chunk))
+    if passes == 4:   # fp16 pairs are made from the fp32 operands themselves
+        _lib.check(lib.glp_gemm_tf32(0, st, 4, M, K, N, P.data_ptr(), 0, ldp, Q.data_ptr(), 0, ldp, D.data_ptr(), ldd, k_chunk))
+    else:
+        _lib.check(lib.glp_gemm_tf32(0, st, passes, M, K, N, Ph.data_ptr(), Pl.data_ptr(), ldp, Qh.data_ptr(), Ql.data_ptr(),
+                                     ldp, D.data_ptr(), ldd, k_chunk))
     torch.cuda.synchronize()
     return P, Q, Ph, Pl, Qh, Ql, D[:, :M].t()
 
@@ -111,3 +114,40 @@ def test_transposing_split():
     torch.cuda.synchronize()
     assert torch.equal(hi[:, :193] + lo[:, :193], A.t())
     assert torch.equal(_tf32_trunc(hi), hi)
+
+
+@pytest.mark.parametrize("scales", [(1.0, 1.0), (1e-4, 3e5), (7e6, 1e-9)])
+@pytest.mark.parametrize("k_chunk", [4, -4])
+@pytest.mark.parametrize("shape", [(128, 64, 16), (128, 256, 64), (300, 4096, 256), (1000, 333, 200), (2048, 8192, 128),
+                                   (70, 40, 4)])
+def test_fp16_pairs_reach_fp32_class_accuracy(shape, k_chunk, scales):
+    """passes = 4: both operands as pairs of fp16 numbers of the power-of-two-scaled value (the same 11-bit
+    significands as TF32 hi/lo at half the bytes), three kind::f16 products, the scale undone in the epilogue.
+    Same bar as 3xTF32 with the fp32 accumulator flushed every 256 elements of K, whatever the operands' magnitude."""
+    M, K, N = shape
+    P, Q, Ph, Pl, Qh, Ql, D = _run(M, K, N, 4, k_chunk, p_scale=scales[0], q_scale=scales[1])
+    full = P.double() @ Q.double().t()
+    scale = P.double().abs() @ Q.double().abs().t() + 1e-300
+    err = ((D - full).abs() / scale).max().item()
+    assert err <= 5e-7, err
+
+
+def test_fp16_pairs_keep_normwise_accuracy_over_a_wide_dynamic_range():
+    """Entries 2^18 and more below the operand's maximum lose relative (not norm-wise) precision: the error stays
+    at the 2^-22 level relative to |P||Q|."""
+    import torch
+    from glprox import _lib
+    lib = _lib.load()
+    M, K, N = 256, 2048, 32
+    g = torch.Generator(device="cuda").manual_seed(5)
+    P = torch.randn((M, K), generator=g, device="cuda") * torch.exp(12.0 * torch.randn((M, K), generator=g, device="cuda"))
+    Q = torch.randn((N, K), generator=g, device="cuda") * torch.exp(12.0 * torch.randn((N, K), generator=g, device="cuda"))
+    D = torch.full((N, M), float("nan"), device="cuda", dtype=torch.float64)
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.check(lib.glp_gemm_tf32(0, st, 4, M, K, N, P.data_ptr(), 0, K, Q.data_ptr(), 0, K, D.data_ptr(), M, 4))
+    torch.cuda.synchronize()
+    full = P.double() @ Q.double().t()
+    Pa, Qa = P.double().abs(), Q.double().abs()
+    normwise = Qa.sum(dim=1)[:, None] * Pa.max() + Pa.sum(dim=1)[None, :] * Qa.max()      # [N][M]
+    assert torch.isfinite(D).all()
+    assert ((D - full.t()).abs() / normwise).max().item() <= 5e-7

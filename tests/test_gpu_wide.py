@@ -28,7 +28,8 @@ def test_wide_mode_matches_fp64_oracle(shape, algo):
     A, b, x0, mu, opts = _case(m, n, l, 7, 15)
     xr, kr, outr = orc.solve(algo, x0.astype(np.float64), A.astype(np.float64), b.astype(np.float64), mu, opts)
     ref_h = np.asarray(outr["f_hist"])
-    for mode, tol, tol_hist in (("3xtf32", 1e-5, 1e-5), ("tf32+bf16", 1e-5, 1e-5), ("tf32", 5e-2, 1e-1), ("off", 1e-5, 1e-5)):
+    for mode, tol, tol_hist in (("3xtf32", 1e-5, 1e-5), ("tf32+bf16", 1e-5, 1e-5), ("f16x2", 1e-5, 1e-5), ("tf32", 5e-2, 1e-1),
+                                ("off", 1e-5, 1e-5)):
         x, k, out = fn(x0, A, b, mu, dict(opts, tensor_cores=mode))
         assert k == kr == 45 and x.dtype == np.float32
         fh = np.asarray(out["f_hist"])
@@ -109,7 +110,7 @@ def _solve_with_env(monkeypatch, env, algo, A, b, x0, mu, opts):
 
 
 @pytest.mark.parametrize("algo", ["FProxGD", "ProxGD"])
-@pytest.mark.parametrize("mode", ["3xtf32", "tf32+bf16"])
+@pytest.mark.parametrize("mode", ["3xtf32", "tf32+bf16", "f16x2"])
 @pytest.mark.parametrize("shape", [(256, 1024, 16), (300, 1100, 24), (512, 2048, 128)])
 def test_wide_threshold_correction_equals_direct_product(monkeypatch, shape, algo, mode):
     """A.thr(x) = A.x - A.(x - thr(x)) (csrc/glp_thrfix.cuh) against the direct product over both operand halves.
