@@ -241,7 +241,8 @@ def run_ours(args):
         # wide multi-RHS mode: both products run on tcgen05 (3xTF32); the bounding roofline is the tensor pipe
         # tensor time in TF32-product units: 3xTF32 issues 3 TF32 products; tf32+bf16 one TF32 product and two
         # bf16 products at twice the rate (= 2 units); plain TF32 one
-        passes = {"tf32": 1.0, "tf32+bf16": 2.0, "f16x2": 1.5}.get(args.tensor_cores, 3.0)
+        tc_mode = "f16x2" if args.tensor_cores == "auto" else args.tensor_cores   # auto = fp16 pairs (finite A)
+        passes = {"tf32": 1.0, "tf32+bf16": 2.0, "f16x2": 1.5}.get(tc_mode, 3.0)
         n_it = max(int(prof.tpass_launches), 1)
         # operand columns on the tensor cores per iteration: l (A.xn) + l (A^T r); the product of the thresholded
         # iterate comes from A.xn by a sparse CUDA-core correction (csrc/glp_thrfix.cuh) unless switched off,
@@ -254,7 +255,7 @@ def run_ours(args):
         tpeak = float(peaks.get("bf16_tflops", 1590.0)) / 2.0
         # bytes of the resident operand per product: 8 per element (fp32 hi + fp32 lo, or fp32 hi + 2 bf16), 4 for
         # plain TF32 and for the fp16 pairs
-        stream_x = 1.0 if args.tensor_cores in ("tf32", "f16x2") else 2.0
+        stream_x = 1.0 if tc_mode in ("tf32", "f16x2") else 2.0
         stream_bytes = stream_x * prof.bytes_per_launch * (prof.fwd_launches + prof.tpass_launches)
         hbm_stream = stream_bytes / max(t_s, 1e-12) / 1e9
         # the binding roofline is the one with the larger minimum time for this work
@@ -275,9 +276,10 @@ def run_ours(args):
                                       "operand streams 4 bytes per element",
                              "tf32+bf16": "Ah.Xh on TF32 + (Ah.Xl + Al.Xh) on bf16 at twice the rate: 2 TF32-product "
                                           "units of tensor time per stream, counted as such"}.get(
-                                 args.tensor_cores, "3 compensated TF32 products per stream: Ah.Xh + Ah.Xl + Al.Xh, issued flops counted"),
+                                 tc_mode, "3 compensated TF32 products per stream: Ah.Xh + Ah.Xl + Al.Xh, issued flops counted"),
+                    "tensor_cores": tc_mode,
                     "tensor_operand_columns_per_iteration": op_cols,
-                    "forward_product": ("A.xn on tcgen05 (l columns) + sparse fp64 correction for A.thr(xn), both inside the "
+                    "forward_product": ("A.xn on tcgen05 (l columns) + sparse CUDA-core correction for A.thr(xn), both inside the "
                                         "fwd window" if thrfix else "A.[xn | thr(xn)] on tcgen05 (2l columns)"),
                     "kernels": {"glp_gemm_tf32_kernel<fwd>": {"launches": int(prof.fwd_launches), "avg_ms": prof.fwd_ms_sum / max(prof.fwd_launches, 1)},
                                 "glp_gemm_tf32_kernel<tpass>": {"launches": int(prof.tpass_launches), "avg_ms": prof.tpass_ms_sum / max(prof.tpass_launches, 1)}}}

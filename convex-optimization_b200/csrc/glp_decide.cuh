@@ -29,6 +29,7 @@ struct DecideArgs {
   double* state[2];           // [3][l][ldn]
   double* f_hist;
   double* f_hist_best;
+  unsigned* r_amax;           // nullable (fp16-pair wide mode): float bits of max|r|, zeroed before the launch
 };
 
 constexpr int DECIDE_THREADS = 256;
@@ -102,6 +103,7 @@ glp_decide_kernel(const DecideArgs a, const Geom g) {
   const double* Axt_old = a.AX[1 - nc] + lenm;
   T* r = static_cast<T*>(a.r);
   double gy = 0.0;
+  unsigned rmx = 0u;   // max|r| as float bits: the scale of the next transposed product's fp16 operand
   const int64_t stride = int64_t(gridDim.x) * DECIDE_THREADS;
   for (int64_t i = int64_t(blockIdx.x) * DECIDE_THREADS + tid; i < lenm; i += stride) {
     double base;
@@ -121,6 +123,12 @@ glp_decide_kernel(const DecideArgs a, const Geom g) {
     const double res = xsub(base, a.b[i]);
     r[i] = T(res);
     gy += res * res;
+    const unsigned u = __float_as_uint(fabsf(float(T(res))));
+    rmx = u > rmx ? u : rmx;
+  }
+  if (a.r_amax != nullptr) {
+    rmx = __reduce_max_sync(0xffffffffu, rmx);
+    if (lane == 0 && rmx != 0u) atomicMax(a.r_amax, rmx);
   }
   if (accel && s_act.reset_v) {
     const double* x = a.state[nc];

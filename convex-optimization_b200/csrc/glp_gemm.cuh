@@ -310,14 +310,40 @@ __global__ void glp_absmax_kernel(const float* __restrict__ src, int64_t rows, i
   mx = __reduce_max_sync(0xffffffffu, mx);
   if ((threadIdx.x & 31) == 0 && mx != 0u) atomicMax(out, mx);
 }
-// contiguous small operand (x or r) with the scale taken from its own max on the device; block 0 publishes
-// inv_scale_out = 1 / (s * s_other) for the product's epilogue.  gate as in glp_split_tf32_kernel.
-__global__ void glp_split_f16_kernel(const float* __restrict__ src, __half* __restrict__ o0, __half* __restrict__ o1,
-                                     int64_t total, const unsigned* amax_bits, float s_other,
-                                     const unsigned* other_amax_bits, double* inv_scale_out,
-                                     const int32_t* gate, int gate_cap) {
+// contiguous small operand (x or r) with the scale taken from its own max on the device: *amax_bits (float bits from
+// glp_absmax_kernel) or, when scal_partial is given, the max over slot 3 of the prox epilogue's per-block partials
+// (max|xn|, ncb blocks) -- every block reduces those few hundred values itself, which saves a pass over the operand.
+// Block 0 publishes inv_scale_out = 1 / (s * s_other) for the product's epilogue.  gate as in glp_split_tf32_kernel.
+__global__ void __launch_bounds__(256)
+glp_split_f16_kernel(const float* __restrict__ src, __half* __restrict__ o0, __half* __restrict__ o1,
+                     int64_t total, const unsigned* amax_bits, const double* scal_partial, int ncb, float s_other,
+                     const unsigned* other_amax_bits, double* inv_scale_out, const int32_t* gate, int gate_cap) {
+  __shared__ float s_mx[8];
   if (gate != nullptr && *gate <= gate_cap) return;
-  const float s = f16_scale_for(__uint_as_float(*amax_bits));
+  float mxf;
+  if (scal_partial != nullptr) {
+    float m = 0.0f;   // NaN-propagating max, as in the prox epilogue
+    for (int q = threadIdx.x; q < ncb; q += blockDim.x) {
+      const float v = float(__ldcg(&scal_partial[SCAL_STRIDE * q + 3]));
+      m = (m != m) ? m : ((v != v) ? v : fmaxf(m, v));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float v = __shfl_xor_sync(0xffffffffu, m, o);
+      m = (m != m) ? m : ((v != v) ? v : fmaxf(m, v));
+    }
+    if ((threadIdx.x & 31) == 0) s_mx[threadIdx.x >> 5] = m;
+    __syncthreads();
+    m = s_mx[0];
+    for (int w = 1; w < int(blockDim.x >> 5); ++w) {
+      const float v = s_mx[w];
+      m = (m != m) ? m : ((v != v) ? v : fmaxf(m, v));
+    }
+    mxf = m;
+  } else {
+    mxf = __uint_as_float(*amax_bits);
+  }
+  const float s = f16_scale_for(mxf);
   if (inv_scale_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
     const float so = other_amax_bits != nullptr ? f16_scale_for(__uint_as_float(*other_amax_bits)) : s_other;
     *inv_scale_out = 1.0 / (double(s) * double(so));

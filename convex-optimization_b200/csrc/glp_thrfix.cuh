@@ -8,7 +8,7 @@
 // entry in a thousand.  So here
 //     A.xnt = A.xn - A.E,        column c:  (A.E)(:, c) = sum over the entries (j, c) of E:  A(:, j) E_jc
 // The entries are listed per operand column in ascending row order by one block per column (fixed order ->
-// run-to-run identical bits) and applied by a CUDA-core kernel in fp64.  A(:, j) is read from the resident
+// run-to-run identical bits) and applied by a CUDA-core kernel (fp32 products and sums, subtracted from the fp64 product).  A(:, j) is read from the resident
 // transposed split (row j of At_hi + At_lo: coalesced over the output rows); |E| < thres makes the 2^-22 relative
 // gap between hi + lo and A irrelevant next to the rounding of the TF32 product itself.  Cost: entries x m x 8
 // bytes of L2/HBM traffic instead of a second product.
@@ -123,11 +123,14 @@ struct ThrFixArgs {
   const __half* At_f0;              // fp16-pair operand set: A^T s = f0 + f1 (then At_hi is nullptr)
   const __half* At_f1;
   float inv_s;                      // 1 / s
-  float pad2;
+  float thres;                      // the hard threshold: every |vals| is below it
+  const double* inv_x;              // fp16-pair set: 1 / (s s_x) of the current operand, max|xn| s_x in [2^14, 2^15)
   double* AX[2];                    // [2l][ldm]: column l + c := column c - sum_r At[rows_r][:] * vals_r
 };
 
-// grid (ceil(ldm / 128), l): block (ib, c) owns 128 output rows of column c
+// grid (ceil(ldm / 512), l): block (ib, c) owns 512 output rows of column c, 4 consecutive rows per thread
+// (8-byte loads from the fp16 arrays, 16-byte loads from the fp32 ones; ldm is a multiple of 64)
+constexpr int THRFIX_ROWS = 4;
 __global__ void __launch_bounds__(THRFIX_THREADS)
 glp_thr_fix_kernel(const ThrFixArgs a, const Geom g) {
   __shared__ int32_t s_j[THRFIX_THREADS];
@@ -137,38 +140,79 @@ glp_thr_fix_kernel(const ThrFixArgs a, const Geom g) {
   const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : 0;
   const int tid = threadIdx.x, c = blockIdx.y, l = g.l;
   const int R = a.col_count[c];
-  const int64_t i = int64_t(blockIdx.x) * THRFIX_THREADS + tid;
+  const int64_t i = (int64_t(blockIdx.x) * THRFIX_THREADS + tid) * THRFIX_ROWS;
   const bool live = i < g.ldm;
   const int32_t* rows = a.rows + int64_t(c) * a.cap;
   const float* vals = a.vals + int64_t(c) * a.cap;
-  double acc = 0.0;
+  // fp32 arithmetic: the correction is at most thres / max|xn| of the product, so its own 2^-24 rounding is far
+  // below the product's 2^-22; conversions to fp64 run at 1/8 of the FFMA rate and would dominate the kernel
+  float acc[THRFIX_ROWS] = {0.f, 0.f, 0.f, 0.f};
+  // fp16 pairs: f1 adds 2^-11 (relative) to terms that are at most thres / max|xn| of the product's own; it is read
+  // only when that ratio exceeds 2^-10, i.e. when leaving it out could reach the 2^-22 the product itself is good for
+  // (max|xn| >= 2^14 / s_x = 2^14 inv_x s).  Halves the traffic of the correction at the default thres.
+  const bool need_f1 = !(a.At_f0 != nullptr && a.inv_x != nullptr &&
+                         double(a.thres) * double(a.inv_s) <= 16.0 * __ldg(a.inv_x));
+  // 4 values of row j of A^T (times s for the fp16 pairs) starting at output row i; f0 + f1 and hi + lo are exact in fp32
+  auto at4 = [&](int64_t at, float (&v)[THRFIX_ROWS]) {
+    if (a.At_f0 != nullptr) {
+      const uint2 u0 = *reinterpret_cast<const uint2*>(a.At_f0 + at);
+      const float2 f00 = __half22float2(*reinterpret_cast<const __half2*>(&u0.x));
+      const float2 f01 = __half22float2(*reinterpret_cast<const __half2*>(&u0.y));
+      v[0] = f00.x; v[1] = f00.y; v[2] = f01.x; v[3] = f01.y;
+      if (need_f1) {
+        const uint2 u1 = *reinterpret_cast<const uint2*>(a.At_f1 + at);
+        const float2 f10 = __half22float2(*reinterpret_cast<const __half2*>(&u1.x));
+        const float2 f11 = __half22float2(*reinterpret_cast<const __half2*>(&u1.y));
+        v[0] += f10.x; v[1] += f10.y; v[2] += f11.x; v[3] += f11.y;
+      }
+      return;
+    }
+    const float4 h = *reinterpret_cast<const float4*>(a.At_hi + at);
+    v[0] = h.x; v[1] = h.y; v[2] = h.z; v[3] = h.w;
+    if (a.At_lo != nullptr) {
+      const float4 q = *reinterpret_cast<const float4*>(a.At_lo + at);
+      v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
+    } else if (a.At_lb != nullptr) {
+      const uint2 u = *reinterpret_cast<const uint2*>(a.At_lb + at);
+      const float2 q0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
+      const float2 q1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
+      v[0] += q0.x; v[1] += q0.y; v[2] += q1.x; v[3] += q1.y;
+    }
+  };
   for (int r0 = 0; r0 < R; r0 += THRFIX_THREADS) {
     const int nr = R - r0 < THRFIX_THREADS ? R - r0 : THRFIX_THREADS;
     __syncthreads();
     if (tid < nr) { s_j[tid] = rows[r0 + tid]; s_v[tid] = vals[r0 + tid]; }
     __syncthreads();
     if (!live) continue;
-    auto at_value = [&](int64_t at) {
-      if (a.At_f0 != nullptr)
-        return (double(__half2float(a.At_f0[at])) + double(__half2float(a.At_f1[at]))) * double(a.inv_s);
-      double v = double(a.At_hi[at]);
-      if (a.At_lo != nullptr) v += double(a.At_lo[at]);
-      else if (a.At_lb != nullptr) v += double(__bfloat162float(a.At_lb[at]));
-      return v;
-    };
     int r = 0;
-    for (; r + 4 <= nr; r += 4) {   // four independent row loads in flight
-      double av[4];
+    for (; r + 4 <= nr; r += 4) {   // four independent row segments in flight
+      float av[4][THRFIX_ROWS];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) av[q] = at_value(int64_t(s_j[r + q]) * g.ldm + i);
+      for (int q = 0; q < 4; ++q) at4(int64_t(s_j[r + q]) * g.ldm + i, av[q]);
 #pragma unroll
-      for (int q = 0; q < 4; ++q) acc = fma(av[q], double(s_v[r + q]), acc);
+      for (int q = 0; q < 4; ++q) {
+        const float d = s_v[r + q];
+#pragma unroll
+        for (int t = 0; t < THRFIX_ROWS; ++t) acc[t] = fmaf(av[q][t], d, acc[t]);
+      }
     }
-    for (; r < nr; ++r) acc = fma(at_value(int64_t(s_j[r]) * g.ldm + i), double(s_v[r]), acc);
+    for (; r < nr; ++r) {
+      float av[THRFIX_ROWS];
+      at4(int64_t(s_j[r]) * g.ldm + i, av);
+      const float d = s_v[r];
+#pragma unroll
+      for (int t = 0; t < THRFIX_ROWS; ++t) acc[t] = fmaf(av[t], d, acc[t]);
+    }
   }
   if (!live) return;
+  const double sc = a.At_f0 != nullptr ? double(a.inv_s) : 1.0;   // a power of two
   double* ax = a.AX[sel];
-  ax[int64_t(l + c) * g.ldm + i] = ax[int64_t(c) * g.ldm + i] - acc;
+  const double4 src = *reinterpret_cast<const double4*>(ax + int64_t(c) * g.ldm + i);
+  double4 dst;
+  dst.x = src.x - double(acc[0]) * sc; dst.y = src.y - double(acc[1]) * sc;
+  dst.z = src.z - double(acc[2]) * sc; dst.w = src.w - double(acc[3]) * sc;
+  *reinterpret_cast<double4*>(ax + int64_t(l + c) * g.ldm + i) = dst;
 }
 
 }  // namespace glp

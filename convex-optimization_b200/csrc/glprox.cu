@@ -750,18 +750,17 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
   const int64_t q2 = int64_t(g.l) * g.ldn;
   const GemmGate xnt_gate{h->thr_count + 1, 0};
   if (f16) {
-    // fp16 pairs of xn s_x, s_x from max|xn| on the device (max|xnt| <= max|xn|: one scale for both halves)
-    CU_TRY(cudaMemsetAsync(h->f16_amax, 0, sizeof(unsigned), h->stream));
+    // fp16 pairs of xn s_x; s_x from max|xn|, which the prox epilogue left per column block in scal_partial
+    // (max|xnt| <= max|xn|: one scale for both halves)
     const int sg = int(std::min<int64_t>((q2 + 1023) / 1024, int64_t(h->num_sms) * 16));
-    glp_absmax_kernel<<<sg, 256, 0, h->stream>>>(xop, g.l, g.ldn, g.ldn, h->f16_amax);
     if (h->thr_cap < 0) {
-      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop, h->xop_f0, h->xop_f1, 2 * q2, h->f16_amax, h->f16_sA, nullptr,
-                                                      h->f16_inv, nullptr, 0);
+      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop, h->xop_f0, h->xop_f1, 2 * q2, nullptr, h->scal_partial, g.ncb,
+                                                      h->f16_sA, nullptr, h->f16_inv, nullptr, 0);
     } else {
-      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop, h->xop_f0, h->xop_f1, q2, h->f16_amax, h->f16_sA, nullptr,
-                                                      h->f16_inv, nullptr, 0);
-      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop + q2, h->xop_f0 + q2, h->xop_f1 + q2, q2, h->f16_amax, h->f16_sA,
-                                                      nullptr, nullptr, xnt_gate.count, xnt_gate.cap);
+      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop, h->xop_f0, h->xop_f1, q2, nullptr, h->scal_partial, g.ncb,
+                                                      h->f16_sA, nullptr, h->f16_inv, nullptr, 0);
+      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop + q2, h->xop_f0 + q2, h->xop_f1 + q2, q2, nullptr, h->scal_partial,
+                                                      g.ncb, h->f16_sA, nullptr, nullptr, xnt_gate.count, xnt_gate.cap);
       h->n_launches++;
     }
     CU_TRY(cudaGetLastError());
@@ -812,9 +811,11 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
     if (f16) {
       fa.At_hi = nullptr; fa.At_lo = nullptr; fa.At_lb = nullptr;
       fa.At_f0 = h->At_f0; fa.At_f1 = h->At_f1; fa.inv_s = 1.0f / h->f16_sA;
+      fa.thres = float(h->sc.thres); fa.inv_x = h->f16_inv;
     }
     fa.AX[0] = h->AX[0]; fa.AX[1] = h->AX[1];
-    const dim3 fgrid(unsigned((g.ldm + THRFIX_THREADS - 1) / THRFIX_THREADS), unsigned(g.l));
+    const int64_t frows = int64_t(THRFIX_THREADS) * THRFIX_ROWS;
+    const dim3 fgrid(unsigned((g.ldm + frows - 1) / frows), unsigned(g.l));
     glp_thr_fix_kernel<<<fgrid, THRFIX_THREADS, 0, h->stream>>>(fa, g);
     CU_TRY(cudaGetLastError());
     h->n_launches += 2;
@@ -844,10 +845,9 @@ static int enqueue_wide_tpass(glp_handle* h, const Ctrl* ctrl) {
   const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes};
   if (wide_passes(h) == 4) {
     const int64_t tot = int64_t(g.l) * g.ldm;
-    CU_TRY(cudaMemsetAsync(h->f16_amax + 1, 0, sizeof(unsigned), h->stream));
+    // max|r| was left in f16_amax[1] by the decide kernel that wrote r
     const int sg = int(std::min<int64_t>((tot + 1023) / 1024, int64_t(h->num_sms) * 16));
-    glp_absmax_kernel<<<sg, 256, 0, h->stream>>>(r, g.l, g.ldm, g.ldm, h->f16_amax + 1);
-    glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(r, h->r_f0, h->r_f1, tot, h->f16_amax + 1, h->f16_sA, nullptr,
+    glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(r, h->r_f0, h->r_f1, tot, h->f16_amax + 1, nullptr, 0, h->f16_sA, nullptr,
                                                     h->f16_inv + 1, nullptr, 0);
     CU_TRY(cudaGetLastError());
     h->n_launches++;
@@ -1131,6 +1131,10 @@ static int phase_decide(glp_handle* h) {
   d.AX[0] = h->AX[0]; d.AX[1] = h->AX[1]; d.Av = h->Av; d.b = h->b; d.r = h->r;
   d.state[0] = h->state[0]; d.state[1] = h->state[1];
   d.f_hist = h->f_hist; d.f_hist_best = h->f_hist_best;
+  if (wide_active(h) && wide_passes(h) == 4) {
+    CU_TRY(cudaMemsetAsync(h->f16_amax + 1, 0, sizeof(unsigned), h->stream));
+    d.r_amax = h->f16_amax + 1;
+  }
   CU_TRY(launch_decide(h, d));
   h->cur_ctrl = cout;
   return GLP_OK;
@@ -2030,8 +2034,8 @@ extern "C" int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, in
     const int g1 = int(std::min<size_t>((pe + 255) / 256, 148 * 16)), g2 = int(std::min<size_t>((qe + 255) / 256, 148 * 16));
     glp_absmax_kernel<<<g1, 256, 0, st>>>(Pf, M, K, ldp, amax);
     glp_absmax_kernel<<<g2, 256, 0, st>>>(Qf, N, K, ldq, amax + 1);
-    glp_split_f16_kernel<<<g1, 256, 0, st>>>(Pf, p0, p1, int64_t(pe), amax, 1.0f, nullptr, nullptr, nullptr, 0);
-    glp_split_f16_kernel<<<g2, 256, 0, st>>>(Qf, q0, q1, int64_t(qe), amax + 1, 1.0f, amax, inv, nullptr, 0);
+    glp_split_f16_kernel<<<g1, 256, 0, st>>>(Pf, p0, p1, int64_t(pe), amax, nullptr, 0, 1.0f, nullptr, nullptr, nullptr, 0);
+    glp_split_f16_kernel<<<g2, 256, 0, st>>>(Qf, q0, q1, int64_t(qe), amax + 1, nullptr, 0, 1.0f, amax, inv, nullptr, 0);
     CU_TRY(cudaGetLastError());
     rc = gemm_enqueue(st, sms, 4, M, K, N, reinterpret_cast<const float*>(p0), reinterpret_cast<const float*>(p1), ldp,
                       reinterpret_cast<const float*>(q0), reinterpret_cast<const float*>(q1), ldq, D_dev, ldd, kc, nullptr,

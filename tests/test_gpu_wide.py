@@ -88,7 +88,7 @@ def test_wide_mode_sharded_matches_single_handle_and_oracle(G, shape, algo):
         assert all(r["iters"] == k and r["fval"] == pr[0]["fval"] and r["n_fwd"] == pr[0]["n_fwd"] for r in pr)
         # 2 product launches (one gated off on the device) + entry lists / correction + 3 exchange kernels per
         # forward instead of 2l/4 CUDA-core streams
-        assert out["glprox"]["n_launches"] < 45 * 32
+        assert out["glprox"]["n_launches"] < 45 * 40
     single.close()
     for p in probs:
         p.close()
