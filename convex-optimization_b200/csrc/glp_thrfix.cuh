@@ -128,55 +128,69 @@ struct ThrFixArgs {
   double* AX[2];                    // [2l][ldm]: column l + c := column c - sum_r At[rows_r][:] * vals_r
 };
 
-// grid (ceil(ldm / 512), l): block (ib, c) owns 512 output rows of column c, 4 consecutive rows per thread
-// (8-byte loads from the fp16 arrays, 16-byte loads from the fp32 ones; ldm is a multiple of 64)
-constexpr int THRFIX_ROWS = 4;
+// grid (ceil(ldm / (128 ROWS)), l): block (ib, c) owns 128 ROWS output rows of column c, ROWS consecutive rows per
+// thread.  The kernel is a gather of row segments of A^T from HBM (the entries of different columns sit in different
+// rows), so what matters is bytes in flight: ROWS = 8 with 8 entries unrolled keeps 8 x 16 bytes (fp16) or 8 x 32
+// bytes (fp32) of independent loads per thread outstanding.  Per output element the sum still runs over the entries
+// in ascending row order with one fmaf each, so the result does not depend on ROWS or the unroll.
+constexpr int THRFIX_ROWS = 8;
+constexpr int THRFIX_UNROLL = 8;
 __global__ void __launch_bounds__(THRFIX_THREADS)
 glp_thr_fix_kernel(const ThrFixArgs a, const Geom g) {
+  constexpr int RW = THRFIX_ROWS;
   __shared__ int32_t s_j[THRFIX_THREADS];
   __shared__ float s_v[THRFIX_THREADS];
   if (a.ctrl != nullptr && a.ctrl->done) return;
   if (a.count[1] > 0) return;
-  const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : 0;
+  const bool sel1 = a.ctrl != nullptr ? a.ctrl->cur == 0 : false;
   const int tid = threadIdx.x, c = blockIdx.y, l = g.l;
   const int R = a.col_count[c];
-  const int64_t i = (int64_t(blockIdx.x) * THRFIX_THREADS + tid) * THRFIX_ROWS;
-  const bool live = i < g.ldm;
+  const int64_t i = (int64_t(blockIdx.x) * THRFIX_THREADS + tid) * RW;
+  const bool live = i < g.ldm;   // ldm is a multiple of 64: a live thread owns RW in-range rows
   const int32_t* rows = a.rows + int64_t(c) * a.cap;
   const float* vals = a.vals + int64_t(c) * a.cap;
   // fp32 arithmetic: the correction is at most thres / max|xn| of the product, so its own 2^-24 rounding is far
   // below the product's 2^-22; conversions to fp64 run at 1/8 of the FFMA rate and would dominate the kernel
-  float acc[THRFIX_ROWS] = {0.f, 0.f, 0.f, 0.f};
+  float acc[RW];
+#pragma unroll
+  for (int t = 0; t < RW; ++t) acc[t] = 0.f;
   // fp16 pairs: f1 adds 2^-11 (relative) to terms that are at most thres / max|xn| of the product's own; it is read
   // only when that ratio exceeds 2^-10, i.e. when leaving it out could reach the 2^-22 the product itself is good for
   // (max|xn| >= 2^14 / s_x = 2^14 inv_x s).  Halves the traffic of the correction at the default thres.
-  const bool need_f1 = !(a.At_f0 != nullptr && a.inv_x != nullptr &&
-                         double(a.thres) * double(a.inv_s) <= 16.0 * __ldg(a.inv_x));
-  // 4 values of row j of A^T (times s for the fp16 pairs) starting at output row i; f0 + f1 and hi + lo are exact in fp32
-  auto at4 = [&](int64_t at, float (&v)[THRFIX_ROWS]) {
-    if (a.At_f0 != nullptr) {
-      const uint2 u0 = *reinterpret_cast<const uint2*>(a.At_f0 + at);
-      const float2 f00 = __half22float2(*reinterpret_cast<const __half2*>(&u0.x));
-      const float2 f01 = __half22float2(*reinterpret_cast<const __half2*>(&u0.y));
-      v[0] = f00.x; v[1] = f00.y; v[2] = f01.x; v[3] = f01.y;
-      if (need_f1) {
-        const uint2 u1 = *reinterpret_cast<const uint2*>(a.At_f1 + at);
-        const float2 f10 = __half22float2(*reinterpret_cast<const __half2*>(&u1.x));
-        const float2 f11 = __half22float2(*reinterpret_cast<const __half2*>(&u1.y));
-        v[0] += f10.x; v[1] += f10.y; v[2] += f11.x; v[3] += f11.y;
-      }
+  const bool f16 = a.At_f0 != nullptr;
+  const bool need_f1 = !(f16 && a.inv_x != nullptr && double(a.thres) * double(a.inv_s) <= 16.0 * __ldg(a.inv_x));
+  auto h8 = [](const uint4& u, float (&v)[RW], bool add) {   // 8 fp16 values -> fp32 (set or add: both exact)
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[q]));
+      if (add) { v[2 * q] += f.x; v[2 * q + 1] += f.y; } else { v[2 * q] = f.x; v[2 * q + 1] = f.y; }
+    }
+  };
+  auto b8 = [](const uint4& u, float (&v)[RW]) {             // + 8 bf16 values
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[q]));
+      v[2 * q] += f.x; v[2 * q + 1] += f.y;
+    }
+  };
+  // RW values of row j of A^T (times s for the fp16 pairs) starting at output row i; f0 + f1 and hi + lo are exact in fp32
+  auto at8 = [&](int64_t at, float (&v)[RW]) {
+    if (f16) {
+      h8(__ldg(reinterpret_cast<const uint4*>(a.At_f0 + at)), v, false);
+      if (need_f1) h8(__ldg(reinterpret_cast<const uint4*>(a.At_f1 + at)), v, true);
       return;
     }
-    const float4 h = *reinterpret_cast<const float4*>(a.At_hi + at);
-    v[0] = h.x; v[1] = h.y; v[2] = h.z; v[3] = h.w;
+    const float4 h0 = __ldg(reinterpret_cast<const float4*>(a.At_hi + at));
+    const float4 h1 = __ldg(reinterpret_cast<const float4*>(a.At_hi + at + 4));
+    v[0] = h0.x; v[1] = h0.y; v[2] = h0.z; v[3] = h0.w; v[4] = h1.x; v[5] = h1.y; v[6] = h1.z; v[7] = h1.w;
     if (a.At_lo != nullptr) {
-      const float4 q = *reinterpret_cast<const float4*>(a.At_lo + at);
-      v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
+      const float4 q0 = __ldg(reinterpret_cast<const float4*>(a.At_lo + at));
+      const float4 q1 = __ldg(reinterpret_cast<const float4*>(a.At_lo + at + 4));
+      v[0] += q0.x; v[1] += q0.y; v[2] += q0.z; v[3] += q0.w; v[4] += q1.x; v[5] += q1.y; v[6] += q1.z; v[7] += q1.w;
     } else if (a.At_lb != nullptr) {
-      const uint2 u = *reinterpret_cast<const uint2*>(a.At_lb + at);
-      const float2 q0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
-      const float2 q1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
-      v[0] += q0.x; v[1] += q0.y; v[2] += q1.x; v[3] += q1.y;
+      b8(__ldg(reinterpret_cast<const uint4*>(a.At_lb + at)), v);
     }
   };
   for (int r0 = 0; r0 < R; r0 += THRFIX_THREADS) {
@@ -186,33 +200,38 @@ glp_thr_fix_kernel(const ThrFixArgs a, const Geom g) {
     __syncthreads();
     if (!live) continue;
     int r = 0;
-    for (; r + 4 <= nr; r += 4) {   // four independent row segments in flight
-      float av[4][THRFIX_ROWS];
+    for (; r + THRFIX_UNROLL <= nr; r += THRFIX_UNROLL) {   // independent row segments in flight
+      float av[THRFIX_UNROLL][RW];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) at4(int64_t(s_j[r + q]) * g.ldm + i, av[q]);
+      for (int q = 0; q < THRFIX_UNROLL; ++q) at8(int64_t(s_j[r + q]) * g.ldm + i, av[q]);
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
+      for (int q = 0; q < THRFIX_UNROLL; ++q) {
         const float d = s_v[r + q];
 #pragma unroll
-        for (int t = 0; t < THRFIX_ROWS; ++t) acc[t] = fmaf(av[q][t], d, acc[t]);
+        for (int t = 0; t < RW; ++t) acc[t] = fmaf(av[q][t], d, acc[t]);
       }
     }
     for (; r < nr; ++r) {
-      float av[THRFIX_ROWS];
-      at4(int64_t(s_j[r]) * g.ldm + i, av);
+      float av[RW];
+      at8(int64_t(s_j[r]) * g.ldm + i, av);
       const float d = s_v[r];
 #pragma unroll
-      for (int t = 0; t < THRFIX_ROWS; ++t) acc[t] = fmaf(av[t], d, acc[t]);
+      for (int t = 0; t < RW; ++t) acc[t] = fmaf(av[t], d, acc[t]);
     }
   }
   if (!live) return;
-  const double sc = a.At_f0 != nullptr ? double(a.inv_s) : 1.0;   // a power of two
-  double* ax = a.AX[sel];
-  const double4 src = *reinterpret_cast<const double4*>(ax + int64_t(c) * g.ldm + i);
-  double4 dst;
-  dst.x = src.x - double(acc[0]) * sc; dst.y = src.y - double(acc[1]) * sc;
-  dst.z = src.z - double(acc[2]) * sc; dst.w = src.w - double(acc[3]) * sc;
-  *reinterpret_cast<double4*>(ax + int64_t(l + c) * g.ldm + i) = dst;
+  const double sc = f16 ? double(a.inv_s) : 1.0;   // a power of two
+  double* ax = sel1 ? a.AX[1] : a.AX[0];
+  const double* src = ax + int64_t(c) * g.ldm + i;
+  double* dst = ax + int64_t(l + c) * g.ldm + i;
+#pragma unroll
+  for (int t = 0; t < RW; t += 2) {
+    const double2 s2 = *reinterpret_cast<const double2*>(src + t);
+    double2 d2;
+    d2.x = s2.x - double(acc[t]) * sc;
+    d2.y = s2.y - double(acc[t + 1]) * sc;
+    *reinterpret_cast<double2*>(dst + t) = d2;
+  }
 }
 
 }  // namespace glp
