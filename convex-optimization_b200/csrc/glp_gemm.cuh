@@ -75,6 +75,18 @@ template <int NT, int PASSES> constexpr int gemm_smem_bytes() {
   return gemm_stages<NT, PASSES>() * gemm_stage_bytes<NT, PASSES>() + 1024 /*align*/ + 256 /*barriers*/;
 }
 
+// Split operand rings of the fp16-pair product (RINGS): the P tiles stream from HBM, the Q tiles are re-read from
+// L2 by every M tile.  With one ring of {P | Q} stages half of the shared memory holds Q, and only 2 x 32 KB of P
+// per SM are in flight ahead of the tensor core -- too little to cover the loaded HBM latency (ncu: 5.0 TB/s at 60 %
+// tensor activity, profiles/r01_ncu_full_gemm_f16x2_fwd_tpass_C5.csv).  Two rings with their own depths put 224 KB
+// to work: a deeper one for P (HBM latency), a shallower one for Q (L2 latency).
+template <int NT> constexpr int gemm_ring_p_stages() { return NT == 128 ? 4 : (NT == 64 ? 5 : 6); }
+template <int NT> constexpr int gemm_ring_q_stages() { return NT == 128 ? 3 : 4; }
+template <int NT> constexpr int gemm_ring_smem_bytes() {
+  return gemm_ring_p_stages<NT>() * 2 * GEMM_BM * 128 + gemm_ring_q_stages<NT>() * 2 * NT * 128 + 1024 /*align*/ + 256 /*barriers*/;
+}
+constexpr int GEMM_RING_THREADS = GEMM_THREADS + 32;   // + the Q producer warp
+
 // ---- tcgen05 wrappers (hand-written PTX) -----------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -425,8 +437,8 @@ __global__ void glp_sum_splits_kernel(const double* __restrict__ part, int split
   }
 }
 
-template <int NT, int PASSES>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+template <int NT, int PASSES, bool RINGS = false>
+__global__ void __launch_bounds__(RINGS ? GEMM_RING_THREADS : GEMM_THREADS, 1)
 glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_constant__ CUtensorMap tmPl,
                      const __grid_constant__ CUtensorMap tmQh, const __grid_constant__ CUtensorMap tmQl,
                      const __grid_constant__ CUtensorMap tmPx, const __grid_constant__ CUtensorMap tmQx,
@@ -450,12 +462,20 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
   constexpr uint32_t TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
   constexpr int HC = NT / 2;  // columns per epilogue thread
   static_assert(NT == 32 || NT == 64 || NT == 128, "NT");
+  static_assert(!RINGS || PASSES == 4, "split rings: fp16-pair product only");
+  // RINGS: P ring [SP] of {P0 | P1} (barriers full / empty, freed by this CTA's MMAs alone: P is not shared),
+  //        Q ring [SQ] of {Q0 | Q1} (barriers fullq / emptyq, freed in every CTA of the cluster); launched with cg = 1
+  constexpr int SP = RINGS ? gemm_ring_p_stages<NT>() : STAGES, SQ = RINGS ? gemm_ring_q_stages<NT>() : 0;
+  constexpr int RING_BYTES = RINGS ? SP * 2 * P_BYTES + SQ * 2 * Q_BYTES : STAGES * STAGE_BYTES;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
-  uint64_t* empty = full + STAGES;
-  uint64_t* tfull = empty + STAGES;   // [2] chunk accumulator ready
+  uint8_t* smem_q = smem + SP * 2 * P_BYTES;   // RINGS only
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + RING_BYTES);
+  uint64_t* empty = full + SP;
+  uint64_t* fullq = empty + SP;       // [SQ]
+  uint64_t* emptyq = fullq + SQ;      // [SQ]
+  uint64_t* tfull = emptyq + SQ;      // [2] chunk accumulator ready
   uint64_t* tempty = tfull + 2;       // [2] chunk accumulator drained
   uint64_t* cempty = tempty + 2;      // [1] correction accumulator drained
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(cempty + 1);
@@ -486,7 +506,8 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
   const uint16_t mask_all = uint16_t((1u << CS) - 1u);
 
   if (tid == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], uint32_t(CS)); }
+    for (int s = 0; s < SP; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], RINGS ? 1u : uint32_t(CS)); }
+    for (int s = 0; s < SQ; ++s) { mbar_init(&fullq[s], 1); mbar_init(&emptyq[s], uint32_t(CS)); }
     for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], GEMM_EPI_WARPS); }
     mbar_init(cempty, GEMM_EPI_WARPS);
     fence_mbar_init();
@@ -519,6 +540,17 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
       for (int64_t w = cl_id; w < items; w += ncl) {
         const GemmItem it = gemm_item(w, tblocks, gblocks, S, nchunks, kc, nkb);
         const int32_t r0 = int32_t((it.tile * CT + dt) * GEMM_BM), q0 = int32_t((it.group * CG + dg) * NT);
+        if (RINGS) {   // P only: my own tile, my own slot (the Q producer is warp 10)
+          for (int64_t kb = it.kb0; kb < it.kb1; ++kb) {
+            mbar_wait(&empty[stage], phase ^ 1u, a.fault);
+            mbar_arrive_expect_tx(&full[stage], 2 * P_BYTES);
+            uint8_t* s = smem + stage * 2 * P_BYTES;
+            const int32_t k0 = int32_t(kb * BK);
+            tma_load_2d(s, &tmPh, &full[stage], k0, r0, pol_stream);
+            tma_load_2d(s + P_BYTES, &tmPl, &full[stage], k0, r0, pol_stream);
+            if (++stage == SP) { stage = 0; phase ^= 1u; }
+          }
+        } else
         for (int64_t kb = it.kb0; kb < it.kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1u, a.fault);   // the slot is free in EVERY CTA I multicast into
           mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
@@ -541,11 +573,38 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
         }
       }
     }
+  } else if (RINGS && warp == GEMM_THREADS / 32) {
+    // ------------------------------------------------------------------ TMA producer of the Q ring (RINGS)
+    if (lane == 0) {
+      prefetch_tensormap(&tmQh); prefetch_tensormap(&tmQl);
+      const uint64_t pol_keep = policy_evict_normal();
+      int stage = 0; uint32_t phase = 0;
+      const int qr = dt * (NT / CT);   // my share of the rows of the Q tile the cluster's M tiles have in common
+      for (int64_t w = cl_id; w < items; w += ncl) {
+        const GemmItem it = gemm_item(w, tblocks, gblocks, S, nchunks, kc, nkb);
+        const int32_t q0 = int32_t(it.group * NT);
+        for (int64_t kb = it.kb0; kb < it.kb1; ++kb) {
+          mbar_wait(&emptyq[stage], phase ^ 1u, a.fault);   // the slot is free in EVERY CTA I multicast into
+          mbar_arrive_expect_tx(&fullq[stage], 2 * Q_BYTES);
+          uint8_t* s = smem_q + stage * 2 * Q_BYTES;
+          const int32_t k0 = int32_t(kb * BK);
+          if (CT > 1) {
+            tma_load_2d_mc(s + qr * 128, &tmQh, &fullq[stage], k0, q0 + qr, mask_q, pol_keep);
+            tma_load_2d_mc(s + Q_BYTES + qr * 128, &tmQl, &fullq[stage], k0, q0 + qr, mask_q, pol_keep);
+          } else {
+            tma_load_2d(s, &tmQh, &fullq[stage], k0, q0, pol_keep);
+            tma_load_2d(s + Q_BYTES, &tmQl, &fullq[stage], k0, q0, pol_keep);
+          }
+          if (++stage == SQ) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (one thread)
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_tf32<NT>();
       int stage = 0; uint32_t phase = 0;
+      int qstage = 0; uint32_t qphase = 0;   // RINGS
       int acc = 0; uint32_t acc_phase = 0, c_phase = 0;
       const uint32_t c_tmem = tmem_base + uint32_t(2 * NT);
       for (int64_t w = cl_id; w < items; w += ncl) {
@@ -563,14 +622,16 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
           uint32_t accumulate = 0;
           for (int64_t kb = ch * kc; kb < kb1; ++kb) {
             mbar_wait(&full[stage], phase, a.fault);
+            if (RINGS) mbar_wait(&fullq[qstage], qphase, a.fault);
             tc_fence_after();
-            const uint32_t sbase = smem_u32(smem + stage * STAGE_BYTES);
-            const uint64_t dPh = umma_desc_k_sw128(sbase), dQh = umma_desc_k_sw128(sbase + P_BYTES);
+            const uint32_t sbase = smem_u32(smem + stage * (RINGS ? 2 * P_BYTES : STAGE_BYTES));
+            const uint32_t qbase = RINGS ? smem_u32(smem_q + qstage * 2 * Q_BYTES) : sbase + P_BYTES;
+            const uint64_t dPh = umma_desc_k_sw128(sbase), dQh = umma_desc_k_sw128(qbase);
             if (F16X2) {
               // 4 instructions of K = 16 fp16 (32 bytes) per 128-byte row, like the 4 x 8 fp32 of the TF32 tile
               constexpr uint32_t idesc_h = umma_idesc_f16<NT>();
-              const uint64_t dPl = umma_desc_k_sw128(sbase + P_BYTES + Q_BYTES);
-              const uint64_t dQl = umma_desc_k_sw128(sbase + 2 * P_BYTES + Q_BYTES);
+              const uint64_t dPl = umma_desc_k_sw128(RINGS ? sbase + P_BYTES : sbase + P_BYTES + Q_BYTES);
+              const uint64_t dQl = umma_desc_k_sw128(RINGS ? qbase + Q_BYTES : sbase + 2 * P_BYTES + Q_BYTES);
 #pragma unroll
               for (int k4 = 0; k4 < 4; ++k4) {
                 umma_bf16(d_tmem, dPh + uint64_t(2 * k4), dQh + uint64_t(2 * k4), idesc_h, accumulate);
@@ -613,16 +674,21 @@ glp_gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmPh, const __grid_cons
             }
             // frees the smem stage when these MMAs have read it -- in every CTA of the cluster, whose producers
             // multicast into this slot
-            if (CS > 1) umma_commit_mc(&empty[stage], mask_all);
+            if (RINGS) {
+              umma_commit(&empty[stage]);                                   // my P slot: mine alone
+              if (CS > 1) umma_commit_mc(&emptyq[qstage], mask_all);        // the Q slot: the whole cluster writes it
+              else umma_commit(&emptyq[qstage]);
+              if (++qstage == SQ) { qstage = 0; qphase ^= 1u; }
+            } else if (CS > 1) umma_commit_mc(&empty[stage], mask_all);
             else umma_commit(&empty[stage]);
-            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+            if (++stage == SP) { stage = 0; phase ^= 1u; }
           }
           umma_commit(&tfull[acc]);      // chunk accumulator (and, after the last chunk, the corrections) complete
           if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
         }
       }
     }
-  } else {
+  } else if (warp < GEMM_THREADS / 32) {
     // ------------------------------------------------------------------ epilogue (8 warps)
     // warp -> (TMEM lane quarter it may read, half of the NT columns); fp64 accumulators live in registers
     // across the K chunks of a tile, so the tensor core's fp32 accumulation never spans more than one chunk

@@ -1848,17 +1848,17 @@ static int make_map_bf16_k64(CUtensorMap* map, const void* base, uint64_t inner,
   return GLP_OK;
 }
 
-template <int NT, int PASSES>
+template <int NT, int PASSES, bool RINGS = false>
 static cudaError_t launch_gemm_t(cudaStream_t st, int num_sms, int64_t cluster_items, const CUtensorMap& ph,
                                  const CUtensorMap& pl, const CUtensorMap& qh, const CUtensorMap& ql,
                                  const CUtensorMap& px, const CUtensorMap& qx, const GemmArgs& a) {
-  auto kfn = glp_gemm_tf32_kernel<NT, PASSES>;
-  constexpr int smem = gemm_smem_bytes<NT, PASSES>();
+  auto kfn = glp_gemm_tf32_kernel<NT, PASSES, RINGS>;
+  constexpr int smem = RINGS ? gemm_ring_smem_bytes<NT>() : gemm_smem_bytes<NT, PASSES>();
   cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   const int cs = std::max(1, a.ct) * std::max(1, a.cg);
   cudaLaunchConfig_t cfg = {};
-  cfg.blockDim = dim3(GEMM_THREADS, 1, 1);
+  cfg.blockDim = dim3(RINGS ? GEMM_RING_THREADS : GEMM_THREADS, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -1972,10 +1972,22 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   a.gate = gate.count; a.gate_cap = gate.cap;
   a.scale = scale;
   const int64_t items = ((tiles + ct - 1) / ct) * ((groups + cg - 1) / cg) * S;   // cluster items
+  // fp16-pair product with one column group (P not shared inside the cluster): separate P / Q operand rings
+  // (glp_gemm.cuh, RINGS) when GLPROX_GEMM_RINGS=1.  Off by default: measured at C5 on one B200 in the same run
+  // (profiles/r01_ab_gemm_rings_c5.log) 372.8 it/s with the rings (fwd / tpass windows 1.174 / 1.023 ms) against
+  // 389.1 it/s with the single ring (1.116 / 0.966 ms), identical objective bits and all GPU tests green with
+  // either -- more P bytes in flight do not help, the kernel is not HBM-latency-bound.
+  static const bool rings_on = [] { const char* e = getenv("GLPROX_GEMM_RINGS"); return e != nullptr && atoi(e) != 0; }();
+  const bool rings = passes == 4 && cg == 1 && rings_on;
   cudaError_t e;
 #define GLP_GEMM_LAUNCH(NTV, PV) launch_gemm_t<NTV, PV>(st, num_sms, items, mph, mpl, mqh, mql, mpx, mqx, a)
   if (passes == 1) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 1) : NT == 64 ? GLP_GEMM_LAUNCH(64, 1) : GLP_GEMM_LAUNCH(128, 1);
   else if (passes == 2) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 2) : NT == 64 ? GLP_GEMM_LAUNCH(64, 2) : GLP_GEMM_LAUNCH(128, 2);
+  else if (passes == 4 && rings) {
+#define GLP_GEMM_LAUNCH_R(NTV) launch_gemm_t<NTV, 4, true>(st, num_sms, items, mph, mpl, mqh, mql, mpx, mqx, a)
+    e = NT == 32 ? GLP_GEMM_LAUNCH_R(32) : NT == 64 ? GLP_GEMM_LAUNCH_R(64) : GLP_GEMM_LAUNCH_R(128);
+#undef GLP_GEMM_LAUNCH_R
+  }
   else if (passes == 4) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 4) : NT == 64 ? GLP_GEMM_LAUNCH(64, 4) : GLP_GEMM_LAUNCH(128, 4);
   else e = NT == 32 ? GLP_GEMM_LAUNCH(32, 3) : NT == 64 ? GLP_GEMM_LAUNCH(64, 3) : GLP_GEMM_LAUNCH(128, 3);
 #undef GLP_GEMM_LAUNCH
