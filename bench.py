@@ -399,9 +399,10 @@ def run_homework(args):
     final objective (drop-in defaults) and (ii) the true optimum f* with opts={'thres': 1e-8}."""
     import torch
     from glprox import GroupLassoProblem
-    from oracle import glprox_oracle as orc
+    from glprox.dataset import gen_data
+    from oracle import glprox_oracle as orc   # CPU leg only: the port timed beside the GPU solves
     F_STAR = 6.1037724766016532e-01   # high-accuracy optimum (SURVEY.md 8(c)); Mosek/Gurobi publish 6.10377E-01
-    A, b, x0, u, mu = orc.gen_data(97006855, 256, 512, 2)
+    _, _, _, mu, A, b, u, x0 = gen_data(97006855, 512, 256, 2)
     prob = GroupLassoProblem(torch.from_numpy(A).cuda(), torch.from_numpy(b).cuda())
     x0d = torch.from_numpy(x0).cuda()
     res = {"workload": "Test_group_lasso fixture m=256 n=512 l=2 mu=1e-2 fp64, default opts",
