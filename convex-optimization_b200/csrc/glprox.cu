@@ -147,8 +147,8 @@ struct glp_handle {
   int gather_grid = 0;
   const Ctrl* cur_ctrl = nullptr;  // control block the launches of the current slot read
   int backend_used = GLP_BACKEND_STREAM;
-  // wide multi-RHS mode (K5, glp_gemm.cuh): resident TF32 hi/lo splits of A and A^T
-  int tensor_mode = 0;             // 0 auto (3xTF32 when eligible), 1 off, 2 plain TF32
+  // wide multi-RHS mode (K5, glp_gemm.cuh): resident tensor-core operand sets of A and A^T
+  int tensor_mode = 0;             // glp_set_tensor_mode: 0 auto (fp16 pairs), 1 off, 2 TF32, 3 TF32 + bf16, 4 fp16 pairs, 5 3xTF32
   float *A_hi = nullptr, *A_lo = nullptr, *At_hi = nullptr, *At_lo = nullptr;
   float *xop_lo = nullptr, *r_lo = nullptr;
   double* cnt_g = nullptr;
@@ -591,9 +591,11 @@ static int alloc_zero(Q** p, size_t bytes, cudaStream_t st) {
   return GLP_OK;
 }
 
-// One-time set-up per operand set: A = A_hi + A_lo and A^T = At_hi + At_lo resident in HBM (fp32 hi always;
-// the lo parts as fp32 for the 3xTF32 mode or hi/lo as bf16 for the TF32 + bf16-corrections mode: 4 x |A|
-// either way, "memory laid out for 180 GB"), plus the matching halves of the two small operands.
+// One-time set-up per operand set, resident in HBM afterwards ("memory laid out for 180 GB"), plus the matching
+// halves of the two small operands:
+//   fp16 pairs (default):  A s = A_f0 + A_f1 and A^T s = At_f0 + At_f1 in fp16, s from max|A|: 2 x |A| in all
+//   3xTF32:                A = A_hi + A_lo and A^T = At_hi + At_lo in fp32: 4 x |A|
+//   TF32 + bf16:           fp32 hi plus bf16 copies of hi and lo: 4 x |A|
 static int ensure_wide(glp_handle* h) {
   const Geom& g = h->g;
   const size_t a_el = size_t(g.m) * g.ldn, at_el = size_t(g.n) * g.ldm;
