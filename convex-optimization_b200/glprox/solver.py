@@ -39,8 +39,16 @@ ADMM_DUAL_DEFAULT_OPTS = {"maxit": 100, "thres": 1e-3, "tau": (1 + 5 ** 0.5) * 0
 ALGO_ID = {"ProxGD": _lib.GLP_PROXGD, "FProxGD": _lib.GLP_FPROXGD, "FGD": _lib.GLP_FGD, "GD": _lib.GLP_GD,
            "SGD": _lib.GLP_SGD}
 # additive keys (not in the reference): dtype 'fp32'|'fp64', backend 'auto'|'stream'|'persistent',
-# device (int), poll_interval (int), dist (bool), tensor_cores 'auto'|'off'|'tf32'|'3xtf32'|'tf32+bf16' (wide l >= 16 mode)
+# device (int), poll_interval (int), dist (bool), tensor_cores (wide l >= 16 mode) 'auto' (= fp16 pairs) | 'f16x2' |
+# '3xtf32' | 'tf32+bf16' | 'tf32' | 'off'
 TENSOR_MODES = {"auto": 0, "off": 1, "tf32": 2, "tf32+bf16": 3, "f16x2": 4, "3xtf32": 5}
+
+
+def _tensor_mode(merged):
+    mode = merged.get("tensor_cores", "auto")
+    if mode not in TENSOR_MODES:
+        raise ValueError("opts['tensor_cores'] must be one of %s, got %r" % (sorted(TENSOR_MODES), mode))
+    return TENSOR_MODES[mode]
 
 
 def merge_opts(algo, opts):
@@ -148,11 +156,10 @@ def solve(algo, x0, A, b, mu_0, opts):
         is_torch = False
     if is_torch:
         return _solve_torch(algo, x0, A, b, mu_0, merged, o)
-    if merged.get("tensor_cores", "auto") not in TENSOR_MODES:
-        raise ValueError("opts['tensor_cores'] must be one of %s" % sorted(TENSOR_MODES))
+    mode = _tensor_mode(merged)
     if merged.get("dist"):
         return _solve_numpy_sharded(algo, x0, A, b, mu_0, merged, o)
-    if TENSOR_MODES[merged.get("tensor_cores", "auto")] != 0:
+    if mode != 0:
         # the one-shot host entry point always uses the default tensor mode; explicit modes go through a handle
         import torch
         dt = _mode_dtype(np.asarray(A).dtype, merged)
@@ -308,6 +315,7 @@ class GroupLassoProblem:
         lib = _lib.load()
         merged = merge_opts(algo, opts)
         o = pack_opts(algo, merged)
+        mode = _tensor_mode(merged)
         x0d = x0.to(device=self.device, dtype=self.dtype).contiguous()
         x = torch.empty_like(x0d)
         cap = 3 * int(o.maxit) + 8
@@ -315,7 +323,7 @@ class GroupLassoProblem:
         res = _lib.GlpResult()
         t0 = time.perf_counter()
         with torch.cuda.device(self.device):
-            _lib.check(lib.glp_set_tensor_mode(self._h, TENSOR_MODES[merged.get("tensor_cores", "auto")]))
+            _lib.check(lib.glp_set_tensor_mode(self._h, mode))
             rc = lib.glp_solve(self._h, ALGO_ID[algo], x0d.data_ptr(), float(mu_0), C.byref(o), x.data_ptr(),
                                C.byref(res), f_hist.ctypes.data, cap)
         _raise_for(rc)
@@ -323,7 +331,6 @@ class GroupLassoProblem:
         fh = f_hist[:res.iters]
         _log_history(fh, res)
         return x, int(res.iters), _format_out(res, fh, tt)
-
 
     def metrics(self, x, ref=None, mu=0.0, group=None):
         """Driver metrics of code/main.py:30-34,48-50 for an iterate that stays on the device.
@@ -359,7 +366,6 @@ class GroupLassoProblem:
             else:
                 max_abs = met.max_abs
         return combine_metrics(sums, max_abs, None if getattr(self, "world", 1) > 1 else met.rr, mu, ref is not None)
-
 
     def solve_admm_dual(self, x0, mu, opts=None):
         """gl_Admm_dual (code/gl_ADMM_dual.py) on this problem; x0 a CUDA tensor, returns (x, k, out)."""

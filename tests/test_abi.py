@@ -69,6 +69,19 @@ def test_option_semantics_mirror_the_reference():
             solver.pack_opts(algo, solver.merge_opts(algo, {"step_type": "no_such_rule"}))
 
 
+def test_additive_keys_are_validated_before_any_launch():
+    """tensor_cores / backend / dtype are additive keys (not in the reference): a bad value is a ValueError raised on the
+    host, on every entry path, before the library is asked to compute anything."""
+    from gl_FProxGD_primal import gl_FProxGD_primal
+    from glprox import solver
+    assert solver._tensor_mode({}) == 0 and solver._tensor_mode({"tensor_cores": "f16x2"}) == 4
+    assert sorted(solver.TENSOR_MODES.values()) == [0, 1, 2, 3, 4, 5]   # the modes of glp_set_tensor_mode (include/glprox.h)
+    x0, A, b = np.zeros((8, 2)), np.zeros((4, 8)), np.zeros((4, 2))
+    for bad in ({"tensor_cores": "fp8"}, {"backend": "cpu"}, {"dtype": "bf16"}):
+        with pytest.raises(ValueError):
+            gl_FProxGD_primal(x0, A, b, 1e-2, bad)
+
+
 def test_product_path_never_imports_the_oracle():
     pkg = os.path.join(ROOT, "convex-optimization_b200")
     for dirpath, _, files in os.walk(pkg):
