@@ -1,6 +1,6 @@
 """GPU parity tests of the wide multi-RHS mode (l >= 16, fp32): both products on tcgen05 tensor cores
-(K5).  Bars: 3xTF32 (default) -- the fp32 bar of BASELINE.json, relative objective difference <= 1e-5
-versus the fp64 oracle on the fp32-rounded inputs; plain TF32 (opt-in, approximate) -- 10-bit operand
+(K5).  Bars: fp16 pairs (default), 3xTF32 and TF32 + bf16 corrections -- the fp32 bar of BASELINE.json, relative
+objective difference <= 1e-5 versus the fp64 oracle on the fp32-rounded inputs; plain TF32 (opt-in, approximate) -- 10-bit operand
 mantissas perturb every product by ~1e-3, which the 45 iterations amplify: the trajectory is held to 1e-1
 and the final objective to 5e-2 (stated here because the north star gives no TF32 tolerance)."""
 import numpy as np
