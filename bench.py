@@ -218,11 +218,12 @@ def run_ours(args):
     n_str = prof.fwd_launches + prof.tpass_launches
     avg_ms = (prof.fwd_ms_sum + prof.tpass_ms_sum) / max(n_str, 1)
     achieved = prof.bytes_per_launch / (avg_ms * 1e-3) / 1e9 if n_str else 0.0
-    traffic = None
+    traffic, cap_entry = None, None
     try:  # dram__bytes_read+write per launch from the committed `ncu --set full` capture of this workload
         cap = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
         key = "%s_m%d_n%d_l%d_g%d" % (args.dtype, args.m, args.n, args.l, world)
-        traffic = cap.get(key, {}).get("bytes_per_launch")
+        cap_entry = cap.get(key) if isinstance(cap.get(key), dict) else None
+        traffic = (cap_entry or {}).get("bytes_per_launch")
     except (OSError, ValueError):
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -265,7 +266,8 @@ def run_ours(args):
         hbm_part = {"achieved": hbm_stream, "peak": peak, "unit": "GB/s", "frac": hbm_stream / peak,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write)" if peaks else "fallback 6650 GB/s"}
         bound = "hbm" if t_min_hbm > t_min_tensor else "tensor"
-        roofline = {"bound": bound, **(hbm_part if bound == "hbm" else tensor_part), "traffic": None,
+        wide_traffic = traffic if (cap_entry or {}).get("tensor_cores") == tc_mode else None   # captured per operand set
+        roofline = {"bound": bound, **(hbm_part if bound == "hbm" else tensor_part), "traffic": wide_traffic,
                     "other_roofline": {"bound": "tensor" if bound == "hbm" else "hbm",
                                        **(tensor_part if bound == "hbm" else hbm_part)},
                     "min_ms_per_iteration": {"tensor": 1e3 * t_min_tensor / n_it, "hbm": 1e3 * t_min_hbm / n_it,
