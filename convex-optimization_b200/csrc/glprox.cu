@@ -1979,8 +1979,8 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   // (profiles/r01_ab_gemm_rings_c5.log) 372.8 it/s with the rings (fwd / tpass windows 1.174 / 1.023 ms) against
   // 389.1 it/s with the single ring (1.116 / 0.966 ms), identical objective bits and all GPU tests green with
   // either -- more P bytes in flight do not help, the kernel is not HBM-latency-bound.
-  static const bool rings_on = [] { const char* e = getenv("GLPROX_GEMM_RINGS"); return e != nullptr && atoi(e) != 0; }();
-  const bool rings = passes == 4 && cg == 1 && rings_on;
+  const char* e_rings = getenv("GLPROX_GEMM_RINGS");   // read per call: tests switch it inside one process
+  const bool rings = passes == 4 && cg == 1 && e_rings != nullptr && atoi(e_rings) != 0;
   cudaError_t e;
 #define GLP_GEMM_LAUNCH(NTV, PV) launch_gemm_t<NTV, PV>(st, num_sms, items, mph, mpl, mqh, mql, mpx, mqx, a)
   if (passes == 1) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 1) : NT == 64 ? GLP_GEMM_LAUNCH(64, 1) : GLP_GEMM_LAUNCH(128, 1);

@@ -139,3 +139,18 @@ def test_wide_threshold_correction_equals_direct_product(monkeypatch, shape, alg
     assert abs(outl["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
     # the correction replaces half of the forward product: fewer tensor-core column groups, a few small launches
     assert outl["glprox"]["n_launches"] >= outd["glprox"]["n_launches"]
+
+
+@pytest.mark.parametrize("shape", [(256, 1024, 16), (512, 2048, 128)])
+def test_split_operand_rings_compute_the_same_bits(monkeypatch, shape):
+    """GLPROX_GEMM_RINGS=1 (opt-in staging of the fp16-pair product: separate P / Q rings, csrc/glp_gemm.cuh) changes
+    how the operand tiles reach shared memory, not the sequence of tensor-core instructions: same history, bit for bit."""
+    m, n, l = shape
+    A, b, x0, mu, opts = _case(m, n, l, 5, 8)
+    x0_, k0, out0 = _solve_with_env(monkeypatch, {"GLPROX_GEMM_RINGS": "0"}, "FProxGD", A, b, x0, mu, opts)
+    x1_, k1, out1 = _solve_with_env(monkeypatch, {"GLPROX_GEMM_RINGS": "1"}, "FProxGD", A, b, x0, mu, opts)
+    assert k0 == k1 == 24
+    assert np.array_equal(np.asarray(out0["f_hist"]), np.asarray(out1["f_hist"])) and np.array_equal(x0_, x1_)
+    xr, kr, outr = orc.solve("FProxGD", x0.astype(np.float64), A.astype(np.float64), b.astype(np.float64), mu, opts)
+    assert abs(out1["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
+
