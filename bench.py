@@ -1,27 +1,61 @@
 #!/usr/bin/env python
-"""bench.py -- FProxGD iterations/s on the BASELINE.json workload, with roofline and CPU baseline.
+"""bench.py -- FProxGD iterations/s on the BASELINE.json workload, with roofline, parity and CPU baseline.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
 
-A "step" is one drop-in solve of the hot path (gl_FProxGD_primal semantics) with `maxit` iterations
-per continuation stage (3*maxit iterations, no early stop possible for maxit <= 70) on the synthetic
-workload  m=32768 n=131072 l=2 fp32 (BASELINE.json configs[3]; ~17 GB of A, column-group sharded
-over the ranks).  value = iterations/s of the whole job with A resident in HBM; e2e = the same
-metric through the host-buffer entry point (NumPy in, NumPy out: upload of A, b, x0 and download of
-x inside the timed region).  One JSON line is printed by rank 0.
-"""
-import argparse
-import ctypes as C
-import json
-import math
-import os
-import subprocess
-import sys
-import threading
-import time
+Our arm.  A "step" is one drop-in solve of the hot path (gl_FProxGD_primal semantics) with `maxit`
+iterations per continuation stage (3*maxit iterations, no early stop possible for maxit <= 70) on the
+synthetic workload  m=32768 n=131072 l=2 fp32 (BASELINE.json configs[3]; ~17 GB of A, column-group
+sharded over the ranks).  value = iterations/s of the whole job with A resident in HBM; e2e = the same
+metric through the host-buffer entry point (NumPy in, NumPy out: upload of A, b, x0 and download of x
+inside the timed region).  Beside the headline (outside its timed region): `parity` (the same solve with
+the CPU sample's iteration budget, objective compared with the CPU run), `extra` (BASELINE configs[2] and
+[4] and ProxGD on the headline problem, each with its roofline), `time_to_tol`, `homework_fixture`.
 
-import numpy as np
+Reference arm (--impl reference).  The reference's own CPU implementation of the path -- the unmodified
+solver files staged under oracle/_ref by oracle/make_ref.py, else the oracle port -- on the box's host
+cores, same metric / config, every step a bounded sample of the workload.  It never loads the product
+library: the problem comes from the CPU restatement of the generator (oracle/gen.py), which is
+bit-identical to the device generator.  Rank 0 alone works; torchrun's OMP_NUM_THREADS=1 is undone first.
+
+One JSON line is printed by rank 0.
+"""
+import os
+import sys
+
+
+def _host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def _reference_arm(argv):
+    for i, a in enumerate(argv):
+        if a == "--impl" and i + 1 < len(argv) and argv[i + 1] == "reference":
+            return True
+        if a == "--impl=reference":
+            return True
+    return False
+
+
+if _reference_arm(sys.argv):
+    # torch.distributed.run exports OMP_NUM_THREADS=1 to every rank; the CPU arm wants every host core.
+    # Must happen before NumPy (OpenBLAS) and libgomp are loaded.
+    for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_v] = str(_host_cores())
+
+import argparse  # noqa: E402
+import ctypes as C  # noqa: E402
+import json  # noqa: E402
+import math  # noqa: E402
+import subprocess  # noqa: E402
+import threading  # noqa: E402
+import time  # noqa: E402
+
+import numpy as np  # noqa: E402
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for p in (ROOT, os.path.join(ROOT, "convex-optimization_b200")):
@@ -30,6 +64,8 @@ for p in (ROOT, os.path.join(ROOT, "convex-optimization_b200")):
 
 METRIC = "FProxGD iterations/s"
 UNIT = "it/s"
+CPU_SAMPLE_MAXIT = 2          # iterations per stage of every CPU sample and of the GPU parity solve
+REFERENCE_BUDGET_S = 100.0    # wall-clock target of the reference arm's K + W steps
 
 
 def parse_args():
@@ -48,6 +84,7 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=97006855)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the C3 / C5 / ProxGD side measurements")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="multi-GPU exchange: peer-mailbox push fused into the kernels (product) or the ncclAllReduce baseline")
     ap.add_argument("--tensor-cores", default="auto", choices=["auto", "3xtf32", "tf32+bf16", "f16x2", "tf32", "off"],
@@ -59,6 +96,16 @@ def parse_args():
 def mp_step(m, n):
     """Marchenko-Pastur bound on 1/lambda_max(A^T A); the reference defaults diverge off the fixture."""
     return float(1.0 / (math.sqrt(m) + math.sqrt(n)) ** 2)
+
+
+def bench_config(args):
+    """`config` of the JSON line: a function of the command line only, so both arms print the same object."""
+    es = 4 if args.dtype == "f32" else 8
+    return {"workload": "group-lasso %s m=%d n=%d l=%d %s, mu=1e-2, alpha0=1/(sqrt(m)+sqrt(n))^2; A ~ N(0,1) from the "
+                        "counter-based stream of seed %d, u with 10%% non-zero row groups, b = A u, x0 ~ N(0,1)" % (
+                            args.algo, args.m, args.n, args.l, args.dtype, args.seed),
+            "l2_policy": "A (%.1f GB over %d GPU(s)) is far larger than the 126 MB L2; no flush needed" % (
+                args.m * args.n * es / 1e9, args.gpus)}
 
 
 def mem_available_gb():
@@ -139,172 +186,205 @@ def dist_setup(args):
     return rank, local, world
 
 
-def make_problem(args, rank, world):
+def make_problem(m, n, l, seed, dtype, rank, world):
     """Synthetic problem of code/main.py:37-51 at scale (glprox.dataset.gen_data_device): A ~ N(0,1) from
     the counter-based device generator (identical values for any sharding), 10% non-zero row groups in
     u, b = A u."""
     from glprox import dataset
-    A, b, x0_loc, _u, mu, _ = dataset.gen_data_device(args.m, args.n, args.l, args.seed, args.dtype, rank, world)
+    A, b, x0_loc, _u, mu, _ = dataset.gen_data_device(m, n, l, seed, dtype, rank, world)
     return A, b, x0_loc, mu
 
 
-def solver_opts(args):
-    o = {"maxit": args.maxit, "alpha0": mp_step(args.m, args.n)}
-    if args.tensor_cores != "auto":
-        o["tensor_cores"] = args.tensor_cores
-    return o
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        return {}
+
+
+def device_max(ms, world):
+    if world == 1:
+        return ms
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item()
+
+
+def barrier(world):
+    import torch
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def timed_solves(prob, algo, x0, mu, opts, steps, warmup, world, sampler=None):
+    """W untimed solves, then K solves between barrier + synchronize, CUDA events on the solve stream, max
+    over ranks.  The library's own per-launch CUDA-event profile is switched on for the timed solves."""
+    import torch
+    from glprox import _lib
+    lib = _lib.load()
+    for _ in range(warmup):
+        x, k, out = prob.solve(algo, x0, mu, opts)
+    _lib.check(lib.glp_set_profiling(prob.handle, 1))
+    barrier(world)
+    t_wall0 = time.time()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    iters = launches = 0
+    for _ in range(steps):
+        x, k, out = prob.solve(algo, x0, mu, opts)
+        iters += k
+        launches += out["glprox"]["n_launches"]
+    ev1.record()
+    barrier(world)
+    t_wall1 = time.time()
+    ms = device_max(ev0.elapsed_time(ev1), world)
+    prof = _lib.GlpProfile()
+    _lib.check(lib.glp_get_profile(prob.handle, C.byref(prof)))
+    _lib.check(lib.glp_set_profiling(prob.handle, 0))
+    return {"iters": iters, "ms": ms, "launches": launches, "out": out, "prof": prof, "wall": (t_wall0, t_wall1)}
+
+
+def ncu_traffic(dtype, m, n, l, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` capture of this workload (profiles/ncu_traffic.json names the .csv); None if not captured."""
+    try:
+        cap = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except (OSError, ValueError):
+        return None
+    e = cap.get("%s_m%d_n%d_l%d_g%d" % (dtype, m, n, l, world))
+    return e if isinstance(e, dict) else None
+
+
+def stream_roofline(prof, value, peaks, cap):
+    """l = 2: the two streams of A (K1 forward, K2 transposed) against the measured HBM copy peak."""
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    n_str = prof.fwd_launches + prof.tpass_launches
+    avg_ms = (prof.fwd_ms_sum + prof.tpass_ms_sum) / max(n_str, 1)
+    achieved = prof.bytes_per_launch / (avg_ms * 1e-3) / 1e9 if n_str else 0.0
+    per = lambda cnt, ms: {"launches": int(cnt), "avg_ms": ms / max(cnt, 1),
+                           "GBps": prof.bytes_per_launch * cnt / max(ms, 1e-9) / 1e6}
+    return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": (cap or {}).get("bytes_per_launch"),
+            "traffic_source": (cap or {}).get("source", None),
+            "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write)" if peaks else "fallback 6650 GB/s",
+            "kernels": {"glp_fwd_kernel": per(prof.fwd_launches, prof.fwd_ms_sum),
+                        "glp_tpass_kernel": per(prof.tpass_launches, prof.tpass_ms_sum)},
+            "bytes_per_launch": prof.bytes_per_launch,
+            "whole_iteration_GBps": 2.0 * prof.bytes_per_launch * value / 1e9}
+
+
+def wide_roofline(prof, value, peaks, cap, m, n_local, l, tensor_cores):
+    """l >= 16 (fp32): both products run on tcgen05; report the binding roofline of the two (HBM stream of the
+    resident operand set vs tensor pipe in TF32-product units) and the other one beside it."""
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    tc_mode = "f16x2" if tensor_cores == "auto" else tensor_cores   # auto = fp16 pairs (finite A)
+    # tensor time in TF32-product units: 3xTF32 issues 3 TF32 products; tf32+bf16 one TF32 product and two bf16
+    # products at twice the rate (= 2 units); fp16 pairs three kind::f16 products at twice the rate (= 1.5)
+    passes = {"tf32": 1.0, "tf32+bf16": 2.0, "f16x2": 1.5}.get(tc_mode, 3.0)
+    n_it = max(int(prof.tpass_launches), 1)
+    # operand columns on the tensor cores per iteration: l (A.xn) + l (A^T r); the product of the thresholded
+    # iterate comes from A.xn by a sparse CUDA-core correction (csrc/glp_thrfix.cuh) unless switched off
+    thrfix = os.environ.get("GLPROX_WIDE_THRFIX", "1") != "0"
+    op_cols = (2 if thrfix else 3) * l
+    flops = passes * 2.0 * m * n_local * op_cols * n_it
+    t_s = (prof.fwd_ms_sum + prof.tpass_ms_sum) * 1e-3
+    tf = flops / max(t_s, 1e-12) / 1e12
+    tpeak = float(peaks.get("bf16_tflops", 1590.0)) / 2.0
+    stream_x = 1.0 if tc_mode in ("tf32", "f16x2") else 2.0   # bytes of the resident set per fp32 element / 4
+    stream_bytes = stream_x * prof.bytes_per_launch * (prof.fwd_launches + prof.tpass_launches)
+    hbm_stream = stream_bytes / max(t_s, 1e-12) / 1e9
+    t_min_tensor, t_min_hbm = flops / (tpeak * 1e12), stream_bytes / (peak * 1e9)
+    tensor_part = {"achieved": tf, "peak": tpeak, "unit": "TFLOP/s", "frac": tf / tpeak,
+                   "peak_source": "MEASURED_PEAKS.json bf16_tflops / 2 (TF32-product units)"}
+    hbm_part = {"achieved": hbm_stream, "peak": peak, "unit": "GB/s", "frac": hbm_stream / peak,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write)" if peaks else "fallback 6650 GB/s"}
+    bound = "hbm" if t_min_hbm > t_min_tensor else "tensor"
+    wide_traffic = (cap or {}).get("bytes_per_launch") if (cap or {}).get("tensor_cores") == tc_mode else None
+    return {"bound": bound, **(hbm_part if bound == "hbm" else tensor_part), "traffic": wide_traffic,
+            "traffic_source": (cap or {}).get("source") if wide_traffic else None,
+            "other_roofline": {"bound": "tensor" if bound == "hbm" else "hbm",
+                               **(tensor_part if bound == "hbm" else hbm_part)},
+            "min_ms_per_iteration": {"tensor": 1e3 * t_min_tensor / n_it, "hbm": 1e3 * t_min_hbm / n_it,
+                                     "measured_products": 1e3 * t_s / n_it},
+            "whole_iteration_frac_of_hbm": stream_x * 2.0 * prof.bytes_per_launch * value / 1e9 / peak,
+            "tensor_cores": tc_mode, "tensor_operand_columns_per_iteration": op_cols,
+            "forward_product": ("A.xn on tcgen05 (l columns) + sparse CUDA-core correction for A.thr(xn), both inside the "
+                                "fwd window" if thrfix else "A.[xn | thr(xn)] on tcgen05 (2l columns)"),
+            "kernels": {"glp_gemm_tf32_kernel<fwd>": {"launches": int(prof.fwd_launches),
+                                                      "avg_ms": prof.fwd_ms_sum / max(prof.fwd_launches, 1)},
+                        "glp_gemm_tf32_kernel<tpass>": {"launches": int(prof.tpass_launches),
+                                                        "avg_ms": prof.tpass_ms_sum / max(prof.tpass_launches, 1)}}}
+
+
+def exchange_text(args, world):
+    if world == 1:
+        return "none (1 GPU)"
+    if args.exchange == "nccl":
+        return ("BASELINE: two ncclAllReduce calls per forward stream (MAX of one double, SUM of the m x 2l "
+                "partial product + 8 scalars) on the solver stream")
+    if args.l >= 16 and args.dtype == "f32":
+        return ("reduce-scatter + all-gather of the m x 2l partial products over row slices, pushed through peer "
+                "mailboxes over NVLink (3 small kernels per forward product); no NCCL on the data path")
+    return ("m x 2l partial products + 5 scalars pushed into peer mailboxes over NVLink from inside the forward "
+            "kernel; rank-ordered sum on every rank; no NCCL on the data path")
 
 
 def run_ours(args):
     import torch
     from glprox import GroupLassoProblem, _lib
     rank, local, world = dist_setup(args)
-    lib = _lib.load()
+    _lib.load()
     if world != args.gpus:
         raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch with torch.distributed.run)" % (args.gpus, world))
-    A, b, x0, mu = make_problem(args, rank, world)
-    opts = solver_opts(args)
+    A, b, x0, mu = make_problem(args.m, args.n, args.l, args.seed, args.dtype, rank, world)
+    opts = {"maxit": args.maxit, "alpha0": mp_step(args.m, args.n)}
+    if args.tensor_cores != "auto":
+        opts["tensor_cores"] = args.tensor_cores
     prob = GroupLassoProblem(A, b)
     if world > 1:
         from glprox import attach_distributed
         attach_distributed(prob, args.n, exchange=args.exchange)
 
-    def barrier():
-        if world > 1:
-            import torch.distributed as dist
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- device-resident throughput
+    # ---- device-resident throughput (the headline)
     sampler = ClockSampler(local)
     sampler.start()
-    for _ in range(args.warmup):
-        x, k, out = prob.solve(args.algo, x0, mu, opts)
-    _lib.check(lib.glp_set_profiling(prob.handle, 1))
-    barrier()
-    t_wall0 = time.time()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    iters = launches = 0
-    for _ in range(args.steps):
-        x, k, out = prob.solve(args.algo, x0, mu, opts)
-        iters += k
-        launches += out["glprox"]["n_launches"]
-    ev1.record()
-    barrier()
-    t_wall1 = time.time()
+    r = timed_solves(prob, args.algo, x0, mu, opts, args.steps, args.warmup, world)
+    t_wall0, t_wall1 = r["wall"]
     if t_wall1 - t_wall0 < 0.5:
         time.sleep(0.3)  # let one more nvidia-smi sample land
     clocks = sampler.stop(t_wall0, t_wall1)
-    ms = ev0.elapsed_time(ev1)
-    if world > 1:
-        import torch.distributed as dist
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = t.item()
-    prof = _lib.GlpProfile()
-    _lib.check(lib.glp_get_profile(prob.handle, C.byref(prof)))
-    _lib.check(lib.glp_set_profiling(prob.handle, 0))
+    ms, iters, prof = r["ms"], r["iters"], r["prof"]
     value = iters / (ms / 1e3)
-    fval = float(out["fval"])
-
-    # ---- roofline of the dominant kernels (the two streams of A), CUDA events on the solve stream
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except (OSError, ValueError):
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    n_str = prof.fwd_launches + prof.tpass_launches
-    avg_ms = (prof.fwd_ms_sum + prof.tpass_ms_sum) / max(n_str, 1)
-    achieved = prof.bytes_per_launch / (avg_ms * 1e-3) / 1e9 if n_str else 0.0
-    traffic, cap_entry = None, None
-    try:  # dram__bytes_read+write per launch from the committed `ncu --set full` capture of this workload
-        cap = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        key = "%s_m%d_n%d_l%d_g%d" % (args.dtype, args.m, args.n, args.l, world)
-        cap_entry = cap.get(key) if isinstance(cap.get(key), dict) else None
-        traffic = (cap_entry or {}).get("bytes_per_launch")
-    except (OSError, ValueError):
-        pass
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic,
-                "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write)" if peaks else "fallback 6650 GB/s",
-                "kernels": {"glp_fwd_kernel": {"launches": int(prof.fwd_launches),
-                                               "avg_ms": prof.fwd_ms_sum / max(prof.fwd_launches, 1),
-                                               "GBps": prof.bytes_per_launch * prof.fwd_launches / max(prof.fwd_ms_sum, 1e-9) / 1e6},
-                            "glp_tpass_kernel": {"launches": int(prof.tpass_launches),
-                                                 "avg_ms": prof.tpass_ms_sum / max(prof.tpass_launches, 1),
-                                                 "GBps": prof.bytes_per_launch * prof.tpass_launches / max(prof.tpass_ms_sum, 1e-9) / 1e6}},
-                "bytes_per_launch": prof.bytes_per_launch,
-                "whole_iteration_GBps": 2.0 * prof.bytes_per_launch * value / 1e9}
-
+    peaks = load_peaks()
+    cap = ncu_traffic(args.dtype, args.m, args.n, args.l, world)
     if args.l >= 16 and args.dtype == "f32":
-        # wide multi-RHS mode: both products run on tcgen05 (3xTF32); the bounding roofline is the tensor pipe
-        # tensor time in TF32-product units: 3xTF32 issues 3 TF32 products; tf32+bf16 one TF32 product and two
-        # bf16 products at twice the rate (= 2 units); plain TF32 one
-        tc_mode = "f16x2" if args.tensor_cores == "auto" else args.tensor_cores   # auto = fp16 pairs (finite A)
-        passes = {"tf32": 1.0, "tf32+bf16": 2.0, "f16x2": 1.5}.get(tc_mode, 3.0)
-        n_it = max(int(prof.tpass_launches), 1)
-        # operand columns on the tensor cores per iteration: l (A.xn) + l (A^T r); the product of the thresholded
-        # iterate comes from A.xn by a sparse CUDA-core correction (csrc/glp_thrfix.cuh) unless switched off,
-        # in which case the forward product has 2l columns.  The correction's time is inside the fwd window.
-        thrfix = os.environ.get("GLPROX_WIDE_THRFIX", "1") != "0"
-        op_cols = (2 if thrfix else 3) * args.l
-        flops = passes * 2.0 * args.m * A.shape[1] * op_cols * n_it   # this rank's column shard
-        t_s = (prof.fwd_ms_sum + prof.tpass_ms_sum) * 1e-3
-        tf = flops / max(t_s, 1e-12) / 1e12
-        tpeak = float(peaks.get("bf16_tflops", 1590.0)) / 2.0
-        # bytes of the resident operand per product: 8 per element (fp32 hi + fp32 lo, or fp32 hi + 2 bf16), 4 for
-        # plain TF32 and for the fp16 pairs
-        stream_x = 1.0 if tc_mode in ("tf32", "f16x2") else 2.0
-        stream_bytes = stream_x * prof.bytes_per_launch * (prof.fwd_launches + prof.tpass_launches)
-        hbm_stream = stream_bytes / max(t_s, 1e-12) / 1e9
-        # the binding roofline is the one with the larger minimum time for this work
-        t_min_tensor, t_min_hbm = flops / (tpeak * 1e12), stream_bytes / (peak * 1e9)
-        tensor_part = {"achieved": tf, "peak": tpeak, "unit": "TFLOP/s", "frac": tf / tpeak,
-                       "peak_source": "MEASURED_PEAKS.json bf16_tflops / 2 (kind::tf32 runs at half the bf16 rate)"}
-        hbm_part = {"achieved": hbm_stream, "peak": peak, "unit": "GB/s", "frac": hbm_stream / peak,
-                    "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write)" if peaks else "fallback 6650 GB/s"}
-        bound = "hbm" if t_min_hbm > t_min_tensor else "tensor"
-        wide_traffic = traffic if (cap_entry or {}).get("tensor_cores") == tc_mode else None   # captured per operand set
-        roofline = {"bound": bound, **(hbm_part if bound == "hbm" else tensor_part), "traffic": wide_traffic,
-                    "other_roofline": {"bound": "tensor" if bound == "hbm" else "hbm",
-                                       **(tensor_part if bound == "hbm" else hbm_part)},
-                    "min_ms_per_iteration": {"tensor": 1e3 * t_min_tensor / n_it, "hbm": 1e3 * t_min_hbm / n_it,
-                                             "measured_products": 1e3 * t_s / n_it},
-                    "work": {"tf32": "1 TF32 product per stream (approximate mode)",
-                             "f16x2": "3 kind::f16 products of fp16 pairs (P0.Q0 + P0.Q1 + P1.Q0) at twice the TF32 rate: "
-                                      "1.5 TF32-product units of tensor time per stream, counted as such; the resident "
-                                      "operand streams 4 bytes per element",
-                             "tf32+bf16": "Ah.Xh on TF32 + (Ah.Xl + Al.Xh) on bf16 at twice the rate: 2 TF32-product "
-                                          "units of tensor time per stream, counted as such"}.get(
-                                 tc_mode, "3 compensated TF32 products per stream: Ah.Xh + Ah.Xl + Al.Xh, issued flops counted"),
-                    "tensor_cores": tc_mode,
-                    "tensor_operand_columns_per_iteration": op_cols,
-                    "forward_product": ("A.xn on tcgen05 (l columns) + sparse CUDA-core correction for A.thr(xn), both inside the "
-                                        "fwd window" if thrfix else "A.[xn | thr(xn)] on tcgen05 (2l columns)"),
-                    "kernels": {"glp_gemm_tf32_kernel<fwd>": {"launches": int(prof.fwd_launches), "avg_ms": prof.fwd_ms_sum / max(prof.fwd_launches, 1)},
-                                "glp_gemm_tf32_kernel<tpass>": {"launches": int(prof.tpass_launches), "avg_ms": prof.tpass_ms_sum / max(prof.tpass_launches, 1)}}}
+        roofline = wide_roofline(prof, value, peaks, cap, args.m, A.shape[1], args.l, args.tensor_cores)
+    else:
+        roofline = stream_roofline(prof, value, peaks, cap)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": "group-lasso %s m=%d n=%d l=%d %s, mu=1e-2, alpha0=1/(sqrt(m)+sqrt(n))^2, "
-                                   "maxit=%d per stage (%d iterations per step)" % (
-                                       args.algo, args.m, args.n, args.l, args.dtype, args.maxit, 3 * args.maxit),
-                       "sharding": "column groups of A / row groups of x over %d rank(s)" % world,
-                       "exchange": "none (1 GPU)" if world == 1 else
-                                   ("BASELINE: two ncclAllReduce calls per forward stream (MAX of one double, SUM of the m x 2l "
-                                    "partial product + 8 scalars) on the solver stream" if args.exchange == "nccl" else
-                                    "reduce-scatter + all-gather of the m x 2l partial products over row slices, pushed "
-                                    "through peer mailboxes over NVLink (3 small kernels per forward product); no NCCL on "
-                                    "the data path" if args.l >= 16 and args.dtype == "f32" else
-                                    "m x 2l partial products + 5 scalars pushed into peer mailboxes over NVLink from "
-                                    "inside the forward kernel; rank-ordered sum on every rank; no NCCL on the data path"),
-                       "l2_policy": "A (%.1f GB per rank) is far larger than the 126 MB L2; no flush needed" % (
-                           A.numel() * A.element_size() / 1e9)},
-            "iterations_per_step": iters // max(args.steps, 1), "final_objective": fval,
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline}
+            "config": bench_config(args),
+            "parallel": {"sharding": "column groups of A / row groups of x over %d rank(s)" % world,
+                         "exchange": exchange_text(args, world)},
+            "maxit_per_stage": args.maxit, "iterations_per_step": iters // max(args.steps, 1),
+            "final_objective": float(r["out"]["fval"]),
+            "gpu_launches": int(r["launches"]), "clocks": clocks, "roofline": roofline}
     return line, (prob, A, b, x0, mu, opts, rank, world)
+
+
+def run_parity_gpu(args, ctx):
+    """The GPU half of `parity`: the same solver, same inputs, with the CPU sample's iteration budget."""
+    prob, A, b, x0, mu, opts, rank, world = ctx
+    o = dict(opts, maxit=CPU_SAMPLE_MAXIT)
+    x, k, out = prob.solve(args.algo, x0, mu, o)
+    return {"maxit": CPU_SAMPLE_MAXIT, "iters": int(k), "gpu_fval": float(out["fval"]),
+            "gpu_f_hist": [float(v) for v in out["f_hist"]], "bar": 1e-5 if args.dtype == "f32" else 1e-10,
+            "cpu_fval": None, "rel_diff": None}
 
 
 def run_e2e(args, ctx, steps):
@@ -341,6 +421,7 @@ def run_e2e(args, ctx, steps):
     dt = time.perf_counter() - t0
     h2d = An.nbytes + bn.nbytes + x0n.nbytes
     d2h = x.nbytes + 8 * k
+    h2d_rank = h2d
     if world > 1:
         t = torch.tensor([dt, float(h2d), float(d2h)], device="cuda", dtype=torch.float64)
         dist.all_reduce(t[:1], op=dist.ReduceOp.MAX)
@@ -348,6 +429,8 @@ def run_e2e(args, ctx, steps):
         dt, h2d, d2h = t[0].item(), t[1].item(), t[2].item()
     return {"value": iters / dt, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
             "ms_per_step": 1e3 * dt / steps, "final_objective": float(out["fval"]),
+            "h2d_bytes_per_rank_per_step": int(h2d_rank),
+            "upload_ms_per_step": out["glprox"].get("upload_ms"),
             "api": "gl_%s_primal(x0, A, b, mu, opts) with NumPy arrays (pinned host memory)" % args.algo}, (An, bn, x0n)
 
 
@@ -373,13 +456,7 @@ def run_convergence(args, ctx):
     full = dict(opts)
     full["maxit"] = DEFAULT_OPTS[args.algo]["maxit"]
     x, k, out = prob.solve(args.algo, x0, mu, full)
-    secs = out["glprox"]["device_ms"] * 1e-3
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        t = torch.tensor([secs], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        secs = t.item()
+    secs = device_max(out["glprox"]["device_ms"], world) * 1e-3
     fh = np.asarray(out["f_hist"], dtype=np.float64)
     k8, s8 = time_to_tol(fh, float(fh[-1]), secs, 1e-8)
     k6, s6 = time_to_tol(fh, float(fh[-1]), secs, 1e-6)
@@ -392,6 +469,50 @@ def run_convergence(args, ctx):
             "note": "when the iteration budget ends before the stop rule fires (k_to == iters) the objective is still "
                     "decreasing: fp32 trajectories of such un-converged runs decorrelate at the 1e-4 level between "
                     "summation orders (1/2/4/8 shards), as they do between NumPy fp32 and fp64 (SURVEY.md 8(c))"}
+
+
+def run_extra(args, ctx):
+    """Side measurements the driver would otherwise never see (outside the headline's timed region), at every N:
+    BASELINE configs[2] (C3, 8192 x 32768, l = 2), configs[4] (C5, 16384 x 65536, l = 128 on tcgen05, default
+    operand set) and ProxGD on the headline problem.  Each: W = 1 solve, K = 2 timed solves of maxit = 10."""
+    import torch
+    from glprox import GroupLassoProblem, attach_distributed
+    prob, A, b, x0, mu, opts, rank, world = ctx
+    peaks = load_peaks()
+    res = {}
+
+    def one(name, pr, algo, x0_, mu_, o, m, n, n_loc, l, wide, note):
+        try:
+            r = timed_solves(pr, algo, x0_, mu_, o, 2, 1, world)
+            v = r["iters"] / (r["ms"] / 1e3)
+            cap = ncu_traffic("f32", m, n, l, world)
+            rf = wide_roofline(r["prof"], v, peaks, cap, m, n_loc, l, "auto") if wide else stream_roofline(r["prof"], v, peaks, cap)
+            res[name] = {"workload": note, "value": v, "unit": UNIT, "iters_timed": r["iters"],
+                         "ms_per_iteration": r["ms"] / max(r["iters"], 1), "final_objective": float(r["out"]["fval"]),
+                         "gpu_launches": int(r["launches"]), "n_fwd": int(r["out"]["glprox"]["n_fwd"]),
+                         "n_tpass": int(r["out"]["glprox"]["n_tpass"]), "roofline": rf}
+        except Exception as e:  # noqa: BLE001  (secondary report; never lose the headline line)
+            res[name] = {"workload": note, "error": repr(e)}
+
+    if args.dtype == "f32" and args.l == 2:
+        one("proxgd_c4", prob, "ProxGD", x0, mu, dict(opts, maxit=10), args.m, args.n, A.shape[1], args.l, False,
+            "gl_ProxGD_primal on the headline problem, maxit=10 per stage")
+    for name, (m, n, l, wide) in (("c3", (8192, 32768, 2, False)), ("c5", (16384, 65536, 128, True))):
+        note = "group-lasso FProxGD m=%d n=%d l=%d f32, maxit=10 per stage%s" % (
+            m, n, l, ", wide multi-RHS mode on tcgen05 (fp16 pairs)" if wide else "")
+        try:
+            A2, b2, x02, mu2 = make_problem(m, n, l, args.seed, "f32", rank, world)
+            p2 = GroupLassoProblem(A2, b2)
+            if world > 1:
+                attach_distributed(p2, n, exchange=args.exchange)
+        except Exception as e:  # noqa: BLE001
+            res[name] = {"workload": note, "error": repr(e)}
+            continue
+        one(name, p2, "FProxGD", x02, mu2, {"maxit": 10, "alpha0": mp_step(m, n)}, m, n, A2.shape[1], l, wide, note)
+        p2.close()
+        del A2, b2, x02, p2
+        torch.cuda.empty_cache()
+    return res
 
 
 def run_homework(args):
@@ -409,6 +530,7 @@ def run_homework(args):
     x0d = torch.from_numpy(x0).cuda()
     res = {"workload": "Test_group_lasso fixture m=256 n=512 l=2 mu=1e-2 fp64, default opts",
            "published_optimum_mosek_gurobi": 6.10377e-01, "f_star": F_STAR}
+    smem_bytes = 2.0 * A.nbytes   # K4 reads the resident A twice per iteration from shared memory
     for algo in ("FProxGD", "ProxGD"):
         row = {}
         for be in ("persistent", "stream"):
@@ -419,8 +541,16 @@ def run_homework(args):
                 best = ms if best is None else min(best, ms)
             kk, tsec = time_to_tol(out["f_hist"], float(out["fval"]), best / 1e3)
             row[be] = {"iters": k, "fval": float(out["fval"]), "ms": best, "it_per_s": k / (best / 1e3),
+                       "us_per_iteration": 1e3 * best / max(k, 1),
                        "k_to_1e-8_of_final": kk, "s_to_1e-8_of_final": tsec,
-                       "launches": out["glprox"]["n_launches"]}
+                       "launches": out["glprox"]["n_launches"], "n_fwd": int(out["glprox"]["n_fwd"])}
+        # shared-memory roofline of the persistent kernel: each CTA of the cluster reads its slice of A twice per
+        # iteration; B300_MICROARCH.md: 128 B/clk/SM of shared-memory bandwidth
+        ctas = int(os.environ.get("GLPROX_CLUSTER", "0")) or 8
+        smem_peak_gbs = ctas * 128.0 * 1.965   # bytes/clk/SM x GHz at the maximum SM clock
+        row["persistent"]["smem_roofline_frac"] = (smem_bytes * row["persistent"]["it_per_s"] / 1e9) / smem_peak_gbs
+        row["persistent"]["smem_roofline"] = "2 x |A| = %.0f KiB per iteration over %d CTAs at 128 B/clk/SM x 1.965 GHz" % (
+            smem_bytes / 1024, ctas)
         x, k, out = prob.solve(algo, x0d, mu, {"backend": "persistent", "thres": 1e-8})
         kk, tsec = time_to_tol(out["f_hist"], F_STAR, out["glprox"]["device_ms"] / 1e3)
         row["persistent_thres1e-8"] = {"iters": k, "fval": float(out["fval"]), "ms": out["glprox"]["device_ms"],
@@ -455,78 +585,102 @@ def run_homework(args):
     return res
 
 
-def cpu_reference_solve(args, An, bn, x0n, mu, opts, sample_maxit, row_frac=1.0):
-    """The oracle port of the reference (same pass structure: 5 products with A per FProxGD iteration,
-    NumPy/BLAS on all host cores), on a bounded sample of the workload."""
-    from oracle import glprox_oracle as orc
-    o = dict(opts)
-    o["maxit"] = sample_maxit
-    x, k, out = orc.solve(args.algo, x0n, An, bn, mu, o)
-    return k, out["tt"], float(out["fval"])
-
-
+# ---- CPU legs -----------------------------------------------------------------------------------------
 def blas_threads():
     try:
         from threadpoolctl import threadpool_info
         return max([p.get("num_threads", 1) for p in threadpool_info()] or [1])
     except Exception:
-        return len(os.sched_getaffinity(0))
+        return _host_cores()
 
 
-def host_problem(args):
-    """Host copy of the synthetic problem for the CPU legs.  Uses the GPU generator when a device is
-    present (identical values to the GPU arm), NumPy otherwise."""
-    import torch
-    if torch.cuda.is_available():
-        torch.cuda.set_device(0)
-        A, b, x0, mu = make_problem(args, 0, 1)
-        An, bn, x0n = A.cpu().numpy(), b.cpu().numpy(), x0.cpu().numpy()
-        del A
-        torch.cuda.empty_cache()
-        return An, bn, x0n, mu
+def cpu_solver(algo):
+    """(callable, kind): the unmodified reference function staged under oracle/_ref (kind "reference") when
+    oracle/make_ref.py has run, else the oracle port of it (kind "port")."""
+    from oracle import make_ref
+    staged = make_ref.load()
+    if staged is not None:
+        return staged[0 if algo == "ProxGD" else 1], "reference"
     from oracle import glprox_oracle as orc
-    A, b, x0, u, mu = orc.gen_data(args.seed, args.m, args.n, args.l, np.float32 if args.dtype == "f32" else np.float64)
-    return A, b, x0, mu
+    return (lambda x0, A, b, mu, o: orc.solve(algo, x0, A, b, mu, o)), "port"
+
+
+def cpu_solve(algo, An, bn, x0n, mu, alpha0, maxit):
+    """One CPU solve with every host core: (iterations, seconds, fval, f_hist, kind, threads)."""
+    from threadpoolctl import threadpool_limits
+    fn, kind = cpu_solver(algo)
+    with threadpool_limits(limits=_host_cores()):
+        threads = blas_threads()
+        t0 = time.perf_counter()
+        x, k, out = fn(x0n, An, bn, mu, {"alpha0": alpha0, "maxit": maxit})
+        secs = time.perf_counter() - t0
+    return int(k), secs, float(out["fval"]), [float(v) for v in out["f_hist"]], kind, threads
+
+
+def product_library_mapped():
+    """True when libglprox.so is mapped into this process (it must not be in the reference arm)."""
+    try:
+        return any("libglprox.so" in ln for ln in open("/proc/self/maps"))
+    except OSError:
+        return None
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU algorithm (oracle port; the Python reference cannot
-    travel to the GPU box) on the box's host cores, same config / metric / unit."""
+    """--impl reference (see the module docstring).  Never imports glprox / loads libglprox.so."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return None
-    need_gb = args.m * args.n * (4 if args.dtype == "f32" else 8) / 1e9
+    from oracle import gen
+    es = 4 if args.dtype == "f32" else 8
+    need_gb = args.m * args.n * es / 1e9
     rows = args.m
-    if mem_available_gb() < 1.6 * need_gb + 4:
-        rows = max(64, int(args.m * (mem_available_gb() - 4) / (1.6 * need_gb)) // 64 * 64)
-    sub = argparse.Namespace(**vars(args))
-    sub.m = rows
-    An, bn, x0n, mu = host_problem(sub)
-    opts = {"alpha0": mp_step(args.m, args.n)}
-    cores = blas_threads()
-    sample_maxit = 1  # 3 iterations per step (one per continuation stage), ~5 products with A each
-    scale = rows / args.m  # a row sample does proportionally less work per iteration
-    for _ in range(min(args.warmup, 1)):
-        cpu_reference_solve(args, An, bn, x0n, mu, opts, sample_maxit)
-    iters, secs = 0, 0.0
+    if mem_available_gb() < 1.3 * need_gb + 4:
+        rows = max(64, int(args.m * (mem_available_gb() - 4) / (1.3 * need_gb)) // 64 * 64)
+    t0 = time.perf_counter()
+    An, bn, x0n, _u, mu = gen.gen_problem(args.m, args.n, args.l, args.seed, np.float32 if args.dtype == "f32" else np.float64,
+                                          rows=rows)
+    t_gen = time.perf_counter() - t0
+    alpha0 = mp_step(args.m, args.n)
+    # calibrate the sample: one forward + one transposed product on the rows held, 5 products per FProxGD
+    # iteration and one for the exit fval (gl_FProxGD_primal.py:25,63,66 x2,129 / :156)
+    from threadpoolctl import threadpool_limits
+    with threadpool_limits(limits=_host_cores()):
+        An @ x0n
+        t0 = time.perf_counter()
+        r = An @ x0n
+        An.T @ r
+        t_pair = time.perf_counter() - t0
+    prods = (5 if args.algo == "FProxGD" else 4) * 3 * CPU_SAMPLE_MAXIT + 1
+    est_step = 0.5 * t_pair * prods
+    n_steps = args.steps + args.warmup
+    frac = min(1.0, REFERENCE_BUDGET_S / max(est_step * n_steps, 1e-9))
+    use = rows if frac >= 1.0 else max(64, int(rows * frac) // 64 * 64)
+    As, bs = An[:use], bn[:use]
+    scale = use / args.m    # a row sample does proportionally less work per iteration
+    kind = threads = None
+    for _ in range(args.warmup):
+        cpu_solve(args.algo, As, bs, x0n, mu, alpha0, CPU_SAMPLE_MAXIT)
+    iters, secs, fval = 0, 0.0, None
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        k, tt, fval = cpu_reference_solve(args, An, bn, x0n, mu, opts, sample_maxit)
+        k, tt, fval, _fh, kind, threads = cpu_solve(args.algo, As, bs, x0n, mu, alpha0, CPU_SAMPLE_MAXIT)
         iters += k
         secs += tt
     wall = time.perf_counter() - t0
     value = iters / secs * scale
-    sample = "%d iterations per step (maxit=1 per stage) on rows 0..%d of %d, all %d columns%s" % (
-        3 * sample_maxit, rows, args.m, args.n, "" if rows == args.m else "; it/s scaled by rows/m")
+    sample = ("%d iterations per step (maxit=%d per stage) on rows 0..%d of %d, all %d columns%s; problem generated on "
+              "the host in %.1f s (oracle/glprox_gen.c, bit-identical to the device generator)" % (
+                  3 * CPU_SAMPLE_MAXIT, CPU_SAMPLE_MAXIT, use, args.m, args.n,
+                  "" if use == args.m else "; it/s scaled by rows/m (cost per iteration is linear in m)", t_gen))
     return {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * wall / max(args.steps, 1),
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / max(args.steps, 1),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype,
-            "data": "synthetic",
-            "config": {"workload": "group-lasso %s m=%d n=%d l=%d %s, mu=1e-2, alpha0=1/(sqrt(m)+sqrt(n))^2" % (
-                args.algo, args.m, args.n, args.l, args.dtype)},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "data": "synthetic", "config": bench_config(args),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "sample_final_objective": fval, "host_cores": _host_cores(),
+            "omp_num_threads_env": os.environ.get("OMP_NUM_THREADS"), "gpu_launches": 0,
+            "product_library_mapped": product_library_mapped()}
 
 
 def main():
@@ -539,10 +693,14 @@ def main():
     line, ctx = run_ours(args)
     prob, A, b, x0, mu, opts, rank, world = ctx
     host = None
+    try:
+        line["parity"] = run_parity_gpu(args, ctx)
+    except Exception as e:  # noqa: BLE001  (secondary report; never lose the headline line)
+        line["parity"] = {"error": repr(e)}
     if not args.no_converge:
         try:
             line["time_to_tol"] = run_convergence(args, ctx)
-        except Exception as e:  # noqa: BLE001  (secondary report; never lose the headline line)
+        except Exception as e:  # noqa: BLE001
             line["time_to_tol"] = {"error": repr(e)}
     if not args.no_e2e:
         e2e, host = run_e2e(args, ctx, args.steps)
@@ -550,25 +708,44 @@ def main():
                                                    "d2h_bytes_per_step": 0, "skipped": host}
         if e2e is None:
             host = None
+    if not args.no_extra:
+        line["extra"] = run_extra(args, ctx)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             line["homework_fixture"] = run_homework(args)
-        except Exception as e:  # noqa: BLE001  (secondary report; never lose the headline line)
+        except Exception as e:  # noqa: BLE001
             line["homework_fixture"] = {"error": repr(e)}
         if host is None:
             need_gb = A.numel() * A.element_size() / 1e9
             if mem_available_gb() >= 1.6 * need_gb + 4:
                 host = (A.cpu().numpy(), b.cpu().numpy(), x0.cpu().numpy())
         if host is not None:
+            # the CPU sample: same inputs (downloaded from HBM), same options, CPU_SAMPLE_MAXIT iterations per stage;
+            # it is both the reported cpu_baseline and the checker of `parity`
             An, bn, x0n = host
-            k, tt, fval = cpu_reference_solve(args, An, bn, x0n, mu, opts, 2)
-            line["cpu_baseline"] = {"value": k / tt, "unit": UNIT, "cores": blas_threads(), "kind": "port",
-                                    "sample": "%d iterations (maxit=2 per stage) of the full-size workload, "
-                                              "oracle port of the reference on NumPy/BLAS" % k,
+            k, tt, fval, fh, kind, threads = cpu_solve(args.algo, An, bn, x0n, mu, opts["alpha0"], CPU_SAMPLE_MAXIT)
+            line["cpu_baseline"] = {"value": k / tt, "unit": UNIT, "cores": threads, "kind": kind,
+                                    "sample": "%d iterations (maxit=%d per stage) of the full-size workload on the inputs "
+                                              "downloaded from HBM; %s on NumPy/BLAS" % (
+                                                  k, CPU_SAMPLE_MAXIT, "unmodified reference solver (oracle/_ref)"
+                                                  if kind == "reference" else "oracle port of the reference"),
                                     "seconds": tt}
+            par = line.get("parity", {})
+            if "gpu_fval" in par:
+                gh = np.asarray(par["gpu_f_hist"])
+                ch = np.asarray(fh)
+                par["cpu_fval"] = fval
+                par["cpu_arithmetic"] = "NumPy %s (what the reference computes on these arrays)" % An.dtype
+                par["rel_diff"] = abs(par["gpu_fval"] - fval) / abs(fval)
+                par["iters_match"] = bool(par["iters"] == k)
+                par["f_hist_max_rel_diff"] = (float(np.max(np.abs(gh - ch) / np.abs(ch)))
+                                              if gh.shape == ch.shape and ch.size else None)
+                par["ok"] = bool(par["rel_diff"] <= par["bar"] and par["iters_match"])
         else:
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": blas_threads(), "kind": "port",
                                     "sample": "skipped: host RAM too small"}
+    if "parity" in line and isinstance(line["parity"], dict):
+        line["parity"].pop("gpu_f_hist", None)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()

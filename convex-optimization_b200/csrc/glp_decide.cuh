@@ -29,6 +29,7 @@ struct DecideArgs {
   double* state[2];           // [3][l][ldn]
   double* f_hist;
   double* f_hist_best;
+  double* s_hist;             // nullable: sparsity of every recorded iterate (the reference's sparsity_hist)
   unsigned* r_amax;           // nullable (fp16-pair wide mode): float bits of max|r|, zeroed before the launch
 };
 
@@ -86,7 +87,7 @@ glp_decide_kernel(const DecideArgs a, const Geom g) {
     }
     const bool writer = blockIdx.x == 0;
     decide_step(a.sc, cin, red, double(g.n_total) * double(g.l), s_out, s_act,
-                writer ? a.f_hist : nullptr, writer ? a.f_hist_best : nullptr);
+                writer ? a.f_hist : nullptr, writer ? a.f_hist_best : nullptr, writer ? a.s_hist : nullptr);
     if (s_act.action == GLP_ACT_ITERATE) s_out.gy_sel = 1 - cin.gy_sel;
     if (writer) *a.cout = s_out;
   }

@@ -7,7 +7,7 @@
 // stable_len, the `while inner_iter < maxit` bound, the mu-continuation stage switch (v and t reset
 // for FProxGD) and the step rule of the next iteration.
 // Compiled for the device (decide kernel, persistent kernel) and for the host (CPU unit test
-// against the golden vectors: tests/test_decide_host.py builds it with g++ -ffp-contract=off).
+// against the golden vectors: tests/test_host_logic.py builds it through tests/host_shim with g++ -ffp-contract=off).
 #pragma once
 #include <math.h>
 #include <stdint.h>
@@ -87,9 +87,9 @@ GLP_HDI double bb_step(const SolveConst& sc, double t, const Reduced& red) {
   return bb < lo ? lo : (bb > hi ? hi : bb);
 }
 
-// f_hist may be null (then values are not stored).  size_total = n_total * l.
+// f_hist / f_hist_best / s_hist may be null (then values are not stored).  size_total = n_total * l.
 GLP_HDI void decide_step(const SolveConst& sc, const Ctrl& in, const Reduced& red, double size_total,
-                         Ctrl& out, DecideOut& act, double* f_hist, double* f_hist_best) {
+                         Ctrl& out, DecideOut& act, double* f_hist, double* f_hist_best, double* s_hist = nullptr) {
   out = in;
   act.action = GLP_ACT_NONE; act.reset_v = 0; act.first_commit = in.first_commit;
   act.new_cur = in.cur; act.theta_old = in.theta;
@@ -148,6 +148,7 @@ GLP_HDI void decide_step(const SolveConst& sc, const Ctrl& in, const Reduced& re
       if (f_hist != nullptr && out.k < sc.hist_cap) f_hist[out.k] = out.f_cur;
       out.f_best = out.f_cur < out.f_best ? out.f_cur : out.f_best;  // min(f_best, f_now)
       if (f_hist_best != nullptr && out.k < sc.hist_cap) f_hist_best[out.k] = out.f_best;
+      if (s_hist != nullptr && out.k < sc.hist_cap) s_hist[out.k] = out.s_cur;   // sparsity_hist (:116 / :119)
       out.k += 1;
       out.inner += 1;
       bool stable_now = false;

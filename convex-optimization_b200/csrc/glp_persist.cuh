@@ -39,6 +39,7 @@ struct PersistArgs {
   Ctrl* ctrl_out;
   double* f_hist;
   double* f_hist_best;
+  double* s_hist;
   SolveConst sc;
   int32_t m, n, l, nc;    // nc = columns per CTA (multiple of 2)
   int64_t ldm, ldn;
@@ -327,7 +328,7 @@ glp_persist_kernel(const PersistArgs a) {
       if (lane == 0) {
         Reduced red = {rr_tot, gd, dd, reg, cn, r_gy, sx, sy};
         decide_step(a.sc, *s_ctrl, red, double(a.n) * double(L), *s_new, *s_act, rank == 0 ? a.f_hist : nullptr,
-                    rank == 0 ? a.f_hist_best : nullptr);
+                    rank == 0 ? a.f_hist_best : nullptr, rank == 0 ? a.s_hist : nullptr);
         *s_ctrl = *s_new;
       }
     }

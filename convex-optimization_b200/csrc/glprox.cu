@@ -128,8 +128,9 @@ struct glp_handle {
   unsigned *f_counter = nullptr, *t_counter = nullptr;
   Ctrl* ctrl = nullptr;  // [2]
   int32_t* fault = nullptr;
-  double *f_hist = nullptr, *f_hist_best = nullptr;
+  double *f_hist = nullptr, *f_hist_best = nullptr, *s_hist = nullptr;   // one allocation: [3][hist_cap]
   int hist_cap = 0;
+  int last_k = 0;                  // recorded iterations of the last finished solve (glp_solve_sparsity_hist)
   int decide_grid = 0;
   int n_fchunks = 0;
 
@@ -1053,10 +1054,12 @@ static int phase_prepare(glp_handle* h, int algo, const void* x0_dev, double mu0
   if (h->hist_cap < sc.hist_cap) {
     if (h->f_hist) CU_TRY(cudaFree(h->f_hist));
     h->f_hist = nullptr;
-    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->f_hist), size_t(2) * sc.hist_cap * sizeof(double)));
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->f_hist), size_t(3) * sc.hist_cap * sizeof(double)));
     h->hist_cap = sc.hist_cap;
   }
   h->f_hist_best = h->f_hist + h->hist_cap;
+  h->s_hist = h->f_hist + 2 * size_t(h->hist_cap);
+  h->last_k = 0;
   h->n_launches = 0;
   h->n_gemm = 0;
   if (wide_active(h)) GLP_TRY(ensure_wide(h));
@@ -1132,7 +1135,7 @@ static int phase_decide(glp_handle* h) {
   d.gy_partial[0] = h->gy_partial[0]; d.gy_partial[1] = h->gy_partial[1]; d.n_gy = h->decide_grid;
   d.AX[0] = h->AX[0]; d.AX[1] = h->AX[1]; d.Av = h->Av; d.b = h->b; d.r = h->r;
   d.state[0] = h->state[0]; d.state[1] = h->state[1];
-  d.f_hist = h->f_hist; d.f_hist_best = h->f_hist_best;
+  d.f_hist = h->f_hist; d.f_hist_best = h->f_hist_best; d.s_hist = h->s_hist;
   if (wide_active(h) && wide_passes(h) == 4) {
     CU_TRY(cudaMemsetAsync(h->f16_amax + 1, 0, sizeof(unsigned), h->stream));
     d.r_amax = h->f16_amax + 1;
@@ -1229,6 +1232,7 @@ extern "C" int glp_solve_end(glp_handle* h, void* x_out_dev, glp_result* res, do
   GLP_TRY(check_fault(h, cudaStreamSynchronize(h->stream)));
   const Ctrl c = h->h_ctrl[0];
   h->solving = false;
+  h->last_k = std::min(c.k, h->sc.hist_cap);
   if (res) memset(res, 0, sizeof(*res));
   if (fault != 0) {
     if (res) res->status = GLP_ERR_DEVICE_FAULT;
@@ -1353,7 +1357,8 @@ static int drive_until_done(glp_handle** hs, int G, const glp_opts* o) {
   // Host runs ahead of the device: batch i+1 is enqueued before the control snapshot taken after
   // batch i is inspected, so the stream never drains while the solve is in progress.
   glp_handle* h0 = hs[0];
-  const int64_t max_slots = int64_t(3) * o->maxit * (int64_t(o->maxit_line_search_iter) + 1) + 8;
+  // a negative maxit_line_search_iter is an empty range() in the reference (alpha0 taken untested): one trial per iteration
+  const int64_t max_slots = int64_t(3) * o->maxit * (std::max<int64_t>(o->maxit_line_search_iter, 0) + 1) + 8;
   const int batch = o->poll_interval > 0 ? o->poll_interval : 32;
   int64_t issued = 0;
   int pending = -1;  // snapshot slot whose event has not been inspected yet
@@ -1434,7 +1439,7 @@ static int enqueue_persist(glp_handle* h, const PersistPlan& pl) {
   a.A = h->A; a.lda = h->lda; a.b = h->b;
   a.x0 = h->state[1]; a.x_out = h->state[0];
   a.ctrl_out = &h->ctrl[0];
-  a.f_hist = h->f_hist; a.f_hist_best = h->f_hist_best;
+  a.f_hist = h->f_hist; a.f_hist_best = h->f_hist_best; a.s_hist = h->s_hist;
   a.sc = h->sc;
   a.m = h->g.m; a.n = h->g.n; a.l = h->g.l; a.nc = pl.nc;
   a.ldm = h->g.ldm; a.ldn = h->g.ldn;
@@ -2110,7 +2115,7 @@ extern "C" int glp_admm_dual(glp_handle* h, const void* x0_dev, double mu, const
   if (h->hist_cap < ac.hist_cap) {
     if (h->f_hist) CU_TRY(cudaFree(h->f_hist));
     h->f_hist = nullptr;
-    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->f_hist), size_t(2) * ac.hist_cap * sizeof(double)));
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->f_hist), size_t(3) * ac.hist_cap * sizeof(double)));
     h->hist_cap = ac.hist_cap;
   }
   h->f_hist_best = h->f_hist + h->hist_cap;
@@ -2292,3 +2297,5 @@ extern "C" int glp_randn(void* dst_dev, int dtype, int64_t rows, int64_t cols, i
 // without NCCL and has no link-time dependency on torch's bundled copy.
 // ------------------------------------------------------------------------------------------------
 #include "glp_nccl.inl"
+
+#include "glp_abi_step.inl"

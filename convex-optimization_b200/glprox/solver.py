@@ -118,11 +118,16 @@ def _format_out(res, f_hist, tt):
     }
 
 
-def _raise_for(rc):
+def _raise_for(rc, res=None):
     if rc == _lib.GLP_ERR_UNBOUND:
         # gl_FProxGD_primal.py:156,161 with maxit == 0
         raise UnboundLocalError("cannot access local variable 'x' where it is not associated with a value")
     _lib.check(rc)
+    if res is not None and res.status != _lib.GLP_OK:
+        # the library returned before the device-side state machine reached `done`: never hand a truncated
+        # solve back as a normal (x, k, out)
+        raise RuntimeError("libglprox: solve ended with status %d before the stop rule or the iteration budget was "
+                           "reached (k=%d)" % (res.status, res.iters))
 
 
 def _mode_dtype(A_dtype, merged):
@@ -136,13 +141,38 @@ def _mode_dtype(A_dtype, merged):
     return table[want]
 
 
-def _log_history(f_hist, res):
-    """The reference emits these at DEBUG level while iterating (gl_*_primal.py:45,54,134-136);
-    here they are reproduced after the fact from the device-recorded history."""
+def _log_history(f_hist, res, merged=None, mu_0=None, s_hist=None):
+    """The reference's DEBUG lines (gl_ProxGD_primal.py:45,54,134-136 / gl_FProxGD_primal.py:45,56,149-151), in the
+    reference's order, reproduced after the solve from what the device recorded: `alpha0=` once, `new mu=` at
+    the start of every continuation stage, and every 100th iteration `iter / objective / sparsity`, where the
+    objective is the one recorded AT iteration k and the sparsity is that of the iterate PRODUCED by iteration
+    k (the reference prints sparsity_func(x) of the new x): s_hist[k] when the next iteration recorded it, the
+    returned iterate's sparsity when k is the last iteration."""
     if not logger.isEnabledFor(logging.DEBUG):
         return
-    for k in range(100, len(f_hist) + 1, 100):
-        logger.debug("iter= {:5}, objective= {:10E}".format(k, float(f_hist[k - 1])))
+    if merged is not None:
+        logger.debug("alpha0= {:10E}".format(float(merged["alpha0"])))
+    stage_end = [int(v) for v in res.stage_end]
+    k_total = len(f_hist)
+    start = 0
+    for stage, factor in enumerate((100.0, 10.0, 1.0)):
+        if mu_0 is not None:
+            logger.debug("new mu= {:10E}".format(factor * mu_0))
+        end = stage_end[stage] if stage_end[stage] > 0 or stage == 0 else start
+        end = min(max(end, start), k_total)
+        # a stage shorter than maxit ended on the stop rule: the reference breaks before it reaches the log line
+        # of that last iteration (:123-125 / :132-134)
+        broke = merged is not None and (end - start) < int(merged["maxit"])
+        for k in range(start + 1, end + 1):
+            if k % 100 == 0 and not (broke and k == end):
+                if s_hist is not None and k < len(s_hist):
+                    sp = float(s_hist[k])
+                elif k == k_total:
+                    sp = float(res.sparsity)
+                else:
+                    sp = float("nan")
+                logger.debug("iter= {:5}, objective= {:10E}, sparsity= {:3f}".format(k, float(f_hist[k - 1]), sp))
+        start = end
 
 
 def solve(algo, x0, A, b, mu_0, opts):
@@ -159,8 +189,9 @@ def solve(algo, x0, A, b, mu_0, opts):
     mode = _tensor_mode(merged)
     if merged.get("dist"):
         return _solve_numpy_sharded(algo, x0, A, b, mu_0, merged, o)
-    if mode != 0:
-        # the one-shot host entry point always uses the default tensor mode; explicit modes go through a handle
+    if mode != 0 or logger.isEnabledFor(logging.DEBUG):
+        # the one-shot host entry point always uses the default tensor mode and keeps no handle to read the
+        # sparsity history from (DEBUG log lines): explicit modes and DEBUG logging go through a handle
         import torch
         dt = _mode_dtype(np.asarray(A).dtype, merged)
         dev = torch.device("cuda", int(merged.get("device", 0)))
@@ -194,10 +225,10 @@ def _solve_numpy(algo, x0, A, b, mu_0, merged, o):
                             _lib.GLP_F32 if dt == np.float32 else _lib.GLP_F64, m, n, l,
                             Ac.ctypes.data, Ac.strides[0] // Ac.itemsize, bc.ctypes.data, x0c.ctypes.data,
                             float(mu_0), C.byref(o), x.ctypes.data, C.byref(res), f_hist.ctypes.data, cap)
-    _raise_for(rc)
+    _raise_for(rc, res)
     tt = time.perf_counter() - t0
     fh = f_hist[:res.iters]
-    _log_history(fh, res)
+    _log_history(fh, res, merged, float(mu_0))
     return x, int(res.iters), _format_out(res, fh, tt)
 
 
@@ -251,6 +282,11 @@ class GroupLassoProblem:
             Ap[:, :A.shape[1]] = A
             A = Ap[:, :A.shape[1]]
         self.A = A
+        if not isinstance(b, torch.Tensor) or b.dim() != 2 or b.shape[0] != A.shape[0] or b.shape[1] < 1:
+            # the reference fails with NumPy's shape error in A @ x - b (gl_ProxGD_primal.py:25); the C ABI takes raw
+            # pointers, so the check has to happen here
+            raise ValueError("b must be a 2-D tensor of shape (%d, l), got %s" % (
+                A.shape[0], tuple(b.shape) if isinstance(b, torch.Tensor) else type(b).__name__))
         self.b = b.to(device=A.device, dtype=A.dtype).contiguous()
         self.m, self.n = A.shape
         self.l = self.b.shape[1]
@@ -295,6 +331,31 @@ class GroupLassoProblem:
         import torch
         return torch.cuda.device(self.device)
 
+    def _iterate(self, x, what="x0"):
+        """Validate an (n_local, l) iterate and bring it to the handle's device / dtype.  The library reads n*l
+        elements from the raw pointer whatever the tensor holds, so a wrong shape must be refused here (the
+        reference raises NumPy's broadcasting error at its first product)."""
+        import torch
+        if not isinstance(x, torch.Tensor):
+            raise ValueError("%s must be a torch tensor on the handle path (NumPy arrays take the gl_* entry points)" % what)
+        if x.dim() != 2 or tuple(x.shape) != (self.n, self.l):
+            raise ValueError("%s must have shape (%d, %d), got %s" % (what, self.n, self.l, tuple(x.shape)))
+        return x.to(device=self.device, dtype=self.dtype).contiguous()
+
+    def _order_after_caller(self):
+        """Casts / copies of the arguments ran on the caller's current stream; the library launches on the stream
+        captured at construction.  Make the latter wait for the former (no-op when they are the same stream)."""
+        import torch
+        cur = torch.cuda.current_stream(self.device)
+        if cur.cuda_stream != self.stream.cuda_stream:
+            self.stream.wait_stream(cur)
+
+    def _order_before_caller(self):
+        import torch
+        cur = torch.cuda.current_stream(self.device)
+        if cur.cuda_stream != self.stream.cuda_stream:
+            cur.wait_stream(self.stream)
+
     def close(self):
         if self._h:
             _lib.load().glp_destroy(self._h)
@@ -316,20 +377,24 @@ class GroupLassoProblem:
         merged = merge_opts(algo, opts)
         o = pack_opts(algo, merged)
         mode = _tensor_mode(merged)
-        x0d = x0.to(device=self.device, dtype=self.dtype).contiguous()
+        x0d = self._iterate(x0)
         x = torch.empty_like(x0d)
         cap = 3 * int(o.maxit) + 8
         f_hist = np.empty(cap, dtype=np.float64)
         res = _lib.GlpResult()
         t0 = time.perf_counter()
         with torch.cuda.device(self.device):
+            self._order_after_caller()
             _lib.check(lib.glp_set_tensor_mode(self._h, mode))
             rc = lib.glp_solve(self._h, ALGO_ID[algo], x0d.data_ptr(), float(mu_0), C.byref(o), x.data_ptr(),
                                C.byref(res), f_hist.ctypes.data, cap)
-        _raise_for(rc)
+        _raise_for(rc, res)
         tt = time.perf_counter() - t0
         fh = f_hist[:res.iters]
-        _log_history(fh, res)
+        if logger.isEnabledFor(logging.DEBUG):
+            s_hist = np.empty(max(int(res.iters), 1), dtype=np.float64)
+            got = lib.glp_solve_sparsity_hist(self._h, s_hist.ctypes.data, int(res.iters))
+            _log_history(fh, res, merged, float(mu_0), s_hist[:max(got, 0)])
         return x, int(res.iters), _format_out(res, fh, tt)
 
     def metrics(self, x, ref=None, mu=0.0, group=None):
@@ -341,10 +406,9 @@ class GroupLassoProblem:
         is taken against the global max) and the objective is left to the solve's out["fval"]."""
         import torch
         lib = _lib.load()
-        xd = x.to(device=self.device, dtype=self.dtype).contiguous()
-        rd = None if ref is None else ref.to(device=self.device, dtype=self.dtype).contiguous()
-        if xd.shape != (self.n, self.l) or (rd is not None and rd.shape != xd.shape):
-            raise ValueError("x / ref must be (%d, %d)" % (self.n, self.l))
+        xd = self._iterate(x, "x")
+        rd = None if ref is None else self._iterate(ref, "ref")
+        self._order_after_caller()
         met = _lib.GlpMetrics()
         call = lambda mx: _lib.check(lib.glp_metrics_eval(self._h, xd.data_ptr(), rd.data_ptr() if rd is not None else None,
                                                           float(mu), float(mx), C.byref(met)))
@@ -375,13 +439,14 @@ class GroupLassoProblem:
         merged.update(opts or {})
         o = _lib.GlpAdmmOpts(maxit=int(merged["maxit"]), converge_len=int(merged["converge_len"]),
                              thres=float(merged["thres"]), tau=float(merged["tau"]), rho=float(merged["rho"]))
-        x0d = x0.to(device=self.device, dtype=self.dtype).contiguous()
+        x0d = self._iterate(x0)
         x = torch.empty_like(x0d)
         cap = int(o.maxit) + 8
         f_hist = np.empty(cap, dtype=np.float64)
         res = _lib.GlpResult()
         t0 = time.perf_counter()
         with torch.cuda.device(self.device):
+            self._order_after_caller()
             _lib.check(lib.glp_admm_dual(self._h, x0d.data_ptr(), float(mu), C.byref(o), x.data_ptr(), C.byref(res),
                                          f_hist.ctypes.data, cap))
         tt = time.perf_counter() - t0
@@ -504,7 +569,11 @@ def solve_group(probs, algo, x0_shards, mu_0, opts=None):
     G = len(probs)
     merged = merge_opts(algo, opts)
     o = pack_opts(algo, merged)
-    x0d = [x0.to(device=p.device, dtype=p.dtype).contiguous() for p, x0 in zip(probs, x0_shards)]
+    if len(x0_shards) != G:
+        raise ValueError("expected %d x0 shards, got %d" % (G, len(x0_shards)))
+    x0d = [p._iterate(x0, "x0 shard %d" % i) for i, (p, x0) in enumerate(zip(probs, x0_shards))]
+    for p in probs:
+        p._order_after_caller()
     xs = [torch.empty_like(x) for x in x0d]
     cap = 3 * int(o.maxit) + 8
     f_hist = np.empty(cap, dtype=np.float64)
@@ -514,7 +583,7 @@ def solve_group(probs, algo, x0_shards, mu_0, opts=None):
     xp = (C.c_void_p * G)(*[x.data_ptr() for x in xs])
     t0 = time.perf_counter()
     rc = lib.glp_group_solve(hs, G, ALGO_ID[algo], x0p, float(mu_0), C.byref(o), xp, res, f_hist.ctypes.data, cap)
-    _raise_for(rc)
+    _raise_for(rc, res[0])
     tt = time.perf_counter() - t0
     fh = f_hist[:res[0].iters]
     out = _format_out(res[0], fh, tt)

@@ -146,6 +146,37 @@ int glp_solve_step(glp_handle* h, int slots);
 int glp_solve_poll(glp_handle* h, glp_result* res);
 int glp_solve_end(glp_handle* h, void* x_out_dev, glp_result* res, double* f_hist_host, int hist_cap);
 
+/* ---- K3 step level: the control state machine of the solvers on the device -----------------------------
+ * Replaces one pass through the scalar control flow of gl_ProxGD_primal.py:53,76,103-132 /
+ * gl_FProxGD_primal.py:55,68-69,79,108-147: sufficient-decrease test of the pending trial, step shrink,
+ * commit, f_hist / f_hist_best / sparsity bookkeeping, the two-ratio stop rule, the mu-continuation stage
+ * switch and the step rule of the next iteration.  The PODs mirror the library's internal control blocks. */
+typedef struct glp_solve_const {
+  int32_t algo, step_type, maxit, stable_cap, ls_cap, hist_cap;
+  double thres, alpha0, ftol, atten, mu0, delta;
+} glp_solve_const;
+typedef struct glp_ctrl {
+  int32_t done, stage, inner, k, stable, trial, cur, retry, tested, first_commit, ran_any, fault;
+  int32_t stage_end[3];
+  int32_t gy_sel;
+  double t, t_k, theta, mu, f_cur, s_cur, f_prev, s_prev, f_best, g_base;
+  int64_t n_fwd, n_tpass;
+} glp_ctrl;
+typedef struct glp_reduced { double rr, gd, dd, reg, cnt, gbase, sx, sy; } glp_reduced;
+typedef struct glp_decide_out {
+  int32_t action;       /* 0 none, 1 retry (trial rejected), 2 iterate (candidate committed), 3 finish */
+  int32_t reset_v, first_commit, new_cur;
+  double theta_old;
+} glp_decide_out;
+/* Applies the device build of the state machine to `count` independent (ctrl_in, reduced) pairs (host arrays in,
+ * host arrays out).  hist3_host (nullable): [count][3] = the (f_hist, f_hist_best, sparsity_hist) entry the step
+ * recorded, NaN where it recorded none.  size_total = n_total * l (sparsity denominator). */
+int glp_decide(int device, const glp_solve_const* sc, const glp_ctrl* ctrl_in_host, const glp_reduced* red_host,
+               double size_total, glp_ctrl* ctrl_out_host, glp_decide_out* act_host, double* hist3_host, int count);
+/* sparsity_hist of the last finished solve (gl_ProxGD_primal.py:116 / gl_FProxGD_primal.py:119): copies
+ * min(cap, iters) values, returns how many (>= 0) or a negative glp_status. */
+int glp_solve_sparsity_hist(glp_handle* h, double* out_host, int cap);
+
 /* ---- measurement: CUDA-event timing of every streaming launch on the handle's stream ------------
  * With profiling on, each forward / transposed launch of a solve is bracketed by a pair of events;
  * glp_get_profile (after glp_solve/glp_solve_end) aggregates the launches that actually streamed A

@@ -62,8 +62,9 @@ def shim():
     return _shim
 
 
-def emulate(algo, x0, A, b, mu0, opts=None, matmul=None, rmatmul=None, n_shards=1):
-    """Run the GPU schedule on the CPU.  Returns (x, k, out, info)."""
+def emulate(algo, x0, A, b, mu0, opts=None, matmul=None, rmatmul=None, n_shards=1, decide_log=None):
+    """Run the GPU schedule on the CPU.  Returns (x, k, out, info).  decide_log, if a list, receives one
+    (SolveConst, Ctrl in, Reduced, size_total, Ctrl out, DecideOut, (f, f_best) recorded or None) per decide step."""
     lib = shim()
     o = dict(orc.DEFAULTS[algo])
     o.update(opts or {})
@@ -107,8 +108,14 @@ def emulate(algo, x0, A, b, mu0, opts=None, matmul=None, rmatmul=None, n_shards=
         red = Reduced(rr=rr, gd=scal["gd"], dd=scal["dd"], reg=scal["reg"], cnt=cnt, gbase=gy[cin.gy_sel],
                       sx=scal["sx"], sy=scal["sy"])
         act = DecideOut()
+        k_before = cin.k
+        cin_copy = Ctrl.from_buffer_copy(cin)
         lib.shim_decide(C.byref(sc), C.byref(cin), C.byref(red), float(n * l), C.byref(cout), C.byref(act),
                         f_hist.ctypes.data, f_best.ctypes.data)
+        if decide_log is not None:
+            rec = (float(f_hist[k_before]), float(f_best[k_before])) if cout.k > k_before else None
+            decide_log.append((sc, cin_copy, Reduced.from_buffer_copy(red), float(n * l), Ctrl.from_buffer_copy(cout),
+                               DecideOut.from_buffer_copy(act), rec))
         if act.action == ACT_ITERATE:
             cout.gy_sel = 1 - cin.gy_sel
         j += 1

@@ -72,3 +72,52 @@ def test_partition_covers_every_tile_once_and_slots_are_unique():
             for c in touching:
                 assert (c + blk) not in slots and c + blk < G + nblk
                 slots.add(c + blk)
+
+
+def test_handle_path_refuses_wrong_shapes():
+    """the C ABI takes raw pointers, so b / x0 / x / ref shapes are validated on the host before any
+    library call (the reference raises NumPy's shape error at its first product)."""
+    import torch
+    from glprox.solver import GroupLassoProblem
+    p = object.__new__(GroupLassoProblem)
+    p.n, p.l, p.device, p.dtype = 12, 2, torch.device("cpu"), torch.float64
+    good = torch.zeros(12, 2)
+    assert p._iterate(good).shape == (12, 2) and p._iterate(good).dtype == torch.float64
+    for bad in (torch.zeros(12, 3), torch.zeros(11, 2), torch.zeros(24), torch.zeros(12, 2, 1), np.zeros((12, 2))):
+        with pytest.raises(ValueError):
+            p._iterate(bad)
+    # constructor: A must be a CUDA tensor (no CPU fallback), checked before b
+    with pytest.raises(ValueError):
+        GroupLassoProblem(torch.zeros(4, 8), torch.zeros(4, 2))
+
+
+def test_truncated_solve_is_an_error():
+    from glprox import _lib
+    from glprox.solver import _raise_for
+    res = _lib.GlpResult()
+    res.status = _lib.GLP_OK
+    _raise_for(_lib.GLP_OK, res)
+    res.status, res.iters = _lib.GLP_ERR_STATE, 7
+    with pytest.raises(RuntimeError):
+        _raise_for(_lib.GLP_OK, res)
+
+
+def test_debug_log_lines_follow_the_reference_format(caplog):
+    """_log_history (host side of SURVEY 8a-14): alpha0=, new mu= per stage, every 100th iteration with the
+    sparsity of the iterate produced by that iteration, nothing for the iteration a stage broke on."""
+    import logging
+    from glprox import _lib
+    from glprox.solver import _log_history
+    res = _lib.GlpResult()
+    res.iters, res.sparsity = 450, 0.125
+    res.stage_end[0], res.stage_end[1], res.stage_end[2] = 200, 300, 450      # stage 2 broke early at k=300
+    f = np.arange(1, 451, dtype=np.float64)
+    s = np.linspace(0.9, 0.1, 450)
+    with caplog.at_level(logging.DEBUG, logger="opt"):
+        _log_history(f, res, {"alpha0": 1e-3, "maxit": 200}, 1e-2, s)
+    msgs = [r.getMessage() for r in caplog.records]
+    assert msgs[0] == "alpha0= {:10E}".format(1e-3)
+    assert msgs[1] == "new mu= {:10E}".format(1.0) and "new mu= {:10E}".format(0.1) in msgs and "new mu= {:10E}".format(1e-2) in msgs
+    iters = [m for m in msgs if m.startswith("iter=")]
+    assert iters[0] == "iter= {:5}, objective= {:10E}, sparsity= {:3f}".format(100, 100.0, s[100])
+    assert [int(m.split(",")[0].split("=")[1]) for m in iters] == [100, 200, 400]   # 300: the stage broke there
