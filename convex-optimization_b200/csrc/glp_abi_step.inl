@@ -18,12 +18,19 @@ __global__ void glp_decide_probe_kernel(const SolveConst sc, const Ctrl* __restr
   const Ctrl cin = in[i];
   Ctrl cout;
   DecideOut a;
-  // decide_step records at index k of the history arrays: give every state a private 3-word window
-  double* win = hist + size_t(3) * i;
-  win[0] = win[1] = win[2] = __longlong_as_double(0x7ff8000000000000ll);
+  // decide_step records at index k, k+1, ... of the history arrays (one entry, or one per stage it crosses: a stage
+  // that ends on the stop rule is followed by the first record of the next stage in the same step): give every state
+  // a private window per array and report the first entry
+  const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+  double wf[4] = {qnan, qnan, qnan, qnan}, wb[4] = {qnan, qnan, qnan, qnan}, ws[4] = {qnan, qnan, qnan, qnan};
+  SolveConst scl = sc;
   const bool fits = cin.k >= 0 && cin.k < sc.hist_cap;
-  decide_step(sc, cin, red[i], size_total, cout, a, fits ? win - cin.k : nullptr, fits ? win + 1 - cin.k : nullptr,
-              fits ? win + 2 - cin.k : nullptr);
+  scl.hist_cap = fits ? min(sc.hist_cap, cin.k + 4) : sc.hist_cap;
+  decide_step(scl, cin, red[i], size_total, cout, a, fits ? wf - cin.k : nullptr, fits ? wb - cin.k : nullptr,
+              fits ? ws - cin.k : nullptr);
+  hist[size_t(3) * i + 0] = wf[0];
+  hist[size_t(3) * i + 1] = wb[0];
+  hist[size_t(3) * i + 2] = ws[0];
   out[i] = cout;
   act[i] = a;
 }

@@ -130,11 +130,9 @@ struct GatherArgs {
 };
 constexpr int GATHER_THREADS = 256;
 
-__global__ void __launch_bounds__(GATHER_THREADS)
-glp_gather_kernel(const GatherArgs a, const Geom g) {
-  __shared__ double s_red[GATHER_THREADS / 32];
-  if (a.ctrl != nullptr && a.ctrl->done) return;
-  const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : a.sel;
+// The gather proper: executed by every CTA of a grid of GATHER_THREADS-wide CTAs (the stand-alone gather kernel, or the
+// first half of the fused gather + decide kernel).
+__device__ __forceinline__ void gather_phase(const GatherArgs& a, const Geom& g, int sel, double* s_red) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int W = a.comm.world, me = a.comm.rank;
   if (tid < W) wait_flag(mail_flag(a.comm, me, MAIL_FLAG_AX, tid), a.seq_f, a.fault);
@@ -174,6 +172,16 @@ glp_gather_kernel(const GatherArgs a, const Geom g) {
       a.cnt_red[0] = cnt;
     }
   }
+}
+
+__global__ void __launch_bounds__(GATHER_THREADS)
+glp_gather_kernel(const GatherArgs a, const Geom g) {
+  __shared__ double s_red[GATHER_THREADS / 32];
+  pdl_wait();
+  pdl_launch();
+  if (a.ctrl != nullptr && a.ctrl->done) return;
+  const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : a.sel;
+  gather_phase(a, g, sel, s_red);
 }
 
 }  // namespace glp

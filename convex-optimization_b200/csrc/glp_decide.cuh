@@ -39,20 +39,19 @@ __device__ __forceinline__ double dec_nmax(double a, double b) {
   return (a != a) ? a : ((b != b) ? b : fmax(a, b));
 }
 
-template <typename T>
-__global__ void __launch_bounds__(DECIDE_THREADS)
-glp_decide_kernel(const DecideArgs a, const Geom g) {
-  __shared__ double s_part[DECIDE_THREADS / 32][8];
-  __shared__ Ctrl s_out;
-  __shared__ DecideOut s_act;
-  __shared__ double s_gy[DECIDE_THREADS / 32];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const Ctrl cin = *a.cin;
+// Shared-memory scratch of the decide phase (one instance per CTA).
+struct DecideSmem {
+  double part[DECIDE_THREADS / 32][8];
+  Ctrl out;
+  DecideOut act;
+  double gy[DECIDE_THREADS / 32];
+};
 
-  if (cin.done) {  // keep both control blocks identical once finished
-    if (blockIdx.x == 0 && tid == 0) *a.cout = cin;
-    return;
-  }
+// The decide phase proper, executed by every CTA of a grid of DECIDE_THREADS-wide CTAs (the stand-alone decide
+// kernel, or the second half of the fused gather + decide kernel of the multi-GPU path).
+template <typename T>
+__device__ __forceinline__ void decide_phase(const DecideArgs& a, const Geom& g, const Ctrl& cin, DecideSmem& sm) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   // ---- (a) fixed-order reductions: strided per thread, shuffle tree per warp, warps in order
   double v_rr = 0.0, v_gd = 0.0, v_dd = 0.0, v_reg = 0.0, v_cnt = 0.0, v_gy = 0.0, v_sx = 0.0, v_sy = 0.0;
@@ -71,9 +70,9 @@ glp_decide_kernel(const DecideArgs a, const Geom g) {
   v_reg = warp_sum(v_reg); v_cnt = warp_sum(v_cnt); v_gy = warp_sum(v_gy);
   v_sx = warp_sum(v_sx); v_sy = warp_sum(v_sy);
   if (lane == 0) {
-    s_part[warp][0] = v_rr; s_part[warp][1] = v_gd; s_part[warp][2] = v_dd;
-    s_part[warp][3] = v_reg; s_part[warp][4] = v_cnt; s_part[warp][5] = v_gy;
-    s_part[warp][6] = v_sx; s_part[warp][7] = v_sy;
+    sm.part[warp][0] = v_rr; sm.part[warp][1] = v_gd; sm.part[warp][2] = v_dd;
+    sm.part[warp][3] = v_reg; sm.part[warp][4] = v_cnt; sm.part[warp][5] = v_gy;
+    sm.part[warp][6] = v_sx; sm.part[warp][7] = v_sy;
   }
   __syncthreads();
 
@@ -81,23 +80,23 @@ glp_decide_kernel(const DecideArgs a, const Geom g) {
   if (tid == 0) {
     Reduced red = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     for (int w = 0; w < DECIDE_THREADS / 32; ++w) {
-      red.rr += s_part[w][0]; red.gd += s_part[w][1]; red.dd += s_part[w][2];
-      red.reg += s_part[w][3]; red.cnt += s_part[w][4]; red.gbase += s_part[w][5];
-      red.sx += s_part[w][6]; red.sy += s_part[w][7];
+      red.rr += sm.part[w][0]; red.gd += sm.part[w][1]; red.dd += sm.part[w][2];
+      red.reg += sm.part[w][3]; red.cnt += sm.part[w][4]; red.gbase += sm.part[w][5];
+      red.sx += sm.part[w][6]; red.sy += sm.part[w][7];
     }
     const bool writer = blockIdx.x == 0;
-    decide_step(a.sc, cin, red, double(g.n_total) * double(g.l), s_out, s_act,
+    decide_step(a.sc, cin, red, double(g.n_total) * double(g.l), sm.out, sm.act,
                 writer ? a.f_hist : nullptr, writer ? a.f_hist_best : nullptr, writer ? a.s_hist : nullptr);
-    if (s_act.action == GLP_ACT_ITERATE) s_out.gy_sel = 1 - cin.gy_sel;
-    if (writer) *a.cout = s_out;
+    if (sm.act.action == GLP_ACT_ITERATE) sm.out.gy_sel = 1 - cin.gy_sel;
+    if (writer) *a.cout = sm.out;
   }
   __syncthreads();
-  if (s_act.action != GLP_ACT_ITERATE) return;
+  if (sm.act.action != GLP_ACT_ITERATE) return;
 
   // ---- (c) vector work of the commit, sliced over the grid
-  const int nc = s_act.new_cur;
+  const int nc = sm.act.new_cur;
   const bool accel = a.sc.algo == ALGO_FPROXGD || a.sc.algo == ALGO_FGD;
-  const double th_old = s_act.theta_old, th = s_out.theta, omt = xsub(1.0, th);
+  const double th_old = sm.act.theta_old, th = sm.out.theta, omt = xsub(1.0, th);
   const int64_t lenm = int64_t(g.l) * g.ldm, lenn = int64_t(g.l) * g.ldn;
   const double* Axn = a.AX[nc];
   const double* Axnt = a.AX[nc] + lenm;
@@ -110,16 +109,16 @@ glp_decide_kernel(const DecideArgs a, const Geom g) {
     double base;
     if (accel) {
       double av;
-      if (s_act.reset_v) {
-        av = Axn[i];
+      if (sm.act.reset_v) {
+        av = __ldcg(&Axn[i]);
       } else {
-        const double o = Axt_old[i];
-        av = xadd(o, xdiv(xsub(Axn[i], o), th_old));
+        const double o = __ldcg(&Axt_old[i]);
+        av = xadd(o, xdiv(xsub(__ldcg(&Axn[i]), o), th_old));
       }
       a.Av[i] = av;
-      base = xadd(xmul(omt, Axnt[i]), xmul(th, av));
+      base = xadd(xmul(omt, __ldcg(&Axnt[i])), xmul(th, av));
     } else {
-      base = Axnt[i];
+      base = __ldcg(&Axnt[i]);
     }
     const double res = xsub(base, a.b[i]);
     r[i] = T(res);
@@ -131,19 +130,33 @@ glp_decide_kernel(const DecideArgs a, const Geom g) {
     rmx = __reduce_max_sync(0xffffffffu, rmx);
     if (lane == 0 && rmx != 0u) atomicMax(a.r_amax, rmx);
   }
-  if (accel && s_act.reset_v) {
+  if (accel && sm.act.reset_v) {
     const double* x = a.state[nc];
     double* v = a.state[nc] + 2 * lenn;
     for (int64_t i = int64_t(blockIdx.x) * DECIDE_THREADS + tid; i < lenn; i += stride) v[i] = x[i];
   }
   gy = warp_sum(gy);
-  if (lane == 0) s_gy[warp] = gy;
+  if (lane == 0) sm.gy[warp] = gy;
   __syncthreads();
   if (tid == 0) {
     double tot = 0.0;
-    for (int w = 0; w < DECIDE_THREADS / 32; ++w) tot += s_gy[w];
-    a.gy_partial[s_out.gy_sel][blockIdx.x] = tot;
+    for (int w = 0; w < DECIDE_THREADS / 32; ++w) tot += sm.gy[w];
+    a.gy_partial[sm.out.gy_sel][blockIdx.x] = tot;
   }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(DECIDE_THREADS)
+glp_decide_kernel(const DecideArgs a, const Geom g) {
+  __shared__ DecideSmem sm;
+  pdl_wait();
+  pdl_launch();
+  const Ctrl cin = *a.cin;
+  if (cin.done) {  // keep both control blocks identical once finished
+    if (blockIdx.x == 0 && threadIdx.x == 0) *a.cout = cin;
+    return;
+  }
+  decide_phase<T>(a, g, cin, sm);
 }
 
 }  // namespace glp

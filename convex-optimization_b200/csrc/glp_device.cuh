@@ -152,6 +152,15 @@ __device__ __forceinline__ uint64_t policy_evict_normal() {
 __device__ __forceinline__ void prefetch_tensormap(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }
+// Programmatic dependent launch (griddepcontrol): a kernel launched with the programmatic-stream-serialization
+// attribute may become resident while its predecessor in the stream is still running; everything before pdl_wait()
+// (shared-memory carve-up, mbarrier init, tensor-map prefetch) overlaps the predecessor's tail.  pdl_wait() returns
+// once the predecessor grid has completed and its memory is visible; NO global memory written by an earlier kernel of
+// the stream may be read before it.  pdl_launch() lets the successor's CTAs be scheduled as this kernel's CTAs retire.
+// Both are no-ops for a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Named barrier among the consumer warps only (the producer / aux warps keep running).
 __device__ __forceinline__ void consumer_bar() {
   asm volatile("bar.sync 1, %0;" ::"n"(CONSUMER_THREADS) : "memory");

@@ -73,9 +73,6 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
   constexpr uint32_t STAGE_TX = TILE_BYTES + RC * TILE_ROW_BYTES;
   constexpr int NV = ROWS_PER_WARP * RC;  // values per lane entering the butterfly
 
-  if (a.ctrl != nullptr && a.ctrl->done) return;  // grid-uniform
-  const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : a.sel;
-
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + NUM_STAGES * STRIDE);
@@ -96,13 +93,18 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
     }
     fence_mbar_init();
     fence_proxy_async();
+    prefetch_tensormap(&tmapA);
   }
   __syncthreads();
+  // ---- everything above overlapped the predecessor's tail (programmatic dependent launch)
+  pdl_wait();
+  pdl_launch();
+  if (a.ctrl != nullptr && a.ctrl->done) return;  // grid-uniform
+  const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : a.sel;
 
   if (warp == NUM_CONSUMER_WARPS) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0 && lo < hi) {
-      prefetch_tensormap(&tmapA);
       const uint64_t pol = evict_first ? policy_evict_first() : policy_evict_normal();
       const T* X = static_cast<const T*>(a.X[sel]);
       int32_t rb = int32_t(lo / ncb), cb = int32_t(lo % ncb);
@@ -221,11 +223,18 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
         const int64_t grow = rb * TILE_ROWS + row;
         if (a.comm.world > 1) {
           // push this rank's finished row block into everybody's slab (NVLink stores, 512 B runs)
+          // The stores become visible to the peers through the ONE system fence of fwd_finish (lane 0 of warp 0,
+          // after the consumer barrier below): no fence per row block.  Peers are visited starting at rank + 1 so
+          // that the W ranks do not all hit the same NVLink port at the same time.
           if (grow < g.m) {
             const int64_t off = int64_t(a.col0 + q) * g.ldm + grow;
-            for (int r = 0; r < a.comm.world; ++r) mail_slab(a.comm, r, a.par, a.comm.rank)[off] = sum;
+            int r = a.comm.rank;
+            for (int k = 0; k < a.comm.world; ++k) {
+              r = r + 1 == a.comm.world ? 0 : r + 1;
+              mail_slab(a.comm, r, a.par, a.comm.rank)[off] = sum;
+            }
           }
-          __threadfence_system();
+          if (a.push_fence_per_block) __threadfence_system();   // A/B switch (GLPROX_PUSH_FENCE=block)
         } else if (grow < g.m) {
           a.AX[sel][int64_t(q) * g.ldm + grow] = sum;
           if (q < a.nb_cols) {

@@ -345,6 +345,8 @@ __global__ void __launch_bounds__(CONSUMER_THREADS)
 glp_prox_kernel(const ProxArgs p, const Geom g, const int only_if_retry) {
   __shared__ double s_red[NUM_CONSUMER_WARPS][6];
   __shared__ double s_row[NUM_CONSUMER_WARPS][32];
+  pdl_wait();
+  pdl_launch();
   if (p.ctrl != nullptr) {
     if (p.ctrl->done) return;
     if (only_if_retry && !p.ctrl->retry) return;

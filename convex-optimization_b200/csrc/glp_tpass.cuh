@@ -40,8 +40,6 @@ glp_tpass_kernel(const __grid_constant__ CUtensorMap tmapA, const TpassArgs a, c
   constexpr uint32_t STAGE_TX = TILE_BYTES + LC * R_SLICE;
   constexpr int RV = ROWS_PER_WARP / VEC;  // Vec loads covering a warp's 8 residual rows
 
-  if (a.ctrl != nullptr && a.ctrl->done) return;  // grid-uniform
-
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + NUM_STAGES * STRIDE);
@@ -51,6 +49,21 @@ glp_tpass_kernel(const __grid_constant__ CUtensorMap tmapA, const TpassArgs a, c
   __shared__ double s_red[NUM_CONSUMER_WARPS][6];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    for (int s = 0; s < NUM_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], NUM_CONSUMER_WARPS);
+    }
+    fence_mbar_init();
+    fence_proxy_async();
+    prefetch_tensormap(&tmapA);
+  }
+  __syncthreads();
+  // ---- everything above overlapped the predecessor's tail (programmatic dependent launch)
+  pdl_wait();
+  pdl_launch();
+  if (a.ctrl != nullptr && a.ctrl->done) return;  // grid-uniform
 
   if (a.ctrl != nullptr && a.ctrl->retry) {
     // A rejected line-search trial: the gradient is unchanged, only the epilogue is re-evaluated
@@ -68,20 +81,9 @@ glp_tpass_kernel(const __grid_constant__ CUtensorMap tmapA, const TpassArgs a, c
   const int64_t N = nrb * int64_t(g.ncb);
   const int64_t lo = tile_lo(c, G, N), hi = tile_lo(c + 1, G, N);
 
-  if (tid == 0) {
-    for (int s = 0; s < NUM_STAGES; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&empty[s], NUM_CONSUMER_WARPS);
-    }
-    fence_mbar_init();
-    fence_proxy_async();
-  }
-  __syncthreads();
-
   if (warp == NUM_CONSUMER_WARPS) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0 && lo < hi) {
-      prefetch_tensormap(&tmapA);
       const uint64_t pol = evict_first ? policy_evict_first() : policy_evict_normal();
       const T* R = static_cast<const T*>(a.R);
       int32_t cb = int32_t(lo / nrb), rb = int32_t(lo % nrb);

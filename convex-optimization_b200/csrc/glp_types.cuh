@@ -105,6 +105,7 @@ struct FwdArgs {
   int32_t par;                 // mailbox double-buffer index of this forward group
   int32_t col0;                // first column of this chunk inside the 2l-column slab
   unsigned* fin;               // local finish counter, zero between launches
+  int32_t push_fence_per_block;  // 1: system fence after every pushed row block (round-1 behaviour, A/B only)
 };
 
 // Transposed stream  G[:, c] = A^T * R[:, c]  for LC residual columns, optional fused epilogue.

@@ -19,6 +19,7 @@
 #include "glp_comm.cuh"
 #include "glp_decide.cuh"
 #include "glp_fwd.cuh"
+#include "glp_gather_decide.cuh"
 #include "glp_gemm.cuh"
 #include "glp_metrics.cuh"
 #include "glp_misc.cuh"
@@ -146,6 +147,16 @@ struct glp_handle {
   unsigned *fin_f = nullptr, *fin_t = nullptr;
   double *rr_g = nullptr, *scal_red = nullptr, *cnt_red = nullptr;
   int gather_grid = 0;
+  // launch-latency switches (each read from the environment at glp_create so that A/B runs need no rebuild):
+  bool pdl = true;                 // GLPROX_PDL=0: plain stream serialization instead of programmatic dependent launch
+  bool fused_gather = true;        // GLPROX_FUSED_GATHER=0: glp_gather_kernel + glp_decide_kernel as two launches
+  bool push_fence_block = false;   // GLPROX_PUSH_FENCE=block: system fence per pushed row block (round-1 behaviour)
+  int fused_grid = 0;              // CTAs of glp_gather_decide_kernel (all co-resident: grid-wide barrier inside)
+  unsigned* gd_count = nullptr;
+  unsigned long long* gd_flag = nullptr;
+  unsigned long long gd_gen = 0;
+  int prof_stride = 1;             // profile every prof_stride-th slot (events between launches defeat the overlap)
+  bool prof_slot = true;
   const Ctrl* cur_ctrl = nullptr;  // control block the launches of the current slot read
   int backend_used = GLP_BACKEND_STREAM;
   // wide multi-RHS mode (K5, glp_gemm.cuh): resident tensor-core operand sets of A and A^T
@@ -233,7 +244,7 @@ static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 // CUDA-event profile of the streaming launches (roofline evidence measured on the launching stream)
 // ------------------------------------------------------------------------------------------------
 static void prof_mark(glp_handle* h, int tag, int end) {
-  if (!h->profiling) return;
+  if (!h->profiling || !h->prof_slot) return;
   const size_t idx = 2 * h->ev_used + size_t(end);
   while (h->ev_pool.size() <= idx) {
     cudaEvent_t e = nullptr;
@@ -274,6 +285,24 @@ static void prof_collect(glp_handle* h) {
 // ------------------------------------------------------------------------------------------------
 // kernel launch helpers (dtype / chunk-width dispatch)
 // ------------------------------------------------------------------------------------------------
+// Every kernel of the streaming schedule is launched with the programmatic-stream-serialization attribute: its CTAs
+// may become resident while the predecessor drains, run their prologue (mbarrier init, tensor-map prefetch) and block
+// in griddepcontrol.wait until the predecessor's memory is visible (glp_device.cuh: pdl_wait).
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_k(const glp_handle* h, void (*kfn)(KArgs...), dim3 grid, dim3 block, size_t smem, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = h->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = h->pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kfn, std::forward<Args>(args)...);
+}
+
 template <typename T, int RC>
 static cudaError_t launch_fwd_t(glp_handle* h, const FwdArgs& a) {
   static bool attr_set[64] = {false};
@@ -284,10 +313,10 @@ static cudaError_t launch_fwd_t(glp_handle* h, const FwdArgs& a) {
     attr_set[h->device & 63] = true;
   }
   prof_mark(h, 0, 0);
-  kfn<<<h->g.grid, FWD_THREADS, fwd_smem_bytes<RC>(), h->stream>>>(h->tmap, a, h->g, h->evict_first);
+  const cudaError_t e = launch_k(h, kfn, dim3(h->g.grid), dim3(FWD_THREADS), fwd_smem_bytes<RC>(), h->tmap, a, h->g, h->evict_first);
   prof_mark(h, 0, 1);
   h->n_launches++;
-  return cudaGetLastError();
+  return e;
 }
 
 static cudaError_t launch_fwd(glp_handle* h, int rc, const FwdArgs& a) {
@@ -311,10 +340,10 @@ static cudaError_t launch_tpass_t(glp_handle* h, const TpassArgs& a, const ProxA
     attr_set[h->device & 63] = true;
   }
   prof_mark(h, 1, 0);
-  kfn<<<h->g.grid, TP_THREADS, tp_smem_bytes<T, LC>(), h->stream>>>(h->tmap, a, p, h->g, h->evict_first);
+  const cudaError_t e = launch_k(h, kfn, dim3(h->g.grid), dim3(TP_THREADS), tp_smem_bytes<T, LC>(), h->tmap, a, p, h->g, h->evict_first);
   prof_mark(h, 1, 1);
   h->n_launches++;
-  return cudaGetLastError();
+  return e;
 }
 
 static cudaError_t launch_tpass(glp_handle* h, int lc, const TpassArgs& a, const ProxArgs& p) {
@@ -324,21 +353,24 @@ static cudaError_t launch_tpass(glp_handle* h, int lc, const TpassArgs& a, const
 
 static cudaError_t launch_prox(glp_handle* h, const ProxArgs& p, int only_if_retry) {
   const int grid = std::min<int>(h->g.ncb, 4 * h->num_sms);
-  if (h->dtype == GLP_F32)
-    glp_prox_kernel<float><<<grid, CONSUMER_THREADS, 0, h->stream>>>(p, h->g, only_if_retry);
-  else
-    glp_prox_kernel<double><<<grid, CONSUMER_THREADS, 0, h->stream>>>(p, h->g, only_if_retry);
   h->n_launches++;
-  return cudaGetLastError();
+  if (h->dtype == GLP_F32) return launch_k(h, glp_prox_kernel<float>, dim3(grid), dim3(CONSUMER_THREADS), 0, p, h->g, only_if_retry);
+  return launch_k(h, glp_prox_kernel<double>, dim3(grid), dim3(CONSUMER_THREADS), 0, p, h->g, only_if_retry);
 }
 
 static cudaError_t launch_decide(glp_handle* h, const DecideArgs& a) {
-  if (h->dtype == GLP_F32)
-    glp_decide_kernel<float><<<h->decide_grid, DECIDE_THREADS, 0, h->stream>>>(a, h->g);
-  else
-    glp_decide_kernel<double><<<h->decide_grid, DECIDE_THREADS, 0, h->stream>>>(a, h->g);
   h->n_launches++;
-  return cudaGetLastError();
+  if (h->dtype == GLP_F32) return launch_k(h, glp_decide_kernel<float>, dim3(h->decide_grid), dim3(DECIDE_THREADS), 0, a, h->g);
+  return launch_k(h, glp_decide_kernel<double>, dim3(h->decide_grid), dim3(DECIDE_THREADS), 0, a, h->g);
+}
+
+// multi-GPU, l = 2 streaming path: gather of the forward group just launched + decide, one launch
+static cudaError_t launch_gather_decide(glp_handle* h, const GatherArgs& ga, const DecideArgs& da) {
+  h->n_launches++;
+  const GridBarrier bar{h->gd_count, h->gd_flag, ++h->gd_gen};
+  if (h->dtype == GLP_F32)
+    return launch_k(h, glp_gather_decide_kernel<float>, dim3(h->fused_grid), dim3(DECIDE_THREADS), 0, ga, da, h->g, bar);
+  return launch_k(h, glp_gather_decide_kernel<double>, dim3(h->fused_grid), dim3(DECIDE_THREADS), 0, ga, da, h->g, bar);
 }
 
 // Operand columns of the forward stream are processed in chunks of 4, 2 or 1.
@@ -480,13 +512,24 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
   const size_t o_xop = carve(dtype == GLP_F32 ? 2 * ln * 4 : 0);
   const size_t o_scal = carve(size_t(g.ncb) * SCAL_STRIDE * 8), o_cnt = carve(size_t(g.grid) * 8);
   const size_t o_rr = carve(size_t(h->n_fchunks) * g.nrb * 8);
-  const size_t o_gy0 = carve(size_t(h->decide_grid) * 8), o_gy1 = carve(size_t(h->decide_grid) * 8);
+  h->gather_grid = int(std::max<int64_t>(1, std::min<int64_t>(int64_t(num_sms) * 8, (int64_t(2) * lm + GATHER_THREADS - 1) / GATHER_THREADS)));
+  // the fused gather + decide kernel synchronises its whole grid: clamp it to what is resident at once
+  {
+    int per_sm = 0;
+    cudaError_t eo = dtype == GLP_F32
+        ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, glp_gather_decide_kernel<float>, DECIDE_THREADS, 0)
+        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, glp_gather_decide_kernel<double>, DECIDE_THREADS, 0);
+    if (eo != cudaSuccess || per_sm < 1) { cudaGetLastError(); per_sm = 1; }
+    h->fused_grid = int(std::min<int64_t>(std::max(h->gather_grid, h->decide_grid), int64_t(per_sm) * num_sms));
+  }
+  const int part_grid = std::max(std::max(h->decide_grid, h->gather_grid), h->fused_grid);
+  const size_t o_gy0 = carve(size_t(part_grid) * 8), o_gy1 = carve(size_t(part_grid) * 8);
   const size_t o_fp = carve(size_t(g.grid + g.nrb) * TILE_ROWS * 4 * 8);
   const size_t o_tp = carve(size_t(g.grid + g.ncb) * 2 * tc * 8);
   const size_t o_fc = carve(size_t(g.nrb) * 4), o_tc = carve(size_t(g.ncb) * 4);
   const size_t o_ctrl = carve(2 * sizeof(Ctrl)), o_fault = carve(16);
-  h->gather_grid = int(std::max<int64_t>(1, std::min<int64_t>(int64_t(num_sms) * 8, (int64_t(2) * lm + GATHER_THREADS - 1) / GATHER_THREADS)));
-  const size_t o_fin = carve(16), o_rrg = carve(size_t(h->gather_grid) * 8), o_sred = carve(SCAL_STRIDE * 8), o_cred = carve(8);
+  const size_t o_fin = carve(16), o_rrg = carve(size_t(part_grid) * 8), o_sred = carve(SCAL_STRIDE * 8), o_cred = carve(8);
+  const size_t o_gd = carve(32);
   cudaError_t e = cudaMalloc(&h->arena, off);
   if (e != cudaSuccess) { glp_destroy(h); return fail(GLP_ERR_CUDA, "cudaMalloc(%zu) failed: %s", off, cudaGetErrorString(e)); }
   e = cudaMemsetAsync(h->arena, 0, off, h->stream);
@@ -517,6 +560,13 @@ extern "C" int glp_create(glp_handle** out, int device, int m, int n_local, int 
   h->rr_g = reinterpret_cast<double*>(base + o_rrg);
   h->scal_red = reinterpret_cast<double*>(base + o_sred);
   h->cnt_red = reinterpret_cast<double*>(base + o_cred);
+  h->gd_flag = reinterpret_cast<unsigned long long*>(base + o_gd);
+  h->gd_count = reinterpret_cast<unsigned*>(base + o_gd + 16);
+  if (const char* e_pdl = getenv("GLPROX_PDL")) h->pdl = atoi(e_pdl) != 0;
+  if (const char* e_fg = getenv("GLPROX_FUSED_GATHER")) h->fused_gather = atoi(e_fg) != 0;
+  if (const char* e_pf = getenv("GLPROX_PUSH_FENCE")) h->push_fence_block = strcmp(e_pf, "block") == 0;
+  h->prof_stride = h->pdl ? 4 : 1;
+  if (const char* e_ps = getenv("GLPROX_PROF_STRIDE")) h->prof_stride = std::max(1, atoi(e_ps));
 
   // b: row-major [m][l] dtype T -> planar fp64 [l][ldm]
   if (dtype == GLP_F32) e = to_planar(h->stream, static_cast<const float*>(b_dev), h->b, m, l, g.ldm);
@@ -907,6 +957,7 @@ static int enqueue_fwd(glp_handle* h, const Ctrl* ctrl, int sel, const void* con
       a.par = h->group & 1;
       a.col0 = q;
       a.fin = h->fin_f;
+      a.push_fence_per_block = h->push_fence_block ? 1 : 0;
     }
     CU_TRY(launch_fwd(h, rc, a));
     q += rc;
@@ -1000,17 +1051,8 @@ static int enqueue_solver_fwd(glp_handle* h, const Ctrl* ctrl) {
   return enqueue_fwd(h, ctrl, 0, Xb, h->AX, xc, 2 * h->g.l, 1, true);
 }
 
-// Multi-GPU: sum the W slabs of the forward group that was just launched (rank order) into the
-// candidate product buffers, with the residual norm and the exchanged scalars.
-static int enqueue_gather(glp_handle* h, const Ctrl* ctrl) {
-  if (!multi(h)) return GLP_OK;
-  if (h->xch_nccl) {
-    glp_nccl_post_kernel<<<h->gather_grid, GATHER_THREADS, 0, h->stream>>>(nccl_args(h, ctrl), h->g);
-    CU_TRY(cudaGetLastError());
-    h->n_launches++;
-    return GLP_OK;
-  }
-  if (wide_active(h)) return enqueue_wide_exchange(h, ctrl, 1);
+// Gather arguments of the forward group that was launched last.
+static GatherArgs gather_args(const glp_handle* h, const Ctrl* ctrl) {
   GatherArgs a{};
   a.comm = h->comm;
   a.ctrl = ctrl;
@@ -1024,9 +1066,28 @@ static int enqueue_gather(glp_handle* h, const Ctrl* ctrl) {
   a.scal_red = h->scal_red;
   a.cnt_red = h->cnt_red;
   a.fault = h->fault;
-  glp_gather_kernel<<<h->gather_grid, GATHER_THREADS, 0, h->stream>>>(a, h->g);
+  return a;
+}
+// l = 2 streaming path over peer mailboxes: gather and decide run as one launch
+static bool fused_gather_active(const glp_handle* h) {
+  return h->fused_gather && peer_push(h) && !wide_active(h);
+}
+
+// Multi-GPU: sum the W slabs of the forward group that was just launched (rank order) into the
+// candidate product buffers, with the residual norm and the exchanged scalars.
+static int enqueue_gather(glp_handle* h, const Ctrl* ctrl) {
+  if (!multi(h)) return GLP_OK;
+  if (h->xch_nccl) {
+    glp_nccl_post_kernel<<<h->gather_grid, GATHER_THREADS, 0, h->stream>>>(nccl_args(h, ctrl), h->g);
+    CU_TRY(cudaGetLastError());
+    h->n_launches++;
+    return GLP_OK;
+  }
+  if (wide_active(h)) return enqueue_wide_exchange(h, ctrl, 1);
+  if (fused_gather_active(h)) return GLP_OK;   // the next decide launch gathers first (glp_gather_decide_kernel)
+  const GatherArgs a = gather_args(h, ctrl);
   h->n_launches++;
-  CU_TRY(cudaGetLastError());
+  CU_TRY(launch_k(h, glp_gather_kernel, dim3(h->gather_grid), dim3(GATHER_THREADS), 0, a, h->g));
   return GLP_OK;
 }
 
@@ -1075,8 +1136,10 @@ static int phase_prepare(glp_handle* h, int algo, const void* x0_dev, double mu0
   CU_TRY(cudaMemcpyAsync(&h->ctrl[0], &c0, sizeof(Ctrl), cudaMemcpyHostToDevice, h->stream));
   CU_TRY(cudaMemcpyAsync(&h->ctrl[1], &c0, sizeof(Ctrl), cudaMemcpyHostToDevice, h->stream));
   CU_TRY(cudaMemsetAsync(h->fault, 0, sizeof(int32_t), h->stream));
-  CU_TRY(cudaMemsetAsync(h->gy_partial[0], 0, size_t(h->decide_grid) * 8, h->stream));
-  CU_TRY(cudaMemsetAsync(h->gy_partial[1], 0, size_t(h->decide_grid) * 8, h->stream));
+  const int part_grid = std::max(std::max(h->decide_grid, h->gather_grid), h->fused_grid);
+  CU_TRY(cudaMemsetAsync(h->gy_partial[0], 0, size_t(part_grid) * 8, h->stream));
+  CU_TRY(cudaMemsetAsync(h->gy_partial[1], 0, size_t(part_grid) * 8, h->stream));
+  h->prof_slot = true;
   // x0 -> candidate slot of cur = 0
   if (h->dtype == GLP_F32) CU_TRY(to_planar(h->stream, static_cast<const float*>(x0_dev), h->state[1], g.n, g.l, g.ldn));
   else CU_TRY(to_planar(h->stream, static_cast<const double*>(x0_dev), h->state[1], g.n, g.l, g.ldn));
@@ -1119,7 +1182,13 @@ static int phase_decide(glp_handle* h) {
   Ctrl* cout = &h->ctrl[(j + 1) & 1];
   DecideArgs d{};
   d.cin = cin; d.cout = cout; d.sc = h->sc;
-  if (multi(h)) {
+  h->prof_slot = (j % h->prof_stride) == 0;
+  const bool fused = fused_gather_active(h);
+  if (fused) {
+    d.rr_partial = h->rr_g; d.n_rr = h->fused_grid;
+    d.scal_partial = h->scal_red; d.n_scal = 1;
+    d.cnt_partial = h->cnt_red; d.n_cnt = 1;
+  } else if (multi(h)) {
     d.rr_partial = h->rr_g; d.n_rr = h->gather_grid;
     d.scal_partial = h->scal_red; d.n_scal = 1;
     d.cnt_partial = h->cnt_red; d.n_cnt = 1;
@@ -1132,7 +1201,7 @@ static int phase_decide(glp_handle* h) {
     d.scal_partial = h->scal_partial; d.n_scal = h->g.ncb;
     d.cnt_partial = h->cnt_partial; d.n_cnt = h->g.grid;
   }
-  d.gy_partial[0] = h->gy_partial[0]; d.gy_partial[1] = h->gy_partial[1]; d.n_gy = h->decide_grid;
+  d.gy_partial[0] = h->gy_partial[0]; d.gy_partial[1] = h->gy_partial[1]; d.n_gy = fused ? h->fused_grid : h->decide_grid;
   d.AX[0] = h->AX[0]; d.AX[1] = h->AX[1]; d.Av = h->Av; d.b = h->b; d.r = h->r;
   d.state[0] = h->state[0]; d.state[1] = h->state[1];
   d.f_hist = h->f_hist; d.f_hist_best = h->f_hist_best; d.s_hist = h->s_hist;
@@ -1140,7 +1209,8 @@ static int phase_decide(glp_handle* h) {
     CU_TRY(cudaMemsetAsync(h->f16_amax + 1, 0, sizeof(unsigned), h->stream));
     d.r_amax = h->f16_amax + 1;
   }
-  CU_TRY(launch_decide(h, d));
+  if (fused) CU_TRY(launch_gather_decide(h, gather_args(h, cin), d));
+  else CU_TRY(launch_decide(h, d));
   h->cur_ctrl = cout;
   return GLP_OK;
 }

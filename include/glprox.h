@@ -169,8 +169,8 @@ typedef struct glp_decide_out {
   double theta_old;
 } glp_decide_out;
 /* Applies the device build of the state machine to `count` independent (ctrl_in, reduced) pairs (host arrays in,
- * host arrays out).  hist3_host (nullable): [count][3] = the (f_hist, f_hist_best, sparsity_hist) entry the step
- * recorded, NaN where it recorded none.  size_total = n_total * l (sparsity denominator). */
+ * host arrays out).  hist3_host (nullable): [count][3] = the first (f_hist, f_hist_best, sparsity_hist) entry the
+ * step recorded, NaN where it recorded none.  size_total = n_total * l (sparsity denominator). */
 int glp_decide(int device, const glp_solve_const* sc, const glp_ctrl* ctrl_in_host, const glp_reduced* red_host,
                double size_total, glp_ctrl* ctrl_out_host, glp_decide_out* act_host, double* hist3_host, int count);
 /* sparsity_hist of the last finished solve (gl_ProxGD_primal.py:116 / gl_FProxGD_primal.py:119): copies
