@@ -82,3 +82,19 @@ extern "C" int glp_solve_sparsity_hist(glp_handle* h, double* out_host, int cap)
   CU_TRY(cudaStreamSynchronize(h->stream));
   return n;
 }
+
+// Right-hand side of the synthetic recipe, bit-identical to the CPU restatement (see rhs_exact_kernel).
+// u_dev: [n_local][l] fp64 row-major; nz_dev: ascending indices of its non-zero rows; y_dev: [m][l] fp64 row-major.
+extern "C" int glp_rhs_exact(const void* A_dev, int dtype, int64_t m, int64_t lda, const double* u_dev, int l,
+                             const int64_t* nz_dev, int64_t nnz, double* y_dev, void* stream) {
+  if (A_dev == nullptr || u_dev == nullptr || y_dev == nullptr || (nnz > 0 && nz_dev == nullptr) || m < 0 || l < 1 || nnz < 0)
+    return fail(GLP_ERR_ARG, "bad argument");
+  if (dtype != GLP_F32 && dtype != GLP_F64) return fail(GLP_ERR_ARG, "dtype must be GLP_F32 or GLP_F64");
+  if (m == 0) return GLP_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = int((m + 127) / 128);
+  if (dtype == GLP_F32) rhs_exact_kernel<float><<<grid, 128, 0, st>>>(static_cast<const float*>(A_dev), m, lda, u_dev, l, nz_dev, nnz, y_dev);
+  else rhs_exact_kernel<double><<<grid, 128, 0, st>>>(static_cast<const double*>(A_dev), m, lda, u_dev, l, nz_dev, nnz, y_dev);
+  CU_TRY(cudaGetLastError());
+  return GLP_OK;
+}

@@ -163,4 +163,25 @@ __global__ void randn_kernel(T* __restrict__ dst, int64_t rows, int64_t cols, in
   }
 }
 
+// b = A u of the synthetic recipe (code/main.py:45) with fp64 accumulation over the non-zero row groups of u in
+// ascending column order, one rounded multiply and one rounded add per term: the order and the arithmetic of the CPU
+// restatement (oracle/glprox_gen.c: glp_oracle_matmul), so that both sides build the same right-hand side bit for bit.
+// One thread per row of A; nz[] lists the non-zero rows of u.  Set-up only (the rows are read with a stride).
+template <typename T>
+__global__ void rhs_exact_kernel(const T* __restrict__ A, int64_t m, int64_t lda, const double* __restrict__ u, int l,
+                                 const int64_t* __restrict__ nz, int64_t nnz, double* __restrict__ y) {
+  const int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  if (i >= m) return;
+  for (int c0 = 0; c0 < l; c0 += 8) {
+    double acc[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    const int cw = l - c0 < 8 ? l - c0 : 8;
+    for (int64_t q = 0; q < nnz; ++q) {
+      const int64_t j = nz[q];
+      const double v = double(A[i * lda + j]);
+      for (int c = 0; c < cw; ++c) acc[c] = rn_add(acc[c], rn_mul(v, u[j * l + c0 + c]));
+    }
+    for (int c = 0; c < cw; ++c) y[i * l + c0 + c] = acc[c];
+  }
+}
+
 }  // namespace glp

@@ -21,6 +21,7 @@
 #include "glp_fwd.cuh"
 #include "glp_gather_decide.cuh"
 #include "glp_gemm.cuh"
+#include "glp_gemm_pair.cuh"
 #include "glp_metrics.cuh"
 #include "glp_misc.cuh"
 #include "glp_persist.cuh"
@@ -179,6 +180,8 @@ struct glp_handle {
   float* thr_vals = nullptr;
   int32_t thr_cap = -1;            // list entries per operand column
   double* admm_L = nullptr;    // gl_Admm_dual: m x m Cholesky factor of I + rho A A^T
+  void* pair_ws = nullptr;     // K5 on CTA pairs (glp_gemm_pair.cuh): arrival counters + partial-tile slots
+  size_t pair_ws_bytes = 0;
   double* gemm_ws = nullptr;   // split-K partial products of K5
   size_t gemm_ws_bytes = 0;
   int64_t n_gemm = 0;              // tensor-core launches of the current solve
@@ -437,6 +440,7 @@ extern "C" int glp_destroy(glp_handle* h) {
   if (h->thr_col_count) cudaFree(h->thr_col_count);
   if (h->thr_count) cudaFree(h->thr_count);
   if (h->gemm_ws) cudaFree(h->gemm_ws);
+  if (h->pair_ws) cudaFree(h->pair_ws);
   if (h->admm_L) cudaFree(h->admm_L);
   if (h->nccl_stage) cudaFree(h->nccl_stage);
   for (__half* q : {h->A_f0, h->A_f1, h->At_f0, h->At_f1, h->xop_f0, h->xop_f1, h->r_f0, h->r_f1})
@@ -674,6 +678,8 @@ static int ensure_wide(glp_handle* h) {
     const size_t tps = size_t(gemm_splits(g.n, g.m, g.l, WIDE_K_CHUNK, h->num_sms)) * g.l * g.ldn * 8;
     h->gemm_ws_bytes = std::max(fwd, tps);
     CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->gemm_ws), h->gemm_ws_bytes));
+    h->pair_ws_bytes = pair_ws_bytes(h->num_sms, 128);
+    GLP_TRY(alloc_zero(&h->pair_ws, h->pair_ws_bytes, h->stream));
   }
   if (wide_passes(h) == 4) {
     if (h->A_f0 != nullptr) return GLP_OK;
@@ -740,7 +746,9 @@ static int ensure_wide(glp_handle* h) {
   return GLP_OK;
 }
 
-struct GemmWs { double* buf; size_t bytes; };  // split-K partial products (nullptr: no splitting)
+// split-K partial products (buf == nullptr: no splitting) and the workspace of the CTA-pair kernel (pair == nullptr:
+// the one-CTA kernel runs instead)
+struct GemmWs { double* buf; size_t bytes; void* pair = nullptr; size_t pair_bytes = 0; };
 struct GemmBf16 { const __nv_bfloat16 *Phb, *Plb, *Qhb, *Qlb; };  // passes = 2: bf16 copies of hi / lo, same pitches
 static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms, int bk);
 static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
@@ -832,7 +840,7 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
     h->n_launches++;
   }
   prof_mark(h, 0, 0);
-  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes};
+  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes, h->pair_ws, h->pair_ws_bytes};
   // operand pointers of the selected set (fp16 pairs travel as float* through gemm_enqueue, pitches in elements)
   const float* Ph = f16 ? reinterpret_cast<const float*>(h->A_f0) : h->A_hi;
   const float* Pl = f16 ? reinterpret_cast<const float*>(h->A_f1) : h->A_lo;
@@ -895,7 +903,7 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
 static int enqueue_wide_tpass(glp_handle* h, const Ctrl* ctrl) {
   const Geom& g = h->g;
   float* r = static_cast<float*>(h->r);
-  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes};
+  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes, h->pair_ws, h->pair_ws_bytes};
   if (wide_passes(h) == 4) {
     const int64_t tot = int64_t(g.l) * g.ldm;
     // max|r| was left in f16_amax[1] by the decide kernel that wrote r
@@ -1959,6 +1967,36 @@ static cudaError_t launch_gemm_t(cudaStream_t st, int num_sms, int64_t cluster_i
   return cudaLaunchKernelEx(&cfg, kfn, ph, pl, qh, ql, px, qx, a);
 }
 
+// K5 on CTA pairs (glp_gemm_pair.cuh): clusters of 2, one pair per TPC, stream-K ranges over the pairs.
+template <int NT>
+static cudaError_t launch_gemm_pair_t(cudaStream_t st, int num_sms, const CUtensorMap& p0, const CUtensorMap& p1,
+                                      const CUtensorMap& q0, const CUtensorMap& q1, const PairArgs& a) {
+  auto kfn = glp_gemm_pair_kernel<NT>;
+  constexpr int smem = pair_smem_bytes<NT>();
+  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(GEMM_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int pairs = num_sms / 2;
+  cfg.gridDim = dim3(unsigned(2 * pairs), 1, 1);
+  int max_cl = 0;
+  e = cudaOccupancyMaxActiveClusters(&max_cl, kfn, &cfg);
+  if (e != cudaSuccess) return e;
+  if (max_cl < 1) return cudaErrorInvalidConfiguration;
+  pairs = std::min(pairs, max_cl);
+  cfg.gridDim = dim3(unsigned(2 * pairs), 1, 1);
+  return cudaLaunchKernelEx(&cfg, kfn, p0, p1, q0, q1, a);
+}
+
 // Number of K splits.  Measured on B200 (tests/bench_gemm_probe.py split): the kernel runs under the
 // board's power cap, so filling the SMs left idle by the tail wave buys nothing at 128+ items (3.15 ms
 // unsplit vs 3.56 ms with 4 splits at M=16384 K=65536 N=256) and fine splits cost epilogue + workspace
@@ -2022,6 +2060,30 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
     GLP_TRY(make_map_f32_k128(&mqh, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, qbox));
   }
   mpx = mph; mqx = mqh;
+  // fp16 pairs: the CTA-pair kernel (cta_group::2 + stream-K) unless GLPROX_GEMM_PAIR=0 or no workspace was given
+  const char* e_pair = getenv("GLPROX_GEMM_PAIR");   // read per call: tests switch it inside one process
+  if (passes == 4 && ws.pair != nullptr && (e_pair == nullptr || atoi(e_pair) != 0)) {
+    const int ctas = 2 * (num_sms / 2);
+    if (ws.pair_bytes < pair_ws_bytes(ctas, NT)) return fail(GLP_ERR_ARG, "gemm: pair workspace too small");
+    if (tiles * groups > PAIR_COUNTER_WORDS) return fail(GLP_ERR_ARG, "gemm: too many output tiles for the pair kernel");
+    CUtensorMap p0, p1, q0, q1;
+    GLP_TRY(make_map_f16_k128(&p0, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
+    GLP_TRY(make_map_f16_k128(&p1, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
+    GLP_TRY(make_map_f16_k128(&q0, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, uint32_t(NT / 2)));
+    GLP_TRY(make_map_f16_k128(&q1, Ql, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, uint32_t(NT / 2)));
+    PairArgs pa{};
+    pa.M = M; pa.K = K; pa.N = N; pa.k_chunk_blocks = k_chunk; pa.D = D; pa.ldd = ldd; pa.fault = fault;
+    pa.ctrl = ctrl; pa.D_alt = D_alt; pa.role = role;
+    pa.gate = gate.count; pa.gate_cap = gate.cap;
+    pa.scale = scale;
+    pa.counters = static_cast<unsigned*>(ws.pair);
+    pa.slots = reinterpret_cast<double*>(static_cast<char*>(ws.pair) + size_t(PAIR_COUNTER_WORDS) * 4);
+    const cudaError_t ep = NT == 32 ? launch_gemm_pair_t<32>(st, num_sms, p0, p1, q0, q1, pa)
+                         : NT == 64 ? launch_gemm_pair_t<64>(st, num_sms, p0, p1, q0, q1, pa)
+                                    : launch_gemm_pair_t<128>(st, num_sms, p0, p1, q0, q1, pa);
+    if (ep != cudaSuccess) return fail(GLP_ERR_CUDA, "gemm (CTA pairs) launch failed: %s", cudaGetErrorString(ep));
+    return GLP_OK;
+  }
   if (passes == 4) {
   } else if (passes == 2) {
     if (bf.Phb == nullptr || bf.Plb == nullptr || bf.Qhb == nullptr || bf.Qlb == nullptr)
@@ -2126,9 +2188,13 @@ extern "C" int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, in
     glp_split_f16_kernel<<<g1, 256, 0, st>>>(Pf, p0, p1, int64_t(pe), amax, nullptr, 0, 1.0f, nullptr, nullptr, nullptr, 0);
     glp_split_f16_kernel<<<g2, 256, 0, st>>>(Qf, q0, q1, int64_t(qe), amax + 1, nullptr, 0, 1.0f, amax, inv, nullptr, 0);
     CU_TRY(cudaGetLastError());
+    ws.pair_bytes = pair_ws_bytes(sms, 128);
+    CU_TRY(cudaMallocAsync(&ws.pair, ws.pair_bytes, st));
+    CU_TRY(cudaMemsetAsync(ws.pair, 0, size_t(PAIR_COUNTER_WORDS) * 4, st));
     rc = gemm_enqueue(st, sms, 4, M, K, N, reinterpret_cast<const float*>(p0), reinterpret_cast<const float*>(p1), ldp,
                       reinterpret_cast<const float*>(q0), reinterpret_cast<const float*>(q1), ldq, D_dev, ldd, kc, nullptr,
                       nullptr, nullptr, 0, ws, bf, GemmGate{nullptr, 0}, inv);
+    cudaFreeAsync(ws.pair, st);
     cudaFreeAsync(t4, st);
   } else {
     rc = gemm_enqueue(st, sms, passes, M, K, N, static_cast<const float*>(P_hi), static_cast<const float*>(P_lo), ldp,

@@ -7,7 +7,8 @@ on-disk or wire format.  At 17 GB per problem that does not scale, so this modul
 * ``gen_data_device(...)``      -- the same recipe at scale: A ~ N(0,1) from the library's counter-based
                                    device generator (``glp_randn``: any column block of the same logical
                                    matrix can be produced independently on any rank), 10 % non-zero row
-                                   groups in u, b = A u through the forward streaming kernel;
+                                   groups in u, b = A u accumulated in fp64 (``glp_rhs_exact``); every value is
+                                   bit-identical to the CPU restatement in oracle/gen.py;
 * ``write_shard / open_shard / read_columns`` -- a flat binary format, one file per column block of A
                                    (the sharding of SURVEY.md 8(e)), readable by any world size:
                                    a rank's columns are gathered from whichever stored shards hold them.
@@ -66,7 +67,7 @@ def gen_data_device(m, n, l, seed, dtype="f32", rank=0, world=1, mu=1e-2, group=
     Returns (A[m, n_local], b[m, l], x0[n_local, l], u[n_local, l], mu, (col0, col1))."""
     import torch
     from . import _lib
-    from .solver import GroupLassoProblem, shard_bounds
+    from .solver import shard_bounds
     lib = _lib.load()
     f32 = dtype in ("f32", np.float32, torch.float32)
     tdt = torch.float32 if f32 else torch.float64
@@ -78,14 +79,16 @@ def gen_data_device(m, n, l, seed, dtype="f32", rank=0, world=1, mu=1e-2, group=
     u, x0 = sparse_truth(seed, n, l)
     u_loc = torch.from_numpy(u[col0:col1]).to("cuda", tdt)
     x0_loc = torch.from_numpy(x0[col0:col1]).to("cuda", tdt)
-    # b = A u through the forward stream (partial product per rank, summed over ranks)
-    tmp = GroupLassoProblem(A, torch.zeros((m, l), dtype=tdt, device="cuda"))
+    # b = A u with fp64 accumulation in ascending column order (glp_rhs_exact: the same order and rounding as the
+    # CPU restatement oracle/glprox_gen.c, so both build the same b); partial product per rank, summed over ranks
+    u_rounded = u[col0:col1].astype(np.float32 if f32 else np.float64).astype(np.float64)
+    u_loc64 = torch.from_numpy(u_rounded).to("cuda")
+    nz = torch.from_numpy(np.flatnonzero(np.any(u_rounded != 0.0, axis=1)).astype(np.int64)).to("cuda")
     Au = torch.empty((m, l), dtype=torch.float64, device="cuda")
-    try:
-        _lib.check(lib.glp_fwd(tmp.handle, u_loc.data_ptr(), l, Au.data_ptr(), None))
-        torch.cuda.synchronize()
-    finally:
-        tmp.close()
+    _lib.check(lib.glp_rhs_exact(A.data_ptr(), _lib.GLP_F32 if f32 else _lib.GLP_F64, m, A.stride(0), u_loc64.data_ptr(), l,
+                                 nz.data_ptr() if nz.numel() else None, nz.numel(), Au.data_ptr(),
+                                 torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
     if world > 1:
         import torch.distributed as dist
         dist.all_reduce(Au, group=group)

@@ -311,6 +311,13 @@ int glp_metrics_eval(glp_handle* h, const void* x_dev, const void* ref_dev, doub
 int glp_randn(void* dst_dev, int dtype, int64_t rows, int64_t cols, int64_t ld, uint64_t seed,
               int64_t row0, int64_t col0, void* stream);
 
+/* b = A u of the same recipe (code/main.py:45): fp64 accumulation over the non-zero row groups of u in ascending
+ * column order (nz_dev: their indices), rounded multiply then rounded add -- bit-identical to the CPU restatement
+ * (oracle/glprox_gen.c), so that a CPU arm that never loads this library works on the very same right-hand side.
+ * u_dev [n_local][l] and y_dev [m][l] are fp64 row-major; a column shard yields its partial product. */
+int glp_rhs_exact(const void* A_dev, int dtype, int64_t m, int64_t lda, const double* u_dev, int l,
+                  const int64_t* nz_dev, int64_t nnz, double* y_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -76,7 +76,7 @@ def test_sparsity_history_and_debug_log_lines(caplog):
                 x, k, out = fn(np.copy(x0), A, b, mu, dict(opts))
             lines.append([r.getMessage() for r in caplog.records if r.name == "opt"])
         ref, got = lines
-        assert len(ref) == len(got) and len(ref) >= 1 + 3 + 6, (len(ref), len(got))
+        assert len(ref) == len(got) and len(ref) >= 1 + 3 + 4, (len(ref), len(got))
         for a, c in zip(ref, got):
             if a.startswith("iter="):
                 pa = [float(t.split("=")[1]) for t in a.split(",")]

@@ -151,3 +151,25 @@ def test_fp16_pairs_keep_normwise_accuracy_over_a_wide_dynamic_range():
     normwise = Qa.sum(dim=1)[:, None] * Pa.max() + Pa.sum(dim=1)[None, :] * Qa.max()      # [N][M]
     assert torch.isfinite(D).all()
     assert ((D - full.t()).abs() / normwise).max().item() <= 5e-7
+
+
+@pytest.mark.parametrize("shape", [(16384, 8192, 128), (512, 65536, 128), (4096, 16384, 256), (1000, 3333, 200), (300, 700, 16),
+                                   (65536, 2048, 64)])
+def test_cta_pair_kernel_equals_the_one_cta_kernel(shape, monkeypatch):
+    """K5 on CTA pairs (tcgen05.mma.cta_group::2, M = 256 over two SMs, stream-K over the 74 pairs; csrc/glp_gemm_pair.cuh)
+    against the one-CTA kernel on the same fp16-pair operands: the tensor core sees the same 256-element chunks, the
+    fp64 sums only differ in association (partial tiles of a stream-K range are added in pair order), and a rerun is
+    bit-identical (fixed summation order).  Shapes: tiles shared by 2 pairs, by ~37 pairs, two column groups, ragged."""
+    import torch
+    M, K, N = shape
+    monkeypatch.setenv("GLPROX_GEMM_PAIR", "0")
+    D0 = _run(M, K, N, 4, 4, seed=3)[-1]
+    monkeypatch.setenv("GLPROX_GEMM_PAIR", "1")
+    P, Q, _, _, _, _, D1 = _run(M, K, N, 4, 4, seed=3)
+    D2 = _run(M, K, N, 4, 4, seed=3)[-1]
+    assert not torch.isnan(D1).any()
+    assert torch.equal(D1, D2)
+    scale = P.double().abs() @ Q.double().abs().t() + 1e-300
+    assert ((D1 - D0).abs() / scale).max().item() <= 1e-12
+    full = P.double() @ Q.double().t()
+    assert ((D1 - full).abs() / scale).max().item() <= 5e-7
