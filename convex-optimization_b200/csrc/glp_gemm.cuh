@@ -399,6 +399,55 @@ __global__ void glp_transpose_split_f16_kernel(const float* __restrict__ src, __
   }
 }
 
+// ---- tiled resident operand of the CTA-pair kernel (glp_gemm_pair.cuh) ------------------------------------------
+// The streamed operand P [rows x cols] (cols = K) is stored as [rows/128][K/64] tiles of 128 rows x 64 fp16 (128 bytes
+// per row, 16 KB per tile, contiguous): the tile a CTA fetches for one K block is ONE contiguous 16 KB run of HBM
+// instead of 128 runs of 128 bytes that are a whole matrix row (>= 32 KB) apart -- the access pattern that kept the
+// row-major operand at 53 % of the DRAM peak (ncu, profiles/r02_ncu_gemm_pair_rowmajor.txt).
+__host__ __device__ __forceinline__ int64_t f16_tiled_off(int64_t r, int64_t k, int64_t nkb) {
+  return (((r >> 7) * nkb + (k >> 6)) << 13) + ((r & 127) << 6) + (k & 63);
+}
+__global__ void glp_split_f16_tiled_kernel(const float* __restrict__ src, __half* __restrict__ o0, __half* __restrict__ o1,
+                                           int64_t rows, int64_t cols, int64_t ld_src, int64_t nkb, float s) {
+  const int64_t total = rows * cols;
+  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t i = e / cols, j = e - i * cols;
+    const int64_t o = f16_tiled_off(i, j, nkb);
+    split_f16_one(src[i * ld_src + j], s, o0[o], o1[o]);
+  }
+}
+// the same with the scale taken on the device from the operand's maximum (test / probe entry point glp_gemm_tf32)
+__global__ void glp_split_f16_tiled_dev_scale_kernel(const float* __restrict__ src, __half* __restrict__ o0,
+                                                     __half* __restrict__ o1, int64_t rows, int64_t cols, int64_t ld_src,
+                                                     int64_t nkb, const unsigned* amax_bits) {
+  const float s = f16_scale_for(__uint_as_float(*amax_bits));
+  const int64_t total = rows * cols;
+  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t i = e / cols, j = e - i * cols;
+    const int64_t o = f16_tiled_off(i, j, nkb);
+    split_f16_one(src[i * ld_src + j], s, o0[o], o1[o]);
+  }
+}
+// the transposed operand: dst(j, i) = src(i, j), tiled over (rows = j < cols of src, K = i < rows of src)
+__global__ void glp_transpose_split_f16_tiled_kernel(const float* __restrict__ src, __half* __restrict__ o0,
+                                                     __half* __restrict__ o1, int64_t rows, int64_t cols, int64_t ld_src,
+                                                     int64_t nkb, float s) {
+  __shared__ float t[32][33];
+  const int64_t bi = int64_t(blockIdx.y) * 32, bj = int64_t(blockIdx.x) * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int64_t i = bi + r, j = bj + threadIdx.x;
+    t[r][threadIdx.x] = (i < rows && j < cols) ? src[i * ld_src + j] : 0.f;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int64_t j = bj + r, i = bi + threadIdx.x;
+    if (j < cols && i < rows) {
+      const int64_t o = f16_tiled_off(j, i, nkb);
+      split_f16_one(t[threadIdx.x][r], s, o0[o], o1[o]);
+    }
+  }
+}
+
 // work item w -> (K split, M tile, column group), column group fastest: the CTAs that take the column
 // groups of one P tile run side by side, so P is read from HBM once and from L2 by the others (with
 // N = 2l = 256 the product would otherwise stream A twice and turn HBM-bound); neighbouring CTAs also

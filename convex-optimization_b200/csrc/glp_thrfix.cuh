@@ -19,6 +19,7 @@
 #include <cuda_fp16.h>
 
 #include "glp_device.cuh"
+#include "glp_gemm.cuh"
 #include "glp_types.cuh"
 
 namespace glp {
@@ -126,6 +127,7 @@ struct ThrFixArgs {
   float thres;                      // the hard threshold: every |vals| is below it
   const double* inv_x;              // fp16-pair set: 1 / (s s_x) of the current operand, max|xn| s_x in [2^14, 2^15)
   double* AX[2];                    // [2l][ldm]: column l + c := column c - sum_r At[rows_r][:] * vals_r
+  int64_t tiled_nkb;                // > 0: At_f0 / At_f1 are stored as 128 x 64 tiles with this many K blocks (glp_gemm.cuh)
 };
 
 // grid (ceil(ldm / (128 ROWS)), l): block (ib, c) owns 128 ROWS output rows of column c, ROWS consecutive rows per
@@ -193,6 +195,10 @@ glp_thr_fix_kernel(const ThrFixArgs a, const Geom g) {
       b8(__ldg(reinterpret_cast<const uint4*>(a.At_lb + at)), v);
     }
   };
+  // offset of the RW values (row j of A^T, output rows i .. i + RW - 1; i is a multiple of RW = 8, so they share a tile row)
+  auto at_off = [&](int32_t j) {
+    return a.tiled_nkb > 0 ? f16_tiled_off(int64_t(j), i, a.tiled_nkb) : int64_t(j) * g.ldm + i;
+  };
   for (int r0 = 0; r0 < R; r0 += THRFIX_THREADS) {
     const int nr = R - r0 < THRFIX_THREADS ? R - r0 : THRFIX_THREADS;
     __syncthreads();
@@ -203,7 +209,7 @@ glp_thr_fix_kernel(const ThrFixArgs a, const Geom g) {
     for (; r + THRFIX_UNROLL <= nr; r += THRFIX_UNROLL) {   // independent row segments in flight
       float av[THRFIX_UNROLL][RW];
 #pragma unroll
-      for (int q = 0; q < THRFIX_UNROLL; ++q) at8(int64_t(s_j[r + q]) * g.ldm + i, av[q]);
+      for (int q = 0; q < THRFIX_UNROLL; ++q) at8(at_off(s_j[r + q]), av[q]);
 #pragma unroll
       for (int q = 0; q < THRFIX_UNROLL; ++q) {
         const float d = s_v[r + q];
@@ -213,7 +219,7 @@ glp_thr_fix_kernel(const ThrFixArgs a, const Geom g) {
     }
     for (; r < nr; ++r) {
       float av[RW];
-      at8(int64_t(s_j[r]) * g.ldm + i, av);
+      at8(at_off(s_j[r]), av);
       const float d = s_v[r];
 #pragma unroll
       for (int t = 0; t < RW; ++t) acc[t] = fmaf(av[t], d, acc[t]);

@@ -175,6 +175,7 @@ struct glp_handle {
   double* f16_inv = nullptr;       // [2] 1 / (s_A s_x), 1 / (s_A s_r): what the product epilogues multiply by
   float f16_sA = 1.0f;             // power-of-two scale of the resident A
   bool f16_unusable = false;       // auto mode found non-finite entries in A: 3xTF32 instead
+  bool f16_tiled = false;          // A_f0.. / At_f0.. are stored as 128 x 64 tiles for the CTA-pair kernel (glp_gemm.cuh)
   // A.xnt from A.xn by a sparse correction (glp_thrfix.cuh); thr_cap < 0: off (GLPROX_WIDE_THRFIX=0)
   int32_t *thr_rows = nullptr, *thr_col_count = nullptr, *thr_count = nullptr;
   float* thr_vals = nullptr;
@@ -703,18 +704,31 @@ static int ensure_wide(glp_handle* h) {
       return ensure_wide(h);
     }
     h->f16_sA = f16_scale_for(amax);
-    GLP_TRY(alloc_zero(&h->A_f0, a_el * 2, h->stream));
-    GLP_TRY(alloc_zero(&h->A_f1, a_el * 2, h->stream));
-    GLP_TRY(alloc_zero(&h->At_f0, at_el * 2, h->stream));
-    GLP_TRY(alloc_zero(&h->At_f1, at_el * 2, h->stream));
+    // the CTA-pair kernel streams a tiled operand (GLPROX_GEMM_PAIR=0 keeps the row-major set of the one-CTA kernel)
+    const char* e_pair = getenv("GLPROX_GEMM_PAIR");
+    h->f16_tiled = e_pair == nullptr || atoi(e_pair) != 0;
+    // K blocks of the tiled sets: what the product kernel derives from its K (n for A, m for A^T)
+    const int64_t nkb_a = (g.n + 63) / 64, nkb_at = (g.m + 63) / 64;
+    const size_t a_tiled = size_t((g.m + 127) / 128) * 128 * size_t(nkb_a) * 64;
+    const size_t at_tiled = size_t((g.n + 127) / 128) * 128 * size_t(nkb_at) * 64;
+    GLP_TRY(alloc_zero(&h->A_f0, (h->f16_tiled ? a_tiled : a_el) * 2, h->stream));
+    GLP_TRY(alloc_zero(&h->A_f1, (h->f16_tiled ? a_tiled : a_el) * 2, h->stream));
+    GLP_TRY(alloc_zero(&h->At_f0, (h->f16_tiled ? at_tiled : at_el) * 2, h->stream));
+    GLP_TRY(alloc_zero(&h->At_f1, (h->f16_tiled ? at_tiled : at_el) * 2, h->stream));
     GLP_TRY(alloc_zero(&h->xop_f0, x_el * 2, h->stream));
     GLP_TRY(alloc_zero(&h->xop_f1, x_el * 2, h->stream));
     GLP_TRY(alloc_zero(&h->r_f0, r_el * 2, h->stream));
     GLP_TRY(alloc_zero(&h->r_f1, r_el * 2, h->stream));
-    glp_split_f16_2d_kernel<<<ag, 256, 0, h->stream>>>(A, h->A_f0, h->A_f1, g.m, g.n, h->lda, g.ldn, h->f16_sA);
     dim3 tgrid(unsigned((g.n + 31) / 32), unsigned((g.m + 31) / 32));
     if (tgrid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
-    glp_transpose_split_f16_kernel<<<tgrid, dim3(32, 8), 0, h->stream>>>(A, h->At_f0, h->At_f1, g.m, g.n, h->lda, g.ldm, h->f16_sA);
+    if (h->f16_tiled) {
+      glp_split_f16_tiled_kernel<<<ag, 256, 0, h->stream>>>(A, h->A_f0, h->A_f1, g.m, g.n, h->lda, nkb_a, h->f16_sA);
+      glp_transpose_split_f16_tiled_kernel<<<tgrid, dim3(32, 8), 0, h->stream>>>(A, h->At_f0, h->At_f1, g.m, g.n, h->lda,
+                                                                                 nkb_at, h->f16_sA);
+    } else {
+      glp_split_f16_2d_kernel<<<ag, 256, 0, h->stream>>>(A, h->A_f0, h->A_f1, g.m, g.n, h->lda, g.ldn, h->f16_sA);
+      glp_transpose_split_f16_kernel<<<tgrid, dim3(32, 8), 0, h->stream>>>(A, h->At_f0, h->At_f1, g.m, g.n, h->lda, g.ldm, h->f16_sA);
+    }
     CU_TRY(cudaGetLastError());
     return GLP_OK;
   }
@@ -748,7 +762,7 @@ static int ensure_wide(glp_handle* h) {
 
 // split-K partial products (buf == nullptr: no splitting) and the workspace of the CTA-pair kernel (pair == nullptr:
 // the one-CTA kernel runs instead)
-struct GemmWs { double* buf; size_t bytes; void* pair = nullptr; size_t pair_bytes = 0; };
+struct GemmWs { double* buf; size_t bytes; void* pair = nullptr; size_t pair_bytes = 0; bool p_tiled = false; };
 struct GemmBf16 { const __nv_bfloat16 *Phb, *Plb, *Qhb, *Qlb; };  // passes = 2: bf16 copies of hi / lo, same pitches
 static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms, int bk);
 static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
@@ -840,7 +854,7 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
     h->n_launches++;
   }
   prof_mark(h, 0, 0);
-  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes, h->pair_ws, h->pair_ws_bytes};
+  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes, h->pair_ws, h->pair_ws_bytes, f16 && h->f16_tiled};
   // operand pointers of the selected set (fp16 pairs travel as float* through gemm_enqueue, pitches in elements)
   const float* Ph = f16 ? reinterpret_cast<const float*>(h->A_f0) : h->A_hi;
   const float* Pl = f16 ? reinterpret_cast<const float*>(h->A_f1) : h->A_lo;
@@ -873,6 +887,7 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
       fa.At_hi = nullptr; fa.At_lo = nullptr; fa.At_lb = nullptr;
       fa.At_f0 = h->At_f0; fa.At_f1 = h->At_f1; fa.inv_s = 1.0f / h->f16_sA;
       fa.thres = float(h->sc.thres); fa.inv_x = h->f16_inv;
+      fa.tiled_nkb = h->f16_tiled ? (g.m + 63) / 64 : 0;   // == ldm / 64: the padded output rows stay inside the last tile
     }
     fa.AX[0] = h->AX[0]; fa.AX[1] = h->AX[1];
     const int64_t frows = int64_t(THRFIX_THREADS) * THRFIX_ROWS;
@@ -903,7 +918,7 @@ static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
 static int enqueue_wide_tpass(glp_handle* h, const Ctrl* ctrl) {
   const Geom& g = h->g;
   float* r = static_cast<float*>(h->r);
-  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes, h->pair_ws, h->pair_ws_bytes};
+  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes, h->pair_ws, h->pair_ws_bytes, wide_passes(h) == 4 && h->f16_tiled};
   if (wide_passes(h) == 4) {
     const int64_t tot = int64_t(g.l) * g.ldm;
     // max|r| was left in f16_amax[1] by the decide kernel that wrote r
@@ -1976,7 +1991,7 @@ static cudaError_t launch_gemm_pair_t(cudaStream_t st, int num_sms, const CUtens
   cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   cudaLaunchConfig_t cfg = {};
-  cfg.blockDim = dim3(GEMM_THREADS, 1, 1);
+  cfg.blockDim = dim3(PAIR_THREADS, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -2062,13 +2077,21 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
   mpx = mph; mqx = mqh;
   // fp16 pairs: the CTA-pair kernel (cta_group::2 + stream-K) unless GLPROX_GEMM_PAIR=0 or no workspace was given
   const char* e_pair = getenv("GLPROX_GEMM_PAIR");   // read per call: tests switch it inside one process
+  if (passes == 4 && ws.p_tiled && (ws.pair == nullptr || (e_pair != nullptr && atoi(e_pair) == 0)))
+    return fail(GLP_ERR_STATE, "gemm: the resident fp16 operands are tiled for the CTA-pair kernel, which is switched off");
   if (passes == 4 && ws.pair != nullptr && (e_pair == nullptr || atoi(e_pair) != 0)) {
     const int ctas = 2 * (num_sms / 2);
     if (ws.pair_bytes < pair_ws_bytes(ctas, NT)) return fail(GLP_ERR_ARG, "gemm: pair workspace too small");
     if (tiles * groups > PAIR_COUNTER_WORDS) return fail(GLP_ERR_ARG, "gemm: too many output tiles for the pair kernel");
     CUtensorMap p0, p1, q0, q1;
-    GLP_TRY(make_map_f16_k128(&p0, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
-    GLP_TRY(make_map_f16_k128(&p1, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
+    if (ws.p_tiled) {   // [tiles * nkb * 128 rows][64 fp16]: every 128-row box is one contiguous 16 KB tile
+      const uint64_t trows = uint64_t((M + 127) / 128) * uint64_t((K + 63) / 64) * 128;
+      GLP_TRY(make_map_f16_k128(&p0, Ph, 64, trows, 128, GEMM_BM));
+      GLP_TRY(make_map_f16_k128(&p1, Pl, 64, trows, 128, GEMM_BM));
+    } else {
+      GLP_TRY(make_map_f16_k128(&p0, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
+      GLP_TRY(make_map_f16_k128(&p1, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
+    }
     GLP_TRY(make_map_f16_k128(&q0, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, uint32_t(NT / 2)));
     GLP_TRY(make_map_f16_k128(&q1, Ql, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, uint32_t(NT / 2)));
     PairArgs pa{};
@@ -2076,6 +2099,7 @@ static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int
     pa.ctrl = ctrl; pa.D_alt = D_alt; pa.role = role;
     pa.gate = gate.count; pa.gate_cap = gate.cap;
     pa.scale = scale;
+    pa.p_tiled = ws.p_tiled ? 1 : 0;
     pa.counters = static_cast<unsigned*>(ws.pair);
     pa.slots = reinterpret_cast<double*>(static_cast<char*>(ws.pair) + size_t(PAIR_COUNTER_WORDS) * 4);
     const cudaError_t ep = NT == 32 ? launch_gemm_pair_t<32>(st, num_sms, p0, p1, q0, q1, pa)
@@ -2174,9 +2198,13 @@ extern "C" int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, in
   if (passes == 4) {
     // fp16 pairs of P_hi and Q_hi themselves (the lo arguments are not used): scales from the operands' maxima,
     // all on the device in stream-ordered temporaries (test / probe entry point)
-    const size_t pe = size_t(M) * ldp, qe = size_t(N) * ldq;
+    const char* e_pair = getenv("GLPROX_GEMM_PAIR");
+    const bool tiled = e_pair == nullptr || atoi(e_pair) != 0;
+    const int64_t nkb_t = (K + 63) / 64;
+    const size_t pe = tiled ? size_t((M + 127) / 128) * 128 * size_t(nkb_t) * 64 : size_t(M) * ldp, qe = size_t(N) * ldq;
     uint8_t* t4 = nullptr;
     CU_TRY(cudaMallocAsync(reinterpret_cast<void**>(&t4), (2 * pe + 2 * qe) * 2 + 64, st));
+    if (tiled) CU_TRY(cudaMemsetAsync(t4, 0, (2 * pe + 2 * qe) * 2 + 64, st));
     __half *p0 = reinterpret_cast<__half*>(t4 + 64), *p1 = p0 + pe, *q0 = p1 + pe, *q1 = q0 + qe;
     unsigned* amax = reinterpret_cast<unsigned*>(t4);
     double* inv = reinterpret_cast<double*>(t4 + 16);
@@ -2185,9 +2213,11 @@ extern "C" int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, in
     const int g1 = int(std::min<size_t>((pe + 255) / 256, 148 * 16)), g2 = int(std::min<size_t>((qe + 255) / 256, 148 * 16));
     glp_absmax_kernel<<<g1, 256, 0, st>>>(Pf, M, K, ldp, amax);
     glp_absmax_kernel<<<g2, 256, 0, st>>>(Qf, N, K, ldq, amax + 1);
-    glp_split_f16_kernel<<<g1, 256, 0, st>>>(Pf, p0, p1, int64_t(pe), amax, nullptr, 0, 1.0f, nullptr, nullptr, nullptr, 0);
+    if (tiled) glp_split_f16_tiled_dev_scale_kernel<<<g1, 256, 0, st>>>(Pf, p0, p1, M, K, ldp, nkb_t, amax);
+    else glp_split_f16_kernel<<<g1, 256, 0, st>>>(Pf, p0, p1, int64_t(pe), amax, nullptr, 0, 1.0f, nullptr, nullptr, nullptr, 0);
     glp_split_f16_kernel<<<g2, 256, 0, st>>>(Qf, q0, q1, int64_t(qe), amax + 1, nullptr, 0, 1.0f, amax, inv, nullptr, 0);
     CU_TRY(cudaGetLastError());
+    ws.p_tiled = tiled;
     ws.pair_bytes = pair_ws_bytes(sms, 128);
     CU_TRY(cudaMallocAsync(&ws.pair, ws.pair_bytes, st));
     CU_TRY(cudaMemsetAsync(ws.pair, 0, size_t(PAIR_COUNTER_WORDS) * 4, st));

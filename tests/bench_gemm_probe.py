@@ -34,6 +34,10 @@ if len(sys.argv) > 1 and sys.argv[1] == "one4":   # the two fp16-pair launches p
         torch.cuda.synchronize()
         del P, Q, D
     sys.exit(0)
+if len(sys.argv) > 1 and sys.argv[1] == "pair":   # fp16-pair product at the solver's chunk (256 elements of K), C5 shapes; GLPROX_GEMM_PAIR selects the kernel
+    for (M, K, N) in [(16384, 65536, 128), (65536, 16384, 128)]:
+        run(M, K, N, 4, 4, reps=int(sys.argv[2]) if len(sys.argv) > 2 else 5)
+    sys.exit(0)
 if len(sys.argv) > 1 and sys.argv[1] == "alias":   # is the 3-pass product bound by the P stream from HBM?
     for (M, K, N) in [(16384, 65536, 128), (65536, 16384, 128), (16384, 65536, 256)]:
         for al in (False, True):

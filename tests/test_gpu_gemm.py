@@ -170,6 +170,6 @@ def test_cta_pair_kernel_equals_the_one_cta_kernel(shape, monkeypatch):
     assert not torch.isnan(D1).any()
     assert torch.equal(D1, D2)
     scale = P.double().abs() @ Q.double().abs().t() + 1e-300
-    assert ((D1 - D0).abs() / scale).max().item() <= 1e-12
+    assert ((D1 - D0).abs() / scale).max().item() <= 1e-7   # the fp32 correction accumulator spans a stream-K range (here up to 37 per tile), not a tile
     full = P.double() @ Q.double().t()
     assert ((D1 - full).abs() / scale).max().item() <= 5e-7
