@@ -12,8 +12,9 @@
 // which also does the two triangular solves with L in one CTA); ONE transposed stream (K2) gives A^T z and
 // `update` applies the row-local projection / multiplier step.  A is streamed exactly twice per iteration,
 // the control (k, the converge_len counter, histories) lives on the device.
-// Scope: homework-sized systems -- the m x m factor is built and applied by single-CTA kernels (m <= 2048),
-// l <= 2 (the residual 2-norms are taken from the l x l Gram matrices in closed form).
+// Scope of THIS file: the kernels of the iteration and the single-CTA factor / solves used for m <= 2048; larger
+// systems take the blocked set-up of glp_dense.cuh and apply the factor as two streams of Y = L^-T
+// (glp_admm_host.inl).  l <= 2 (the residual 2-norms are taken from the l x l Gram matrices in closed form).
 #pragma once
 #include "glp_decide.h"
 #include "glp_device.cuh"
@@ -169,6 +170,8 @@ struct AdmmMidArgs {
   double* f_hist;
   double* f_hist_best;
   double size_total;          // n_total * l
+  double* w_out;              // blocked path: w = P1 - b goes to this planar fp64 buffer [l][w_ld] and the kernel ends
+  int64_t w_ld;               // there (the solves are two streams of Y = L^-T); nullptr: solve here with L
 };
 
 // largest singular value of a matrix with Gram matrix [[a, b], [b, c]] (l = 2) or [[a]] (l = 1)
@@ -258,6 +261,14 @@ __global__ void __launch_bounds__(ADMM_THREADS) glp_admm_mid_kernel(const AdmmMi
   __syncthreads();
   if (s_out.done) return;
 
+  if (a.w_out != nullptr) {   // blocked path: right-hand side to global memory, the streams of Y do the rest
+    for (int i = tid; i < m; i += ADMM_THREADS)
+      for (int c = 0; c < l; ++c) {
+        a.w_out[c * a.w_ld + i] = xsub(P1[c * ldm + i], a.b[c * ldm + i]);
+        a.Au_prev[c * ldm + i] = P2[c * ldm + i];
+      }
+    return;
+  }
   // ---- w = P1 - b ; A u_prev <- A u ; then the two triangular solves in shared memory
   for (int i = tid; i < m; i += ADMM_THREADS)
     for (int c = 0; c < l; ++c) {

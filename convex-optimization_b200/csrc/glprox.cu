@@ -18,6 +18,7 @@
 #include "glp_admm.cuh"
 #include "glp_comm.cuh"
 #include "glp_decide.cuh"
+#include "glp_dense.cuh"
 #include "glp_fwd.cuh"
 #include "glp_gather_decide.cuh"
 #include "glp_gemm.cuh"
@@ -181,6 +182,10 @@ struct glp_handle {
   float* thr_vals = nullptr;
   int32_t thr_cap = -1;            // list entries per operand column
   double* admm_L = nullptr;    // gl_Admm_dual: m x m Cholesky factor of I + rho A A^T
+  double* admm_Y = nullptr;    // blocked path (m > 2048): Y = L^-T, streamed by the inner handle (glp_dense.cuh)
+  int64_t admm_ldy = 0;
+  glp_handle* admm_inner = nullptr;   // m x m fp64 problem over Y: K1 / K2 apply z = Y (Y^T w)
+  double* admm_zero_b = nullptr;
   void* pair_ws = nullptr;     // K5 on CTA pairs (glp_gemm_pair.cuh): arrival counters + partial-tile slots
   size_t pair_ws_bytes = 0;
   double* gemm_ws = nullptr;   // split-K partial products of K5
@@ -443,6 +448,9 @@ extern "C" int glp_destroy(glp_handle* h) {
   if (h->gemm_ws) cudaFree(h->gemm_ws);
   if (h->pair_ws) cudaFree(h->pair_ws);
   if (h->admm_L) cudaFree(h->admm_L);
+  if (h->admm_inner) { glp_handle* in = h->admm_inner; h->admm_inner = nullptr; glp_destroy(in); }
+  if (h->admm_Y) cudaFree(h->admm_Y);
+  if (h->admm_zero_b) cudaFree(h->admm_zero_b);
   if (h->nccl_stage) cudaFree(h->nccl_stage);
   for (__half* q : {h->A_f0, h->A_f1, h->At_f0, h->At_f1, h->xop_f0, h->xop_f1, h->r_f0, h->r_f1})
     if (q) cudaFree(q);
@@ -2254,142 +2262,7 @@ extern "C" int glp_tf32_split(void* stream, const void* src, int64_t rows, int64
   return GLP_OK;
 }
 
-// ------------------------------------------------------------------------------------------------
-// gl_Admm_dual (glp_admm.cuh)
-// ------------------------------------------------------------------------------------------------
-extern "C" int glp_admm_default_opts(glp_admm_opts* o) {
-  if (o == nullptr) return fail(GLP_ERR_ARG, "null opts");
-  o->maxit = 100; o->converge_len = 20; o->thres = 1e-3; o->tau = (1.0 + std::sqrt(5.0)) * 0.5; o->rho = 1e2;
-  return GLP_OK;
-}
-
-extern "C" int glp_admm_dual(glp_handle* h, const void* x0_dev, double mu, const glp_admm_opts* o, void* x_out_dev,
-                             glp_result* res, double* f_hist_host, int hist_cap) {
-  if (h == nullptr || x0_dev == nullptr || o == nullptr) return fail(GLP_ERR_ARG, "null argument");
-  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
-  if (multi(h)) return fail(GLP_ERR_ARG, "gl_Admm_dual runs on one GPU");
-  const Geom& g = h->g;
-  if (g.m > ADMM_MAX_M || g.l > 2)
-    return fail(GLP_ERR_ARG, "gl_Admm_dual supports m <= %d and l <= 2 (got m = %d, l = %d)", ADMM_MAX_M, g.m, g.l);
-  if (o->maxit < 0 || !(o->rho > 0.0)) return fail(GLP_ERR_ARG, "bad opts (maxit >= 0, rho > 0)");
-  CU_TRY(cudaSetDevice(h->device));
-  const bool f32 = h->dtype == GLP_F32;
-  const int64_t ll = int64_t(g.l) * g.ldn, lm = int64_t(g.l) * g.ldm;
-  AdmmConst ac{};
-  ac.maxit = o->maxit; ac.converge_len = o->converge_len; ac.hist_cap = std::max(o->maxit, 1) + 8;
-  ac.thres = o->thres; ac.tau = o->tau; ac.rho = o->rho; ac.mu = mu;
-  if (h->hist_cap < ac.hist_cap) {
-    if (h->f_hist) CU_TRY(cudaFree(h->f_hist));
-    h->f_hist = nullptr;
-    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->f_hist), size_t(3) * ac.hist_cap * sizeof(double)));
-    h->hist_cap = ac.hist_cap;
-  }
-  h->f_hist_best = h->f_hist + h->hist_cap;
-  h->n_launches = 0;
-  h->backend_used = GLP_BACKEND_STREAM;
-  CU_TRY(cudaEventRecord(h->ev0, h->stream));
-  // ---- one-time factor (inside the call, like :57 of the reference)
-  if (h->admm_L == nullptr) CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->admm_L), size_t(g.m) * g.m * 8));
-  CU_TRY(cudaMemsetAsync(h->admm_L, 0, size_t(g.m) * g.m * 8, h->stream));
-  CU_TRY(cudaMemsetAsync(h->fault, 0, sizeof(int32_t), h->stream));
-  {
-    const int tb = (g.m + 31) / 32;
-    if (f32) glp_admm_gram_kernel<float><<<dim3(tb, tb), dim3(32, 32), 0, h->stream>>>(static_cast<const float*>(h->A), h->lda, g.m, g.n, ac.rho, h->admm_L);
-    else glp_admm_gram_kernel<double><<<dim3(tb, tb), dim3(32, 32), 0, h->stream>>>(static_cast<const double*>(h->A), h->lda, g.m, g.n, ac.rho, h->admm_L);
-    glp_admm_chol_kernel<<<1, ADMM_THREADS, 0, h->stream>>>(h->admm_L, g.m, h->fault);
-    CU_TRY(cudaGetLastError());
-    h->n_launches += 2;
-  }
-  // ---- state: x, u in state[1]; operands [x - rho u | u] in xop (fp32) or state[0] (fp64); A u_prev in Av
-  double* x = h->state[1];
-  double* u = h->state[1] + ll;
-  void* xop = f32 ? h->xop : static_cast<void*>(h->state[0]);
-  if (f32) CU_TRY(to_planar(h->stream, static_cast<const float*>(x0_dev), x, g.n, g.l, g.ldn));
-  else CU_TRY(to_planar(h->stream, static_cast<const double*>(x0_dev), x, g.n, g.l, g.ldn));
-  CU_TRY(cudaMemsetAsync(h->Av, 0, size_t(lm) * 8, h->stream));
-  Ctrl c0;
-  memset(&c0, 0, sizeof(c0));
-  c0.cur = 1;   // forward stream: sel = 1 - cur = 0
-  c0.f_best = INFINITY;
-  c0.n_fwd = 1;
-  CU_TRY(cudaMemcpyAsync(&h->ctrl[0], &c0, sizeof(Ctrl), cudaMemcpyHostToDevice, h->stream));
-  CU_TRY(cudaMemcpyAsync(&h->ctrl[1], &c0, sizeof(Ctrl), cudaMemcpyHostToDevice, h->stream));
-  h->solving = true;
-  const int upd_threads = f32 ? Elem<float>::TILE_COLS : Elem<double>::TILE_COLS;
-  auto launch_update = [&](const Ctrl* ctrl, int init) -> cudaError_t {
-    AdmmUpdArgs ua{};
-    ua.ctrl = ctrl; ua.init = init; ua.x = x; ua.u = u; ua.grad = h->grad; ua.xop = xop;
-    ua.scal_partial = h->scal_partial; ua.c = ac;
-    if (f32) glp_admm_update_kernel<float><<<g.ncb, upd_threads, 0, h->stream>>>(ua, g);
-    else glp_admm_update_kernel<double><<<g.ncb, upd_threads, 0, h->stream>>>(ua, g);
-    h->n_launches++;
-    return cudaGetLastError();
-  };
-  int rc = GLP_OK;
-  auto body = [&]() -> int {
-    CU_TRY(launch_update(nullptr, 1));
-    const void* Xb[2] = {xop, xop};
-    double* AXb[2] = {h->AX[0], h->AX[0]};
-    const double* xc[2] = {x, x};
-    const int64_t max_slots = int64_t(o->maxit) + 1;
-    int64_t issued = 0, launches = 0;
-    bool done = false;
-    while (!done && issued < max_slots + 16) {
-      for (int s = 0; s < 16; ++s) {
-        const Ctrl* cin = &h->ctrl[launches & 1];
-        Ctrl* cout = &h->ctrl[(launches + 1) & 1];
-        GLP_TRY(enqueue_fwd(h, cin, 0, Xb, AXb, xc, 2 * g.l, 1, false));
-        AdmmMidArgs ma{};
-        ma.cin = cin; ma.cout = cout; ma.c = ac;
-        ma.P = h->AX[0]; ma.b = h->b; ma.Au_prev = h->Av; ma.L = h->admm_L;
-        ma.scal_partial = h->scal_partial; ma.n_scal = g.ncb;
-        ma.cnt_partial = h->cnt_partial; ma.n_cnt = g.grid;
-        ma.r = h->r; ma.f_hist = h->f_hist; ma.f_hist_best = h->f_hist_best;
-        ma.size_total = double(g.n) * double(g.l);
-        const size_t smem = size_t(g.l) * g.m * 8;
-        if (f32) glp_admm_mid_kernel<float><<<1, ADMM_THREADS, smem, h->stream>>>(ma, g);
-        else glp_admm_mid_kernel<double><<<1, ADMM_THREADS, smem, h->stream>>>(ma, g);
-        CU_TRY(cudaGetLastError());
-        h->n_launches++;
-        ++launches;
-        GLP_TRY(enqueue_tpass(h, cout, nullptr, h->grad, false));
-        CU_TRY(launch_update(cout, 0));
-      }
-      issued += 16;
-      CU_TRY(cudaMemcpyAsync(&h->h_ctrl[0], &h->ctrl[launches & 1], sizeof(Ctrl), cudaMemcpyDeviceToHost, h->stream));
-      GLP_TRY(check_fault(h, cudaStreamSynchronize(h->stream)));
-      done = h->h_ctrl[0].done != 0;
-    }
-    return GLP_OK;
-  };
-  rc = body();
-  h->solving = false;
-  if (rc != GLP_OK) return rc;
-  int32_t fault = 0;
-  CU_TRY(cudaMemcpyAsync(&fault, h->fault, sizeof(fault), cudaMemcpyDeviceToHost, h->stream));
-  CU_TRY(cudaStreamSynchronize(h->stream));
-  if (res) memset(res, 0, sizeof(*res));
-  if (fault != 0) {
-    if (res) res->status = GLP_ERR_DEVICE_FAULT;
-    return fail(GLP_ERR_DEVICE_FAULT, fault == 3 ? "I + rho A A^T is not positive definite (NaN / inf in A?)"
-                                                 : "pipeline watchdog fired inside a streaming kernel");
-  }
-  const Ctrl c = h->h_ctrl[0];
-  if (x_out_dev != nullptr) {
-    if (f32) CU_TRY(from_planar(h->stream, x, static_cast<float*>(x_out_dev), g.n, g.l, g.ldn));
-    else CU_TRY(from_planar(h->stream, x, static_cast<double*>(x_out_dev), g.n, g.l, g.ldn));
-  }
-  if (f_hist_host != nullptr && hist_cap > 0 && c.k > 0)
-    CU_TRY(cudaMemcpyAsync(f_hist_host, h->f_hist, sizeof(double) * std::min(hist_cap, std::min(c.k, ac.hist_cap)),
-                           cudaMemcpyDeviceToHost, h->stream));
-  CU_TRY(cudaEventRecord(h->ev1, h->stream));
-  CU_TRY(cudaStreamSynchronize(h->stream));
-  float ms = 0.f;
-  CU_TRY(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
-  fill_result(h, c, res);
-  if (res) { res->device_ms = ms; res->status = c.done ? GLP_OK : GLP_ERR_STATE; }
-  return GLP_OK;
-}
+#include "glp_admm_host.inl"
 
 // ------------------------------------------------------------------------------------------------
 // caller-side metrics (code/main.py:30-34,48-50) on the device

@@ -80,3 +80,54 @@ def test_admm_on_a_device_resident_problem_and_in_the_driver_table(capsys):
     rows = driver.main(["--solvers", "ADMM_dual", "--log-level", "WARNING"])
     assert rows[0]["solver"] == "ADMM Dual" and rows[0]["iter"] == "   71" and rows[0]["optval"] == "6.10786E-01"
     assert rows[0]["sparsity"] == "0.0996" and rows[0]["err-to-exact"] == "1.98E-04"
+
+
+@pytest.mark.parametrize("name", ["admm_fixture", "admm_ragged", "admm_l1", "admm_rho10"])
+def test_blocked_path_matches_the_reference_on_the_goldens(name, monkeypatch):
+    """The streaming-size schedule (csrc/glp_dense.cuh, glp_admm_host.inl: blocked fp64 Cholesky, Y = L^-T, the factor
+    applied as two streams of Y through K2 / K1) forced onto the golden cases: same k, f_hist within 1e-10, same support."""
+    monkeypatch.setenv("GLPROX_ADMM_BLOCKED", "1")
+    rec = load_golden(name)
+    A, b, x0, u, mu = golden_inputs(rec)
+    x, k, out = _fn()(x0, A, b, mu, dict(rec["opts"]))
+    assert k == int(rec["ADMM_dual_k"])
+    fh, ref = np.asarray(out["f_hist"]), rec["ADMM_dual_f_hist"]
+    assert fh.shape == ref.shape and np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-10
+    assert abs(out["fval"] - rec["ADMM_dual_fval"]) <= 1e-10 * abs(rec["ADMM_dual_fval"])
+    assert np.max(np.abs(x - rec["ADMM_dual_x"])) <= 1e-9
+    ax = np.abs(x)
+    assert np.array_equal(np.flatnonzero((ax > 1e-6 * ax.max()).any(axis=1)), rec["ADMM_dual_support_rule"])
+
+
+def test_blocked_path_fp64_parity_at_1024_x_4096(monkeypatch):
+    """parity with oracle.solve_admm_dual (code/gl_ADMM_dual.py:57-99) <= 1e-10 in fp64 at
+    1024 x 4096 on the blocked schedule (8 diagonal blocks of 128)."""
+    monkeypatch.setenv("GLPROX_ADMM_BLOCKED", "1")
+    A, b, x0, u, mu = orc.gen_data(5, 1024, 4096, 2)
+    opts = {"maxit": 40}
+    x, k, out = _fn()(x0, A, b, mu, dict(opts))
+    xr, kr, outr = orc.solve_admm_dual(x0, A, b, mu, dict(opts))
+    assert k == kr
+    fh, ref = np.asarray(out["f_hist"]), np.asarray(outr["f_hist"])
+    assert np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-10
+    assert abs(out["fval"] - outr["fval"]) <= 1e-10 * abs(outr["fval"])
+    assert np.max(np.abs(x - xr)) <= 1e-8 * max(1.0, np.max(np.abs(xr)))
+
+
+@pytest.mark.parametrize("gram", ["tensor", "cuda"])
+def test_streaming_size_fp32_admm_matches_the_fp64_oracle(gram, monkeypatch):
+    """m = 2560 > 2048: the blocked schedule is the only one.  fp32 data: the Gram matrix comes from the tensor cores
+    (K5 fp16 pairs, 'tensor') or from fp64 FMAs ('cuda'); bar: objective within 1e-5 of the fp64 oracle on the
+    fp32-rounded inputs (north_star, fp32 mode)."""
+    if gram == "cuda":
+        monkeypatch.setenv("GLPROX_ADMM_GRAM", "cuda")
+    m, n, l = 2560, 8192, 2
+    A, b, x0, u, mu = orc.gen_data(9, m, n, l, np.float32)
+    opts = {"maxit": 15}
+    x, k, out = _fn()(x0, A, b, mu, dict(opts))
+    xr, kr, outr = orc.solve_admm_dual(x0.astype(np.float64), A.astype(np.float64), b.astype(np.float64), mu, dict(opts))
+    assert k == kr == 15
+    fh, ref = np.asarray(out["f_hist"]), np.asarray(outr["f_hist"])
+    assert np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-5
+    assert abs(out["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
+    assert out["glprox"]["n_fwd"] == k + 1 and out["glprox"]["n_tpass"] == k

@@ -29,5 +29,4 @@ run pdl_off          GLPROX_PDL=0
 run fused_gather_off GLPROX_FUSED_GATHER=0
 run fence_per_block  GLPROX_PUSH_FENCE=block
 run all_off_round1   GLPROX_PDL=0 GLPROX_FUSED_GATHER=0 GLPROX_PUSH_FENCE=block
-run default_on_again GLPROX_PDL=1
 cat $OUT/multigpu_ab_n$N.log
