@@ -322,6 +322,32 @@ __global__ void glp_absmax_kernel(const float* __restrict__ src, int64_t rows, i
   mx = __reduce_max_sync(0xffffffffu, mx);
   if ((threadIdx.x & 31) == 0 && mx != 0u) atomicMax(out, mx);
 }
+// Per-column and per-row maxima of |src| as float bits (col_max[cols], row_max[rows], zeroed by the caller): the
+// dynamic range of the COLUMN / ROW scales of A.  The fp16-pair operand set keeps ~2^-40 of the matrix maximum in
+// absolute terms: entries that are small only because their whole column (or row) is scaled down -- un-normalised
+// feature columns -- would lose their significance against a large x entry, while an fp32 product keeps 2^-24 of
+// every entry.  Isolated small entries of a normally scaled column do not matter (their products are small too).
+__global__ void glp_rowcol_absmax_kernel(const float* __restrict__ src, int64_t rows, int64_t cols, int64_t ld,
+                                         unsigned* __restrict__ col_max, unsigned* __restrict__ row_max) {
+  const int64_t total = rows * cols;
+  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < total; e += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t i = e / cols, j = e - i * cols;
+    const unsigned u = __float_as_uint(fabsf(src[i * ld + j]));
+    if (u > __ldg(&col_max[j])) atomicMax(&col_max[j], u);
+    if (u > __ldg(&row_max[i])) atomicMax(&row_max[i], u);
+  }
+}
+// out[0] / out[1] = largest / smallest non-zero entry of v (float bits); out zero-initialised to {0, 0x7f800000}
+__global__ void glp_minmax_nonzero_kernel(const unsigned* __restrict__ v, int64_t n, unsigned* out) {
+  unsigned mx = 0u, mn = 0x7f800000u;
+  for (int64_t e = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; e < n; e += int64_t(gridDim.x) * blockDim.x) {
+    const unsigned u = v[e];
+    if (u != 0u) { mx = u > mx ? u : mx; mn = u < mn ? u : mn; }
+  }
+  mx = __reduce_max_sync(0xffffffffu, mx);
+  mn = __reduce_min_sync(0xffffffffu, mn);
+  if ((threadIdx.x & 31) == 0) { if (mx != 0u) atomicMax(&out[0], mx); atomicMin(&out[1], mn); }
+}
 // contiguous small operand (x or r) with the scale taken from its own max on the device: *amax_bits (float bits from
 // glp_absmax_kernel) or, when scal_partial is given, the max over slot 3 of the prox epilogue's per-block partials
 // (max|xn|, ncb blocks) -- every block reduces those few hundred values itself, which saves a pass over the operand.

@@ -151,7 +151,10 @@ struct glp_handle {
   int gather_grid = 0;
   // launch-latency switches (each read from the environment at glp_create so that A/B runs need no rebuild):
   bool pdl = true;                 // GLPROX_PDL=0: plain stream serialization instead of programmatic dependent launch
-  bool fused_gather = true;        // GLPROX_FUSED_GATHER=0: glp_gather_kernel + glp_decide_kernel as two launches
+  // GLPROX_FUSED_GATHER=1: gather + decide as ONE launch with a grid barrier (glp_gather_decide.cuh).  Measured on
+  // 8 B200 at C4 (profiles/r02_ab_latency_switches_c4_n8.log): 1397.9 it/s fused vs 1405.1 with the two launches --
+  // under programmatic dependent launch the second launch costs no more than the grid barrier.  Off by default.
+  bool fused_gather = false;
   bool push_fence_block = false;   // GLPROX_PUSH_FENCE=block: system fence per pushed row block (round-1 behaviour)
   int fused_grid = 0;              // CTAs of glp_gather_decide_kernel (all co-resident: grid-wide barrier inside)
   unsigned* gd_count = nullptr;
@@ -175,7 +178,7 @@ struct glp_handle {
   unsigned* f16_amax = nullptr;    // [2] float bits of max|xn| / max|r| of the current operands
   double* f16_inv = nullptr;       // [2] 1 / (s_A s_x), 1 / (s_A s_r): what the product epilogues multiply by
   float f16_sA = 1.0f;             // power-of-two scale of the resident A
-  bool f16_unusable = false;       // auto mode found non-finite entries in A: 3xTF32 instead
+  bool f16_unusable = false;       // auto mode found non-finite entries or badly scaled columns / rows in A: 3xTF32 instead
   bool f16_tiled = false;          // A_f0.. / At_f0.. are stored as 128 x 64 tiles for the CTA-pair kernel (glp_gemm.cuh)
   // A.xnt from A.xn by a sparse correction (glp_thrfix.cuh); thr_cap < 0: off (GLPROX_WIDE_THRFIX=0)
   int32_t *thr_rows = nullptr, *thr_col_count = nullptr, *thr_count = nullptr;
@@ -710,6 +713,33 @@ static int ensure_wide(glp_handle* h) {
       if (h->tensor_mode != 0) return fail(GLP_ERR_ARG, "A holds non-finite values: the fp16-pair operand set cannot be scaled");
       h->f16_unusable = true;   // auto: propagate them through the 3xTF32 operand set like any fp32 product would
       return ensure_wide(h);
+    }
+    // dynamic range of the column / row scales of A: beyond 2^18 the fp16 pairs (2^-40 of the matrix maximum) fall
+    // below fp32 accuracy on the small columns -> auto takes the 3xTF32 operand set, an explicit 'f16x2' is refused
+    {
+      unsigned* rc = nullptr;
+      CU_TRY(cudaMalloc(reinterpret_cast<void**>(&rc), size_t(g.m + g.n + 4) * sizeof(unsigned)));
+      CU_TRY(cudaMemsetAsync(rc, 0, size_t(g.m + g.n + 4) * sizeof(unsigned), h->stream));
+      const unsigned init[4] = {0u, 0x7f800000u, 0u, 0x7f800000u};
+      CU_TRY(cudaMemcpyAsync(rc + g.m + g.n, init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
+      glp_rowcol_absmax_kernel<<<ag, 256, 0, h->stream>>>(A, g.m, g.n, h->lda, rc, rc + g.n);
+      glp_minmax_nonzero_kernel<<<64, 256, 0, h->stream>>>(rc, g.n, rc + g.m + g.n);
+      glp_minmax_nonzero_kernel<<<64, 256, 0, h->stream>>>(rc + g.n, g.m, rc + g.m + g.n + 2);
+      unsigned mm[4] = {0, 0, 0, 0};
+      cudaError_t e1 = cudaMemcpyAsync(mm, rc + g.m + g.n, sizeof(mm), cudaMemcpyDeviceToHost, h->stream);
+      if (e1 == cudaSuccess) e1 = cudaStreamSynchronize(h->stream);
+      cudaFree(rc);
+      if (e1 != cudaSuccess) return fail(GLP_ERR_CUDA, "dynamic-range probe failed: %s", cudaGetErrorString(e1));
+      float fv[4];
+      memcpy(fv, mm, sizeof(fv));
+      const float range = std::max(fv[1] > 0.f ? fv[0] / fv[1] : 1.f, fv[3] > 0.f ? fv[2] / fv[3] : 1.f);
+      if (range > 262144.0f) {
+        if (h->tensor_mode != 0)
+          return fail(GLP_ERR_ARG, "the column / row scales of A span a factor %.3g > 2^18: the fp16-pair operand set would lose "
+                                   "the small ones; use tensor_cores 'auto' or '3xtf32'", double(range));
+        h->f16_unusable = true;
+        return ensure_wide(h);
+      }
     }
     h->f16_sA = f16_scale_for(amax);
     // the CTA-pair kernel streams a tiled operand (GLPROX_GEMM_PAIR=0 keeps the row-major set of the one-CTA kernel)

@@ -31,7 +31,7 @@ def main():
         A, b, x0 = (z.astype(np.float32) for z in (A, b, x0))
         opts = {"maxit": 4, "alpha0": float(1.0 / (np.sqrt(m) + np.sqrt(n)) ** 2)}
         Ad, bd = torch.from_numpy(A).cuda(), torch.from_numpy(b).cuda()
-        for mode in ("3xtf32", "tf32+bf16", "tf32"):
+        for mode in ("auto", "3xtf32", "tf32+bf16", "tf32"):   # auto = fp16 pairs on the CTA-pair kernel (cta_group::2)
             prob = GroupLassoProblem(Ad, bd)
             x, k, out = prob.solve("FProxGD", torch.from_numpy(x0).cuda(), mu, dict(opts, tensor_cores=mode))
             prob.close()
@@ -53,6 +53,16 @@ def main():
             for p in probs:
                 p.close()
             print("sharded", G, ll, k, float(out["fval"]), flush=True)
+    if which in ("all", "admm"):
+        A, b, x0, u, mu = orc.gen_data(3, 96, 300, 2)
+        for blocked in ("0", "1"):   # single-CTA factor / blocked Cholesky + streams of Y = L^-T
+            os.environ["GLPROX_ADMM_BLOCKED"] = blocked
+            for dt in (np.float64, np.float32):
+                prob = GroupLassoProblem(torch.from_numpy(A.astype(dt)).cuda(), torch.from_numpy(b.astype(dt)).cuda())
+                x, k, out = prob.solve_admm_dual(torch.from_numpy(x0.astype(dt)).cuda(), mu, {"maxit": 5})
+                prob.close()
+                print("admm blocked=" + blocked, dt.__name__, k, float(out["fval"]), flush=True)
+        os.environ.pop("GLPROX_ADMM_BLOCKED", None)
     torch.cuda.synchronize()
     print("SANITIZE_PROBE_DONE", flush=True)
 

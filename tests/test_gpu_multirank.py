@@ -79,3 +79,24 @@ def test_sharded_fp32_matches_single_handle(algo):
     single.close()
     for p in probs:
         p.close()
+
+
+@pytest.mark.parametrize("algo", ["ProxGD", "FProxGD"])
+def test_fused_gather_decide_kernel_gives_identical_bits(algo, monkeypatch):
+    """GLPROX_FUSED_GATHER=1 (glp_gather_decide_kernel: gather, grid barrier, decide in one launch) against the
+    default two launches: same partial layout and reduction order, hence the same history bit for bit."""
+    import torch
+    from glprox import solve_group
+    rec = load_golden("harsh_ls")
+    A, b, x0, u, mu = golden_inputs(rec)
+    hist = []
+    for fused in ("0", "1"):
+        monkeypatch.setenv("GLPROX_FUSED_GATHER", fused)
+        probs, bounds, keep = _shards(A, b, 2, "f8")
+        x0s = [torch.from_numpy(x0[c0:c1].copy()).cuda() for c0, c1 in bounds]
+        xs, k, out = solve_group(probs, algo, x0s, mu, dict(rec["opts"]))
+        hist.append((k, list(out["f_hist"]), torch.cat(xs, 0).cpu().numpy()))
+        for p in probs:
+            p.close()
+    assert hist[0][0] == hist[1][0] == int(rec[algo + "_k"])
+    assert hist[0][1] == hist[1][1] and np.array_equal(hist[0][2], hist[1][2])

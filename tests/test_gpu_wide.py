@@ -154,3 +154,44 @@ def test_split_operand_rings_compute_the_same_bits(monkeypatch, shape):
     xr, kr, outr = orc.solve("FProxGD", x0.astype(np.float64), A.astype(np.float64), b.astype(np.float64), mu, opts)
     assert abs(out1["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
 
+
+
+def test_auto_mode_falls_back_to_3xtf32_on_badly_scaled_columns():
+    """the fp16-pair set keeps ~2^-40 of max|A| in absolute terms; when whole columns of A are scaled
+    down by more than 2^18 (un-normalised features) and meet large x entries, that is below fp32 accuracy.  'auto'
+    measures the range of the column / row maxima and takes the 3xTF32 set instead; an explicit 'f16x2' is refused."""
+    import torch
+    from glprox import GroupLassoProblem, _lib
+    m, n, l = 256, 1024, 16
+    A, b, x0, mu, opts = _case(m, n, l, 11, 5)
+    scale = np.ones(n, dtype=np.float32)
+    scale[::7] = 1e-7                                   # every 7th feature column tiny
+    A = A * scale[None, :]
+    x0 = (x0 / np.maximum(scale, 1e-3)[:, None]).astype(np.float32)   # and its coefficients large
+    xr, kr, outr = orc.solve("FProxGD", x0.astype(np.float64), A.astype(np.float64), b.astype(np.float64), mu, opts)
+    prob = GroupLassoProblem(torch.from_numpy(A).cuda(), torch.from_numpy(b).cuda())
+    x, k, out = prob.solve("FProxGD", torch.from_numpy(x0).cuda(), mu, opts)          # auto
+    assert k == kr and abs(out["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
+    fh, ref = np.asarray(out["f_hist"]), np.asarray(outr["f_hist"])
+    assert np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-5
+    prob.close()
+    prob = GroupLassoProblem(torch.from_numpy(A).cuda(), torch.from_numpy(b).cuda())
+    with pytest.raises(_lib.GlproxError):
+        prob.solve("FProxGD", torch.from_numpy(x0).cuda(), mu, dict(opts, tensor_cores="f16x2"))
+    prob.close()
+
+
+def test_wide_default_mode_with_the_default_stop_rule():
+    """a wide solve that runs to the reference's own stop rule (default opts but the step), compared
+    with the fp64 oracle: same stage ends within a few iterations, final objective within the fp32 bar."""
+    import torch
+    from glprox import GroupLassoProblem
+    m, n, l = 128, 512, 16
+    A, b, x0, mu, _ = _case(m, n, l, 5, 0)
+    opts = {"alpha0": float(1.0 / (np.sqrt(m) + np.sqrt(n)) ** 2), "maxit": 400}
+    xr, kr, outr = orc.solve("FProxGD", x0.astype(np.float64), A.astype(np.float64), b.astype(np.float64), mu, opts)
+    prob = GroupLassoProblem(torch.from_numpy(A).cuda(), torch.from_numpy(b).cuda())
+    x, k, out = prob.solve("FProxGD", torch.from_numpy(x0).cuda(), mu, opts)
+    prob.close()
+    assert abs(k - kr) <= max(3, kr // 50)
+    assert abs(out["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
