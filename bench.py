@@ -495,11 +495,11 @@ def run_extra(args, ctx):
             res[name] = {"workload": note, "error": repr(e)}
 
     if args.dtype == "f32" and args.l == 2:
-        one("proxgd_c4", prob, "ProxGD", x0, mu, dict(opts, maxit=10), args.m, args.n, A.shape[1], args.l, False,
-            "gl_ProxGD_primal on the headline problem, maxit=10 per stage")
+        one("proxgd_c4", prob, "ProxGD", x0, mu, dict(opts), args.m, args.n, A.shape[1], args.l, False,
+            "gl_ProxGD_primal on the headline problem, maxit=%d per stage" % args.maxit)
     for name, (m, n, l, wide) in (("c3", (8192, 32768, 2, False)), ("c5", (16384, 65536, 128, True))):
-        note = "group-lasso FProxGD m=%d n=%d l=%d f32, maxit=10 per stage%s" % (
-            m, n, l, ", wide multi-RHS mode on tcgen05 (fp16 pairs)" if wide else "")
+        note = "group-lasso FProxGD m=%d n=%d l=%d f32, maxit=%d per stage%s" % (
+            m, n, l, args.maxit, ", wide multi-RHS mode on tcgen05 (fp16 pairs, CTA-pair kernel)" if wide else "")
         try:
             A2, b2, x02, mu2 = make_problem(m, n, l, args.seed, "f32", rank, world)
             p2 = GroupLassoProblem(A2, b2)
@@ -508,7 +508,7 @@ def run_extra(args, ctx):
         except Exception as e:  # noqa: BLE001
             res[name] = {"workload": note, "error": repr(e)}
             continue
-        one(name, p2, "FProxGD", x02, mu2, {"maxit": 10, "alpha0": mp_step(m, n)}, m, n, A2.shape[1], l, wide, note)
+        one(name, p2, "FProxGD", x02, mu2, {"maxit": args.maxit, "alpha0": mp_step(m, n)}, m, n, A2.shape[1], l, wide, note)
         p2.close()
         del A2, b2, x02, p2
         torch.cuda.empty_cache()

@@ -194,4 +194,9 @@ def test_wide_default_mode_with_the_default_stop_rule():
     x, k, out = prob.solve("FProxGD", torch.from_numpy(x0).cuda(), mu, opts)
     prob.close()
     assert abs(k - kr) <= max(3, kr // 50)
-    assert abs(out["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
+    # the trajectory meets the fp32 bar wherever both ran; the stop rule (two ratios against ftol = 1e-6) may fire a
+    # few iterations apart in fp32, and the objective is still creeping down there, hence the looser bar on fval
+    kk = min(k, kr)
+    fh, ref = np.asarray(out["f_hist"])[:kk], np.asarray(outr["f_hist"])[:kk]
+    assert np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-5
+    assert abs(out["fval"] - outr["fval"]) <= 1e-4 * abs(outr["fval"])
