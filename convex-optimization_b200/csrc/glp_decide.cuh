@@ -45,6 +45,7 @@ struct DecideSmem {
   Ctrl out;
   DecideOut act;
   double gy[DECIDE_THREADS / 32];
+  unsigned rmx[DECIDE_THREADS / 32];
 };
 
 // The decide phase proper, executed by every CTA of a grid of DECIDE_THREADS-wide CTAs (the stand-alone decide
@@ -126,10 +127,10 @@ __device__ __forceinline__ void decide_phase(const DecideArgs& a, const Geom& g,
     const unsigned u = __float_as_uint(fabsf(float(T(res))));
     rmx = u > rmx ? u : rmx;
   }
-  if (a.r_amax != nullptr) {
-    rmx = __reduce_max_sync(0xffffffffu, rmx);
-    if (lane == 0 && rmx != 0u) atomicMax(a.r_amax, rmx);
-  }
+  // max|r| of the CTA first, then ONE atomic per CTA: same-address L2 atomics serialise (~27 cycles each), and one per
+  // warp (4.7 k of them at C5) was 80 of this kernel's 116 us (profiles/r02_launches_c5_l128.csv)
+  rmx = __reduce_max_sync(0xffffffffu, rmx);
+  if (a.r_amax != nullptr && lane == 0) sm.rmx[warp] = rmx;
   if (accel && sm.act.reset_v) {
     const double* x = a.state[nc];
     double* v = a.state[nc] + 2 * lenn;
@@ -142,6 +143,11 @@ __device__ __forceinline__ void decide_phase(const DecideArgs& a, const Geom& g,
     double tot = 0.0;
     for (int w = 0; w < DECIDE_THREADS / 32; ++w) tot += sm.gy[w];
     a.gy_partial[sm.out.gy_sel][blockIdx.x] = tot;
+    if (a.r_amax != nullptr) {
+      unsigned mx = 0u;
+      for (int w = 0; w < DECIDE_THREADS / 32; ++w) mx = sm.rmx[w] > mx ? sm.rmx[w] : mx;
+      if (mx != 0u) atomicMax(a.r_amax, mx);
+    }
   }
 }
 

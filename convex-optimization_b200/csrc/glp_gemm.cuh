@@ -357,6 +357,8 @@ glp_split_f16_kernel(const float* __restrict__ src, __half* __restrict__ o0, __h
                      int64_t total, const unsigned* amax_bits, const double* scal_partial, int ncb, float s_other,
                      const unsigned* other_amax_bits, double* inv_scale_out, const int32_t* gate, int gate_cap) {
   __shared__ float s_mx[8];
+  pdl_wait();
+  pdl_launch();
   if (gate != nullptr && *gate <= gate_cap) return;
   float mxf;
   if (scal_partial != nullptr) {
@@ -839,6 +841,8 @@ __global__ void __launch_bounds__(256)
 glp_post_fwd_kernel(const PostFwdArgs a, const Geom g) {
   __shared__ double s_red[8];
   __shared__ double s_mx;
+  pdl_wait();
+  pdl_launch();
   if (a.ctrl != nullptr && a.ctrl->done) return;
   const int sel = a.ctrl != nullptr ? 1 - a.ctrl->cur : 0;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;

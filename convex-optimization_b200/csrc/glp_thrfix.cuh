@@ -44,6 +44,8 @@ glp_thr_list_kernel(const ThrListArgs a, const Geom g) {
   __shared__ int s_warp[THRLIST_THREADS / 32];
   __shared__ int s_carry;
   __shared__ bool s_last;
+  pdl_wait();
+  pdl_launch();
   if (a.ctrl != nullptr && a.ctrl->done) return;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int c = blockIdx.x, l = g.l;
@@ -142,6 +144,8 @@ glp_thr_fix_kernel(const ThrFixArgs a, const Geom g) {
   constexpr int RW = THRFIX_ROWS;
   __shared__ int32_t s_j[THRFIX_THREADS];
   __shared__ float s_v[THRFIX_THREADS];
+  pdl_wait();
+  pdl_launch();
   if (a.ctrl != nullptr && a.ctrl->done) return;
   if (a.count[1] > 0) return;
   const bool sel1 = a.ctrl != nullptr ? a.ctrl->cur == 0 : false;

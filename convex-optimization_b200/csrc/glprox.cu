@@ -605,384 +605,8 @@ static bool multi(const glp_handle* h) { return h->comm.world > 1; }
 static bool peer_push(const glp_handle* h) { return h->comm.world > 1 && !h->xch_nccl; }   // mailbox exchange
 static int glp_allreduce_f64(glp_handle* h, double* buf, size_t count, bool is_max);
 
-// ---- wide multi-RHS mode: both products of an iteration run on the tensor cores (K5) ---------------
-static bool wide_active(const glp_handle* h) {
-  return h->dtype == GLP_F32 && h->g.l >= 16 && 2 * h->g.l <= 256 && h->tensor_mode != 1 && !h->xch_nccl;
-}
-static int wide_passes(const glp_handle* h) {   // the PASSES of glp_gemm_tf32_kernel
-  switch (h->tensor_mode) {
-    case 2: return 1;
-    case 3: return 2;
-    case 4: return 4;
-    case 5: return 3;
-    default: return h->f16_unusable ? 3 : 4;   // auto: fp16 pairs unless A cannot be scaled (non-finite entries)
-  }
-}
-static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms, int bk = GEMM_BK);
-constexpr int WIDE_K_CHUNK = 8;  // the tensor core's fp32 accumulator spans 8 x 32 = 256 elements of K, then fp64
+#include "glp_wide_host.inl"
 
-struct GemmGate { const int32_t* count; int32_t cap; };            // run only when *count > cap (nullptr: always)
-static int split_f32(cudaStream_t st, const float* src, int64_t rows, int64_t cols, int64_t ld_src, float* hi, float* lo,
-                     int64_t ld_dst, bool transpose, GemmGate gate = GemmGate{nullptr, 0}) {
-  if (transpose) {
-    dim3 grid(unsigned((cols + 31) / 32), unsigned((rows + 31) / 32));
-    if (grid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
-    glp_transpose_split_kernel<<<grid, dim3(32, 8), 0, st>>>(src, hi, lo, rows, cols, ld_src, ld_dst);
-  } else {
-    const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
-    glp_split_tf32_kernel<<<grid, 256, 0, st>>>(src, hi, lo, rows, cols, ld_src, ld_dst, gate.count, gate.cap);
-  }
-  CU_TRY(cudaGetLastError());
-  return GLP_OK;
-}
-
-static int split_bf16(cudaStream_t st, const float* src, int64_t rows, int64_t cols, int64_t ld_src, float* hi,
-                      __nv_bfloat16* hb, __nv_bfloat16* lb, int64_t ld_dst, bool transpose,
-                      GemmGate gate = GemmGate{nullptr, 0}) {
-  if (transpose) {
-    dim3 grid(unsigned((cols + 31) / 32), unsigned((rows + 31) / 32));
-    if (grid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
-    glp_transpose_split_bf16_kernel<<<grid, dim3(32, 8), 0, st>>>(src, hi, hb, lb, rows, cols, ld_src, ld_dst);
-  } else {
-    const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
-    glp_split_bf16_kernel<<<grid, 256, 0, st>>>(src, hi, hb, lb, rows, cols, ld_src, ld_dst, gate.count, gate.cap);
-  }
-  CU_TRY(cudaGetLastError());
-  return GLP_OK;
-}
-
-template <typename Q>
-static int alloc_zero(Q** p, size_t bytes, cudaStream_t st) {
-  CU_TRY(cudaMalloc(reinterpret_cast<void**>(p), bytes));
-  CU_TRY(cudaMemsetAsync(*p, 0, bytes, st));
-  return GLP_OK;
-}
-
-// One-time set-up per operand set, resident in HBM afterwards ("memory laid out for 180 GB"), plus the matching
-// halves of the two small operands:
-//   fp16 pairs (default):  A s = A_f0 + A_f1 and A^T s = At_f0 + At_f1 in fp16, s from max|A|: 2 x |A| in all
-//   3xTF32:                A = A_hi + A_lo and A^T = At_hi + At_lo in fp32: 4 x |A|
-//   TF32 + bf16:           fp32 hi plus bf16 copies of hi and lo: 4 x |A|
-static int ensure_wide(glp_handle* h) {
-  const Geom& g = h->g;
-  const size_t a_el = size_t(g.m) * g.ldn, at_el = size_t(g.n) * g.ldm;
-  const size_t x_el = size_t(2) * g.l * g.ldn, r_el = size_t(g.l) * g.ldm;
-  const float* A = static_cast<const float*>(h->A);
-  if (h->cnt_g == nullptr) {   // shared by all operand sets
-    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->cnt_g), size_t(h->gather_grid) * 8));
-    // A.xnt by sparse correction: on unless GLPROX_WIDE_THRFIX=0.  Room for n/32 entries per operand column
-    // (>= 64): ~30 x the expected load at thres = 1e-3, and at that load the correction still costs well under
-    // half of the product it replaces.  GLPROX_WIDE_THRFIX_CAP overrides (tests).
-    const char* e_fix = getenv("GLPROX_WIDE_THRFIX");
-    if (e_fix == nullptr || atoi(e_fix) != 0) {
-      int64_t cap = std::max<int64_t>(64, g.n / 32);
-      if (const char* e_cap = getenv("GLPROX_WIDE_THRFIX_CAP")) cap = std::max(0, atoi(e_cap));
-      const size_t el = size_t(std::max<int64_t>(cap, 1)) * g.l;
-      GLP_TRY(alloc_zero(&h->thr_rows, el * 4, h->stream));
-      GLP_TRY(alloc_zero(&h->thr_vals, el * 4, h->stream));
-      GLP_TRY(alloc_zero(&h->thr_col_count, size_t(g.l) * 4, h->stream));
-      GLP_TRY(alloc_zero(&h->thr_count, 4 * 4, h->stream));
-      h->thr_cap = int32_t(cap);
-    }
-    // split-K workspace for the larger of the products
-    size_t fwd = size_t(gemm_splits(g.m, g.n, 2 * g.l, WIDE_K_CHUNK, h->num_sms)) * 2 * g.l * g.ldm * 8;
-    fwd = std::max(fwd, size_t(gemm_splits(g.m, g.n, g.l, WIDE_K_CHUNK, h->num_sms)) * g.l * g.ldm * 8);
-    const size_t tps = size_t(gemm_splits(g.n, g.m, g.l, WIDE_K_CHUNK, h->num_sms)) * g.l * g.ldn * 8;
-    h->gemm_ws_bytes = std::max(fwd, tps);
-    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->gemm_ws), h->gemm_ws_bytes));
-    h->pair_ws_bytes = pair_ws_bytes(h->num_sms, 128);
-    GLP_TRY(alloc_zero(&h->pair_ws, h->pair_ws_bytes, h->stream));
-  }
-  if (wide_passes(h) == 4) {
-    if (h->A_f0 != nullptr) return GLP_OK;
-    // scale of the resident operand from max|A| (one synchronous read-back at set-up)
-    if (h->f16_amax == nullptr) {
-      GLP_TRY(alloc_zero(&h->f16_amax, 4 * sizeof(unsigned), h->stream));
-      GLP_TRY(alloc_zero(&h->f16_inv, 2 * sizeof(double), h->stream));
-    }
-    CU_TRY(cudaMemsetAsync(h->f16_amax + 2, 0, sizeof(unsigned), h->stream));
-    const int ag = int(std::min<int64_t>((int64_t(g.m) * g.n + 255) / 256, int64_t(h->num_sms) * 16));
-    glp_absmax_kernel<<<ag, 256, 0, h->stream>>>(A, g.m, g.n, h->lda, h->f16_amax + 2);
-    CU_TRY(cudaGetLastError());
-    unsigned bits = 0;
-    CU_TRY(cudaMemcpyAsync(&bits, h->f16_amax + 2, sizeof(bits), cudaMemcpyDeviceToHost, h->stream));
-    CU_TRY(cudaStreamSynchronize(h->stream));
-    float amax;
-    memcpy(&amax, &bits, sizeof(amax));
-    if (!(amax < 3.0e38f)) {
-      if (h->tensor_mode != 0) return fail(GLP_ERR_ARG, "A holds non-finite values: the fp16-pair operand set cannot be scaled");
-      h->f16_unusable = true;   // auto: propagate them through the 3xTF32 operand set like any fp32 product would
-      return ensure_wide(h);
-    }
-    // dynamic range of the column / row scales of A: beyond 2^18 the fp16 pairs (2^-40 of the matrix maximum) fall
-    // below fp32 accuracy on the small columns -> auto takes the 3xTF32 operand set, an explicit 'f16x2' is refused
-    {
-      unsigned* rc = nullptr;
-      CU_TRY(cudaMalloc(reinterpret_cast<void**>(&rc), size_t(g.m + g.n + 4) * sizeof(unsigned)));
-      CU_TRY(cudaMemsetAsync(rc, 0, size_t(g.m + g.n + 4) * sizeof(unsigned), h->stream));
-      const unsigned init[4] = {0u, 0x7f800000u, 0u, 0x7f800000u};
-      CU_TRY(cudaMemcpyAsync(rc + g.m + g.n, init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
-      glp_rowcol_absmax_kernel<<<ag, 256, 0, h->stream>>>(A, g.m, g.n, h->lda, rc, rc + g.n);
-      glp_minmax_nonzero_kernel<<<64, 256, 0, h->stream>>>(rc, g.n, rc + g.m + g.n);
-      glp_minmax_nonzero_kernel<<<64, 256, 0, h->stream>>>(rc + g.n, g.m, rc + g.m + g.n + 2);
-      unsigned mm[4] = {0, 0, 0, 0};
-      cudaError_t e1 = cudaMemcpyAsync(mm, rc + g.m + g.n, sizeof(mm), cudaMemcpyDeviceToHost, h->stream);
-      if (e1 == cudaSuccess) e1 = cudaStreamSynchronize(h->stream);
-      cudaFree(rc);
-      if (e1 != cudaSuccess) return fail(GLP_ERR_CUDA, "dynamic-range probe failed: %s", cudaGetErrorString(e1));
-      float fv[4];
-      memcpy(fv, mm, sizeof(fv));
-      const float range = std::max(fv[1] > 0.f ? fv[0] / fv[1] : 1.f, fv[3] > 0.f ? fv[2] / fv[3] : 1.f);
-      if (range > 262144.0f) {
-        if (h->tensor_mode != 0)
-          return fail(GLP_ERR_ARG, "the column / row scales of A span a factor %.3g > 2^18: the fp16-pair operand set would lose "
-                                   "the small ones; use tensor_cores 'auto' or '3xtf32'", double(range));
-        h->f16_unusable = true;
-        return ensure_wide(h);
-      }
-    }
-    h->f16_sA = f16_scale_for(amax);
-    // the CTA-pair kernel streams a tiled operand (GLPROX_GEMM_PAIR=0 keeps the row-major set of the one-CTA kernel)
-    const char* e_pair = getenv("GLPROX_GEMM_PAIR");
-    h->f16_tiled = e_pair == nullptr || atoi(e_pair) != 0;
-    // K blocks of the tiled sets: what the product kernel derives from its K (n for A, m for A^T)
-    const int64_t nkb_a = (g.n + 63) / 64, nkb_at = (g.m + 63) / 64;
-    const size_t a_tiled = size_t((g.m + 127) / 128) * 128 * size_t(nkb_a) * 64;
-    const size_t at_tiled = size_t((g.n + 127) / 128) * 128 * size_t(nkb_at) * 64;
-    GLP_TRY(alloc_zero(&h->A_f0, (h->f16_tiled ? a_tiled : a_el) * 2, h->stream));
-    GLP_TRY(alloc_zero(&h->A_f1, (h->f16_tiled ? a_tiled : a_el) * 2, h->stream));
-    GLP_TRY(alloc_zero(&h->At_f0, (h->f16_tiled ? at_tiled : at_el) * 2, h->stream));
-    GLP_TRY(alloc_zero(&h->At_f1, (h->f16_tiled ? at_tiled : at_el) * 2, h->stream));
-    GLP_TRY(alloc_zero(&h->xop_f0, x_el * 2, h->stream));
-    GLP_TRY(alloc_zero(&h->xop_f1, x_el * 2, h->stream));
-    GLP_TRY(alloc_zero(&h->r_f0, r_el * 2, h->stream));
-    GLP_TRY(alloc_zero(&h->r_f1, r_el * 2, h->stream));
-    dim3 tgrid(unsigned((g.n + 31) / 32), unsigned((g.m + 31) / 32));
-    if (tgrid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
-    if (h->f16_tiled) {
-      glp_split_f16_tiled_kernel<<<ag, 256, 0, h->stream>>>(A, h->A_f0, h->A_f1, g.m, g.n, h->lda, nkb_a, h->f16_sA);
-      glp_transpose_split_f16_tiled_kernel<<<tgrid, dim3(32, 8), 0, h->stream>>>(A, h->At_f0, h->At_f1, g.m, g.n, h->lda,
-                                                                                 nkb_at, h->f16_sA);
-    } else {
-      glp_split_f16_2d_kernel<<<ag, 256, 0, h->stream>>>(A, h->A_f0, h->A_f1, g.m, g.n, h->lda, g.ldn, h->f16_sA);
-      glp_transpose_split_f16_kernel<<<tgrid, dim3(32, 8), 0, h->stream>>>(A, h->At_f0, h->At_f1, g.m, g.n, h->lda, g.ldm, h->f16_sA);
-    }
-    CU_TRY(cudaGetLastError());
-    return GLP_OK;
-  }
-  if (h->A_hi == nullptr) {
-    GLP_TRY(alloc_zero(&h->A_hi, a_el * 4, h->stream));
-    GLP_TRY(alloc_zero(&h->At_hi, at_el * 4, h->stream));
-  }
-  if (wide_passes(h) == 2) {
-    if (h->A_hb == nullptr) {
-      GLP_TRY(alloc_zero(&h->A_hb, a_el * 2, h->stream));
-      GLP_TRY(alloc_zero(&h->A_lb, a_el * 2, h->stream));
-      GLP_TRY(alloc_zero(&h->At_hb, at_el * 2, h->stream));
-      GLP_TRY(alloc_zero(&h->At_lb, at_el * 2, h->stream));
-      GLP_TRY(alloc_zero(&h->xop_hb, x_el * 2, h->stream));
-      GLP_TRY(alloc_zero(&h->xop_lb, x_el * 2, h->stream));
-      GLP_TRY(alloc_zero(&h->r_hb, r_el * 2, h->stream));
-      GLP_TRY(alloc_zero(&h->r_lb, r_el * 2, h->stream));
-      GLP_TRY(split_bf16(h->stream, A, g.m, g.n, h->lda, h->A_hi, h->A_hb, h->A_lb, g.ldn, false));
-      GLP_TRY(split_bf16(h->stream, A, g.m, g.n, h->lda, h->At_hi, h->At_hb, h->At_lb, g.ldm, true));
-    }
-  } else if (h->A_lo == nullptr) {
-    GLP_TRY(alloc_zero(&h->A_lo, a_el * 4, h->stream));
-    GLP_TRY(alloc_zero(&h->At_lo, at_el * 4, h->stream));
-    GLP_TRY(alloc_zero(&h->xop_lo, x_el * 4, h->stream));
-    GLP_TRY(alloc_zero(&h->r_lo, r_el * 4, h->stream));
-    GLP_TRY(split_f32(h->stream, A, g.m, g.n, h->lda, h->A_hi, h->A_lo, g.ldn, false));
-    GLP_TRY(split_f32(h->stream, A, g.m, g.n, h->lda, h->At_hi, h->At_lo, g.ldm, true));
-  }
-  return GLP_OK;
-}
-
-// split-K partial products (buf == nullptr: no splitting) and the workspace of the CTA-pair kernel (pair == nullptr:
-// the one-CTA kernel runs instead)
-struct GemmWs { double* buf; size_t bytes; void* pair = nullptr; size_t pair_bytes = 0; bool p_tiled = false; };
-struct GemmBf16 { const __nv_bfloat16 *Phb, *Plb, *Qhb, *Qlb; };  // passes = 2: bf16 copies of hi / lo, same pitches
-static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms, int bk);
-static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
-                        const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
-                        int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl = nullptr, double* D_alt = nullptr,
-                        int role = 0, GemmWs ws = GemmWs{nullptr, 0},
-                        GemmBf16 bf = GemmBf16{nullptr, nullptr, nullptr, nullptr}, GemmGate gate = GemmGate{nullptr, 0},
-                        const double* scale = nullptr);
-
-static uint64_t seq_base(const glp_handle* h);
-
-// Multi-GPU wide mode (glp_wide_comm.cuh): stage 0 push (right after the local product), 1 reduce, 2 finish.
-// One device-wide stage per phase, so that a multi-rank job on ONE device can enqueue each stage for all
-// of its logical ranks before the next.
-static int enqueue_wide_exchange(glp_handle* h, const Ctrl* ctrl, int stage) {
-  const Geom& g = h->g;
-  WideXArgs a{};
-  a.comm = h->comm;
-  a.ctrl = ctrl;
-  a.sel = 0;
-  a.par = h->group & 1;
-  a.ncols = 2 * g.l;
-  a.slice_rows = int32_t(((g.ldm + h->comm.world - 1) / h->comm.world + 31) / 32 * 32);
-  if (stage == 0) ++h->idx_f;
-  a.seq_f = seq_base(h) | h->idx_f;
-  a.seq_t = h->seq_t_cur;
-  a.AX[0] = h->AX[0]; a.AX[1] = h->AX[1];
-  a.b = h->b;
-  a.xcand[0] = h->state[0]; a.xcand[1] = h->state[1];
-  a.cnt_partial = h->cnt_g;
-  a.rr_partial = h->rr_g;
-  a.scal_red = h->scal_red;
-  a.cnt_red = h->cnt_red;
-  a.fin = h->fin_f;
-  a.fault = h->fault;
-  if (stage == 0) glp_wide_push_kernel<<<h->gather_grid, WIDEX_THREADS, 0, h->stream>>>(a, g);
-  else if (stage == 1) glp_wide_reduce_kernel<<<h->gather_grid, WIDEX_THREADS, 0, h->stream>>>(a, g);
-  else glp_wide_finish_kernel<<<h->gather_grid, WIDEX_THREADS, 0, h->stream>>>(a, g);
-  CU_TRY(cudaGetLastError());
-  h->n_launches++;
-  return GLP_OK;
-}
-
-// forward product of the solver on the tensor cores: AX[1-cur] = A . [xn | xnt], then ||r||^2 and the count
-static int enqueue_wide_fwd(glp_handle* h, const Ctrl* ctrl) {
-  const Geom& g = h->g;
-  float* xop = static_cast<float*>(h->xop);
-  const bool bf = wide_passes(h) == 2;
-  if (h->thr_cap >= 0) {   // list the rows the hard threshold changed, before the split overwrites the operand
-    ThrListArgs la{};
-    la.ctrl = ctrl;
-    la.xop = xop;
-    la.rows = h->thr_rows; la.vals = h->thr_vals; la.col_count = h->thr_col_count; la.count = h->thr_count;
-    la.cap = h->thr_cap;
-    glp_thr_list_kernel<<<g.l, THRLIST_THREADS, 0, h->stream>>>(la, g);
-    CU_TRY(cudaGetLastError());
-    h->n_launches++;
-  }
-  const bool f16 = wide_passes(h) == 4;
-  const int64_t q2 = int64_t(g.l) * g.ldn;
-  const GemmGate xnt_gate{h->thr_count + 1, 0};
-  if (f16) {
-    // fp16 pairs of xn s_x; s_x from max|xn|, which the prox epilogue left per column block in scal_partial
-    // (max|xnt| <= max|xn|: one scale for both halves)
-    const int sg = int(std::min<int64_t>((q2 + 1023) / 1024, int64_t(h->num_sms) * 16));
-    if (h->thr_cap < 0) {
-      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop, h->xop_f0, h->xop_f1, 2 * q2, nullptr, h->scal_partial, g.ncb,
-                                                      h->f16_sA, nullptr, h->f16_inv, nullptr, 0);
-    } else {
-      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop, h->xop_f0, h->xop_f1, q2, nullptr, h->scal_partial, g.ncb,
-                                                      h->f16_sA, nullptr, h->f16_inv, nullptr, 0);
-      glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(xop + q2, h->xop_f0 + q2, h->xop_f1 + q2, q2, nullptr, h->scal_partial,
-                                                      g.ncb, h->f16_sA, nullptr, nullptr, xnt_gate.count, xnt_gate.cap);
-      h->n_launches++;
-    }
-    CU_TRY(cudaGetLastError());
-    h->n_launches++;
-  } else if (h->thr_cap < 0) {
-    if (bf) GLP_TRY(split_bf16(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_hb, h->xop_lb, g.ldn, false));
-    else GLP_TRY(split_f32(h->stream, xop, 2 * g.l, g.ldn, g.ldn, xop, h->xop_lo, g.ldn, false));  // hi in place
-  } else {   // the xnt half is only needed by the gated fallback product
-    if (bf) {
-      GLP_TRY(split_bf16(h->stream, xop, g.l, g.ldn, g.ldn, xop, h->xop_hb, h->xop_lb, g.ldn, false));
-      GLP_TRY(split_bf16(h->stream, xop + q2, g.l, g.ldn, g.ldn, xop + q2, h->xop_hb + q2, h->xop_lb + q2, g.ldn, false, xnt_gate));
-    } else {
-      GLP_TRY(split_f32(h->stream, xop, g.l, g.ldn, g.ldn, xop, h->xop_lo, g.ldn, false));
-      GLP_TRY(split_f32(h->stream, xop + q2, g.l, g.ldn, g.ldn, xop + q2, h->xop_lo + q2, g.ldn, false, xnt_gate));
-    }
-    h->n_launches++;
-  }
-  prof_mark(h, 0, 0);
-  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes, h->pair_ws, h->pair_ws_bytes, f16 && h->f16_tiled};
-  // operand pointers of the selected set (fp16 pairs travel as float* through gemm_enqueue, pitches in elements)
-  const float* Ph = f16 ? reinterpret_cast<const float*>(h->A_f0) : h->A_hi;
-  const float* Pl = f16 ? reinterpret_cast<const float*>(h->A_f1) : h->A_lo;
-  auto qh = [&](int64_t off) { return f16 ? reinterpret_cast<const float*>(h->xop_f0 + off) : xop + off; };
-  auto ql = [&](int64_t off) {
-    return f16 ? reinterpret_cast<const float*>(h->xop_f1 + off) : (bf ? static_cast<const float*>(nullptr) : h->xop_lo + off);
-  };
-  auto qb = [&](int64_t off) {
-    return GemmBf16{h->A_hb, h->A_lb, bf ? h->xop_hb + off : nullptr, bf ? h->xop_lb + off : nullptr};
-  };
-  const double* sc = f16 ? h->f16_inv : nullptr;
-  const int kch = f16 ? WIDE_K_CHUNK / 2 : WIDE_K_CHUNK;   // 256 elements of K per fp32 accumulation either way
-  if (h->thr_cap < 0) {   // one product over both operand halves
-    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, 2 * g.l, Ph, Pl, g.ldn, qh(0), ql(0),
-                         g.ldn, h->AX[0], g.ldm, kch, h->fault, ctrl, h->AX[1], 1, ws, qb(0), GemmGate{nullptr, 0}, sc));
-  } else {
-    // A.xn on the tensor cores; A.xnt = A.xn - A.(xn - xnt) on the CUDA cores from the listed entries, or, when
-    // a list overflowed, by a second product launch that the device gates on the overflow count
-    const int64_t d2 = int64_t(g.l) * g.ldm;
-    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, g.l, Ph, Pl, g.ldn, qh(0), ql(0),
-                         g.ldn, h->AX[0], g.ldm, kch, h->fault, ctrl, h->AX[1], 1, ws, qb(0), GemmGate{nullptr, 0}, sc));
-    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.m, g.n, g.l, Ph, Pl, g.ldn, qh(q2), ql(q2),
-                         g.ldn, h->AX[0] + d2, g.ldm, kch, h->fault, ctrl, h->AX[1] + d2, 1, ws, qb(q2), xnt_gate, sc));
-    ThrFixArgs fa{};
-    fa.ctrl = ctrl;
-    fa.count = h->thr_count; fa.col_count = h->thr_col_count;
-    fa.rows = h->thr_rows; fa.vals = h->thr_vals; fa.cap = h->thr_cap;
-    fa.At_hi = h->At_hi; fa.At_lo = bf ? nullptr : h->At_lo; fa.At_lb = bf ? h->At_lb : nullptr;
-    if (f16) {
-      fa.At_hi = nullptr; fa.At_lo = nullptr; fa.At_lb = nullptr;
-      fa.At_f0 = h->At_f0; fa.At_f1 = h->At_f1; fa.inv_s = 1.0f / h->f16_sA;
-      fa.thres = float(h->sc.thres); fa.inv_x = h->f16_inv;
-      fa.tiled_nkb = h->f16_tiled ? (g.m + 63) / 64 : 0;   // == ldm / 64: the padded output rows stay inside the last tile
-    }
-    fa.AX[0] = h->AX[0]; fa.AX[1] = h->AX[1];
-    const int64_t frows = int64_t(THRFIX_THREADS) * THRFIX_ROWS;
-    const dim3 fgrid(unsigned((g.ldm + frows - 1) / frows), unsigned(g.l));
-    glp_thr_fix_kernel<<<fgrid, THRFIX_THREADS, 0, h->stream>>>(fa, g);
-    CU_TRY(cudaGetLastError());
-    h->n_launches += 2;
-  }
-  prof_mark(h, 0, 1);
-  h->n_launches += 2;
-  if (multi(h)) return enqueue_wide_exchange(h, ctrl, 0);
-  PostFwdArgs pa{};
-  pa.ctrl = ctrl;
-  pa.AX[0] = h->AX[0]; pa.AX[1] = h->AX[1];
-  pa.b = h->b;
-  pa.scal_partial = h->scal_partial;
-  pa.xcand[0] = h->state[0]; pa.xcand[1] = h->state[1];
-  pa.rr_out = h->rr_g;
-  pa.cnt_out = h->cnt_g;
-  glp_post_fwd_kernel<<<h->gather_grid, 256, 0, h->stream>>>(pa, g);
-  CU_TRY(cudaGetLastError());
-  h->n_launches += 2;
-  h->n_gemm++;
-  return GLP_OK;
-}
-
-// transposed product of the solver on the tensor cores: grad = A^T . r  (skipped by the kernel on a retry)
-static int enqueue_wide_tpass(glp_handle* h, const Ctrl* ctrl) {
-  const Geom& g = h->g;
-  float* r = static_cast<float*>(h->r);
-  const GemmWs ws{h->gemm_ws, h->gemm_ws_bytes, h->pair_ws, h->pair_ws_bytes, wide_passes(h) == 4 && h->f16_tiled};
-  if (wide_passes(h) == 4) {
-    const int64_t tot = int64_t(g.l) * g.ldm;
-    // max|r| was left in f16_amax[1] by the decide kernel that wrote r
-    const int sg = int(std::min<int64_t>((tot + 1023) / 1024, int64_t(h->num_sms) * 16));
-    glp_split_f16_kernel<<<sg, 256, 0, h->stream>>>(r, h->r_f0, h->r_f1, tot, h->f16_amax + 1, nullptr, 0, h->f16_sA, nullptr,
-                                                    h->f16_inv + 1, nullptr, 0);
-    CU_TRY(cudaGetLastError());
-    h->n_launches++;
-    prof_mark(h, 1, 0);
-    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, 4, g.n, g.m, g.l, reinterpret_cast<const float*>(h->At_f0),
-                         reinterpret_cast<const float*>(h->At_f1), g.ldm, reinterpret_cast<const float*>(h->r_f0),
-                         reinterpret_cast<const float*>(h->r_f1), g.ldm, h->grad, g.ldn, WIDE_K_CHUNK / 2, h->fault, ctrl,
-                         nullptr, 2, ws, GemmBf16{nullptr, nullptr, nullptr, nullptr}, GemmGate{nullptr, 0}, h->f16_inv + 1));
-  } else {
-    if (wide_passes(h) == 2) GLP_TRY(split_bf16(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_hb, h->r_lb, g.ldm, false));
-    else GLP_TRY(split_f32(h->stream, r, g.l, g.ldm, g.ldm, r, h->r_lo, g.ldm, false));
-    prof_mark(h, 1, 0);
-    GLP_TRY(gemm_enqueue(h->stream, h->num_sms, wide_passes(h), g.n, g.m, g.l, h->At_hi, h->At_lo, g.ldm, r, h->r_lo,
-                         g.ldm, h->grad, g.ldn, WIDE_K_CHUNK, h->fault, ctrl, nullptr, 2, ws,
-                         GemmBf16{h->At_hb, h->At_lb, h->r_hb, h->r_lb}));
-  }
-  prof_mark(h, 1, 1);
-  h->n_launches += 2;
-  h->n_gemm++;
-  return GLP_OK;
-}
 static uint64_t seq_base(const glp_handle* h) { return h->epoch << 32; }
 
 // Forward stream over `ncols` operand columns.  Xb[s] / AXb[s]: planar operand / output bases.
@@ -1393,96 +1017,7 @@ extern "C" int glp_solve_end(glp_handle* h, void* x_out_dev, glp_result* res, do
   return GLP_OK;
 }
 
-// ------------------------------------------------------------------------------------------------
-// multi-GPU: mailbox export / attach, and the one-process group driver
-// ------------------------------------------------------------------------------------------------
-extern "C" int glp_comm_export(glp_handle* h, int world, void* ipc_handle64_out, void** mailbox_dev_out) {
-  if (h == nullptr) return fail(GLP_ERR_ARG, "null handle");
-  if (world < 1 || world > MAX_WORLD) return fail(GLP_ERR_ARG, "world must be 1..%d (got %d)", MAX_WORLD, world);
-  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
-  CU_TRY(cudaSetDevice(h->device));
-  if (h->mailbox == nullptr) {
-    const size_t slab_words = size_t(2) * h->g.l * h->g.ldm;
-    h->mailbox_bytes = (size_t(MAIL_SLAB) + size_t(2) * MAX_WORLD * slab_words) * 8;
-    CU_TRY(cudaMalloc(&h->mailbox, h->mailbox_bytes));  // plain cudaMalloc: IPC-exportable
-    CU_TRY(cudaMemset(h->mailbox, 0, h->mailbox_bytes));
-    CU_TRY(cudaDeviceSynchronize());
-  }
-  if (ipc_handle64_out != nullptr) {
-    cudaIpcMemHandle_t ih;
-    static_assert(sizeof(ih) == 64, "cudaIpcMemHandle_t is 64 bytes");
-    CU_TRY(cudaIpcGetMemHandle(&ih, h->mailbox));
-    memcpy(ipc_handle64_out, &ih, sizeof(ih));
-  }
-  if (mailbox_dev_out != nullptr) *mailbox_dev_out = h->mailbox;
-  return GLP_OK;
-}
-
-extern "C" int glp_comm_attach(glp_handle* h, int rank, int world, int64_t n_total, const void* peers, int kind) {
-  if (h == nullptr || peers == nullptr) return fail(GLP_ERR_ARG, "null argument");
-  if (world < 1 || world > MAX_WORLD || rank < 0 || rank >= world) return fail(GLP_ERR_ARG, "bad rank/world %d/%d", rank, world);
-  if (h->mailbox == nullptr) return fail(GLP_ERR_STATE, "glp_comm_attach before glp_comm_export");
-  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
-  if (kind != 0 && kind != 1) return fail(GLP_ERR_ARG, "kind must be 0 (IPC handles) or 1 (device pointers)");
-  if (n_total < h->g.n) return fail(GLP_ERR_ARG, "n_total (%lld) < local n (%d)", (long long)n_total, h->g.n);
-  CU_TRY(cudaSetDevice(h->device));
-  Comm c{};
-  c.world = world;
-  c.rank = rank;
-  c.slab_words = int64_t(2) * h->g.l * h->g.ldm;
-  for (int r = 0; r < world; ++r) {
-    void* ptr = nullptr;
-    if (r == rank) {
-      ptr = h->mailbox;
-    } else if (kind == 1) {
-      ptr = static_cast<void* const*>(peers)[r];
-      cudaPointerAttributes at{};
-      if (ptr != nullptr && cudaPointerGetAttributes(&at, ptr) == cudaSuccess && at.type == cudaMemoryTypeDevice &&
-          at.device != h->device) {
-        cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
-        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
-          return fail(GLP_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d) failed: %s", at.device, cudaGetErrorString(e));
-        cudaGetLastError();
-      }
-    } else {
-      cudaIpcMemHandle_t ih;
-      memcpy(&ih, static_cast<const char*>(peers) + size_t(r) * sizeof(ih), sizeof(ih));
-      cudaError_t e = cudaIpcOpenMemHandle(&ptr, ih, cudaIpcMemLazyEnablePeerAccess);
-      if (e != cudaSuccess)
-        return fail(GLP_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d) failed: %s", r, cudaGetErrorString(e));
-      h->ipc_mapped[r] = ptr;
-    }
-    if (ptr == nullptr) return fail(GLP_ERR_ARG, "mailbox of rank %d is null", r);
-    c.mail[r] = static_cast<unsigned long long*>(ptr);
-  }
-  h->comm = c;
-  h->g.world = world;
-  h->g.n_total = n_total;
-  return GLP_OK;
-}
-
-extern "C" int glp_comm_attach_nccl(glp_handle* h, void* nccl_comm, int rank, int world, int64_t n_total) {
-  if (h == nullptr || nccl_comm == nullptr) return fail(GLP_ERR_ARG, "null argument");
-  if (world < 1 || world > MAX_WORLD || rank < 0 || rank >= world) return fail(GLP_ERR_ARG, "bad rank/world %d/%d", rank, world);
-  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
-  if (n_total < h->g.n) return fail(GLP_ERR_ARG, "n_total (%lld) < local n (%d)", (long long)n_total, h->g.n);
-  CU_TRY(cudaSetDevice(h->device));
-  if (h->nccl_stage == nullptr) {
-    const size_t words = size_t(2) * h->g.l * h->g.ldm + 16;
-    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->nccl_stage), words * 8));
-    CU_TRY(cudaMemsetAsync(h->nccl_stage, 0, words * 8, h->stream));
-  }
-  Comm c{};
-  c.world = world;
-  c.rank = rank;
-  c.slab_words = int64_t(2) * h->g.l * h->g.ldm;
-  h->comm = c;
-  h->nccl_comm = nccl_comm;
-  h->xch_nccl = true;
-  h->g.world = world;
-  h->g.n_total = n_total;
-  return GLP_OK;
-}
+#include "glp_comm_host.inl"
 
 static int drive_until_done(glp_handle** hs, int G, const glp_opts* o) {
   // Host runs ahead of the device: batch i+1 is enqueued before the control snapshot taken after
@@ -1811,555 +1346,11 @@ extern "C" int glp_debug_read(glp_handle* h, int which, double* out_host) {
   return GLP_OK;
 }
 
-// ------------------------------------------------------------------------------------------------
-// one-shot solve with host buffers
-// ------------------------------------------------------------------------------------------------
-// Host matrix -> HBM.  Page-locked sources (cudaHostAlloc / cudaHostRegister, e.g. torch pinned
-// tensors) are DMA'd in place.  Pageable sources go through pinned bounce buffers filled by a few
-// host threads, each with its own stream, so that the host-side memcpy (one core moves ~10 GB/s)
-// does not cap the PCIe link.
-static int upload_rows_bounced(int device, void* dst, size_t dpitch, const char* src, size_t spitch, size_t width,
-                               size_t row_begin, size_t row_end, cudaError_t* err_out) {
-  const size_t kChunk = size_t(16) << 20;
-  cudaError_t e = cudaSetDevice(device);
-  cudaStream_t st = nullptr;
-  char* pin[2] = {nullptr, nullptr};
-  cudaEvent_t ev[2] = {nullptr, nullptr};
-  size_t rows_per = std::max<size_t>(1, kChunk / std::max<size_t>(width, 1));
-  rows_per = std::min(rows_per, std::max<size_t>(row_end - row_begin, 1));
-  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
-  for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
-    e = cudaMallocHost(reinterpret_cast<void**>(&pin[i]), rows_per * width);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming);
-  }
-  int slot = 0;
-  for (size_t r0 = row_begin; r0 < row_end && e == cudaSuccess; r0 += rows_per, slot ^= 1) {
-    const size_t nr = std::min(rows_per, row_end - r0);
-    e = cudaEventSynchronize(ev[slot]);  // previous DMA out of this bounce buffer finished
-    if (e != cudaSuccess) break;
-    const char* s = src + r0 * spitch;
-    if (spitch == width) memcpy(pin[slot], s, nr * width);
-    else for (size_t r = 0; r < nr; ++r) memcpy(pin[slot] + r * width, s + r * spitch, width);
-    e = cudaMemcpy2DAsync(static_cast<char*>(dst) + r0 * dpitch, dpitch, pin[slot], width, width, nr,
-                          cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaEventRecord(ev[slot], st);
-  }
-  if (e == cudaSuccess && st) e = cudaStreamSynchronize(st);
-  for (int i = 0; i < 2; ++i) {
-    if (ev[i]) cudaEventDestroy(ev[i]);
-    if (pin[i]) cudaFreeHost(pin[i]);
-  }
-  if (st) cudaStreamDestroy(st);
-  *err_out = e;
-  return e == cudaSuccess ? 0 : 1;
-}
-
-static int upload_matrix(int device, cudaStream_t st, void* dst, size_t dpitch, const void* src, size_t spitch,
-                         size_t width, size_t rows) {
-  cudaPointerAttributes at{};
-  const bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
-  cudaGetLastError();
-  if (pinned) {
-    CU_TRY(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, rows, cudaMemcpyHostToDevice, st));
-    CU_TRY(cudaStreamSynchronize(st));
-    return GLP_OK;
-  }
-  CU_TRY(cudaStreamSynchronize(st));  // dst may still be being cleared on st
-  const size_t bytes = width * rows;
-  int nthr = int(std::min<size_t>(6, std::max<size_t>(1, bytes >> 26)));  // one thread per 64 MiB, up to 6
-  nthr = int(std::min<size_t>(size_t(nthr), rows));
-  std::vector<std::thread> pool;
-  std::vector<cudaError_t> errs(size_t(nthr), cudaSuccess);
-  for (int t = 0; t < nthr; ++t) {
-    const size_t r0 = rows * size_t(t) / nthr, r1 = rows * size_t(t + 1) / nthr;
-    pool.emplace_back([=, &errs]() {
-      upload_rows_bounced(device, dst, dpitch, static_cast<const char*>(src), spitch, width, r0, r1, &errs[size_t(t)]);
-    });
-  }
-  for (auto& th : pool) th.join();
-  for (cudaError_t e : errs)
-    if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "matrix upload failed: %s", cudaGetErrorString(e));
-  return GLP_OK;
-}
-
-extern "C" int glp_solve_host(int device, int algo, int dtype, int m, int n, int l, const void* A_host, int64_t lda,
-                              const void* b_host, const void* x0_host, double mu0, const glp_opts* opts,
-                              void* x_out_host, glp_result* res, double* f_hist_host, int hist_cap) {
-  if (A_host == nullptr || b_host == nullptr || x0_host == nullptr || x_out_host == nullptr || opts == nullptr)
-    return fail(GLP_ERR_ARG, "null argument");
-  if (dtype != GLP_F32 && dtype != GLP_F64) return fail(GLP_ERR_ARG, "dtype must be GLP_F32 or GLP_F64");
-  if (m <= 0 || n <= 0 || l <= 0 || lda < n) return fail(GLP_ERR_ARG, "bad shape");
-  int sms = 0;
-  GLP_TRY(check_device(device, &sms));
-  CU_TRY(cudaSetDevice(device));
-  const size_t es = dtype == GLP_F32 ? 4 : 8;
-  const size_t ldd = align_up(size_t(n), 16 / es);  // device pitch in elements, 16-byte aligned rows
-  void *dA = nullptr, *db = nullptr, *dx0 = nullptr, *dx = nullptr;
-  glp_handle* h = nullptr;
-  cudaStream_t st = nullptr;
-  int rc = GLP_OK;
-  auto cleanup = [&]() {
-    if (h) glp_destroy(h);
-    if (st) cudaStreamDestroy(st);
-    if (dA) cudaFree(dA);
-    if (db) cudaFree(db);
-    if (dx0) cudaFree(dx0);
-    if (dx) cudaFree(dx);
-  };
-#define HOST_TRY(expr)                                                                        \
-  do {                                                                                        \
-    cudaError_t e_ = (expr);                                                                  \
-    if (e_ != cudaSuccess) {                                                                  \
-      cleanup();                                                                              \
-      return fail(GLP_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));            \
-    }                                                                                         \
-  } while (0)
-  HOST_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
-  HOST_TRY(cudaMalloc(&dA, size_t(m) * ldd * es));
-  HOST_TRY(cudaMalloc(&db, size_t(m) * l * es));
-  HOST_TRY(cudaMalloc(&dx0, size_t(n) * l * es));
-  HOST_TRY(cudaMalloc(&dx, size_t(n) * l * es));
-  if (ldd != size_t(n)) HOST_TRY(cudaMemsetAsync(dA, 0, size_t(m) * ldd * es, st));
-  rc = upload_matrix(device, st, dA, ldd * es, A_host, size_t(lda) * es, size_t(n) * es, size_t(m));
-  if (rc != GLP_OK) { cleanup(); return rc; }
-  HOST_TRY(cudaMemcpyAsync(db, b_host, size_t(m) * l * es, cudaMemcpyHostToDevice, st));
-  HOST_TRY(cudaMemcpyAsync(dx0, x0_host, size_t(n) * l * es, cudaMemcpyHostToDevice, st));
-  rc = glp_create(&h, device, m, n, l, dtype, dA, int64_t(ldd), db, nullptr, st);
-  if (rc == GLP_OK) rc = glp_solve(h, algo, dx0, mu0, opts, dx, res, f_hist_host, hist_cap);
-  if (rc == GLP_OK) {
-    HOST_TRY(cudaMemcpyAsync(x_out_host, dx, size_t(n) * l * es, cudaMemcpyDeviceToHost, st));
-    HOST_TRY(cudaStreamSynchronize(st));
-  }
-#undef HOST_TRY
-  cleanup();
-  return rc;
-}
-
-// ------------------------------------------------------------------------------------------------
-// K5: tensor-core products (glp_gemm.cuh)
-// ------------------------------------------------------------------------------------------------
-static int make_map_f32_k128(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t stride_bytes,
-                             uint32_t box_outer) {
-  PFN_encodeTiled fn = encode_tiled_fn();
-  if (fn == nullptr) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
-  const cuuint64_t dims[2] = {inner, outer};
-  const cuuint64_t strides[1] = {stride_bytes};
-  const cuuint32_t box[2] = {cuuint32_t(GEMM_BK), box_outer};
-  const cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims,
-                                                     strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled (gemm operand) failed with CUresult %d", int(r));
-  return GLP_OK;
-}
-
-// fp16 operand tile of the fp16-pair mode: 64 elements = 128 bytes of K per row, 128-byte swizzle
-static int make_map_f16_k128(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t stride_bytes,
-                             uint32_t box_outer) {
-  PFN_encodeTiled fn = encode_tiled_fn();
-  if (fn == nullptr) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
-  const cuuint64_t dims[2] = {inner, outer};
-  const cuuint64_t strides[1] = {stride_bytes};
-  const cuuint32_t box[2] = {cuuint32_t(2 * GEMM_BK), box_outer};
-  const cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled (fp16 operand) failed with CUresult %d", int(r));
-  return GLP_OK;
-}
-
-// bf16 operand tile: 32 elements = 64 bytes of K per row, 64-byte swizzle
-static int make_map_bf16_k64(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t stride_bytes,
-                             uint32_t box_outer) {
-  PFN_encodeTiled fn = encode_tiled_fn();
-  if (fn == nullptr) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
-  const cuuint64_t dims[2] = {inner, outer};
-  const cuuint64_t strides[1] = {stride_bytes};
-  const cuuint32_t box[2] = {cuuint32_t(GEMM_BK), box_outer};
-  const cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return fail(GLP_ERR_CUDA, "cuTensorMapEncodeTiled (bf16 operand) failed with CUresult %d", int(r));
-  return GLP_OK;
-}
-
-template <int NT, int PASSES, bool RINGS = false>
-static cudaError_t launch_gemm_t(cudaStream_t st, int num_sms, int64_t cluster_items, const CUtensorMap& ph,
-                                 const CUtensorMap& pl, const CUtensorMap& qh, const CUtensorMap& ql,
-                                 const CUtensorMap& px, const CUtensorMap& qx, const GemmArgs& a) {
-  auto kfn = glp_gemm_tf32_kernel<NT, PASSES, RINGS>;
-  constexpr int smem = RINGS ? gemm_ring_smem_bytes<NT>() : gemm_smem_bytes<NT, PASSES>();
-  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  if (e != cudaSuccess) return e;
-  const int cs = std::max(1, a.ct) * std::max(1, a.cg);
-  cudaLaunchConfig_t cfg = {};
-  cfg.blockDim = dim3(RINGS ? GEMM_RING_THREADS : GEMM_THREADS, 1, 1);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = unsigned(cs);
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = cs > 1 ? 1 : 0;
-  int64_t ncl = num_sms / cs;
-  if (cs > 1) {  // clusters must fit inside a GPC: ask how many can be resident at once
-    cfg.gridDim = dim3(unsigned(ncl * cs), 1, 1);
-    int max_cl = 0;
-    e = cudaOccupancyMaxActiveClusters(&max_cl, kfn, &cfg);
-    if (e != cudaSuccess) return e;
-    if (max_cl < 1) return cudaErrorInvalidConfiguration;
-    ncl = std::min<int64_t>(ncl, max_cl);
-  }
-  ncl = std::max<int64_t>(1, std::min<int64_t>(ncl, cluster_items));
-  cfg.gridDim = dim3(unsigned(ncl * cs), 1, 1);
-  return cudaLaunchKernelEx(&cfg, kfn, ph, pl, qh, ql, px, qx, a);
-}
-
-// K5 on CTA pairs (glp_gemm_pair.cuh): clusters of 2, one pair per TPC, stream-K ranges over the pairs.
-template <int NT>
-static cudaError_t launch_gemm_pair_t(cudaStream_t st, int num_sms, const CUtensorMap& p0, const CUtensorMap& p1,
-                                      const CUtensorMap& q0, const CUtensorMap& q1, const PairArgs& a) {
-  auto kfn = glp_gemm_pair_kernel<NT>;
-  constexpr int smem = pair_smem_bytes<NT>();
-  cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  if (e != cudaSuccess) return e;
-  cudaLaunchConfig_t cfg = {};
-  cfg.blockDim = dim3(PAIR_THREADS, 1, 1);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  int pairs = num_sms / 2;
-  cfg.gridDim = dim3(unsigned(2 * pairs), 1, 1);
-  int max_cl = 0;
-  e = cudaOccupancyMaxActiveClusters(&max_cl, kfn, &cfg);
-  if (e != cudaSuccess) return e;
-  if (max_cl < 1) return cudaErrorInvalidConfiguration;
-  pairs = std::min(pairs, max_cl);
-  cfg.gridDim = dim3(unsigned(2 * pairs), 1, 1);
-  return cudaLaunchKernelEx(&cfg, kfn, p0, p1, q0, q1, a);
-}
-
-// Number of K splits.  Measured on B200 (tests/bench_gemm_probe.py split): the kernel runs under the
-// board's power cap, so filling the SMs left idle by the tail wave buys nothing at 128+ items (3.15 ms
-// unsplit vs 3.56 ms with 4 splits at M=16384 K=65536 N=256) and fine splits cost epilogue + workspace
-// traffic.  K is therefore split only when the items cover less than half of the SMs (column shards of a
-// multi-GPU job), and then just enough to occupy them, keeping >= 8 accumulation chunks per item.
-static int gemm_splits(int64_t M, int64_t K, int N, int k_chunk, int num_sms, int bk) {
-  const int NT = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
-  const int64_t base = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + NT - 1) / NT);
-  const int64_t nkb = (K + bk - 1) / bk;
-  const int64_t kc = k_chunk > 0 ? k_chunk : nkb;
-  const int64_t nchunks = (nkb + kc - 1) / kc;
-  if (const char* e = getenv("GLPROX_GEMM_SPLITS")) {   // measurement override
-    const int64_t S = atoi(e);
-    return int(std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(S, 16), nchunks)));
-  }
-  if (base * 2 > num_sms) return 1;
-  int64_t S = num_sms / base;
-  S = std::min<int64_t>(S, std::max<int64_t>(1, nchunks / 8));
-  return int(std::max<int64_t>(1, std::min<int64_t>(S, 16)));
-}
-
-// D[N][ldd] = P[M x K] . Q[N x K]^T ; passes 1 (TF32), 3 (hi/lo compensated), 2 (bf16 corrections) or 4 (fp16 pairs:
-// Ph / Pl / Qh / Ql then point at __half arrays v0 / v1 with pitches in fp16 elements, and the product is multiplied
-// by *scale); N <= 256 (groups of <= 128 columns)
-static int gemm_enqueue(cudaStream_t st, int num_sms, int passes, int64_t M, int64_t K, int N, const float* Ph,
-                        const float* Pl, int64_t ldp, const float* Qh, const float* Ql, int64_t ldq, double* D,
-                        int64_t ldd, int k_chunk, int32_t* fault, const Ctrl* ctrl, double* D_alt, int role, GemmWs ws,
-                        GemmBf16 bf, GemmGate gate, const double* scale) {
-  if (N < 1 || N > 256) return fail(GLP_ERR_ARG, "gemm: N must be 1..256 per launch (got %d)", N);
-  if (passes < 1 || passes > 4) return fail(GLP_ERR_ARG, "gemm: passes must be 1, 2, 3 or 4");
-  const int es = passes == 4 ? 2 : 4, bk = passes == 4 ? 2 * GEMM_BK : GEMM_BK;
-  if ((ldp * es) % 16 || (ldq * es) % 16 || (reinterpret_cast<uintptr_t>(Ph) % 16) || (reinterpret_cast<uintptr_t>(Qh) % 16))
-    return fail(GLP_ERR_ARG, "gemm: operands must be 16-byte aligned with 16-byte aligned pitches");
-  const int NT = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
-  const int64_t tiles = (M + GEMM_BM - 1) / GEMM_BM, groups = (N + NT - 1) / NT;
-  // cluster geometry (TMA multicast of the shared operand tiles): neighbouring M tiles share every Q tile,
-  // the 2 column groups of N = 256 share every P tile.  Measured in the solver at C5 (it/s, fwd / tpass ms):
-  // 1x1 171.6 (3.45 / 1.78), 2x2 176.0 (3.34 / 1.76), 4 tiles 154.7 (4.28 with 8-CTA clusters / 1.61): 2 x 2 for
-  // the two-group forward product, 4 x 1 for the one-group transposed product.
-  // GLPROX_GEMM_CLUSTER=ct,cg overrides (1,1 = off).
-  int cg = groups == 2 ? 2 : 1;
-  int ct = cg == 2 ? (tiles >= 2 ? 2 : 1) : (tiles >= 4 ? 4 : (tiles >= 2 ? 2 : 1));
-  if (const char* e = getenv("GLPROX_GEMM_CLUSTER")) {
-    int a1 = 0, a2 = 0;
-    if (sscanf(e, "%d,%d", &a1, &a2) == 2 && (a1 == 1 || a1 == 2 || a1 == 4) && (a2 == 1 || a2 == 2)) {
-      ct = std::min<int64_t>(a1, tiles >= a1 ? a1 : 1);
-      cg = groups == 2 ? a2 : 1;
-    }
-  }
-  if (NT / ct < 8) ct = 1;
-  const uint32_t pbox = uint32_t(GEMM_BM / cg), qbox = uint32_t(NT / ct);
-  CUtensorMap mph, mpl, mqh, mql, mpx, mqx;
-  if (passes == 4) {
-    if (Pl == nullptr || Ql == nullptr) return fail(GLP_ERR_ARG, "gemm: passes = 4 needs both halves of the fp16 pairs");
-    GLP_TRY(make_map_f16_k128(&mph, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, pbox));
-    GLP_TRY(make_map_f16_k128(&mqh, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, qbox));
-    GLP_TRY(make_map_f16_k128(&mpl, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, pbox));
-    GLP_TRY(make_map_f16_k128(&mql, Ql, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, qbox));
-  } else {
-    GLP_TRY(make_map_f32_k128(&mph, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, pbox));
-    GLP_TRY(make_map_f32_k128(&mqh, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, qbox));
-  }
-  mpx = mph; mqx = mqh;
-  // fp16 pairs: the CTA-pair kernel (cta_group::2 + stream-K) unless GLPROX_GEMM_PAIR=0 or no workspace was given
-  const char* e_pair = getenv("GLPROX_GEMM_PAIR");   // read per call: tests switch it inside one process
-  if (passes == 4 && ws.p_tiled && (ws.pair == nullptr || (e_pair != nullptr && atoi(e_pair) == 0)))
-    return fail(GLP_ERR_STATE, "gemm: the resident fp16 operands are tiled for the CTA-pair kernel, which is switched off");
-  if (passes == 4 && ws.pair != nullptr && (e_pair == nullptr || atoi(e_pair) != 0)) {
-    const int ctas = 2 * (num_sms / 2);
-    if (ws.pair_bytes < pair_ws_bytes(ctas, NT)) return fail(GLP_ERR_ARG, "gemm: pair workspace too small");
-    if (tiles * groups > PAIR_COUNTER_WORDS) return fail(GLP_ERR_ARG, "gemm: too many output tiles for the pair kernel");
-    CUtensorMap p0, p1, q0, q1;
-    if (ws.p_tiled) {   // [tiles * nkb * 128 rows][64 fp16]: every 128-row box is one contiguous 16 KB tile
-      const uint64_t trows = uint64_t((M + 127) / 128) * uint64_t((K + 63) / 64) * 128;
-      GLP_TRY(make_map_f16_k128(&p0, Ph, 64, trows, 128, GEMM_BM));
-      GLP_TRY(make_map_f16_k128(&p1, Pl, 64, trows, 128, GEMM_BM));
-    } else {
-      GLP_TRY(make_map_f16_k128(&p0, Ph, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
-      GLP_TRY(make_map_f16_k128(&p1, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, GEMM_BM));
-    }
-    GLP_TRY(make_map_f16_k128(&q0, Qh, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, uint32_t(NT / 2)));
-    GLP_TRY(make_map_f16_k128(&q1, Ql, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, uint32_t(NT / 2)));
-    PairArgs pa{};
-    pa.M = M; pa.K = K; pa.N = N; pa.k_chunk_blocks = k_chunk; pa.D = D; pa.ldd = ldd; pa.fault = fault;
-    pa.ctrl = ctrl; pa.D_alt = D_alt; pa.role = role;
-    pa.gate = gate.count; pa.gate_cap = gate.cap;
-    pa.scale = scale;
-    pa.p_tiled = ws.p_tiled ? 1 : 0;
-    pa.counters = static_cast<unsigned*>(ws.pair);
-    pa.slots = reinterpret_cast<double*>(static_cast<char*>(ws.pair) + size_t(PAIR_COUNTER_WORDS) * 4);
-    const cudaError_t ep = NT == 32 ? launch_gemm_pair_t<32>(st, num_sms, p0, p1, q0, q1, pa)
-                         : NT == 64 ? launch_gemm_pair_t<64>(st, num_sms, p0, p1, q0, q1, pa)
-                                    : launch_gemm_pair_t<128>(st, num_sms, p0, p1, q0, q1, pa);
-    if (ep != cudaSuccess) return fail(GLP_ERR_CUDA, "gemm (CTA pairs) launch failed: %s", cudaGetErrorString(ep));
-    return GLP_OK;
-  }
-  if (passes == 4) {
-  } else if (passes == 2) {
-    if (bf.Phb == nullptr || bf.Plb == nullptr || bf.Qhb == nullptr || bf.Qlb == nullptr)
-      return fail(GLP_ERR_ARG, "gemm: passes = 2 needs the bf16 operands");
-    GLP_TRY(make_map_bf16_k64(&mpx, bf.Phb, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, pbox));
-    GLP_TRY(make_map_bf16_k64(&mpl, bf.Plb, uint64_t(K), uint64_t(M), uint64_t(ldp) * 2, pbox));
-    GLP_TRY(make_map_bf16_k64(&mqx, bf.Qhb, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, qbox));
-    GLP_TRY(make_map_bf16_k64(&mql, bf.Qlb, uint64_t(K), uint64_t(N), uint64_t(ldq) * 2, qbox));
-  } else if (passes == 3) {
-    if (Pl == nullptr || Ql == nullptr) return fail(GLP_ERR_ARG, "gemm: passes = 3 needs the lo operands");
-    GLP_TRY(make_map_f32_k128(&mpl, Pl, uint64_t(K), uint64_t(M), uint64_t(ldp) * 4, pbox));
-    GLP_TRY(make_map_f32_k128(&mql, Ql, uint64_t(K), uint64_t(N), uint64_t(ldq) * 4, qbox));
-  } else {
-    mpl = mph; mql = mqh;
-  }
-  int S = ws.buf != nullptr ? gemm_splits(M, K, N, k_chunk, num_sms, bk) : 1;
-  const int64_t stride = int64_t(N) * ldd;
-  while (S > 1 && size_t(S) * stride * 8 > ws.bytes) --S;
-  GemmArgs a{};
-  a.M = M; a.K = K; a.N = N; a.k_chunk_blocks = k_chunk; a.D = D; a.ldd = ldd; a.fault = fault;
-  a.ctrl = ctrl; a.D_alt = D_alt; a.role = role;
-  a.splits = S; a.split_stride = stride;
-  if (S > 1) { a.D = ws.buf; a.D_alt = ws.buf; }   // partials first; the sum below picks the real destination
-  a.ct = ct; a.cg = cg;
-  a.gate = gate.count; a.gate_cap = gate.cap;
-  a.scale = scale;
-  const int64_t items = ((tiles + ct - 1) / ct) * ((groups + cg - 1) / cg) * S;   // cluster items
-  // fp16-pair product with one column group (P not shared inside the cluster): separate P / Q operand rings
-  // (glp_gemm.cuh, RINGS) when GLPROX_GEMM_RINGS=1.  Off by default: measured at C5 on one B200 in the same run
-  // (profiles/r01_ab_gemm_rings_c5.log) 372.8 it/s with the rings (fwd / tpass windows 1.174 / 1.023 ms) against
-  // 389.1 it/s with the single ring (1.116 / 0.966 ms), identical objective bits and all GPU tests green with
-  // either -- more P bytes in flight do not help, the kernel is not HBM-latency-bound.
-  const char* e_rings = getenv("GLPROX_GEMM_RINGS");   // read per call: tests switch it inside one process
-  const bool rings = passes == 4 && cg == 1 && e_rings != nullptr && atoi(e_rings) != 0;
-  cudaError_t e;
-#define GLP_GEMM_LAUNCH(NTV, PV) launch_gemm_t<NTV, PV>(st, num_sms, items, mph, mpl, mqh, mql, mpx, mqx, a)
-  if (passes == 1) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 1) : NT == 64 ? GLP_GEMM_LAUNCH(64, 1) : GLP_GEMM_LAUNCH(128, 1);
-  else if (passes == 2) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 2) : NT == 64 ? GLP_GEMM_LAUNCH(64, 2) : GLP_GEMM_LAUNCH(128, 2);
-  else if (passes == 4 && rings) {
-#define GLP_GEMM_LAUNCH_R(NTV) launch_gemm_t<NTV, 4, true>(st, num_sms, items, mph, mpl, mqh, mql, mpx, mqx, a)
-    e = NT == 32 ? GLP_GEMM_LAUNCH_R(32) : NT == 64 ? GLP_GEMM_LAUNCH_R(64) : GLP_GEMM_LAUNCH_R(128);
-#undef GLP_GEMM_LAUNCH_R
-  }
-  else if (passes == 4) e = NT == 32 ? GLP_GEMM_LAUNCH(32, 4) : NT == 64 ? GLP_GEMM_LAUNCH(64, 4) : GLP_GEMM_LAUNCH(128, 4);
-  else e = NT == 32 ? GLP_GEMM_LAUNCH(32, 3) : NT == 64 ? GLP_GEMM_LAUNCH(64, 3) : GLP_GEMM_LAUNCH(128, 3);
-#undef GLP_GEMM_LAUNCH
-  if (e != cudaSuccess) return fail(GLP_ERR_CUDA, "gemm launch failed: %s", cudaGetErrorString(e));
-  if (S > 1) {
-    const int sgrid = int(std::min<int64_t>((M * N + 255) / 256, int64_t(num_sms) * 8));
-    glp_sum_splits_kernel<<<sgrid, 256, 0, st>>>(ws.buf, S, stride, M, N, ldd, D, D_alt, ctrl, role, gate.count, gate.cap);
-    CU_TRY(cudaGetLastError());
-  }
-  return GLP_OK;
-}
-
-extern "C" int glp_gemm_tf32(int device, void* stream, int passes, int64_t M, int64_t K, int N, const void* P_hi,
-                             const void* P_lo, int64_t ldp, const void* Q_hi, const void* Q_lo, int64_t ldq,
-                             double* D_dev, int64_t ldd, int k_chunk_blocks) {
-  if (P_hi == nullptr || Q_hi == nullptr || D_dev == nullptr || M < 1 || K < 1) return fail(GLP_ERR_ARG, "bad argument");
-  int sms = 0;
-  GLP_TRY(check_device(device, &sms));
-  CU_TRY(cudaSetDevice(device));
-  if (N < 1 || N > 256) return fail(GLP_ERR_ARG, "gemm: N must be 1..256 (got %d)", N);
-  // k_chunk_blocks < 0: also exercise the split-K path (|k_chunk_blocks| blocks per chunk, partials in a
-  // stream-ordered temporary)
-  const int kc = k_chunk_blocks < 0 ? -k_chunk_blocks : k_chunk_blocks;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  GemmWs ws{nullptr, 0};
-  if (k_chunk_blocks < 0) {
-    ws.bytes = size_t(gemm_splits(M, K, N, kc, sms, passes == 4 ? 2 * GEMM_BK : GEMM_BK)) * N * ldd * 8;
-    CU_TRY(cudaMallocAsync(reinterpret_cast<void**>(&ws.buf), ws.bytes, st));
-  }
-  GemmBf16 bf{nullptr, nullptr, nullptr, nullptr};
-  __nv_bfloat16* tmp = nullptr;
-  if (passes == 2) {  // bf16 copies of the caller's hi / lo arrays (stream-ordered temporaries; test / probe entry point)
-    if (P_lo == nullptr || Q_lo == nullptr) return fail(GLP_ERR_ARG, "gemm: passes = 2 needs the lo operands");
-    const size_t pe = size_t(M) * ldp, qe = size_t(N) * ldq;
-    CU_TRY(cudaMallocAsync(reinterpret_cast<void**>(&tmp), (2 * pe + 2 * qe) * 2, st));
-    __nv_bfloat16 *phb = tmp, *plb = tmp + pe, *qhb = tmp + 2 * pe, *qlb = tmp + 2 * pe + qe;
-    const int g1 = int(std::min<size_t>((pe + 255) / 256, 148 * 16)), g2 = int(std::min<size_t>((qe + 255) / 256, 148 * 16));
-    glp_to_bf16_kernel<<<g1, 256, 0, st>>>(static_cast<const float*>(P_hi), phb, int64_t(pe));
-    glp_to_bf16_kernel<<<g1, 256, 0, st>>>(static_cast<const float*>(P_lo), plb, int64_t(pe));
-    glp_to_bf16_kernel<<<g2, 256, 0, st>>>(static_cast<const float*>(Q_hi), qhb, int64_t(qe));
-    glp_to_bf16_kernel<<<g2, 256, 0, st>>>(static_cast<const float*>(Q_lo), qlb, int64_t(qe));
-    bf = GemmBf16{phb, plb, qhb, qlb};
-  }
-  int rc;
-  if (passes == 4) {
-    // fp16 pairs of P_hi and Q_hi themselves (the lo arguments are not used): scales from the operands' maxima,
-    // all on the device in stream-ordered temporaries (test / probe entry point)
-    const char* e_pair = getenv("GLPROX_GEMM_PAIR");
-    const bool tiled = e_pair == nullptr || atoi(e_pair) != 0;
-    const int64_t nkb_t = (K + 63) / 64;
-    const size_t pe = tiled ? size_t((M + 127) / 128) * 128 * size_t(nkb_t) * 64 : size_t(M) * ldp, qe = size_t(N) * ldq;
-    uint8_t* t4 = nullptr;
-    CU_TRY(cudaMallocAsync(reinterpret_cast<void**>(&t4), (2 * pe + 2 * qe) * 2 + 64, st));
-    if (tiled) CU_TRY(cudaMemsetAsync(t4, 0, (2 * pe + 2 * qe) * 2 + 64, st));
-    __half *p0 = reinterpret_cast<__half*>(t4 + 64), *p1 = p0 + pe, *q0 = p1 + pe, *q1 = q0 + qe;
-    unsigned* amax = reinterpret_cast<unsigned*>(t4);
-    double* inv = reinterpret_cast<double*>(t4 + 16);
-    CU_TRY(cudaMemsetAsync(t4, 0, 64, st));
-    const float *Pf = static_cast<const float*>(P_hi), *Qf = static_cast<const float*>(Q_hi);
-    const int g1 = int(std::min<size_t>((pe + 255) / 256, 148 * 16)), g2 = int(std::min<size_t>((qe + 255) / 256, 148 * 16));
-    glp_absmax_kernel<<<g1, 256, 0, st>>>(Pf, M, K, ldp, amax);
-    glp_absmax_kernel<<<g2, 256, 0, st>>>(Qf, N, K, ldq, amax + 1);
-    if (tiled) glp_split_f16_tiled_dev_scale_kernel<<<g1, 256, 0, st>>>(Pf, p0, p1, M, K, ldp, nkb_t, amax);
-    else glp_split_f16_kernel<<<g1, 256, 0, st>>>(Pf, p0, p1, int64_t(pe), amax, nullptr, 0, 1.0f, nullptr, nullptr, nullptr, 0);
-    glp_split_f16_kernel<<<g2, 256, 0, st>>>(Qf, q0, q1, int64_t(qe), amax + 1, nullptr, 0, 1.0f, amax, inv, nullptr, 0);
-    CU_TRY(cudaGetLastError());
-    ws.p_tiled = tiled;
-    ws.pair_bytes = pair_ws_bytes(sms, 128);
-    CU_TRY(cudaMallocAsync(&ws.pair, ws.pair_bytes, st));
-    CU_TRY(cudaMemsetAsync(ws.pair, 0, size_t(PAIR_COUNTER_WORDS) * 4, st));
-    rc = gemm_enqueue(st, sms, 4, M, K, N, reinterpret_cast<const float*>(p0), reinterpret_cast<const float*>(p1), ldp,
-                      reinterpret_cast<const float*>(q0), reinterpret_cast<const float*>(q1), ldq, D_dev, ldd, kc, nullptr,
-                      nullptr, nullptr, 0, ws, bf, GemmGate{nullptr, 0}, inv);
-    cudaFreeAsync(ws.pair, st);
-    cudaFreeAsync(t4, st);
-  } else {
-    rc = gemm_enqueue(st, sms, passes, M, K, N, static_cast<const float*>(P_hi), static_cast<const float*>(P_lo), ldp,
-                      static_cast<const float*>(Q_hi), static_cast<const float*>(Q_lo), ldq, D_dev, ldd, kc, nullptr,
-                      nullptr, nullptr, 0, ws, bf);
-  }
-  if (ws.buf != nullptr) cudaFreeAsync(ws.buf, st);
-  if (tmp != nullptr) cudaFreeAsync(tmp, st);
-  return rc;
-}
-
-extern "C" int glp_tf32_split(void* stream, const void* src, int64_t rows, int64_t cols, int64_t ld_src, void* hi,
-                              void* lo, int64_t ld_dst, int transpose) {
-  if (src == nullptr || hi == nullptr || lo == nullptr || rows < 1 || cols < 1) return fail(GLP_ERR_ARG, "bad argument");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (transpose) {
-    dim3 grid(unsigned((cols + 31) / 32), unsigned((rows + 31) / 32));
-    if (grid.y > 65535u) return fail(GLP_ERR_ARG, "too many rows for the transposing split");
-    glp_transpose_split_kernel<<<grid, dim3(32, 8), 0, st>>>(static_cast<const float*>(src), static_cast<float*>(hi),
-                                                             static_cast<float*>(lo), rows, cols, ld_src, ld_dst);
-  } else {
-    const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
-    glp_split_tf32_kernel<<<grid, 256, 0, st>>>(static_cast<const float*>(src), static_cast<float*>(hi),
-                                                static_cast<float*>(lo), rows, cols, ld_src, ld_dst, nullptr, 0);
-  }
-  CU_TRY(cudaGetLastError());
-  return GLP_OK;
-}
-
+#include "glp_host_io.inl"
+#include "glp_gemm_host.inl"
 #include "glp_admm_host.inl"
 
-// ------------------------------------------------------------------------------------------------
-// caller-side metrics (code/main.py:30-34,48-50) on the device
-// ------------------------------------------------------------------------------------------------
-extern "C" int glp_metrics_eval(glp_handle* h, const void* x_dev, const void* ref_dev, double mu,
-                                double max_abs_override, glp_metrics* out) {
-  if (h == nullptr || x_dev == nullptr || out == nullptr) return fail(GLP_ERR_ARG, "bad argument");
-  if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
-  CU_TRY(cudaSetDevice(h->device));
-  const Geom& g = h->g;
-  const int64_t n = g.n, total = int64_t(g.n) * g.l;
-  const int grid = int(std::max<int64_t>(1, std::min<int64_t>((n + MET_THREADS - 1) / MET_THREADS, 148 * 4)));
-  const bool sharded = h->comm.world > 1;
-  // [grid][MET_STRIDE] records, 8 folded values, rr, then (unsharded) the m x l product
-  const size_t words = size_t(grid) * MET_STRIDE + 16 + (sharded ? 0 : size_t(g.m) * g.l);
-  double* buf = nullptr;
-  CU_TRY(cudaMalloc(&buf, words * sizeof(double)));
-  double* part = buf;
-  double* folded = buf + size_t(grid) * MET_STRIDE;
-  double* rr_dev = folded + 8;
-  double* ax = folded + 16;
-  int rc = GLP_OK;
-  cudaError_t ce = cudaMemsetAsync(buf, 0, (size_t(grid) * MET_STRIDE + 16) * sizeof(double), h->stream);
-  if (ce == cudaSuccess) {
-    if (h->dtype == GLP_F32) {
-      glp_metrics_sums_kernel<float><<<grid, MET_THREADS, 0, h->stream>>>(static_cast<const float*>(x_dev), static_cast<const float*>(ref_dev), n, g.l, part);
-      glp_metrics_count_kernel<float><<<grid, MET_THREADS, 0, h->stream>>>(static_cast<const float*>(x_dev), total, part, grid, max_abs_override);
-    } else {
-      glp_metrics_sums_kernel<double><<<grid, MET_THREADS, 0, h->stream>>>(static_cast<const double*>(x_dev), static_cast<const double*>(ref_dev), n, g.l, part);
-      glp_metrics_count_kernel<double><<<grid, MET_THREADS, 0, h->stream>>>(static_cast<const double*>(x_dev), total, part, grid, max_abs_override);
-    }
-    glp_metrics_fold_kernel<<<1, MET_THREADS, 0, h->stream>>>(part, grid, folded);
-    ce = cudaGetLastError();
-  }
-  if (ce == cudaSuccess && !sharded) rc = glp_fwd(h, x_dev, g.l, ax, rr_dev);
-  double host[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-  if (ce == cudaSuccess && rc == GLP_OK) ce = cudaMemcpyAsync(host, folded, 9 * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
-  if (ce == cudaSuccess && rc == GLP_OK) ce = cudaStreamSynchronize(h->stream);
-  cudaFree(buf);
-  if (rc != GLP_OK) return rc;
-  CU_TRY(ce);
-  out->sumsq_x = host[0]; out->sumsq_ref = host[1]; out->sumsq_diff = host[2];
-  out->reg = host[3]; out->max_abs = host[4]; out->count = host[5];
-  const double nan = std::numeric_limits<double>::quiet_NaN();
-  out->rr = sharded ? nan : host[8];
-  out->objective = sharded ? nan : 0.5 * host[8] + mu * host[3];
-  out->sparsity = total > 0 ? host[5] / double(total) : nan;
-  out->err_exact = ref_dev ? std::sqrt(host[2]) / (1.0 + std::sqrt(host[0])) : nan;
-  out->err_ref = ref_dev ? std::sqrt(host[2]) / (1.0 + std::sqrt(host[1])) : nan;
-  return GLP_OK;
-}
-
-// ------------------------------------------------------------------------------------------------
-// synthetic data
-// ------------------------------------------------------------------------------------------------
-extern "C" int glp_randn(void* dst_dev, int dtype, int64_t rows, int64_t cols, int64_t ld, uint64_t seed, int64_t row0,
-                         int64_t col0, void* stream) {
-  if (dst_dev == nullptr || rows < 0 || cols < 0 || ld < cols) return fail(GLP_ERR_ARG, "bad argument");
-  if (dtype != GLP_F32 && dtype != GLP_F64) return fail(GLP_ERR_ARG, "dtype must be GLP_F32 or GLP_F64");
-  if (rows * cols == 0) return GLP_OK;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int grid = int(std::min<int64_t>((rows * cols + 255) / 256, 148 * 16));
-  if (dtype == GLP_F32) randn_kernel<float><<<grid, 256, 0, st>>>(static_cast<float*>(dst_dev), rows, cols, ld, seed, row0, col0);
-  else randn_kernel<double><<<grid, 256, 0, st>>>(static_cast<double*>(dst_dev), rows, cols, ld, seed, row0, col0);
-  CU_TRY(cudaGetLastError());
-  return GLP_OK;
-}
+#include "glp_metrics_host.inl"
 
 // ------------------------------------------------------------------------------------------------
 // multi-GPU plumbing: NCCL is bound at run time (dlopen) so that the library loads on machines
