@@ -14,7 +14,8 @@
 // the control (k, the converge_len counter, histories) lives on the device.
 // Scope of THIS file: the kernels of the iteration and the single-CTA factor / solves used for m <= 2048; larger
 // systems take the blocked set-up of glp_dense.cuh and apply the factor as two streams of Y = L^-T
-// (glp_admm_host.inl).  l <= 2 (the residual 2-norms are taken from the l x l Gram matrices in closed form).
+// (glp_admm_host.inl).  l <= 8: the residual 2-norms come from the l x l Gram matrices, in closed form for l <= 2,
+// by Jacobi rotations above.
 #pragma once
 #include "glp_decide.h"
 #include "glp_device.cuh"
@@ -24,6 +25,12 @@ namespace glp {
 
 constexpr int ADMM_MAX_M = 2048;
 constexpr int ADMM_THREADS = 1024;
+constexpr int ADMM_MAX_L = 8;
+constexpr int ADMM_NPAIR = ADMM_MAX_L * (ADMM_MAX_L + 1) / 2;   // 36 entries of an upper triangle
+// per-column-block record of the update kernel: [0, 36) Gram matrix of r = u + A^T z (upper triangle, row-major:
+// entry (a, b), a <= b, at a*l - a(a-1)/2 + b - a), [36] sum_i ||x_i||, [37] max|x|
+constexpr int ADMM_GSTRIDE = 40;
+__host__ __device__ inline int admm_pair(int a, int b, int l) { return a * l - a * (a - 1) / 2 + (b - a); }
 
 struct AdmmConst {
   int32_t maxit, converge_len, hist_cap, pad;
@@ -87,13 +94,13 @@ struct AdmmUpdArgs {
   double* u;               // [l][ldn]
   const double* grad;      // [l][ldn] = A^T z
   void* xop;               // [2l][ldn] dtype T: [x - rho u | u]
-  double* scal_partial;    // [ncb][SCAL_STRIDE]: {r00, r01, reg, max|x|, r11, -, -, -}
+  double* gram_partial;    // [ncb][ADMM_GSTRIDE]: Gram of r (upper triangle), sum_i ||x_i||, max|x|
   AdmmConst c;
 };
 
 template <typename T>
 __global__ void glp_admm_update_kernel(const AdmmUpdArgs a, const Geom g) {
-  __shared__ double s_red[8][5];
+  __shared__ double s_red[8][ADMM_NPAIR + 2];
   if (a.ctrl != nullptr && a.ctrl->done) return;
   constexpr int TC = Elem<T>::TILE_COLS;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -101,11 +108,17 @@ __global__ void glp_admm_update_kernel(const AdmmUpdArgs a, const Geom g) {
   const int l = g.l;
   const int64_t ldn = g.ldn;
   T* xop = static_cast<T*>(a.xop);
-  double r00 = 0.0, r01 = 0.0, r11 = 0.0, reg = 0.0, mx = 0.0;
+  double gram[ADMM_NPAIR], reg = 0.0, mx = 0.0;
+#pragma unroll
+  for (int q = 0; q < ADMM_NPAIR; ++q) gram[q] = 0.0;
   if (tid < TC && j < g.n) {
     const double taurho = xmul(a.c.tau, a.c.rho);
-    double nn = 0.0, xv[2], gv[2] = {0.0, 0.0}, vv[2];
-    for (int c = 0; c < l; ++c) {
+    double nn = 0.0, xv[ADMM_MAX_L], gv[ADMM_MAX_L], vv[ADMM_MAX_L], rr[ADMM_MAX_L];
+#pragma unroll
+    for (int c = 0; c < ADMM_MAX_L; ++c) { xv[c] = 0.0; gv[c] = 0.0; vv[c] = 0.0; rr[c] = 0.0; }
+#pragma unroll
+    for (int c = 0; c < ADMM_MAX_L; ++c) {
+      if (c >= l) break;
       xv[c] = a.x[c * ldn + j];
       if (!a.init) {
         gv[c] = __ldcg(&a.grad[c * ldn + j]);
@@ -113,11 +126,13 @@ __global__ void glp_admm_update_kernel(const AdmmUpdArgs a, const Geom g) {
         nn = xadd(nn, xmul(vv[c], vv[c]));
       }
     }
-    double n2 = 0.0, rr[2] = {0.0, 0.0};
+    double n2 = 0.0;
     if (!a.init) {
       const double rn = __dsqrt_rn(nn);
       const double den = rn < a.c.mu ? a.c.mu : rn;    // np.clip(row_norms, a_min=mu)              :47
-      for (int c = 0; c < l; ++c) {
+#pragma unroll
+      for (int c = 0; c < ADMM_MAX_L; ++c) {
+        if (c >= l) break;
         const double un = xdiv(xmul(a.c.mu, vv[c]), den);
         rr[c] = xadd(un, gv[c]);                       // r_k = u + A.T @ z                        :67
         const double xn = xsub(xv[c], xmul(taurho, rr[c]));   // x_k - tau * rho * (u + A.T @ z)   :65
@@ -129,7 +144,9 @@ __global__ void glp_admm_update_kernel(const AdmmUpdArgs a, const Geom g) {
         mx = fmax(mx, fabs(xn));
       }
     } else {
-      for (int c = 0; c < l; ++c) {
+#pragma unroll
+      for (int c = 0; c < ADMM_MAX_L; ++c) {
+        if (c >= l) break;
         a.u[c * ldn + j] = 0.0;
         xop[c * ldn + j] = T(xv[c]);
         xop[(l + c) * ldn + j] = T(0.0);
@@ -138,20 +155,42 @@ __global__ void glp_admm_update_kernel(const AdmmUpdArgs a, const Geom g) {
       }
     }
     reg = __dsqrt_rn(n2);
-    r00 = rr[0] * rr[0]; r01 = rr[0] * rr[1]; r11 = rr[1] * rr[1];
+#pragma unroll
+    for (int c = 0; c < ADMM_MAX_L; ++c)
+#pragma unroll
+      for (int d = c; d < ADMM_MAX_L; ++d)
+        gram[admm_pair(c, d, ADMM_MAX_L)] = rr[c] * rr[d];   // compile-time index (rows / columns >= l are zero)
   }
-  r00 = warp_sum(r00); r01 = warp_sum(r01); r11 = warp_sum(r11); reg = warp_sum(reg);
+#pragma unroll
+  for (int q = 0; q < ADMM_NPAIR; ++q) {
+    const double v = warp_sum(gram[q]);
+    if (lane == 0) s_red[warp][q] = v;
+  }
+  reg = warp_sum(reg);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  if (lane == 0) { s_red[warp][0] = r00; s_red[warp][1] = r01; s_red[warp][2] = reg; s_red[warp][3] = mx; s_red[warp][4] = r11; }
+  if (lane == 0) { s_red[warp][ADMM_NPAIR] = reg; s_red[warp][ADMM_NPAIR + 1] = mx; }
   __syncthreads();
-  if (tid == 0) {
-    double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0, t4 = 0.0;
-    for (int w = 0; w < int(blockDim.x >> 5); ++w) {
-      t0 += s_red[w][0]; t1 += s_red[w][1]; t2 += s_red[w][2]; t3 = fmax(t3, s_red[w][3]); t4 += s_red[w][4];
+  const int nw = int(blockDim.x >> 5);
+  double* out = a.gram_partial + ADMM_GSTRIDE * int64_t(blockIdx.x);
+  if (tid < ADMM_NPAIR) {
+    // fixed index (pair of an 8 x 8 triangle) -> (c, d) -> index in the l x l triangle the mid kernel reads
+    int c = 0, rem = tid;
+    while (rem >= ADMM_MAX_L - c) { rem -= ADMM_MAX_L - c; ++c; }
+    const int d = c + rem;
+    if (d < l) {
+      double t = 0.0;
+      for (int w = 0; w < nw; ++w) t += s_red[w][tid];
+      out[admm_pair(c, d, l)] = t;
     }
-    double* out = a.scal_partial + SCAL_STRIDE * int64_t(blockIdx.x);
-    out[0] = t0; out[1] = t1; out[2] = t2; out[3] = t3; out[4] = t4; out[5] = 0.0;
+  } else if (tid == ADMM_NPAIR) {
+    double t = 0.0;
+    for (int w = 0; w < nw; ++w) t += s_red[w][tid];
+    out[tid] = t;
+  } else if (tid == ADMM_NPAIR + 1) {
+    double t = 0.0;
+    for (int w = 0; w < nw; ++w) t = fmax(t, s_red[w][tid]);
+    out[tid] = t;
   }
 }
 
@@ -164,7 +203,7 @@ struct AdmmMidArgs {
   const double* b;            // [l][ldm]
   double* Au_prev;            // [l][ldm]
   const double* L;            // [m][m] lower Cholesky factor
-  const double* scal_partial; int32_t n_scal;
+  const double* gram_partial; int32_t n_scal;   // [n_scal][ADMM_GSTRIDE] from the update kernel
   const double* cnt_partial;  int32_t n_cnt;
   void* r;                    // [l][ldm] dtype T: z, the operand of the transposed stream
   double* f_hist;
@@ -180,74 +219,126 @@ __device__ __forceinline__ double admm_norm2(double a, double b, double c, int l
   const double h = 0.5 * (a - c);
   return sqrt(0.5 * (a + c) + sqrt(h * h + b * b));
 }
+// l > 2: matrix 2-norm (numpy LA.norm(., 2), gl_ADMM_dual.py:87-88) = sqrt of the largest eigenvalue of the l x l Gram
+// matrix, by cyclic Jacobi rotations (converges quadratically; 12 sweeps are far more than an 8 x 8 matrix needs).
+// gu: upper triangle in admm_pair order.
+__device__ inline double admm_norm2_jacobi(const double* gu, int l) {
+  double M[ADMM_MAX_L][ADMM_MAX_L];
+  for (int a = 0; a < l; ++a)
+    for (int b = a; b < l; ++b) M[a][b] = M[b][a] = gu[admm_pair(a, b, l)];
+  for (int sweep = 0; sweep < 12; ++sweep) {
+    double off = 0.0;
+    for (int p = 0; p < l; ++p)
+      for (int q = p + 1; q < l; ++q) off += M[p][q] * M[p][q];
+    if (off == 0.0) break;
+    for (int p = 0; p < l; ++p)
+      for (int q = p + 1; q < l; ++q) {
+        if (M[p][q] == 0.0) continue;
+        const double theta = (M[q][q] - M[p][p]) / (2.0 * M[p][q]);
+        const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+        const double c = 1.0 / sqrt(t * t + 1.0), sn = t * c;
+        for (int k = 0; k < l; ++k) {   // columns p, q
+          const double kp = M[k][p], kq = M[k][q];
+          M[k][p] = c * kp - sn * kq; M[k][q] = sn * kp + c * kq;
+        }
+        for (int k = 0; k < l; ++k) {   // rows p, q
+          const double pk = M[p][k], qk = M[q][k];
+          M[p][k] = c * pk - sn * qk; M[q][k] = sn * pk + c * qk;
+        }
+      }
+  }
+  double mx = 0.0;
+  for (int a = 0; a < l; ++a) mx = fmax(mx, M[a][a]);
+  return sqrt(mx);
+}
 
 template <typename T>
 __global__ void __launch_bounds__(ADMM_THREADS) glp_admm_mid_kernel(const AdmmMidArgs a, const Geom g) {
   extern __shared__ double s_w[];                 // [l][m] right-hand sides / solution
-  __shared__ double s_red[ADMM_THREADS / 32][8];
+  constexpr int NV = 2 + 2 * ADMM_NPAIR;            // rr, reg, Gram of s (upper), Gram of r (upper)
+  __shared__ double s_red[ADMM_THREADS / 32][NV];
+  __shared__ double s_tot[NV];
   __shared__ Ctrl s_out;
-  __shared__ double s_z[2][32];
+  __shared__ double s_z[ADMM_MAX_L][32];
   __shared__ double s_blk[32][33];
+  __shared__ double s_cnt[ADMM_THREADS / 32];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const Ctrl cin = *a.cin;
   if (cin.done) {
     if (tid == 0) *a.cout = cin;
     return;
   }
-  const int l = g.l, m = g.m;
+  const int l = g.l, m = g.m, npair = l * (l + 1) / 2;
   const int64_t ldm = g.ldm;
   const double* P1 = a.P;
   const double* P2 = a.P + int64_t(l) * ldm;
-  // ---- reductions: ||A x - b||^2 with A x = P1 + rho P2, Gram of s = A u_prev - A u, scalar partials
-  double v[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // rr, s00, s01, s11, r00, r01, r11, reg
-  double mx = 0.0, cnt = 0.0;
+  // ---- reductions (thread-strided, warp tree, warps in order): ||A x - b||^2 with A x = P1 + rho P2, the Gram
+  // matrix of s = A u_prev - A u, and the per-column-block records of the update kernel
+  double rrv = 0.0, regv = 0.0, mx = 0.0, cnt = 0.0;
+  double sg[ADMM_NPAIR], rg[ADMM_NPAIR];
+#pragma unroll
+  for (int q = 0; q < ADMM_NPAIR; ++q) { sg[q] = 0.0; rg[q] = 0.0; }
   for (int i = tid; i < m; i += ADMM_THREADS) {
-    double sv[2] = {0.0, 0.0};
-    for (int c = 0; c < l; ++c) {
-      const double p2 = P2[c * ldm + i];
-      const double d = xsub(xadd(P1[c * ldm + i], xmul(a.c.rho, p2)), a.b[c * ldm + i]);
-      v[0] += d * d;
-      sv[c] = xsub(a.Au_prev[c * ldm + i], p2);
+    double sv[ADMM_MAX_L];
+#pragma unroll
+    for (int c = 0; c < ADMM_MAX_L; ++c) {
+      sv[c] = 0.0;
+      if (c < l) {
+        const double p2 = P2[c * ldm + i];
+        const double d = xsub(xadd(P1[c * ldm + i], xmul(a.c.rho, p2)), a.b[c * ldm + i]);
+        rrv += d * d;
+        sv[c] = xsub(a.Au_prev[c * ldm + i], p2);
+      }
     }
-    v[1] += sv[0] * sv[0]; v[2] += sv[0] * sv[1]; v[3] += sv[1] * sv[1];
+#pragma unroll
+    for (int c = 0; c < ADMM_MAX_L; ++c)
+#pragma unroll
+      for (int d = c; d < ADMM_MAX_L; ++d) sg[admm_pair(c, d, ADMM_MAX_L)] += sv[c] * sv[d];
   }
   for (int i = tid; i < a.n_scal; i += ADMM_THREADS) {
-    const double* p = a.scal_partial + SCAL_STRIDE * int64_t(i);
-    v[4] += __ldcg(p + 0); v[5] += __ldcg(p + 1); v[7] += __ldcg(p + 2); mx = fmax(mx, __ldcg(p + 3)); v[6] += __ldcg(p + 4);
+    const double* p = a.gram_partial + ADMM_GSTRIDE * int64_t(i);
+    for (int q = 0; q < npair; ++q) rg[q] += __ldcg(p + q);          // already in the l x l pair order
+    regv += __ldcg(p + ADMM_NPAIR);
+    mx = fmax(mx, __ldcg(p + ADMM_NPAIR + 1));
   }
   for (int i = tid; i < a.n_cnt; i += ADMM_THREADS) cnt += __ldcg(&a.cnt_partial[i]);
+  rrv = warp_sum(rrv); regv = warp_sum(regv); cnt = warp_sum(cnt);
+  if (lane == 0) { s_red[warp][0] = rrv; s_red[warp][1] = regv; s_cnt[warp] = cnt; }
 #pragma unroll
-  for (int q = 0; q < 8; ++q) v[q] = warp_sum(v[q]);
-  cnt = warp_sum(cnt);
-  if (lane == 0) {
+  for (int c = 0; c < ADMM_MAX_L; ++c)
 #pragma unroll
-    for (int q = 0; q < 8; ++q) s_red[warp][q] = v[q];
+    for (int d = c; d < ADMM_MAX_L; ++d) {
+      const double v = warp_sum(sg[admm_pair(c, d, ADMM_MAX_L)]);
+      if (lane == 0 && d < l) s_red[warp][2 + admm_pair(c, d, l)] = v;
+    }
+#pragma unroll
+  for (int q = 0; q < ADMM_NPAIR; ++q) {
+    const double v = warp_sum(rg[q]);
+    if (lane == 0 && q < npair) s_red[warp][2 + ADMM_NPAIR + q] = v;
   }
   __syncthreads();
-  if (tid == 0) {
-    double t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int w = 0; w < ADMM_THREADS / 32; ++w)
-      for (int q = 0; q < 8; ++q) t[q] += s_red[w][q];
-    s_red[0][0] = t[0]; s_red[0][1] = t[1]; s_red[0][2] = t[2]; s_red[0][3] = t[3];
-    s_red[0][4] = t[4]; s_red[0][5] = t[5]; s_red[0][6] = t[6]; s_red[0][7] = t[7];
+  if (tid < NV) {
+    const bool live = tid < 2 || (tid < 2 + ADMM_NPAIR ? tid - 2 < npair : tid - 2 - ADMM_NPAIR < npair);
+    double t = 0.0;
+    if (live) for (int w = 0; w < ADMM_THREADS / 32; ++w) t += s_red[w][tid];
+    s_tot[tid] = t;
   }
-  __syncthreads();
-  __shared__ double s_cnt[ADMM_THREADS / 32];
-  if (lane == 0) s_cnt[warp] = cnt;
   __syncthreads();
   if (tid == 0) {
     double ctot = 0.0;
     for (int w = 0; w < ADMM_THREADS / 32; ++w) ctot += s_cnt[w];
     Ctrl out = cin;
-    const double f_now = xadd(xmul(0.5, s_red[0][0]), xmul(a.c.mu, s_red[0][7]));
+    const double f_now = xadd(xmul(0.5, s_tot[0]), xmul(a.c.mu, s_tot[1]));
     out.f_cur = f_now;
     out.s_cur = ctot / a.size_total;
     if (cin.k > 0) {   // iteration cin.k has just been completed by the forward stream: record and test it (:72-99)
       if (a.f_hist != nullptr && cin.k - 1 < a.c.hist_cap) a.f_hist[cin.k - 1] = f_now;
       out.f_best = f_now < cin.f_best ? f_now : cin.f_best;
       if (a.f_hist_best != nullptr && cin.k - 1 < a.c.hist_cap) a.f_hist_best[cin.k - 1] = out.f_best;
-      const double rn = admm_norm2(s_red[0][4], s_red[0][5], s_red[0][6], l);
-      const double sn = admm_norm2(s_red[0][1], s_red[0][2], s_red[0][3], l);
+      const double* sgt = s_tot + 2;
+      const double* rgt = s_tot + 2 + ADMM_NPAIR;
+      const double rn = l <= 2 ? admm_norm2(rgt[0], l > 1 ? rgt[1] : 0.0, l > 1 ? rgt[2] : 0.0, l) : admm_norm2_jacobi(rgt, l);
+      const double sn = l <= 2 ? admm_norm2(sgt[0], l > 1 ? sgt[1] : 0.0, l > 1 ? sgt[2] : 0.0, l) : admm_norm2_jacobi(sgt, l);
       out.stable = (rn < a.c.thres && sn < a.c.thres) ? cin.stable + 1 : 0;
       if (out.stable >= a.c.converge_len) out.done = 1;
     }
@@ -301,15 +392,19 @@ __global__ void __launch_bounds__(ADMM_THREADS) glp_admm_mid_kernel(const AdmmMi
     }
     __syncthreads();
     for (int i = j0 + pw + tid; i < m; i += ADMM_THREADS) {
-      double acc0 = 0.0, acc1 = 0.0;
+      double acc[ADMM_MAX_L];
+#pragma unroll
+      for (int c = 0; c < ADMM_MAX_L; ++c) acc[c] = 0.0;
       const double* Li = L + int64_t(i) * m + j0;
       for (int jj = 0; jj < pw; ++jj) {
         const double lij = Li[jj];
-        acc0 += lij * s_z[0][jj];
-        if (l > 1) acc1 += lij * s_z[1][jj];
+#pragma unroll
+        for (int c = 0; c < ADMM_MAX_L; ++c)
+          if (c < l) acc[c] += lij * s_z[c][jj];
       }
-      s_w[i] -= acc0;
-      if (l > 1) s_w[m + i] -= acc1;
+#pragma unroll
+      for (int c = 0; c < ADMM_MAX_L; ++c)
+        if (c < l) s_w[c * m + i] -= acc[c];
     }
     __syncthreads();
   }
@@ -334,14 +429,18 @@ __global__ void __launch_bounds__(ADMM_THREADS) glp_admm_mid_kernel(const AdmmMi
     }
     __syncthreads();
     for (int i = tid; i < j0; i += ADMM_THREADS) {
-      double acc0 = 0.0, acc1 = 0.0;
+      double acc[ADMM_MAX_L];
+#pragma unroll
+      for (int c = 0; c < ADMM_MAX_L; ++c) acc[c] = 0.0;
       for (int jj = 0; jj < pw; ++jj) {
         const double lji = L[int64_t(j0 + jj) * m + i];   // coalesced over i
-        acc0 += lji * s_z[0][jj];
-        if (l > 1) acc1 += lji * s_z[1][jj];
+#pragma unroll
+        for (int c = 0; c < ADMM_MAX_L; ++c)
+          if (c < l) acc[c] += lji * s_z[c][jj];
       }
-      s_w[i] -= acc0;
-      if (l > 1) s_w[m + i] -= acc1;
+#pragma unroll
+      for (int c = 0; c < ADMM_MAX_L; ++c)
+        if (c < l) s_w[c * m + i] -= acc[c];
     }
     __syncthreads();
   }

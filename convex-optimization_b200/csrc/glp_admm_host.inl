@@ -175,7 +175,11 @@ extern "C" int glp_admm_dual(glp_handle* h, const void* x0_dev, double mu, const
   if (h->solving) return fail(GLP_ERR_STATE, "a solve is in progress on this handle");
   if (multi(h)) return fail(GLP_ERR_ARG, "gl_Admm_dual runs on one GPU");
   const Geom& g = h->g;
-  if (g.l > 2) return fail(GLP_ERR_ARG, "gl_Admm_dual supports l <= 2 (got l = %d)", g.l);
+  if (g.l > ADMM_MAX_L) return fail(GLP_ERR_ARG, "gl_Admm_dual supports l <= %d (got l = %d)", ADMM_MAX_L, g.l);
+  if (h->admm_gpart == nullptr) {
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&h->admm_gpart), size_t(g.ncb) * ADMM_GSTRIDE * 8));
+    CU_TRY(cudaMemsetAsync(h->admm_gpart, 0, size_t(g.ncb) * ADMM_GSTRIDE * 8, h->stream));
+  }
   const char* e_blk = getenv("GLPROX_ADMM_BLOCKED");
   const bool blocked = g.m > ADMM_MAX_M || (e_blk != nullptr && atoi(e_blk) != 0);
   if (o->maxit < 0 || !(o->rho > 0.0)) return fail(GLP_ERR_ARG, "bad opts (maxit >= 0, rho > 0)");
@@ -228,7 +232,7 @@ extern "C" int glp_admm_dual(glp_handle* h, const void* x0_dev, double mu, const
   auto launch_update = [&](const Ctrl* ctrl, int init) -> cudaError_t {
     AdmmUpdArgs ua{};
     ua.ctrl = ctrl; ua.init = init; ua.x = x; ua.u = u; ua.grad = h->grad; ua.xop = xop;
-    ua.scal_partial = h->scal_partial; ua.c = ac;
+    ua.gram_partial = h->admm_gpart; ua.c = ac;
     if (f32) glp_admm_update_kernel<float><<<g.ncb, upd_threads, 0, h->stream>>>(ua, g);
     else glp_admm_update_kernel<double><<<g.ncb, upd_threads, 0, h->stream>>>(ua, g);
     h->n_launches++;
@@ -251,13 +255,17 @@ extern "C" int glp_admm_dual(glp_handle* h, const void* x0_dev, double mu, const
         AdmmMidArgs ma{};
         ma.cin = cin; ma.cout = cout; ma.c = ac;
         ma.P = h->AX[0]; ma.b = h->b; ma.Au_prev = h->Av; ma.L = h->admm_L;
-        ma.scal_partial = h->scal_partial; ma.n_scal = g.ncb;
+        ma.gram_partial = h->admm_gpart; ma.n_scal = g.ncb;
         ma.cnt_partial = h->cnt_partial; ma.n_cnt = g.grid;
         ma.r = h->r; ma.f_hist = h->f_hist; ma.f_hist_best = h->f_hist_best;
         ma.size_total = double(g.n) * double(g.l);
         glp_handle* in = h->admm_inner;
         if (blocked) { ma.w_out = static_cast<double*>(in->r); ma.w_ld = in->g.ldm; }
         const size_t smem = blocked ? 0 : size_t(g.l) * g.m * 8;
+        if (smem > 40 * 1024) {   // l > 2 at m near 2048: beyond the default dynamic shared-memory limit
+          if (f32) CU_TRY(cudaFuncSetAttribute(glp_admm_mid_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+          else CU_TRY(cudaFuncSetAttribute(glp_admm_mid_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        }
         if (f32) glp_admm_mid_kernel<float><<<1, ADMM_THREADS, smem, h->stream>>>(ma, g);
         else glp_admm_mid_kernel<double><<<1, ADMM_THREADS, smem, h->stream>>>(ma, g);
         CU_TRY(cudaGetLastError());

@@ -1,3 +1,4 @@
+#include <chrono>
 // glp_host_io.inl -- the one-shot entry point with HOST buffers (glp_solve_host), included by glprox.cu: pinned or
 // bounced upload of A, solve, download of x.
 // ------------------------------------------------------------------------------------------------
@@ -103,14 +104,19 @@ extern "C" int glp_solve_host(int device, int algo, int dtype, int m, int n, int
       return fail(GLP_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));            \
     }                                                                                         \
   } while (0)
+  const bool timing = getenv("GLPROX_HOST_TIMING") != nullptr;
+  auto now = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  const double t0 = now();
   HOST_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
   HOST_TRY(cudaMalloc(&dA, size_t(m) * ldd * es));
   HOST_TRY(cudaMalloc(&db, size_t(m) * l * es));
   HOST_TRY(cudaMalloc(&dx0, size_t(n) * l * es));
   HOST_TRY(cudaMalloc(&dx, size_t(n) * l * es));
   if (ldd != size_t(n)) HOST_TRY(cudaMemsetAsync(dA, 0, size_t(m) * ldd * es, st));
+  const double t1 = now();
   rc = upload_matrix(device, st, dA, ldd * es, A_host, size_t(lda) * es, size_t(n) * es, size_t(m));
   if (rc != GLP_OK) { cleanup(); return rc; }
+  const double t2 = now();
   HOST_TRY(cudaMemcpyAsync(db, b_host, size_t(m) * l * es, cudaMemcpyHostToDevice, st));
   HOST_TRY(cudaMemcpyAsync(dx0, x0_host, size_t(n) * l * es, cudaMemcpyHostToDevice, st));
   rc = glp_create(&h, device, m, n, l, dtype, dA, int64_t(ldd), db, nullptr, st);
@@ -120,6 +126,10 @@ extern "C" int glp_solve_host(int device, int algo, int dtype, int m, int n, int
     HOST_TRY(cudaStreamSynchronize(st));
   }
 #undef HOST_TRY
+  const double t3 = now();
   cleanup();
+  if (timing)
+    fprintf(stderr, "[glp_solve_host] alloc %.1f ms, upload of A %.1f ms (%.1f GB/s), create + solve + download %.1f ms, free %.1f ms\n",
+            t1 - t0, t2 - t1, double(m) * n * es / (t2 - t1) / 1e6, t3 - t2, now() - t3);
   return rc;
 }

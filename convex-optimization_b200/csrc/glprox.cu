@@ -189,6 +189,7 @@ struct glp_handle {
   int64_t admm_ldy = 0;
   glp_handle* admm_inner = nullptr;   // m x m fp64 problem over Y: K1 / K2 apply z = Y (Y^T w)
   double* admm_zero_b = nullptr;
+  double* admm_gpart = nullptr;       // [ncb][ADMM_GSTRIDE] per-column-block records of the update kernel
   void* pair_ws = nullptr;     // K5 on CTA pairs (glp_gemm_pair.cuh): arrival counters + partial-tile slots
   size_t pair_ws_bytes = 0;
   double* gemm_ws = nullptr;   // split-K partial products of K5
@@ -454,6 +455,7 @@ extern "C" int glp_destroy(glp_handle* h) {
   if (h->admm_inner) { glp_handle* in = h->admm_inner; h->admm_inner = nullptr; glp_destroy(in); }
   if (h->admm_Y) cudaFree(h->admm_Y);
   if (h->admm_zero_b) cudaFree(h->admm_zero_b);
+  if (h->admm_gpart) cudaFree(h->admm_gpart);
   if (h->nccl_stage) cudaFree(h->nccl_stage);
   for (__half* q : {h->A_f0, h->A_f1, h->At_f0, h->At_f1, h->xop_f0, h->xop_f1, h->r_f0, h->r_f1})
     if (q) cudaFree(q);

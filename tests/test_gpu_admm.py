@@ -56,9 +56,9 @@ def test_admm_edge_cases():
     x2, k2, _ = _fn()(x0, A, b, mu, {"maxit": 5, "no_such_key": 1})
     xr, kr, _ = orc.solve_admm_dual(x0, A, b, mu, {"maxit": 5})
     assert k2 == kr and np.max(np.abs(x2 - xr)) <= 1e-10
-    A3, b3, x03, _, _ = orc.gen_data(3, 32, 64, 3)
+    A9, b9, x09, _, _ = orc.gen_data(3, 32, 64, 9)
     with pytest.raises(_lib.GlproxError):
-        _fn()(x03, A3, b3, mu, {})
+        _fn()(x09, A9, b9, mu, {})
 
 
 def test_admm_on_a_device_resident_problem_and_in_the_driver_table(capsys):
@@ -131,3 +131,20 @@ def test_streaming_size_fp32_admm_matches_the_fp64_oracle(gram, monkeypatch):
     assert np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-5
     assert abs(out["fval"] - outr["fval"]) <= 1e-5 * abs(outr["fval"])
     assert out["glprox"]["n_fwd"] == k + 1 and out["glprox"]["n_tpass"] == k
+
+
+@pytest.mark.parametrize("blocked", ["0", "1"])
+@pytest.mark.parametrize("l", [3, 5, 8])
+def test_admm_dual_with_more_than_two_right_hand_sides(l, blocked, monkeypatch):
+    """l > 2: the residual test needs the matrix 2-norms of the n x l / m x l residuals
+    (gl_ADMM_dual.py:87-88, numpy LA.norm(., 2)) = sqrt of the largest eigenvalue of their l x l Gram matrices, taken
+    by Jacobi rotations on the device; run to the reference's own stop rule on both schedules."""
+    monkeypatch.setenv("GLPROX_ADMM_BLOCKED", blocked)
+    A, b, x0, u, mu = orc.gen_data(13, 192, 448, l)
+    opts = {"maxit": 80, "converge_len": 5, "thres": 2e-2}
+    x, k, out = _fn()(x0, A, b, mu, dict(opts))
+    xr, kr, outr = orc.solve_admm_dual(x0, A, b, mu, dict(opts))
+    assert k == kr and 5 < k < 80          # the stop rule fired, at the same iteration
+    fh, ref = np.asarray(out["f_hist"]), np.asarray(outr["f_hist"])
+    assert np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-10
+    assert np.max(np.abs(x - xr)) <= 1e-9 * max(1.0, np.max(np.abs(xr)))
