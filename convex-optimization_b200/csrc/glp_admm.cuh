@@ -95,6 +95,7 @@ struct AdmmUpdArgs {
   const double* grad;      // [l][ldn] = A^T z
   void* xop;               // [2l][ldn] dtype T: [x - rho u | u]
   double* gram_partial;    // [ncb][ADMM_GSTRIDE]: Gram of r (upper triangle), sum_i ||x_i||, max|x|
+  double* scal_partial;    // [ncb][SCAL_STRIDE]: slot 3 = max|x| of the block, where K1's sparsity count reads it
   AdmmConst c;
 };
 
@@ -191,6 +192,7 @@ __global__ void glp_admm_update_kernel(const AdmmUpdArgs a, const Geom g) {
     double t = 0.0;
     for (int w = 0; w < nw; ++w) t = fmax(t, s_red[w][tid]);
     out[tid] = t;
+    a.scal_partial[SCAL_STRIDE * int64_t(blockIdx.x) + 3] = t;
   }
 }
 

@@ -232,7 +232,7 @@ extern "C" int glp_admm_dual(glp_handle* h, const void* x0_dev, double mu, const
   auto launch_update = [&](const Ctrl* ctrl, int init) -> cudaError_t {
     AdmmUpdArgs ua{};
     ua.ctrl = ctrl; ua.init = init; ua.x = x; ua.u = u; ua.grad = h->grad; ua.xop = xop;
-    ua.gram_partial = h->admm_gpart; ua.c = ac;
+    ua.gram_partial = h->admm_gpart; ua.scal_partial = h->scal_partial; ua.c = ac;
     if (f32) glp_admm_update_kernel<float><<<g.ncb, upd_threads, 0, h->stream>>>(ua, g);
     else glp_admm_update_kernel<double><<<g.ncb, upd_threads, 0, h->stream>>>(ua, g);
     h->n_launches++;

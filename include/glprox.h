@@ -267,7 +267,7 @@ int glp_tf32_split(void* stream, const void* src, int64_t rows, int64_t cols, in
  * thres 1e-3 (residual test), tau (1+sqrt(5))/2, rho 1e2, converge_len 20.  Replaces the whole function body:
  * the Cholesky factor of I + rho A A^T (:57) is built once on the device, every iteration is one forward and
  * one transposed stream of A plus two triangular solves; objective history, residual norms and the
- * converge_len stop rule (:87-99) are evaluated on the device.  Scope: m <= 2048, l <= 2, one GPU.
+ * converge_len stop rule (:87-99) are evaluated on the device.  Scope: l <= 8, one GPU; m > 2048 takes the blocked fp64 Cholesky and applies the factor as two streams of L^-T.
  * res->iters = k, res->fval = out["fval"]; f_hist_host receives min(k, hist_cap) values. */
 typedef struct glp_admm_opts {
   int32_t maxit;
