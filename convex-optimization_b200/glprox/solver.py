@@ -70,10 +70,8 @@ def pack_opts(algo, merged):
         if st == "line_search":  # the reference returns None as the step and dies with TypeError (gl_GD_primal.py:75-76)
             logger.error("Unsupported type.")
             raise ValueError("gl_%s_primal has no line search: step_type must be fixed, diminishing or diminishing2" % algo)
-        if merged.get("continuous_subgradient_flag"):
-            raise NotImplementedError("continuous_subgradient_flag (alpha0 = 1/lambda_max(A^T A) from a dense n x n "
-                                      "eigendecomposition, gl_GD_primal.py:43-45) is outside the streaming path; "
-                                      "pass alpha0 explicitly")
+        # continuous_subgradient_flag (gl_GD_primal.py:43-45, gl_SGD_primal.py:35-37): the caller has replaced
+        # alpha0 by 1 / lambda_max(A^T A) (GroupLassoProblem.lambda_max: Lanczos on the two stream kernels)
     backend = merged.get("backend", "auto")
     if backend not in _lib.BACKENDS:
         raise ValueError("unknown backend %r" % (backend,))
@@ -189,7 +187,7 @@ def solve(algo, x0, A, b, mu_0, opts):
     mode = _tensor_mode(merged)
     if merged.get("dist"):
         return _solve_numpy_sharded(algo, x0, A, b, mu_0, merged, o)
-    if mode != 0 or logger.isEnabledFor(logging.DEBUG):
+    if mode != 0 or logger.isEnabledFor(logging.DEBUG) or (algo in ("GD", "SGD") and merged.get("continuous_subgradient_flag")):
         # the one-shot host entry point always uses the default tensor mode and keeps no handle to read the
         # sparsity history from (DEBUG log lines): explicit modes and DEBUG logging go through a handle
         import torch
@@ -371,10 +369,68 @@ class GroupLassoProblem:
         except Exception:
             pass
 
+    def lambda_max(self, max_steps=400, tol=1e-14, group=None):
+        """Largest eigenvalue of A^T A (= of A A^T), what `np.max(LA.eigvals(A.T @ A))` returns in
+        gl_GD_primal.py:44 / gl_SGD_primal.py:36 -- without the dense n x n eigendecomposition: symmetric Lanczos
+        on A A^T with full re-orthogonalisation.  The two O(mn) products of a step are the stream kernels
+        (glp_tpass_prox: y = A^T u, glp_fwd: A y; partial products of a column shard are summed over `group`), the
+        O(m) vector updates run in torch on the device, the k x k tridiagonal eigenvalue problem on the host."""
+        import torch
+        lib = _lib.load()
+        m, n, l = self.m, self.n, self.l
+        dev = self.device
+        sharded = getattr(self, "world", 1) > 1
+        null = C.c_void_p()
+        U = torch.zeros((m, l), dtype=torch.float64, device=dev)
+        Y = torch.empty((n, l), dtype=torch.float64, device=dev)
+        Z = torch.empty((m, l), dtype=torch.float64, device=dev)
+
+        def apply(u):   # A A^T u through the two streams (column 0 of the l-column operands)
+            U.zero_()
+            U[:, 0] = u
+            self._order_after_caller()
+            _lib.check(lib.glp_tpass_prox(self._h, None, U.data_ptr(), Y.data_ptr(), null, null, null, null, null, null))
+            self._order_before_caller()
+            Yt = Y.to(self.dtype).contiguous()
+            self._order_after_caller()
+            _lib.check(lib.glp_fwd(self._h, Yt.data_ptr(), l, Z.data_ptr(), None))
+            self._order_before_caller()
+            w = Z[:, 0].clone()
+            if sharded:
+                import torch.distributed as dist
+                dist.all_reduce(w, group=group)
+            return w
+
+        with torch.cuda.device(dev):
+            v = torch.full((m,), 1.0 / np.sqrt(m), dtype=torch.float64, device=dev)
+            v[::2] *= 1.0 + 1e-3            # a fixed, generic start (not orthogonal to the leading eigenvector)
+            v /= v.norm()
+            V = [v]
+            alphas, betas = [], []
+            lam_prev = 0.0
+            for k in range(min(max_steps, m)):
+                w = apply(V[-1])
+                a_k = float(torch.dot(w, V[-1]))
+                alphas.append(a_k)
+                Vm = torch.stack(V, 0)
+                w = w - Vm.t() @ (Vm @ w)                 # full re-orthogonalisation (twice is enough)
+                w = w - Vm.t() @ (Vm @ w)
+                b_k = float(w.norm())
+                T = np.diag(alphas) + np.diag(betas, 1) + np.diag(betas, -1)
+                lam = float(np.linalg.eigvalsh(T)[-1])
+                if k > 0 and (abs(lam - lam_prev) <= tol * abs(lam) or b_k <= 1e-300):
+                    break
+                lam_prev = lam
+                betas.append(b_k)
+                V.append(w / b_k)
+            return lam
+
     def solve(self, algo, x0, mu_0, opts=None):
         import torch
         lib = _lib.load()
         merged = merge_opts(algo, opts)
+        if algo in ("GD", "SGD") and merged.get("continuous_subgradient_flag"):
+            merged["alpha0"] = 1.0 / self.lambda_max()       # gl_GD_primal.py:43-45 / gl_SGD_primal.py:35-37
         o = pack_opts(algo, merged)
         mode = _tensor_mode(merged)
         x0d = self._iterate(x0)

@@ -115,9 +115,9 @@ def solve_smooth(algo, x0, A, b, mu0, opts=None):
     (code/gl_FGD_primal.py:56-163, code/gl_GD_primal.py:53-112, code/gl_SGD_primal.py:47-109)."""
     o = dict(DEFAULTS[algo])
     o.update(opts or {})
-    if o.get("continuous_subgradient_flag"):
-        raise NotImplementedError("continuous_subgradient_flag (alpha0 = 1/lambda_max via eigvals) is out of scope")
     maxit, ftol, alpha0, thres, rule = o["maxit"], o["ftol"], o["alpha0"], o["thres"], o["step_type"]
+    if o.get("continuous_subgradient_flag") and algo in ("GD", "SGD"):   # gl_GD_primal.py:43-45, gl_SGD_primal.py:35-37
+        alpha0 = 1.0 / np.max(np.linalg.eigvals(A.T @ A)).real
     delta = o["delta"]
     f_hist, f_best_hist, s_hist = [], [], []
     f_best = np.inf

@@ -72,6 +72,9 @@ SMOOTH_CASES = {
     "smooth_fixed": (97006855, 256, 512, 2, "f8", {"step_type": "fixed", "alpha0": 5e-4, "maxit": 400}),
     "smooth_dim2": (97006855, 256, 512, 2, "f8", {"step_type": "diminishing2", "alpha0": 5e-4, "maxit": 1100}),
     "smooth_f32in": (97006855, 256, 512, 2, "f4", {"maxit": 200}),
+    # gl_GD_primal.py:43-45 / gl_SGD_primal.py:35-37: alpha0 = 1 / lambda_max(A^T A)
+    "smooth_csf": (97006855, 256, 512, 2, "f8", {"continuous_subgradient_flag": True, "maxit": 300}),
+    "smooth_csf_ragged": (5, 193, 391, 2, "f8", {"continuous_subgradient_flag": True, "maxit": 80, "step_type": "fixed"}),
 }
 
 

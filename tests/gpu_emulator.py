@@ -68,6 +68,9 @@ def emulate(algo, x0, A, b, mu0, opts=None, matmul=None, rmatmul=None, n_shards=
     lib = shim()
     o = dict(orc.DEFAULTS[algo])
     o.update(opts or {})
+    if algo in ("GD", "SGD") and o.get("continuous_subgradient_flag"):
+        # host prologue of GroupLassoProblem.solve: alpha0 <- 1 / lambda_max(A^T A) (= lambda_max(A A^T))
+        o["alpha0"] = 1.0 / float(np.max(np.linalg.eigvalsh(A.astype(np.float64) @ A.astype(np.float64).T)))
     fwd = matmul or (lambda X: A @ X)
     bwd = rmatmul or (lambda R: A.T @ R)
     n, l = x0.shape

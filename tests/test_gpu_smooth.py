@@ -9,7 +9,7 @@ from conftest import golden_inputs, load_golden
 from oracle import glprox_oracle as orc
 
 pytestmark = pytest.mark.gpu
-FGD_LONG = {"smooth_fixed", "smooth_dim2", "smooth_seed2", "smooth_fixture"}
+FGD_LONG = {"smooth_fixed", "smooth_dim2", "smooth_seed2", "smooth_fixture", "smooth_csf"}
 
 
 def _fn(algo):
@@ -80,3 +80,34 @@ def test_smooth_edge_cases():
         assert k == kr and out["glprox"]["backend"] == "stream"
         assert np.max(np.abs(np.asarray(out["f_hist"]) - np.asarray(outr["f_hist"])) / np.abs(outr["f_hist"])) <= 1e-10
         assert np.max(np.abs(x - xr)) <= 1e-9
+
+
+@pytest.mark.parametrize("backend", ["persistent", "stream"])
+@pytest.mark.parametrize("algo", ["GD", "SGD"])
+@pytest.mark.parametrize("name", ["smooth_csf", "smooth_csf_ragged"])
+def test_continuous_subgradient_flag_uses_lambda_max_from_the_stream_kernels(name, algo, backend):
+    """continuous_subgradient_flag (gl_GD_primal.py:43-45 / gl_SGD_primal.py:35-37): alpha0 = 1 / max eig(A^T A).
+    The reference takes a dense n x n eigendecomposition; here lambda_max comes from Lanczos on A A^T whose products
+    are the two stream kernels (GroupLassoProblem.lambda_max).  Same k, objective history within 1e-9 (the step
+    differs from NumPy's by ~1e-13 relative, and the open-loop iteration is contractive)."""
+    rec = load_golden(name)
+    A, b, x0, u, mu = golden_inputs(rec)
+    if backend == "stream" and name == "smooth_csf":
+        pytest.skip("long run once")
+    x, k, out = _fn(algo)(x0, A, b, mu, dict(rec["opts"], backend=backend))
+    assert k == int(rec[algo + "_k"])
+    fh, ref = np.asarray(out["f_hist"]), rec[algo + "_f_hist"]
+    assert np.max(np.abs(fh - ref) / np.abs(ref)) <= 1e-9
+    assert abs(out["fval"] - rec[algo + "_fval"]) <= 1e-9 * abs(rec[algo + "_fval"])
+
+
+def test_lambda_max_matches_numpy():
+    import torch
+    from glprox import GroupLassoProblem
+    for dt, tol in ((np.float64, 1e-12), (np.float32, 1e-5)):
+        A, b, x0, u, mu = orc.gen_data(4, 200, 700, 2, dt)
+        prob = GroupLassoProblem(torch.from_numpy(A).cuda(), torch.from_numpy(b).cuda())
+        lam = prob.lambda_max()
+        prob.close()
+        ref = float(np.max(np.linalg.eigvalsh(A.astype(np.float64) @ A.astype(np.float64).T)))
+        assert abs(lam - ref) <= tol * ref, (lam, ref)

@@ -8,11 +8,12 @@ from conftest import golden_inputs, load_golden
 from gpu_emulator import emulate
 from oracle import glprox_oracle as orc
 
-SMOOTH = ["smooth_maxit40", "smooth_ragged", "smooth_l3", "smooth_fixed", "smooth_dim2", "smooth_seed2"]
+SMOOTH = ["smooth_maxit40", "smooth_ragged", "smooth_l3", "smooth_fixed", "smooth_dim2", "smooth_seed2", "smooth_csf",
+          "smooth_csf_ragged"]
 # FGD (delta = 1e-6: an almost non-smooth gradient, no prox) is chaotic under ANY re-rounding of the products
 # on long runs -- NumPy with a reversed summation order moves k from 2034 to 2045 on the fixture -- so its long
 # cases are held to the final objective only; GD / SGD and short FGD runs are held to the whole trajectory.
-FGD_LONG = {"smooth_fixed", "smooth_dim2", "smooth_seed2", "smooth_fixture"}
+FGD_LONG = {"smooth_fixed", "smooth_dim2", "smooth_seed2", "smooth_fixture", "smooth_csf"}
 
 
 @pytest.mark.parametrize("algo", ["FGD", "GD", "SGD"])
@@ -51,7 +52,8 @@ def test_smooth_option_semantics():
     assert solver.merge_opts("SGD", {"maxit": 5})["maxit"] == 5 and solver.merge_opts("SGD", {})["maxit"] == 2100
     with pytest.raises(ValueError):
         solver.pack_opts("GD", solver.merge_opts("GD", {"step_type": "line_search"}))
-    with pytest.raises(NotImplementedError):
-        solver.pack_opts("SGD", solver.merge_opts("SGD", {"continuous_subgradient_flag": True}))
+    # continuous_subgradient_flag is honoured (alpha0 <- 1 / lambda_max(A^T A) by the handle before packing), not refused
+    o = solver.pack_opts("SGD", solver.merge_opts("SGD", {"continuous_subgradient_flag": True}))
+    assert o.alpha0 == 1e-3
     o = solver.pack_opts("FGD", solver.merge_opts("FGD", {}))
     assert (o.maxit, o.delta, o.line_search_attenuation_coeffi, o.maxit_line_search_iter) == (1500, 1e-6, 0.98, 5)
