@@ -16,6 +16,8 @@
 
 #include "../../include/glprox.h"
 #include "glp_admm.cuh"
+#include "glp_admm_primal.cuh"
+#include "glp_alm.cuh"
 #include "glp_comm.cuh"
 #include "glp_decide.cuh"
 #include "glp_dense.cuh"
@@ -190,6 +192,10 @@ struct glp_handle {
   glp_handle* admm_inner = nullptr;   // m x m fp64 problem over Y: K1 / K2 apply z = Y (Y^T w)
   double* admm_zero_b = nullptr;
   double* admm_gpart = nullptr;       // [ncb][ADMM_GSTRIDE] per-column-block records of the update kernel
+  // gl_Admm_primal / gl_Alm_dual (glp_admm2_host.inl): lazily sized fp64 workspaces in n-space, m-space, per column block
+  double* aux_n = nullptr;  size_t aux_n_len = 0;
+  double* aux_m = nullptr;  size_t aux_m_len = 0;
+  double* aux_rec = nullptr; size_t aux_rec_len = 0;
   void* pair_ws = nullptr;     // K5 on CTA pairs (glp_gemm_pair.cuh): arrival counters + partial-tile slots
   size_t pair_ws_bytes = 0;
   double* gemm_ws = nullptr;   // split-K partial products of K5
@@ -456,6 +462,9 @@ extern "C" int glp_destroy(glp_handle* h) {
   if (h->admm_Y) cudaFree(h->admm_Y);
   if (h->admm_zero_b) cudaFree(h->admm_zero_b);
   if (h->admm_gpart) cudaFree(h->admm_gpart);
+  if (h->aux_n) cudaFree(h->aux_n);
+  if (h->aux_m) cudaFree(h->aux_m);
+  if (h->aux_rec) cudaFree(h->aux_rec);
   if (h->nccl_stage) cudaFree(h->nccl_stage);
   for (__half* q : {h->A_f0, h->A_f1, h->At_f0, h->At_f1, h->xop_f0, h->xop_f1, h->r_f0, h->r_f1})
     if (q) cudaFree(q);
@@ -1351,6 +1360,7 @@ extern "C" int glp_debug_read(glp_handle* h, int which, double* out_host) {
 #include "glp_host_io.inl"
 #include "glp_gemm_host.inl"
 #include "glp_admm_host.inl"
+#include "glp_admm2_host.inl"
 
 #include "glp_metrics_host.inl"
 

@@ -6,7 +6,7 @@ same two streams of A as the proximal solvers.
     x, iter, out = gl_Admm_dual(x0, A, b, mu, opts)
 
 `opts` keys and defaults are the reference's (maxit 100, thres 1e-3, tau (1+sqrt 5)/2, rho 1e2, converge_len 20);
-unknown keys are ignored.  Scope of this build: m <= 2048, l <= 2, one GPU.
+unknown keys are ignored.  Scope of this build: l <= 8, one GPU (m > 2048 takes the blocked factorisation).
 """
 from glprox.solver import solve_admm_dual as _solve
 

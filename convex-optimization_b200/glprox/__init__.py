@@ -6,7 +6,8 @@ fails loudly if it is missing.
 """
 from . import _lib, dataset  # noqa: F401
 from .solver import (DEFAULT_OPTS, GroupLassoProblem, attach_distributed, combine_metrics,  # noqa: F401
-                     exchange_handles, merge_opts, shard_bounds, solve, solve_admm_dual, solve_group)
+                     exchange_handles, merge_opts, shard_bounds, solve, solve_admm_dual, solve_admm_primal, solve_alm_dual,
+                     solve_group)
 
 __all__ = ["solve", "GroupLassoProblem", "DEFAULT_OPTS", "merge_opts", "shard_bounds", "exchange_handles",
-           "attach_distributed", "solve_group", "combine_metrics", "dataset", "solve_admm_dual"]
+           "attach_distributed", "solve_group", "combine_metrics", "dataset", "solve_admm_dual", "solve_admm_primal", "solve_alm_dual"]

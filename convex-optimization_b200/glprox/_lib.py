@@ -49,6 +49,11 @@ class GlpAdmmOpts(C.Structure):
                 ("rho", C.c_double)]
 
 
+class GlpAdmmPrimalOpts(C.Structure):
+    _fields_ = [("maxit", C.c_int32), ("converge_len", C.c_int32), ("step_type", C.c_int32), ("pad", C.c_int32),
+                ("thres", C.c_double), ("tau", C.c_double), ("rho", C.c_double), ("eta_0", C.c_double)]
+
+
 class GlpMetrics(C.Structure):
     _fields_ = [(k, C.c_double) for k in ("sumsq_x", "sumsq_ref", "sumsq_diff", "reg", "max_abs", "count", "rr",
                                           "objective", "sparsity", "err_exact", "err_ref")]
@@ -94,6 +99,9 @@ SIGNATURES = {
     "glp_comm_attach_nccl": (_I, [_VP, _VP, _I, _I, _I64]),
     "glp_admm_default_opts": (_I, [C.POINTER(GlpAdmmOpts)]),
     "glp_admm_dual": (_I, [_VP, _VP, _D, C.POINTER(GlpAdmmOpts), _VP, C.POINTER(GlpResult), _VP, _I]),
+    "glp_admm_primal_default_opts": (_I, [C.POINTER(GlpAdmmPrimalOpts)]),
+    "glp_admm_primal": (_I, [_VP, _VP, _D, C.POINTER(GlpAdmmPrimalOpts), _VP, C.POINTER(GlpResult), _VP, _I]),
+    "glp_alm_dual": (_I, [_VP, _VP, _D, C.POINTER(GlpAdmmOpts), _VP, C.POINTER(GlpResult), _VP, _I]),
     "glp_metrics_eval": (_I, [_VP, _VP, _VP, _D, _D, C.POINTER(GlpMetrics)]),
     "glp_randn": (_I, [_VP, _I, _I64, _I64, _I64, C.c_uint64, _I64, _I64, _VP]),
     "glp_rhs_exact": (_I, [_VP, _I, _I64, _I64, _VP, _I, _VP, _I64, _VP, _VP]),

@@ -36,6 +36,9 @@ DEFAULT_OPTS.update({
 })
 # gl_ADMM_dual.py:11-17
 ADMM_DUAL_DEFAULT_OPTS = {"maxit": 100, "thres": 1e-3, "tau": (1 + 5 ** 0.5) * 0.5, "rho": 1e2, "converge_len": 20}
+ADMM_PRIMAL_DEFAULT_OPTS = {"maxit": 100, "thres": 1e-3, "tau": (1 + 5 ** 0.5) * 0.5, "rho": 1e-2, "eta_0": 100,
+                            "converge_len": 10, "converge_thres": 1e-5, "step_type": "fixed"}   # gl_ADMM_primal.py:11-20
+ALM_DUAL_DEFAULT_OPTS = dict(ADMM_DUAL_DEFAULT_OPTS)                                            # gl_ALM_dual.py:67-73
 ALGO_ID = {"ProxGD": _lib.GLP_PROXGD, "FProxGD": _lib.GLP_FPROXGD, "FGD": _lib.GLP_FGD, "GD": _lib.GLP_GD,
            "SGD": _lib.GLP_SGD}
 # additive keys (not in the reference): dtype 'fp32'|'fp64', backend 'auto'|'stream'|'persistent',
@@ -509,6 +512,59 @@ class GroupLassoProblem:
         return x, int(res.iters), _format_out(res, f_hist[:res.iters], tt)
 
 
+    def _fp64_twin(self):
+        """gl_Admm_primal / gl_Alm_dual compute in fp64 (their m x m forms cancel ~1e5 of the leading digits): an
+        fp32 problem is widened into a temporary fp64 one for the call."""
+        import torch
+        if self.dtype == torch.float64:
+            return self, False
+        if getattr(self, "world", 1) > 1:
+            raise ValueError("gl_Admm_primal / gl_Alm_dual run on one GPU")
+        return GroupLassoProblem(self.A.double(), self.b.double()), True
+
+    def _solve_admm2(self, which, x0, mu, o, cap):
+        import torch
+        lib = _lib.load()
+        prob, temp = self._fp64_twin()
+        try:
+            x0d = prob._iterate(x0.double() if isinstance(x0, torch.Tensor) else x0)
+            x = torch.empty_like(x0d)
+            f_hist = np.empty(cap, dtype=np.float64)
+            res = _lib.GlpResult()
+            t0 = time.perf_counter()
+            with torch.cuda.device(prob.device):
+                prob._order_after_caller()
+                fn = lib.glp_admm_primal if which == "ADMM_primal" else lib.glp_alm_dual
+                rc = fn(prob._h, x0d.data_ptr(), float(mu), C.byref(o), x.data_ptr(), C.byref(res), f_hist.ctypes.data, cap)
+                _raise_for(rc, res)
+            tt = time.perf_counter() - t0
+        finally:
+            if temp:
+                prob.close()
+        return x.to(self.dtype), int(res.iters), _format_out(res, f_hist[:res.iters], tt)
+
+    def solve_admm_primal(self, x0, mu, opts=None):
+        """gl_Admm_primal (code/gl_ADMM_primal.py) on this problem; x0 a CUDA tensor, returns (x, k, out)."""
+        merged = dict(ADMM_PRIMAL_DEFAULT_OPTS)
+        merged.update(opts or {})
+        steps = {k: _lib.STEP_TYPES[k] for k in ("fixed", "diminishing", "diminishing2")}
+        if merged["step_type"] not in steps:
+            # the reference's set_step returns None for any other name and the next line raises TypeError (:66-80)
+            raise TypeError("unsupported operand type(s) for *: 'NoneType' and 'float' (step_type %r)" % (merged["step_type"],))
+        o = _lib.GlpAdmmPrimalOpts(maxit=int(merged["maxit"]), converge_len=int(merged["converge_len"]),
+                                   step_type=steps[merged["step_type"]], pad=0, thres=float(merged["thres"]),
+                                   tau=float(merged["tau"]), rho=float(merged["rho"]), eta_0=float(merged["eta_0"]))
+        return self._solve_admm2("ADMM_primal", x0, mu, o, int(o.maxit) + 8)
+
+    def solve_alm_dual(self, x0, mu, opts=None):
+        """gl_Alm_dual (code/gl_ALM_dual.py) on this problem; x0 a CUDA tensor, returns (x, k, out)."""
+        merged = dict(ALM_DUAL_DEFAULT_OPTS)
+        merged.update(opts or {})
+        o = _lib.GlpAdmmOpts(maxit=int(merged["maxit"]), converge_len=int(merged["converge_len"]),
+                             thres=float(merged["thres"]), tau=float(merged["tau"]), rho=float(merged["rho"]))
+        return self._solve_admm2("ALM_dual", x0, mu, o, int(o.maxit) + 8)
+
+
 def combine_metrics(sums, max_abs, rr, mu, has_ref):
     """Finish the metrics from (sumsq_x, sumsq_ref, sumsq_diff, reg, count, size) totals."""
     sx, sr, sd, reg, cnt, size = sums
@@ -551,6 +607,47 @@ def solve_admm_dual(x0, A, b, mu, opts):
         prob.close()
     out["tt"] = time.perf_counter() - t0
     return xh, k, out
+
+
+def _solve_fp64_dropin(method, defaults, x0, A, b, mu, opts):
+    """Drop-in body shared by gl_Admm_primal and gl_Alm_dual: NumPy arrays (uploaded as fp64 for the call) or CUDA
+    tensors; the result comes back in the dtype of A."""
+    merged = dict(defaults)
+    merged.update(opts or {})
+    import torch
+    if isinstance(A, torch.Tensor):
+        if not A.is_cuda:
+            raise ValueError("torch tensors must live on a CUDA device (NumPy arrays take the host path)")
+        prob = GroupLassoProblem(A, b)
+        try:
+            return getattr(prob, method)(x0, mu, merged)
+        finally:
+            prob.close()
+    A = np.asarray(A)
+    x0, b = np.asarray(x0), np.asarray(b)
+    if A.ndim != 2 or x0.ndim != 2 or b.ndim != 2 or x0.shape[0] != A.shape[1] or b.shape[0] != A.shape[0] or x0.shape[1] != b.shape[1]:
+        raise ValueError("shape mismatch: A %s, x0 %s, b %s" % (A.shape, x0.shape, b.shape))
+    dev = torch.device("cuda", int(merged.get("device", 0)))
+    t0 = time.perf_counter()
+    to = lambda z: torch.from_numpy(np.ascontiguousarray(z, dtype=np.float64)).to(dev)
+    prob = GroupLassoProblem(to(A), to(b))
+    try:
+        x, k, out = getattr(prob, method)(to(x0), mu, merged)
+        xh = x.cpu().numpy().astype(A.dtype if A.dtype in (np.float32, np.float64) else np.float64, copy=False)
+    finally:
+        prob.close()
+    out["tt"] = time.perf_counter() - t0
+    return xh, k, out
+
+
+def solve_admm_primal(x0, A, b, mu, opts):
+    """Drop-in body of gl_Admm_primal (code/gl_ADMM_primal.py:10)."""
+    return _solve_fp64_dropin("solve_admm_primal", ADMM_PRIMAL_DEFAULT_OPTS, x0, A, b, mu, opts)
+
+
+def solve_alm_dual(x0, A, b, mu, opts):
+    """Drop-in body of gl_Alm_dual (code/gl_ALM_dual.py:66)."""
+    return _solve_fp64_dropin("solve_alm_dual", ALM_DUAL_DEFAULT_OPTS, x0, A, b, mu, opts)
 
 
 def shard_bounds(n, world, align=128):

@@ -31,7 +31,9 @@ SOLVERS = {  # name -> (row label of doc/report.md:439-447, algo key)
     "FGD": ("FGD Primal", "FGD"),
     "ProxGD": ("ProxGD Primal", "ProxGD"),
     "FProxGD": ("FProxGD Primal", "FProxGD"),
-    "ADMM_dual": ("ADMM Dual", "ADMM_dual"),   # doc/report.md:571 (m <= 2048, l <= 2)
+    "ALM_dual": ("ALM Dual", "ALM_dual"),         # doc/report.md:570
+    "ADMM_dual": ("ADMM Dual", "ADMM_dual"),      # doc/report.md:571
+    "ADMM_primal": ("ADMM Primal", "ADMM_primal"),   # doc/report.md:572
 }
 HEADERS = ["solver", "cpu", "iter", "optval", "sparsity", "err-to-exact", "err-to-best"]
 
@@ -132,8 +134,9 @@ def main(argv=None):
         if key not in SOLVERS:
             raise SystemExit("unknown solver %r (choose from %s)" % (key, ", ".join(SOLVERS)))
         label, algo = SOLVERS[key]
-        if algo == "ADMM_dual":
-            x, iters, out = prob.solve_admm_dual(x0, mu, {"maxit": args.maxit} if args.maxit else {})
+        if algo in ("ADMM_dual", "ADMM_primal", "ALM_dual"):
+            fn = {"ADMM_dual": prob.solve_admm_dual, "ADMM_primal": prob.solve_admm_primal, "ALM_dual": prob.solve_alm_dual}[algo]
+            x, iters, out = fn(x0, mu, {"maxit": args.maxit} if args.maxit else {})
         else:
             x, iters, out = prob.solve(algo, x0, mu, opts)      # x stays in HBM
         met = prob.metrics(x, u, mu)

@@ -280,6 +280,40 @@ int glp_admm_default_opts(glp_admm_opts* out);
 int glp_admm_dual(glp_handle* h, const void* x0_dev, double mu, const glp_admm_opts* opts, void* x_out_dev,
                   glp_result* res, double* f_hist_host, int hist_cap);
 
+/* ---- gl_Admm_primal (code/gl_ADMM_primal.py:10-117; registered in code/main.py:181) --------------
+ * Linearised ADMM on  min 0.5||A y - b||^2 + mu sum ||x_i||  s.t. x = y.  The reference factors the n x n matrix
+ * rho I + A^T A (:62) and solves with it every iteration (:78).  Here the solve goes through the m x m matrix
+ * G = I + A A^T / rho:  (rho I + A^T A)^-1 v = (v - A^T G^-1 A v / rho) / rho, so that an iteration is one forward
+ * stream of A over [x | v], G^-1 as two streams of the inverse Cholesky factor (the blocked set-up of glp_admm_dual),
+ * one transposed stream and a row-local prox / multiplier kernel (csrc/glp_admm_primal.cuh).  Objective history,
+ * residual 2-norms and the converge_len stop rule (:98-107) on the device.  converge_thres (:18) is read by the
+ * reference but never used; it has no field here.  Scope: fp64 handles (the identity cancels ~cond(rho I + A^T A) of
+ * the leading digits), l <= 8, one GPU.  res / f_hist_host as for glp_admm_dual. */
+typedef struct glp_admm_primal_opts {
+  int32_t maxit;
+  int32_t converge_len;
+  int32_t step_type;        /* GLP_STEP_FIXED (eta_0), GLP_STEP_DIMINISHING (eta_0 / sqrt k), GLP_STEP_DIMINISHING2 (eta_0 / k) :66-72 */
+  int32_t pad;
+  double thres;
+  double tau;
+  double rho;
+  double eta_0;
+} glp_admm_primal_opts;
+int glp_admm_primal_default_opts(glp_admm_primal_opts* out);
+int glp_admm_primal(glp_handle* h, const void* x0_dev, double mu, const glp_admm_primal_opts* opts, void* x_out_dev,
+                    glp_result* res, double* f_hist_host, int hist_cap);
+
+/* ---- gl_Alm_dual (code/gl_ALM_dual.py:66-158; registered in code/main.py:179) ---------------------
+ * Augmented Lagrangian method on the dual: every outer iteration solves for u by 500 accelerated projected-gradient
+ * steps (solve_sub_problem, :10-63), then z, the multiplier step and the shared stop rule (:123-147).  The reference
+ * forms the n x n matrices Q and G of the inner problem explicitly (:33-40); here Q = rho (I - rho A^T T A) and
+ * J = rho (A^T T (A x - b) - x / rho), T = (I + rho A A^T)^-1, are applied as streams (csrc/glp_alm.cuh), so one inner
+ * step is one forward stream, T as two streams of the inverse Cholesky factor, one transposed stream and a row-local
+ * projection kernel.  Options and defaults are glp_admm_opts / glp_admm_default_opts (the reference's two solvers
+ * share them, gl_ALM_dual.py:67-73 == gl_ADMM_dual.py:11-17).  Scope: fp64 handles, l <= 8, one GPU. */
+int glp_alm_dual(glp_handle* h, const void* x0_dev, double mu, const glp_admm_opts* opts, void* x_out_dev,
+                 glp_result* res, double* f_hist_host, int hist_cap);
+
 /* ---- caller-side metrics of the reference driver, evaluated on the device ----------------------
  * Replaces, for an iterate that stays in HBM, the host lambdas of code/main.py:48-50 and obj_func
  * (code/main.py:30-34); these are the columns of the per-solver log line / Markdown row

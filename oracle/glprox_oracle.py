@@ -226,6 +226,135 @@ def solve_admm_dual(x0, A, b, mu, opts=None):
     return x_k, k, {"tt": tt, "fval": objective(A, b, x_k, mu), "f_hist": f_hist, "f_hist_best": f_best_hist}
 
 
+ADMM_PRIMAL_DEFAULTS = dict(maxit=100, thres=1e-3, tau=(1 + math.sqrt(5)) * 0.5, rho=1e-2, eta_0=100, converge_len=10,
+                            converge_thres=1e-5, step_type="fixed")
+
+
+class _ResidualStop:
+    """The stop rule the three ADMM / ALM solvers share (gl_ADMM_primal.py:98-107, gl_ADMM_dual.py:87-99,
+    gl_ALM_dual.py:137-147): converge_len consecutive iterations whose residual 2-norms are both below thres."""
+
+    def __init__(self, thres, converge_len):
+        self.thres, self.cap, self.run = thres, converge_len, 0
+
+    def __call__(self, r_k, s_k):
+        small = np.linalg.norm(r_k, ord=2) < self.thres and np.linalg.norm(s_k, ord=2) < self.thres
+        self.run = self.run + 1 if small else 0
+        return self.run >= self.cap
+
+
+def solve_admm_primal(x0, A, b, mu, opts=None):
+    """Reference-structured restatement of gl_Admm_primal (code/gl_ADMM_primal.py:10-117): linearised ADMM on
+    min 0.5||A y - b||^2 + mu sum ||x_i||  s.t. x = y.  Once: Cholesky factor of rho I + A^T A (:62), A^T b (:63).
+    Per iteration (:75-107): y solves (rho I + A^T A) y = A^T b - z + rho x through two dense solves with the factor
+    (:78); x is one prox-gradient step of length eta on the augmented term (:80, prox_tf :47-51 with the guarded
+    denominator); z the multiplier step (:81); residuals r = x - y, s = y - y_prev (:83-84).  Note y_0 = z_0 = x0
+    (:53-55).  converge_thres is read but never used (:41)."""
+    o = dict(ADMM_PRIMAL_DEFAULTS)
+    o.update(opts or {})
+    maxit, thres, rho, tau, eta_0 = o["maxit"], o["thres"], o["rho"], o["tau"], o["eta_0"]
+    step_type = o["step_type"]
+    stop = _ResidualStop(thres, o["converge_len"])
+    f_hist, f_best_hist = [], []
+    f_best = np.inf
+    x_k = np.copy(x0)
+    y_k = x_k
+    z_k = x_k
+    t_begin = time.time_ns()
+    L = np.linalg.cholesky(rho * np.identity(A.shape[1]) + A.T @ A)
+    AT_b = A.T @ b
+    k = 0
+    while k < maxit:
+        k += 1
+        if step_type == "fixed":
+            eta = eta_0
+        elif step_type == "diminishing":
+            eta = eta_0 / np.sqrt(k)
+        elif step_type == "diminishing2":
+            eta = eta_0 / k
+        else:
+            eta = None      # the reference's set_step falls through; the next line then raises TypeError
+        y = np.linalg.solve(L.T, np.linalg.solve(L, AT_b - z_k + rho * x_k))
+        w = x_k - eta * rho * (x_k - y - z_k / rho)
+        rn = np.linalg.norm(w, axis=1).reshape(-1, 1)
+        x = w * np.clip(rn - eta * mu, a_min=0, a_max=None) / ((rn < thres) + rn)
+        z = z_k - tau * rho * (x - y)
+        r_k = x - y
+        s_k = y - y_k
+        x_k, y_k, z_k = x, y, z
+        f_now = objective(A, b, x_k, mu)
+        f_hist.append(f_now)
+        f_best = min(f_best, f_now)
+        f_best_hist.append(f_best)
+        if stop(r_k, s_k):
+            break
+    tt = _round_us(time.time_ns() - t_begin) / 1e6
+    return x_k, k, {"tt": tt, "fval": objective(A, b, x_k, mu), "f_hist": f_hist, "f_hist_best": f_best_hist}
+
+
+ALM_DUAL_DEFAULTS = dict(maxit=100, thres=1e-3, tau=(1 + math.sqrt(5)) * 0.5, rho=1e2, converge_len=20)
+ALM_INNER_STEPS = 500     # gl_ALM_dual.py:50
+ALM_INNER_T = 1e-2        # gl_ALM_dual.py:54
+
+
+def _alm_subproblem(b, rho, A, x_k, L, mu):
+    """gl_ALM_dual.py:10-63: min over u in the row-wise mu-ball of the augmented Lagrangian with z eliminated -- a
+    quadratic with the dense n x n Hessian Q and linear term J the reference forms explicitly (:33-40) -- by 500
+    accelerated projected-gradient steps from u = 0 (gamma = 2/(k+1), fixed step 1e-2)."""
+    T = np.linalg.solve(L.T, np.linalg.solve(L, np.identity(L.shape[0])))
+    D = A @ x_k - b
+    E = T @ D
+    F = rho * T @ A
+    G = np.identity(F.shape[1]) - A.T @ F
+    H = A.T @ E - x_k / rho
+    Q = F.T @ F + rho * G.T @ G
+    J = rho * G.T @ H - F.T @ E - F.T @ b
+    u_k = np.zeros_like(x_k)
+    v_k = u_k
+    for k in range(1, ALM_INNER_STEPS + 1):
+        gamma = 2 / (k + 1)
+        y = (1 - gamma) * u_k + gamma * v_k
+        w = y - ALM_INNER_T * (Q @ y + J)
+        u = mu * w / np.clip(np.linalg.norm(w, axis=1, ord=2).reshape(-1, 1), a_min=mu, a_max=None)
+        v = u_k + (u - u_k) / gamma
+        u_k, v_k = u, v
+    return u_k
+
+
+def solve_alm_dual(x0, A, b, mu, opts=None):
+    """Reference-structured restatement of gl_Alm_dual (code/gl_ALM_dual.py:66-158): augmented Lagrangian method on
+    the dual.  Once: Cholesky factor of I + rho A A^T (:114).  Per outer iteration (:119-147): u from the inner
+    solver above (:122), z from the factor (:123), multiplier step x (:124), residuals r = u + A^T z,
+    s = A(u_prev - u) (:126-127), the shared stop rule."""
+    o = dict(ALM_DUAL_DEFAULTS)
+    o.update(opts or {})
+    maxit, thres, rho, tau = o["maxit"], o["thres"], o["rho"], o["tau"]
+    stop = _ResidualStop(thres, o["converge_len"])
+    f_hist, f_best_hist = [], []
+    f_best = np.inf
+    x_k = np.copy(x0)
+    u_k = np.zeros_like(x_k)
+    t_begin = time.time_ns()
+    L = np.linalg.cholesky(np.identity(A.shape[0]) + rho * A @ A.T)
+    k = 0
+    while k < maxit:
+        k += 1
+        u = _alm_subproblem(b, rho, A, x_k, L, mu)
+        z = np.linalg.solve(L.T, np.linalg.solve(L, A @ (x_k - rho * u) - b))
+        x = x_k - tau * rho * (u + A.T @ z)
+        r_k = u + A.T @ z
+        s_k = A @ (u_k - u)
+        u_k, x_k = u, x
+        f_now = objective(A, b, x_k, mu)
+        f_hist.append(f_now)
+        f_best = min(f_best, f_now)
+        f_best_hist.append(f_best)
+        if stop(r_k, s_k):
+            break
+    tt = _round_us(time.time_ns() - t_begin) / 1e6
+    return x_k, k, {"tt": tt, "fval": objective(A, b, x_k, mu), "f_hist": f_hist, "f_hist_best": f_best_hist}
+
+
 def _open_loop_step(step_type, alpha0, inner):
     """Non-adaptive step rules, gl_ProxGD_primal.py:79-85 / gl_FProxGD_primal.py:82-88."""
     it_hat = max(inner, 1000) - 999

@@ -20,6 +20,8 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, "/root/reference/code")
 
 from gl_ADMM_dual import gl_Admm_dual  # noqa: E402  (reference)
+from gl_ADMM_primal import gl_Admm_primal  # noqa: E402  (reference)
+from gl_ALM_dual import gl_Alm_dual  # noqa: E402  (reference)
 from gl_FGD_primal import gl_FGD_primal  # noqa: E402  (reference)
 from gl_FProxGD_primal import gl_FProxGD_primal  # noqa: E402  (reference)
 from gl_GD_primal import gl_GD_primal  # noqa: E402  (reference)
@@ -92,8 +94,40 @@ ADMM_CASES = {
 }
 REF_ADMM = {"ADMM_dual": gl_Admm_dual}
 
+# gl_Admm_primal (code/gl_ADMM_primal.py) and gl_Alm_dual (code/gl_ALM_dual.py): the two remaining solvers of the
+# reference's registry (code/main.py:165-183)
+ADMMP_CASES = {
+    "admmp_fixture": (97006855, 256, 512, 2, "f8", {}),
+    "admmp_seed1": (1, 256, 512, 2, "f8", {}),
+    "admmp_maxit7": (97006855, 256, 512, 2, "f8", {"maxit": 7}),
+    "admmp_ragged": (5, 193, 391, 2, "f8", {}),
+    "admmp_l1": (6, 128, 300, 1, "f8", {}),
+    "admmp_l3": (8, 96, 260, 3, "f8", {}),
+    "admmp_dimin": (97006855, 256, 512, 2, "f8", {"step_type": "diminishing", "maxit": 60}),
+    "admmp_dimin2": (2, 256, 512, 2, "f8", {"step_type": "diminishing2", "maxit": 40}),
+    "admmp_rho1": (3, 96, 300, 2, "f8", {"rho": 1.0, "eta_0": 1.0, "tau": 1.0, "thres": 1e-2, "converge_len": 3, "maxit": 200}),
+    "admmp_f32in": (97006855, 256, 512, 2, "f4", {}),
+}
+REF_ADMMP = {"ADMM_primal": gl_Admm_primal}
+ALM_CASES = {
+    "alm_fixture": (97006855, 256, 512, 2, "f8", {}),
+    "alm_maxit3": (1, 256, 512, 2, "f8", {"maxit": 3}),
+    "alm_ragged": (5, 193, 391, 2, "f8", {"maxit": 8}),
+    "alm_l1": (6, 128, 300, 1, "f8", {"maxit": 6}),
+    "alm_l3": (8, 96, 260, 3, "f8", {"maxit": 6}),
+    "alm_loose": (3, 96, 300, 2, "f8", {"thres": 1e-1, "converge_len": 3, "rho": 10.0, "tau": 1.0}),
+    "alm_f32in": (97006855, 256, 512, 2, "f4", {"maxit": 5}),
+}
+REF_ALM = {"ALM_dual": gl_Alm_dual}
+
 
 def run_case(name):
+    if name in ADMMP_CASES:
+        seed, m, n, l, dt, opts = ADMMP_CASES[name]
+        return _run(name, seed, m, n, l, dt, opts, REF_ADMMP)
+    if name in ALM_CASES:
+        seed, m, n, l, dt, opts = ALM_CASES[name]
+        return _run(name, seed, m, n, l, dt, opts, REF_ALM)
     if name in ADMM_CASES:
         seed, m, n, l, dt, opts = ADMM_CASES[name]
         return _run(name, seed, m, n, l, dt, opts, REF_ADMM)
@@ -131,6 +165,6 @@ def _run(name, seed, m, n, l, dt, opts, algos):
 
 
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(CASES) + list(SMOOTH_CASES) + list(ADMM_CASES)
+    names = sys.argv[1:] or list(CASES) + list(SMOOTH_CASES) + list(ADMM_CASES) + list(ADMMP_CASES) + list(ALM_CASES)
     for nm in names:
         np.savez_compressed(os.path.join(HERE, "ref_%s.npz" % nm), **run_case(nm))
