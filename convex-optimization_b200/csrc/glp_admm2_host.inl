@@ -221,7 +221,6 @@ extern "C" int glp_alm_dual(glp_handle* h, const void* x0_dev, double mu, const 
   double* Av = h->aux_m + 2 * lm;
   double* Au_prev = h->aux_m + 3 * lm;
   CU_TRY(to_planar(h->stream, static_cast<const double*>(x0_dev), x, g.n, g.l, g.ldn));
-  CU_TRY(cudaMemcpyAsync(xop, x, size_t(ln) * 8, cudaMemcpyDeviceToDevice, h->stream));
   GLP_TRY(admm2_ctrl_init(h));
   h->solving = true;
   const int m_grid = int(std::max<int64_t>(1, std::min<int64_t>((lm + ALM_THREADS - 1) / ALM_THREADS, int64_t(h->num_sms) * 4)));
@@ -246,6 +245,7 @@ extern "C" int glp_alm_dual(glp_handle* h, const void* x0_dev, double mu, const 
   const double* xc[2] = {x, x};
   double* rdst = static_cast<double*>(h->r);
   auto body = [&]() -> int {
+    CU_TRY(launch_n(&h->ctrl[0], 3, 0));
     int64_t slots = 0;
     bool done = false;
     while (!done && slots < int64_t(o->maxit) + 2) {

@@ -187,6 +187,7 @@ __global__ void __launch_bounds__(ALM_THREADS) glp_alm_m_kernel(const AlmMArgs a
 // mode 1: inner step kk: y = (1 - gamma) u + gamma v ; w = y - t (rho (y - rho grad) + J) ; u' = P_mu(w) ;
 //         v = u + (u' - u) / gamma ; operand <- u'   (:53-60; grad = A^T T A y, taken as 0 for kk = 1 where y = 0)
 // mode 2: outer step: r = u + grad (grad = A^T z) ; x <- x - tau rho r ; operand <- x ; per-block record
+// mode 3: before the first outer iteration: operand <- x0 and the per-block record of x0 (objective / sparsity of k = 0)
 struct AlmNArgs {
   const Ctrl* ctrl;
   int32_t mode, kk;
@@ -247,7 +248,7 @@ __global__ void glp_alm_n_kernel(const AlmNArgs a, const Geom g) {
     }
     return;
   }
-  // mode 2
+  // modes 2 and 3
   double gr[ADMM_NPAIR], reg = 0.0, mx = 0.0;
 #pragma unroll
   for (int q = 0; q < ADMM_NPAIR; ++q) gr[q] = 0.0;
@@ -258,8 +259,11 @@ __global__ void glp_alm_n_kernel(const AlmNArgs a, const Geom g) {
     for (int c = 0; c < ADMM_MAX_L; ++c) {
       rr[c] = 0.0;
       if (c >= l) continue;
-      rr[c] = xadd(a.u[c * ldn + j], __ldcg(&a.grad[c * ldn + j]));          // r_k = u + A.T @ z            :126
-      const double xn = xsub(a.x[c * ldn + j], xmul(taurho, rr[c]));         // x_k - tau * rho * (u + A.T @ z)  :124
+      double xn = a.x[c * ldn + j];
+      if (a.mode == 2) {
+        rr[c] = xadd(a.u[c * ldn + j], __ldcg(&a.grad[c * ldn + j]));        // r_k = u + A.T @ z            :126
+        xn = xsub(xn, xmul(taurho, rr[c]));                                  // x_k - tau * rho * (u + A.T @ z)  :124
+      }
       a.x[c * ldn + j] = xn;
       a.xop[c * ldn + j] = xn;
       n2 = xadd(n2, xmul(xn, xn));

@@ -27,7 +27,7 @@ def _check(rec, algo, x, k, out, tol_f, tol_x):
     assert fh.shape == ref.shape and np.max(np.abs(fh - ref) / np.abs(ref)) <= tol_f
     assert np.array_equal(np.asarray(out["f_hist_best"]), np.minimum.accumulate(fh))
     assert abs(out["fval"] - rec[algo + "_fval"]) <= tol_f * abs(rec[algo + "_fval"])
-    assert np.max(np.abs(x - rec[algo + "_x"])) <= tol_x
+    assert np.max(np.abs(x - rec[algo + "_x"])) <= tol_x * max(1.0, np.max(np.abs(rec[algo + "_x"])))
     ax = np.abs(x)
     assert np.array_equal(np.flatnonzero((ax > 1e-6 * ax.max()).any(axis=1)), rec[algo + "_support_rule"])
     assert abs(out["glprox"]["sparsity"] - float(rec[algo + "_sparsity"])) <= 1e-12
