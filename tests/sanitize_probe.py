@@ -63,6 +63,12 @@ def main():
                 prob.close()
                 print("admm blocked=" + blocked, dt.__name__, k, float(out["fval"]), flush=True)
         os.environ.pop("GLPROX_ADMM_BLOCKED", None)
+        prob = GroupLassoProblem(torch.from_numpy(A).cuda(), torch.from_numpy(b).cuda())
+        x, k, out = prob.solve_admm_primal(torch.from_numpy(x0).cuda(), mu, {"maxit": 5})
+        print("admm primal", k, float(out["fval"]), flush=True)
+        x, k, out = prob.solve_alm_dual(torch.from_numpy(x0).cuda(), mu, {"maxit": 1})
+        print("alm dual", k, float(out["fval"]), flush=True)
+        prob.close()
     torch.cuda.synchronize()
     print("SANITIZE_PROBE_DONE", flush=True)
 
