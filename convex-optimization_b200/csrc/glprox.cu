@@ -4,6 +4,7 @@
 // sm_100 device every entry point that computes returns GLP_ERR_NO_DEVICE.
 #include <cuda.h>
 #include <cuda_runtime.h>
+#include <mutex>
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
@@ -1371,3 +1372,6 @@ extern "C" int glp_debug_read(glp_handle* h, int which, double* out_host) {
 #include "glp_nccl.inl"
 
 #include "glp_abi_step.inl"
+
+// allocation-free metric reductions (fixed device scratch; no counterpart in the reference)
+#include "glp_noalloc.inl"

@@ -103,6 +103,7 @@ SIGNATURES = {
     "glp_admm_primal": (_I, [_VP, _VP, _D, C.POINTER(GlpAdmmPrimalOpts), _VP, C.POINTER(GlpResult), _VP, _I]),
     "glp_alm_dual": (_I, [_VP, _VP, _D, C.POINTER(GlpAdmmOpts), _VP, C.POINTER(GlpResult), _VP, _I]),
     "glp_metrics_eval": (_I, [_VP, _VP, _VP, _D, _D, C.POINTER(GlpMetrics)]),
+    "glp_metrics_sums_noalloc": (_I, [_I, _VP, _I, _VP, _VP, _I64, _I, _D, _VP]),
     "glp_randn": (_I, [_VP, _I, _I64, _I64, _I64, C.c_uint64, _I64, _I64, _VP]),
     "glp_rhs_exact": (_I, [_VP, _I, _I64, _I64, _VP, _I, _VP, _I64, _VP, _VP]),
     "glp_decide": (_I, [_I, _VP, _VP, _VP, _D, _VP, _VP, _VP, _I]),

@@ -339,6 +339,28 @@ typedef struct glp_metrics {
 int glp_metrics_eval(glp_handle* h, const void* x_dev, const void* ref_dev, double mu,
                      double max_abs_override, glp_metrics* out);
 
+/* ---- allocation-free variant of the metric reductions -------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  glp_metrics_eval
+ * allocates and frees its per-CTA records on every call; this entry point runs the same three reduction kernels with
+ * the records in a file-scope `static __device__` array of the library (37,888 bytes; every GPU that loads the
+ * library holds it until exit).  It calls no cudaMalloc / cudaFree / allocating library routine, takes no handle,
+ * does not synchronise and copies nothing to the host.
+ *   x_dev / ref_dev : n x l row-major arrays of `dtype` on `device` (ref_dev may be NULL: sumsq_ref = sumsq_diff = 0)
+ *   out6_dev        : 6 doubles on `device`, written on `stream`:
+ *                     { sumsq_x, sumsq_ref, sumsq_diff, reg = sum_i ||x(i,:)||_2, max|x|, #{|x| > 1e-6 max} }
+ *                     -- bit-identical to the same fields of glp_metrics_eval (same grid, same summation order);
+ *                     sparsity = out[5] / (n l), err_exact = sqrt(out[2]) / (1 + sqrt(out[0])) (code/main.py:48-50)
+ *   max_abs_override: >= 0 to count against a cross-rank max, < 0 to use this array's own max
+ * Limits: n <= GLP_NOALLOC_MAX_ROWS, l <= GLP_NOALLOC_MAX_L; larger inputs are refused with GLP_ERR_ARG (use
+ * glp_metrics_eval).  All calls on a device share the one array, which keeps the previous call's contents (the
+ * records a call uses are cleared first, on `stream`): calls that overlap on the same GPU -- two streams, two
+ * threads -- RACE and must be ordered by the caller. */
+#define GLP_NOALLOC_MAX_ROWS ((int64_t)1 << 24)   /* 16,777,216 row groups */
+#define GLP_NOALLOC_MAX_L 128
+int glp_metrics_sums_noalloc(int device, void* stream, int dtype, const void* x_dev, const void* ref_dev, int64_t n,
+                             int l, double max_abs_override, double* out6_dev);
+
 /* ---- synthetic data: counter-based N(0,1) generator (bench / large fixtures) --------------------
  * Fills dst_dev[rows][ld] (dtype T) with value(seed, global_row, global_col) so that any
  * row/column block of the same logical matrix can be generated independently on any rank. */
