@@ -30,6 +30,23 @@ template <int RC> constexpr int fwd_smem_bytes() {
   return NUM_STAGES * fwd_stage_stride<RC>() + 2 * NUM_STAGES * 8 + 1024 /*align slack*/;
 }
 constexpr int FWD_THREADS = CONSUMER_THREADS + 64;
+// fp32 streams: the per-lane FMAs run in fp32 and are flushed every FWD_FLUSH_TILES tiles (8 products per lane and
+// operand column) into a second level that, like the cross-lane reduction, is kept in fp64.  At C4 the entries of A x are
+// ~114 while the residual entries are ~0.15: with an fp32 second level flushed every 8 tiles (round 1; compile with
+// -DGLP_FWD_ACC64=0 -DGLP_FWD_FLUSH=8) the noise of ||A x - b||^2 exceeded the margin of ProxGD's sufficient-decrease
+// test late in a stage, and the line search flipped coins: 385 forward streams for 150 iterations, against 151 here --
+// the count of the fp64 run.  Same 168 registers, same stream rate (profiles/r02_ab_k1_acc64.log).
+#ifndef GLP_FWD_ACC64
+#define GLP_FWD_ACC64 1
+#endif
+#ifndef GLP_FWD_FLUSH
+#define GLP_FWD_FLUSH 2
+#endif
+constexpr int FWD_FLUSH_TILES = GLP_FWD_FLUSH;
+template <typename T> struct FwdHiAcc { using type = T; };
+#if GLP_FWD_ACC64
+template <> struct FwdHiAcc<float> { using type = double; };
+#endif
 
 __device__ __forceinline__ double nan_max(double a, double b) {
   return (a != a) ? a : ((b != b) ? b : fmax(a, b));
@@ -72,6 +89,7 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
   constexpr int STRIDE = fwd_stage_stride<RC>();
   constexpr uint32_t STAGE_TX = TILE_BYTES + RC * TILE_ROW_BYTES;
   constexpr int NV = ROWS_PER_WARP * RC;  // values per lane entering the butterfly
+  using Hi = typename FwdHiAcc<T>::type;  // type of the blocked-summation accumulators and of the cross-lane reduction
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -155,7 +173,7 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
 
   // -------------------------------------------------------------------- consumers
   T acc[ROWS_PER_WARP][RC];
-  T acc_hi[ROWS_PER_WARP][RC];  // fp32: blocked summation (flush every 8 tiles); unused for fp64
+  Hi acc_hi[ROWS_PER_WARP][RC];  // fp32: blocked summation (flush every FWD_FLUSH_TILES tiles); unused for fp64
   int stage = 0;
   uint32_t phase = 0;
   int64_t t = lo;
@@ -165,7 +183,7 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
 #pragma unroll
     for (int i = 0; i < ROWS_PER_WARP; ++i)
 #pragma unroll
-      for (int q = 0; q < RC; ++q) { acc[i][q] = T(0); acc_hi[i][q] = T(0); }
+      for (int q = 0; q < RC; ++q) { acc[i][q] = T(0); acc_hi[i][q] = Hi(0); }
     int run = 0;
     for (; t < t_end; ++t) {
       mbar_wait(&full[stage], phase, a.fault);
@@ -185,21 +203,21 @@ glp_fwd_kernel(const __grid_constant__ CUtensorMap tmapA, const FwdArgs a, const
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[stage]);
       if (++stage == NUM_STAGES) { stage = 0; phase ^= 1u; }
-      if (sizeof(T) == 4 && ++run == 8) {
+      if (sizeof(T) == 4 && ++run == FWD_FLUSH_TILES) {
         run = 0;
 #pragma unroll
         for (int i = 0; i < ROWS_PER_WARP; ++i)
 #pragma unroll
-          for (int q = 0; q < RC; ++q) { acc_hi[i][q] += acc[i][q]; acc[i][q] = T(0); }
+          for (int q = 0; q < RC; ++q) { acc_hi[i][q] += Hi(acc[i][q]); acc[i][q] = T(0); }
       }
     }
     // ---- one cross-lane reduction per row block
-    T v[NV];
+    Hi v[NV];
 #pragma unroll
     for (int i = 0; i < ROWS_PER_WARP; ++i)
 #pragma unroll
-      for (int q = 0; q < RC; ++q) v[i * RC + q] = acc[i][q] + acc_hi[i][q];
-    warp_transpose_sum<T, NV>(v, lane);
+      for (int q = 0; q < RC; ++q) v[i * RC + q] = Hi(acc[i][q]) + acc_hi[i][q];
+    warp_transpose_sum<Hi, NV>(v, lane);
     // lane j < NV holds value j = i*RC + q of row warp*8 + i
     double* slot = a.partial + (c + rb) * int64_t(TILE_ROWS * RC);
     if (lane < NV) slot[warp * NV + lane] = double(v[0]);
