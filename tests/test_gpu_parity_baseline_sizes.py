@@ -130,3 +130,35 @@ def test_c5_wide_parity_with_oracle():
     torch.cuda.empty_cache()
     xr, kr, outr = orc.solve("FProxGD", x0h.astype(np.float64), gen.BlockedF64(Ah, block_rows=512), bh.astype(np.float64), mu, opts)
     _compare("FProxGD wide l=128", xh, k, out, xr, kr, outr)
+
+
+def test_c4_fp32_line_search_is_not_driven_by_rounding_noise():
+    """BASELINE configs[3] in fp32, 50 iterations per stage: late in a stage |A x| ~ 114 while the residual entries are
+    ~0.15, and the margin of ProxGD's sufficient-decrease test (gl_ProxGD_primal.py:91-92) falls to ~1e-6 of g.  With an
+    fp32 second accumulation level in the forward stream the noise of ||A x - b||^2 exceeded it and the line search
+    rejected at random (385 forward streams for 150 iterations, profiles/r02_ab_k1_acc64.log); the fp64 run, like the
+    reference's arithmetic, accepts every first trial.  Pins: one forward stream per iteration for both solvers, and an
+    fp32 objective within 1e-6 of the fp64 run's after 150 iterations."""
+    import torch
+    from glprox import GroupLassoProblem, dataset
+    m, n, l = 32768, 131072, 2
+    free = torch.cuda.mem_get_info()[0] / 1e9
+    if free < 60:
+        pytest.skip("needs ~52 GB of HBM for the fp32 and the fp64 copy of A (free: %.0f GB)" % free)
+    a0 = float(1.0 / (np.sqrt(m) + np.sqrt(n)) ** 2)
+    fvals = {}
+    for dt in ("f32", "f64"):
+        A, b, x0, u, mu, _ = dataset.gen_data_device(m, n, l, 7, dt)
+        prob = GroupLassoProblem(A, b)
+        for algo in ("ProxGD", "FProxGD"):
+            x, k, out = prob.solve(algo, x0, mu, {"maxit": 50, "alpha0": a0, "backend": "stream"})
+            assert k == 150
+            assert out["glprox"]["n_fwd"] == k + 1, (dt, algo, out["glprox"]["n_fwd"])
+            fvals[dt, algo] = float(out["fval"])
+        prob.close()
+        del A, b, x0, u, prob
+        torch.cuda.empty_cache()
+    for algo in ("ProxGD", "FProxGD"):
+        rel = abs(fvals["f32", algo] - fvals["f64", algo]) / abs(fvals["f64", algo])
+        print("%s after 150 iterations: fp32 %.9e fp64 %.9e rel %.2e" % (algo, fvals["f32", algo], fvals["f64", algo], rel))
+        assert rel <= 1e-6, (algo, rel)
