@@ -431,6 +431,8 @@ def run_e2e(args, ctx, steps):
             "ms_per_step": 1e3 * dt / steps, "final_objective": float(out["fval"]),
             "h2d_bytes_per_rank_per_step": int(h2d_rank),
             "upload_ms_per_step": out["glprox"].get("upload_ms"),
+            "call_breakdown_ms": {k: out["glprox"].get(k) for k in ("upload_ms", "attach_ms", "solve_ms", "teardown_ms")
+                                  if out["glprox"].get(k) is not None} or None,
             "api": "gl_%s_primal(x0, A, b, mu, opts) with NumPy arrays (pinned host memory)" % args.algo}, (An, bn, x0n)
 
 
